@@ -1,0 +1,228 @@
+/* kmerhash_b200.h -- C ABI of the B200-native k-mer hash-table engine.
+ *
+ * This is the drop-in boundary for the hot path of ParBLiSS/kmerhash:
+ * batch insert / find / count / erase of 2-bit packed k-mer keys with count values in an
+ * open-addressing table, k-mer generation in front of it and hash-partitioning for the
+ * multi-GPU exchange behind it.  The reference has no FFI layer; its "operator API" is the
+ * C++ template interface of its containers.  Each entry point below names the reference
+ * interface it replaces (paths relative to the reference tree; KH = include/kmerhash,
+ * KI = ext/kmerind/src).  include/kmerhash_b200.hpp wraps this ABI in classes with the
+ * reference's own names and signatures; INTEGRATION.md shows the binding.
+ *
+ * Conventions
+ *   - plain pointers and sizes only; no C++/torch types.
+ *   - keys are arrays of uint64_t words, `key_words` per key (1: k <= 32, 2: k <= 64),
+ *     word 0 least significant -- the in-memory layout of bliss::common::Kmer<K,DNA,uint64_t>
+ *     (KI/common/kmer.hpp:115-170).
+ *   - every `*_host` entry point takes HOST pointers and moves the data itself (chunked,
+ *     overlapped with the kernels); every `*_dev` entry point takes DEVICE pointers on the
+ *     table's device and is asynchronous only inside the call (it returns after the work
+ *     is complete unless noted).
+ *   - return value: >= 0 result / 0 ok; < 0 error (kh_last_error() has the text).
+ *     KH_ERR_INVALID maps to std::invalid_argument, KH_ERR_NOMEM to std::length_error
+ *     (KH/mem_utils.hpp:47), KH_ERR_FULL/KH_ERR_CUDA to std::logic_error
+ *     (KH/hashmap_linearprobe.hpp:503) in the C++ facade.
+ *   - there is NO CPU fallback: without a CUDA device every call fails with KH_ERR_CUDA.
+ */
+#ifndef KMERHASH_B200_H_
+#define KMERHASH_B200_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define KH_OK            0
+#define KH_ERR_INVALID  -1
+#define KH_ERR_NOMEM    -2
+#define KH_ERR_CUDA     -3
+#define KH_ERR_FULL     -4
+
+/* Hash functor selector = the reference's -DpStoreHash / -DpDistHash choices
+ * (benchmark/BenchmarkHashTables.cpp:131-166; functors in KH/hash_new.hpp:136-351,
+ * KH/murmurhash3_64_avx.hpp:1553, KH/murmurhash3_32_avx.hpp:1252, KH/crc32c_sse.hpp:121).
+ * Values are bit-exact to the reference functor of the same name. */
+typedef enum {
+  KH_HASH_IDEN        = 0,  /* fsc::hash::identity: word 0 of the key */
+  KH_HASH_MURMUR64    = 1,  /* fsc::hash::murmur: MurmurHash3_x64_128, h[0] */
+  KH_HASH_MURMUR64AVX = 2,  /* fsc::hash::murmur3avx64 == murmur_x86: MurmurHash3_x86_128, low 64 bits */
+  KH_HASH_MURMUR32    = 3,  /* fsc::hash::murmur32: MurmurHash3_x86_32 */
+  KH_HASH_MURMUR32AVX = 4,  /* fsc::hash::murmur3avx32 (== murmur32) */
+  KH_HASH_MURMUR32SSE = 5,  /* fsc::hash::murmur3sse32 (== murmur32) */
+  KH_HASH_FARM        = 6,  /* fsc::hash::farm: farmhash Hash64WithSeed */
+  KH_HASH_FARM32      = 7,  /* fsc::hash::farm32: low 32 bits of farm (SSE4.2+AES build) */
+  KH_HASH_CLHASH      = 8,  /* fsc::hash::clhash: key table from glibc srand(seed)/rand() */
+  KH_HASH_CRC32C      = 9,  /* fsc::hash::crc32c: crc32q chain started at seed */
+  KH_HASH_MURMUR32FIN = 10, /* murmur3finalizer_avx32: keys <= 4 bytes only -> rejected for k-mers */
+  KH_HASH_MURMUR_X86  = 11  /* fsc::hash::murmur_x86 (== MURMUR64AVX) */
+} kh_hash_kind;
+
+/* Reducer = the reference's value policy on a repeated key
+ * (KH/robinhood_offset_hashmap_ptr.hpp:85-97,4094,4099). */
+typedef enum {
+  KH_REDUCE_COUNT = 0, /* std::plus: v = v_old + v_new  (hashmap_robinhood_offsets_count) */
+  KH_REDUCE_FIRST = 1, /* DiscardReducer: first inserted value kept (hashmap_robinhood_offsets, RH, LP maps) */
+  KH_REDUCE_LAST  = 2  /* ReplaceReducer: last inserted value kept */
+} kh_reducer;
+
+/* Which reference container the table stands in for.  All three share the GPU engine
+ * (bucketised open addressing); the kind selects the reference's defaults
+ * (initial capacity 128; load factors: offsets 0.2/0.8, robinhood 0.4/0.9, linearprobe
+ * 0.2/0.6 -- KH/robinhood_offset_hashmap_ptr.hpp:407-425, KH/hashmap_robinhood.hpp:218-233,
+ * KH/hashmap_linearprobe.hpp:191-206) and the default reducer semantics. */
+typedef enum {
+  KH_MAP_ROBINHOOD_OFFSETS = 0,
+  KH_MAP_ROBINHOOD         = 1,
+  KH_MAP_LINEARPROBE       = 2
+} kh_map_kind;
+
+#define KH_DEFAULT_SEED       43u        /* store-hash seed, KH/hash_new.hpp */
+#define KH_DEFAULT_CRC_SEED   37u        /* KH/crc32c_sse.hpp:239 */
+#define KH_DIST_SEED          9876543u   /* KH/distributed_batched_robinhood_map.hpp:749 */
+
+typedef struct kh_table kh_table;
+
+const char *kh_last_error(void);
+/* number of CUDA devices visible (<= 0: none) */
+int kh_device_count(void);
+/* number of kernels this library launched since load / since the last reset (bench.py's gpu_launches) */
+uint64_t kh_launch_count(void);
+void kh_reset_launch_count(void);
+
+/* ---- pinned host memory helpers (for the *_host fast path) ---------------------------- */
+void *kh_host_alloc(size_t bytes);   /* cudaHostAlloc; NULL on failure */
+void kh_host_free(void *p);
+
+/* ---- table lifetime and sizing -------------------------------------------------------
+ * replaces: MAP() default ctor, set_max/min_load_factor (KH/robinhood_offset_hashmap_ptr.hpp:407-425,
+ * 631-640), reserve/rehash (:896-981), capacity/size/clear. */
+kh_table *kh_create(int device, int map_kind, int key_words, int hash_kind, uint32_t seed, int reducer);
+void kh_destroy(kh_table *t);
+int kh_set_load_factors(kh_table *t, double min_load, double max_load);
+/* accepted and ignored (software prefetch distances have no meaning on the GPU);
+ * replaces set_insert_lookahead / set_query_lookahead (:646-653) */
+int kh_set_lookahead(kh_table *t, int insert_lookahead, int query_lookahead);
+/* capacity := next_pow2(ceil(n / max_load)) if that is larger than the current one (bulk GPU rebuild) */
+int kh_reserve(kh_table *t, uint64_t n);
+/* force capacity to next_pow2(buckets) (>= what size() needs); replaces rehash(b) */
+int kh_rehash(kh_table *t, uint64_t slots);
+uint64_t kh_capacity(const kh_table *t);
+uint64_t kh_size(const kh_table *t);
+double kh_load_factor(const kh_table *t);
+int kh_clear(kh_table *t);
+int kh_device(const kh_table *t);
+int kh_key_words(const kh_table *t);
+
+/* HyperLogLog distinct estimate of a key batch over the table's store hash, precision 12
+ * (replaces get_hll().update(keys,n) + estimate(), KH/hyperloglog64.hpp:176-239; driver
+ * "estimate" phase benchmark/BenchmarkHashTables.cpp:1232-1248).  Registers are bit-identical
+ * to the reference's; `regs_out` (4096 bytes, may be NULL) receives them. */
+double kh_estimate_distinct_host(kh_table *t, const uint64_t *keys, uint64_t n, uint8_t *regs_out);
+double kh_estimate_distinct_dev(kh_table *t, const uint64_t *d_keys, uint64_t n, uint8_t *regs_out);
+
+/* ---- batch insert --------------------------------------------------------------------
+ * replaces insert(vector<Key> const&, T default) / insert(IT,IT) / insert_no_estimate
+ * (KH/robinhood_offset_hashmap_ptr.hpp:2783-2885) and the per-key insert loops of RH/LP
+ * (KH/hashmap_robinhood.hpp:522-717, KH/hashmap_linearprobe.hpp:430-573).
+ * vals == NULL: every key carries `default_val`.  estimate != 0: HLL-presize first (insert());
+ * 0: grow by doubling only (insert_no_estimate()).  Returns the number of NEW keys, < 0 on error. */
+int64_t kh_insert_host(kh_table *t, const uint64_t *keys, const uint32_t *vals, uint64_t n,
+                       uint32_t default_val, int estimate);
+int64_t kh_insert_dev(kh_table *t, const uint64_t *d_keys, const uint32_t *d_vals, uint64_t n,
+                      uint32_t default_val, int estimate);
+
+/* ---- batch queries -------------------------------------------------------------------
+ * kh_count_*: replaces count(out, b, e) / exists (:3251-3328): out[i] = 0/1; returns #present.
+ * kh_find_*:  replaces find<OT>(out, b, e, nonexistent) (:3376-3417): out[i] = value or `nonexistent`;
+ *             returns #found.
+ * kh_find_existing_*: replaces find_existing (:3425-3454): hits only, in query order; returns #hits. */
+int64_t kh_count_host(kh_table *t, const uint64_t *keys, uint64_t n, uint8_t *out);
+int64_t kh_count_dev(kh_table *t, const uint64_t *d_keys, uint64_t n, uint8_t *d_out);
+int64_t kh_find_host(kh_table *t, const uint64_t *keys, uint64_t n, uint32_t *out, uint32_t nonexistent);
+int64_t kh_find_dev(kh_table *t, const uint64_t *d_keys, uint64_t n, uint32_t *d_out, uint32_t nonexistent);
+int64_t kh_find_existing_host(kh_table *t, const uint64_t *keys, uint64_t n, uint64_t *out_keys, uint32_t *out_vals);
+int64_t kh_find_existing_dev(kh_table *t, const uint64_t *d_keys, uint64_t n, uint64_t *d_out_keys, uint32_t *d_out_vals);
+
+/* replaces update(...) (:3467-3495; KH/hashmap_robinhood.hpp:1274): overwrite the value of keys
+ * that are present, never inserts; returns #updated. */
+int64_t kh_update_host(kh_table *t, const uint64_t *keys, const uint32_t *vals, uint64_t n);
+int64_t kh_update_dev(kh_table *t, const uint64_t *d_keys, const uint32_t *d_vals, uint64_t n);
+
+/* ---- batch erase ---------------------------------------------------------------------
+ * replaces erase(Key const*, Key const*) (:3768-3790; RH :1421-1440; LP :1032-1051):
+ * tombstone-free; returns #keys removed (a key repeated in the batch counts once); shrinks
+ * (bulk rebuild) when the load drops below min_load, like the reference. */
+int64_t kh_erase_host(kh_table *t, const uint64_t *keys, uint64_t n);
+int64_t kh_erase_dev(kh_table *t, const uint64_t *d_keys, uint64_t n);
+
+/* ---- export --------------------------------------------------------------------------
+ * replaces to_vector() / keys() (:861-878): unordered; writes at most `cap` entries, returns size(). */
+int64_t kh_export_host(kh_table *t, uint64_t *out_keys, uint32_t *out_vals, uint64_t cap);
+int64_t kh_export_dev(kh_table *t, uint64_t *d_out_keys, uint32_t *d_out_vals, uint64_t cap);
+
+/* ---- batched hashing (parity surface for the hash functors) --------------------------
+ * replaces Hash::operator()(Key const*, n, out*) (KH/hash_new.hpp:390-1134 batch mode).
+ * out[i] is the functor's value zero-extended to 64 bits. */
+int kh_hash_host(int device, int hash_kind, uint32_t seed, int key_words, const uint64_t *keys, uint64_t n, uint64_t *out);
+int kh_hash_dev(int device, int hash_kind, uint32_t seed, int key_words, const uint64_t *d_keys, uint64_t n, uint64_t *d_out);
+
+/* ---- k-mer generation ----------------------------------------------------------------
+ * replaces KmerParser::operator() over NSplitSequencesIterator + lex_less
+ * (KI/io/kmer_parser.hpp:232-293, KI/io/filtered_sequence_iterator.hpp:225-247,429-440,
+ * KI/common/kmer.hpp:716-726,1078-1087, KI/common/kmer_transform.hpp:109-125):
+ * read r is bases[offsets[r] .. offsets[r+1]); '\n' '\r' skipped; 'N'/'n' split; other bytes
+ * through the DNA table (non-ACGT -> A).  Output order = read order, then position.
+ * out_keys == NULL: count only.  Returns the number of k-mers. */
+int64_t kh_kmers_from_reads_host(int device, const char *bases, const uint64_t *offsets, uint64_t n_reads,
+                                 int k, int canonical, uint64_t *out_keys, uint64_t out_cap);
+int64_t kh_kmers_from_reads_dev(int device, const char *d_bases, const uint64_t *d_offsets, uint64_t n_reads,
+                                int k, int canonical, uint64_t *d_out_keys, uint64_t out_cap);
+/* replaces transform_input with lex_less (KI/containers/distributed_map_base.hpp:287-301): in-place allowed */
+int kh_canonicalize_dev(int device, int k, const uint64_t *d_in, uint64_t n, uint64_t *d_out);
+int kh_canonicalize_host(int device, int k, const uint64_t *in, uint64_t n, uint64_t *out);
+int kh_revcomp_host(int device, int k, const uint64_t *in, uint64_t n, uint64_t *out);
+
+/* ---- hash partitioning for the multi-GPU exchange ------------------------------------
+ * replaces assign_count_permute + permute_by_bucketid
+ * (KH/distributed_batched_robinhood_map.hpp:164-178,291-380,632-741): rank =
+ * DistHash_{seed}(key) & (p-1) for power-of-two p, % p otherwise (in the functor's result
+ * width); STABLE scatter so each destination's keys are contiguous and in input order.
+ * d_out_keys: n keys permuted; d_out_perm (may be NULL): original index of every permuted
+ * position; counts (HOST, p entries): keys per destination. */
+int kh_partition_dev(int device, int hash_kind, uint32_t seed, int key_words, uint32_t p,
+                     const uint64_t *d_keys, uint64_t n, uint64_t *d_out_keys, uint32_t *d_out_perm,
+                     uint64_t *counts);
+int kh_rank_host(int device, int hash_kind, uint32_t seed, int key_words, uint32_t p,
+                 const uint64_t *keys, uint64_t n, uint32_t *out_rank);
+/* out[perm[i]] = in[i] for 1- or 4-byte elements (results of a permuted query back to input order) */
+int kh_unpermute_dev(int device, int elem_bytes, const void *d_in, const uint32_t *d_perm, uint64_t n, void *d_out);
+
+/* ---- single-process multi-GPU map ------------------------------------------------------
+ * replaces dsc::counting_batched_robinhood_map / batched_robinhood_map
+ * (KH/distributed_batched_robinhood_map.hpp:748-832,1187,1535,1901,2428,2542-2649): one table per
+ * GPU, owner = DistHash_{9876543}(canon(key)) mod p, exchange by direct peer stores over NVLink
+ * inside the partition kernel.  Results come back in INPUT order. */
+typedef struct khd_map khd_map;
+khd_map *khd_create(int n_gpus, int key_words, int store_hash, int dist_hash, int reducer, int canonical_k);
+void khd_destroy(khd_map *m);
+int khd_n_gpus(const khd_map *m);
+int64_t khd_insert_host(khd_map *m, const uint64_t *keys, uint64_t n, uint32_t default_val);
+int64_t khd_count_host(khd_map *m, const uint64_t *keys, uint64_t n, uint8_t *out);
+int64_t khd_find_host(khd_map *m, const uint64_t *keys, uint64_t n, uint32_t *out, uint32_t nonexistent);
+int64_t khd_erase_host(khd_map *m, const uint64_t *keys, uint64_t n);
+uint64_t khd_size(const khd_map *m);
+uint64_t khd_local_size(const khd_map *m, int rank);
+int64_t khd_export_rank_host(khd_map *m, int rank, uint64_t *out_keys, uint32_t *out_vals, uint64_t cap);
+
+/* ---- roofline probes (measurement support, not part of the reference API) --------------
+ * Touch `n_access` uniformly random `bytes_per_access`-byte aligned pieces of a `buf_bytes`
+ * buffer: mode 0 = read, 1 = read + atomicAdd (RMW).  Returns the kernel's milliseconds. */
+double kh_probe_random_access(int device, uint64_t buf_bytes, uint64_t n_access, int bytes_per_access, int mode, int iters);
+double kh_probe_stream_copy(int device, uint64_t bytes, int iters);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* KMERHASH_B200_H_ */

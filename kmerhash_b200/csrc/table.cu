@@ -1,0 +1,741 @@
+// table.cu -- kh_table: host side of the HBM k-mer table and its C ABI (include/kmerhash_b200.h).
+//
+// Host logic mirrors the reference containers' public behaviour:
+//   sizing   reserve(n) -> capacity = next_pow2(ceil(n / max_load))      KH/robinhood_offset_hashmap_ptr.hpp:896-981
+//   growth   double while the batch would push size past max_load        :1736, :2802-2885 (insert_no_estimate)
+//   presize  HLL estimate * (1 + est_error) before the batch             :2512-2535 (insert_impl)
+//   shrink   after erase, when size < min_load * capacity                 :3768-3790
+// but every data-touching step is a kernel (kh_table.cuh) and a resize is a bulk GPU rebuild.
+#include <algorithm>
+#include <cmath>
+#include <cstdlib>
+#include <cstring>
+#include <mutex>
+#include <vector>
+#include <cub/device/device_scan.cuh>
+
+#include "kh_common.h"
+#include "kh_table.cuh"
+#include "kh_hll.cuh"
+
+namespace kh {
+
+// ---------------------------------------------------------------------------------------
+// small kernels: init, export, seal, compaction helpers
+// ---------------------------------------------------------------------------------------
+__global__ void init_slots_kernel(uint4 *slots, uint64_t n_units, int words_per_slot_u4) {
+  // a slot is 1 (W=1) or 2 (W=2) uint4 units: {key lo, key hi | val, aux, pad}
+  const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+  for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n_units; i += stride) {
+    uint4 v;
+    if (words_per_slot_u4 == 1) v = make_uint4(0xffffffffu, 0xffffffffu, 0u, 0u);
+    else v = (i & 1) ? make_uint4(0u, 0u, 0u, 0u) : make_uint4(0xffffffffu, 0xffffffffu, 0xffffffffu, 0xffffffffu);
+    slots[i] = v;
+  }
+}
+
+template <int W>
+__global__ void export_kernel(TableView t, uint64_t *out_keys, uint32_t *out_vals, uint64_t cap,
+                              unsigned long long *counter, int include_side) {
+  constexpr int SLOT = 16 * W;
+  const int lane = threadIdx.x & 31;
+  const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+  const uint64_t n_round = (t.capacity + 31) & ~31ULL;
+  for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n_round; i += stride) {
+    uint64_t w[2 * W];
+    bool occ = false;
+    if (i < t.capacity) {
+      LdCg<2 * W>::ld(t.slots + i * SLOT, w);
+      occ = !key_is_empty<W>(w);
+    }
+    const uint32_t m = __ballot_sync(FULL_MASK, occ);
+    if (m == 0) continue;
+    unsigned long long basepos = 0;
+    if (lane == 0) basepos = atomicAdd(counter, (unsigned long long)__popc(m));
+    basepos = __shfl_sync(FULL_MASK, basepos, 0);
+    if (occ) {
+      const uint64_t pos = basepos + __popc(m & ((1u << lane) - 1u));
+      if (pos < cap) {
+#pragma unroll
+        for (int q = 0; q < W; ++q) out_keys[pos * W + q] = w[q];
+        if (out_vals) out_vals[pos] = (uint32_t)w[W];
+      }
+    }
+  }
+  // side slot (all-ones key)
+  if (include_side && blockIdx.x == 0 && threadIdx.x == 0 && t.side[0] == 1u) {
+    const unsigned long long pos = atomicAdd(counter, 1ULL);
+    if (pos < cap) {
+      for (int q = 0; q < W; ++q) out_keys[pos * W + q] = EMPTY_WORD;
+      if (out_vals) out_vals[pos] = t.side[1];
+    }
+  }
+}
+
+// FIRST tables: every occupied slot carries the "sealed" position so later batches never override it
+template <int W>
+__global__ void seal_kernel(TableView t) {
+  constexpr int SLOT = 16 * W;
+  const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+  for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < t.capacity; i += stride) {
+    uint64_t w[2 * W];
+    LdCg<2 * W>::ld(t.slots + i * SLOT, w);
+    if (!key_is_empty<W>(w)) {
+      uint32_t *paux = reinterpret_cast<uint32_t *>(t.slots + i * SLOT + 8 * W) + 1;
+      *paux = (((uint32_t)(w[W] >> 32)) & AUX_STICKY) | AUX_SEALED_FIRST;
+    }
+  }
+  if (blockIdx.x == 0 && threadIdx.x == 0 && t.side[0] == 1u) t.side[2] = AUX_SEALED_FIRST;
+}
+
+// stable compaction of the hits of a query batch (find_existing): flags -> positions by scan
+template <int W>
+__global__ void scatter_hits_kernel(const uint64_t *keys, const uint32_t *vals, const uint8_t *flags,
+                                    const uint64_t *pos, uint64_t n, uint64_t *out_keys, uint32_t *out_vals) {
+  const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+  for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+    if (flags[i]) {
+      const uint64_t p = pos[i];
+#pragma unroll
+      for (int q = 0; q < W; ++q) out_keys[p * W + q] = keys[i * W + q];
+      out_vals[p] = vals[i];
+    }
+  }
+}
+__global__ void widen_flags_kernel(const uint8_t *flags, uint64_t n, uint64_t *out) {
+  const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+  for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) out[i] = flags[i];
+}
+
+}  // namespace kh
+
+using namespace kh;
+
+// ---------------------------------------------------------------------------------------
+// the table object
+// ---------------------------------------------------------------------------------------
+struct kh_table {
+  int device = 0, map_kind = 0, W = 1, hash_kind = 0, reducer = 0;
+  uint32_t seed = KH_DEFAULT_SEED;
+  double min_load = 0.2, max_load = 0.8;
+  int LB = 32, G = 1;                 // probe geometry (DESIGN.md "bucket geometry")
+  uint64_t capacity = 0, size = 0;
+  HashParams hp;
+  DevBuf<unsigned char> slots;
+  DevBuf<uint32_t> side;              // 3 words
+  DevBuf<unsigned long long> counters;  // [0] n_new / n_hit, [1] export counter
+  DevBuf<int> status;
+  unsigned long long *h_counters = nullptr;  // pinned mirror
+  int *h_status = nullptr;
+  cudaStream_t stream[2] = {nullptr, nullptr};
+  cudaEvent_t ev[2] = {nullptr, nullptr};
+  // staging for *_host calls (grown on demand)
+  DevBuf<uint64_t> d_keys[2];
+  DevBuf<uint32_t> d_vals[2];
+  DevBuf<uint8_t> d_u8[2];
+  int sms = 148;
+
+  int slot_bytes() const { return 16 * W; }
+  int bucket_slots() const { return G * (LB / slot_bytes()); }
+  TableView view() { return TableView{slots.p, capacity, side.p}; }
+  int grid_for(uint64_t n_items, int per_block) const {
+    uint64_t need = (n_items + per_block - 1) / per_block;
+    uint64_t cap = (uint64_t)sms * 8;
+    return (int)std::max<uint64_t>(1, std::min(need, cap));
+  }
+};
+
+namespace {
+
+// chunk size (keys) of the host<->device pipeline
+constexpr uint64_t HOST_CHUNK = 1ULL << 23;
+constexpr uint64_t ORDERED_CHUNK = 1ULL << 30;
+
+#define KH_GEOM_CASE_(Wv, LBv, Gv, ...) \
+  { constexpr int W = Wv; constexpr int LB = LBv; constexpr int G = Gv; __VA_ARGS__; }
+#define KH_GEOM_SWITCH(t, ...)                                                                \
+  do {                                                                                        \
+    const int _code = (t)->W * 10000 + (t)->LB * 100 + (t)->G;                                \
+    switch (_code) {                                                                          \
+      case 11602: KH_GEOM_CASE_(1, 16, 2, __VA_ARGS__) break;                                 \
+      case 11604: KH_GEOM_CASE_(1, 16, 4, __VA_ARGS__) break;                                 \
+      case 11608: KH_GEOM_CASE_(1, 16, 8, __VA_ARGS__) break;                                 \
+      case 13201: KH_GEOM_CASE_(1, 32, 1, __VA_ARGS__) break;                                 \
+      case 13202: KH_GEOM_CASE_(1, 32, 2, __VA_ARGS__) break;                                 \
+      case 13204: KH_GEOM_CASE_(1, 32, 4, __VA_ARGS__) break;                                 \
+      case 23201: KH_GEOM_CASE_(2, 32, 1, __VA_ARGS__) break;                                 \
+      case 23202: KH_GEOM_CASE_(2, 32, 2, __VA_ARGS__) break;                                 \
+      case 23204: KH_GEOM_CASE_(2, 32, 4, __VA_ARGS__) break;                                 \
+      default: kh::set_error("unsupported geometry W=%d LB=%d G=%d", (t)->W, (t)->LB, (t)->G); \
+               throw kh::CudaError{KH_ERR_INVALID};                                           \
+    }                                                                                         \
+  } while (0)
+
+bool geometry_ok(int W, int LB, int G) {
+  if (W == 1) return (LB == 16 && (G == 2 || G == 4 || G == 8)) || (LB == 32 && (G == 1 || G == 2 || G == 4));
+  return LB == 32 && (G == 1 || G == 2 || G == 4);
+}
+
+void default_geometry(int W, int &LB, int &G) {
+  LB = 32; G = 1;
+  if (const char *e = getenv("KH_GEOM")) {   // "LBxG", experiments only
+    int lb = 0, g = 0;
+    if (sscanf(e, "%dx%d", &lb, &g) == 2 && geometry_ok(W, lb, g)) { LB = lb; G = g; }
+  }
+}
+
+void alloc_slots(kh_table *t, uint64_t cap, DevBuf<unsigned char> &buf, cudaStream_t s) {
+  buf.alloc(cap * t->slot_bytes());
+  const uint64_t units = cap * t->slot_bytes() / 16;
+  KH_LAUNCH(init_slots_kernel, t->grid_for(units, 256 * 4), 256, 0, s, reinterpret_cast<uint4 *>(buf.p), units, t->W);
+}
+
+uint64_t capacity_for(const kh_table *t, uint64_t n) {
+  uint64_t need = (uint64_t)std::ceil((double)n / t->max_load);
+  uint64_t cap = next_pow2(std::max<uint64_t>(need, 1));
+  return std::max<uint64_t>(cap, 128);
+}
+
+void launch_insert(kh_table *t, const uint64_t *d_keys, const uint32_t *d_vals, uint64_t n, uint32_t dflt,
+                   int mode, cudaStream_t s) {
+  if (n == 0) return;
+  InsertArgs a;
+  a.t = t->view(); a.keys = d_keys; a.vals = d_vals; a.n = n; a.dflt = dflt;
+  a.hash_kind = t->hash_kind; a.hp = t->hp; a.idx_base = 0;
+  a.n_new = t->counters.p; a.status = t->status.p;
+  const int grid = t->grid_for(n, 256);
+  KH_GEOM_SWITCH(t, {
+    if (mode == INS_COUNT) KH_LAUNCH((insert_kernel<W, LB, G, INS_COUNT>), grid, 256, 0, s, a);
+    else if (mode == INS_FIRST) KH_LAUNCH((insert_kernel<W, LB, G, INS_FIRST>), grid, 256, 0, s, a);
+    else KH_LAUNCH((insert_kernel<W, LB, G, INS_LAST>), grid, 256, 0, s, a);
+  });
+}
+
+void launch_lookup(kh_table *t, int op, const uint64_t *d_keys, uint64_t n, uint32_t *out_u32, uint8_t *out_u8,
+                   const uint32_t *vals, uint32_t nonexistent, unsigned long long *counter, cudaStream_t s) {
+  if (n == 0) return;
+  LookupArgs a;
+  a.t = t->view(); a.keys = d_keys; a.n = n; a.hash_kind = t->hash_kind; a.hp = t->hp;
+  a.out_u32 = out_u32; a.out_u8 = out_u8; a.vals = vals; a.nonexistent = nonexistent;
+  a.ins_mode = (uint32_t)t->reducer; a.idx_base = 0; a.n_hit = counter;
+  const int grid = t->grid_for(n, 256);
+  KH_GEOM_SWITCH(t, {
+    switch (op) {
+      case OP_FIND:     KH_LAUNCH((lookup_kernel<W, LB, G, OP_FIND>), grid, 256, 0, s, a); break;
+      case OP_COUNT:    KH_LAUNCH((lookup_kernel<W, LB, G, OP_COUNT>), grid, 256, 0, s, a); break;
+      case OP_ERASE:    KH_LAUNCH((lookup_kernel<W, LB, G, OP_ERASE>), grid, 256, 0, s, a); break;
+      case OP_UPDATE:   KH_LAUNCH((lookup_kernel<W, LB, G, OP_UPDATE>), grid, 256, 0, s, a); break;
+      default:          KH_LAUNCH((lookup_kernel<W, LB, G, OP_FINALIZE>), grid, 256, 0, s, a); break;
+    }
+  });
+}
+
+void zero_counter(kh_table *t, cudaStream_t s) {
+  KH_CUDA(cudaMemsetAsync(t->counters.p, 0, 2 * sizeof(unsigned long long), s));
+  KH_CUDA(cudaMemsetAsync(t->status.p, 0, sizeof(int), s));
+}
+// reads counter[0] and the status flag; synchronises the stream
+uint64_t read_counter(kh_table *t, cudaStream_t s) {
+  KH_CUDA(cudaMemcpyAsync(t->h_counters, t->counters.p, 2 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, s));
+  KH_CUDA(cudaMemcpyAsync(t->h_status, t->status.p, sizeof(int), cudaMemcpyDeviceToHost, s));
+  KH_CUDA(cudaStreamSynchronize(s));
+  if (*t->h_status != 0) { set_error("table full: a key found no slot"); throw CudaError{KH_ERR_FULL}; }
+  return t->h_counters[0];
+}
+
+// compact dump of the live entries into fresh device arrays (used by rebuild and export)
+uint64_t dump_entries(kh_table *t, uint64_t *d_keys, uint32_t *d_vals, uint64_t cap, cudaStream_t s, int include_side = 1) {
+  KH_CUDA(cudaMemsetAsync(t->counters.p + 1, 0, sizeof(unsigned long long), s));
+  TableView v = t->view();
+  const int grid = t->grid_for(t->capacity, 256 * 4);
+  if (t->W == 1) KH_LAUNCH((export_kernel<1>), grid, 256, 0, s, v, d_keys, d_vals, cap, t->counters.p + 1, include_side);
+  else KH_LAUNCH((export_kernel<2>), grid, 256, 0, s, v, d_keys, d_vals, cap, t->counters.p + 1, include_side);
+  KH_CUDA(cudaMemcpyAsync(t->h_counters + 1, t->counters.p + 1, sizeof(unsigned long long), cudaMemcpyDeviceToHost, s));
+  KH_CUDA(cudaStreamSynchronize(s));
+  return t->h_counters[1];
+}
+
+void seal(kh_table *t, cudaStream_t s) {
+  TableView v = t->view();
+  const int grid = t->grid_for(t->capacity, 256 * 4);
+  if (t->W == 1) KH_LAUNCH((seal_kernel<1>), grid, 256, 0, s, v);
+  else KH_LAUNCH((seal_kernel<2>), grid, 256, 0, s, v);
+}
+
+// bulk rebuild into `new_cap` slots: dump -> fresh table -> insert (keys are unique, fresh vals are 0,
+// so the COUNT-mode add is a plain copy for every reducer).  The side slot is not touched.
+void rebuild(kh_table *t, uint64_t new_cap) {
+  cudaStream_t s = t->stream[0];
+  new_cap = std::max<uint64_t>(next_pow2(new_cap), 128);
+  if (t->capacity == 0 || t->size == 0) {
+    t->slots.release();
+    alloc_slots(t, new_cap, t->slots, s);
+    t->capacity = new_cap;
+    KH_CUDA(cudaStreamSynchronize(s));
+    return;
+  }
+  DevBuf<uint64_t> keys(t->size * t->W);
+  DevBuf<uint32_t> vals(t->size);
+  const uint64_t n = dump_entries(t, keys.p, vals.p, t->size, s, 0);
+  t->slots.release();
+  alloc_slots(t, new_cap, t->slots, s);
+  t->capacity = new_cap;
+  zero_counter(t, s);
+  launch_insert(t, keys.p, vals.p, n, 0, INS_COUNT, s);
+  const uint64_t placed = read_counter(t, s);
+  if (placed != n) {
+    set_error("rebuild lost entries: %llu of %llu", (unsigned long long)placed, (unsigned long long)n);
+    throw CudaError{KH_ERR_CUDA};
+  }
+  if (t->reducer == KH_REDUCE_FIRST) { seal(t, s); KH_CUDA(cudaStreamSynchronize(s)); }
+}
+
+void ensure_room(kh_table *t, uint64_t n_more) {
+  const uint64_t want = capacity_for(t, t->size + n_more);
+  if (want > t->capacity) rebuild(t, want);
+}
+
+// one device-resident piece, any reducer.  Returns #new keys.
+uint64_t insert_resident(kh_table *t, const uint64_t *d_keys, const uint32_t *d_vals, uint64_t n, uint32_t dflt,
+                         cudaStream_t s) {
+  uint64_t added = 0;
+  const int mode = t->reducer == KH_REDUCE_COUNT ? INS_COUNT : (t->reducer == KH_REDUCE_FIRST ? INS_FIRST : INS_LAST);
+  const uint64_t step = (mode == INS_COUNT) ? std::max<uint64_t>(n, 1) : ORDERED_CHUNK;
+  for (uint64_t off = 0; off < n; off += step) {
+    const uint64_t m = std::min(step, n - off);
+    zero_counter(t, s);
+    launch_insert(t, d_keys + off * t->W, d_vals ? d_vals + off : nullptr, m, dflt, mode, s);
+    if (mode != INS_COUNT)   // phase B: the winning batch position stores its value (hits go to counters[1])
+      launch_lookup(t, OP_FINALIZE, d_keys + off * t->W, m, nullptr, nullptr, d_vals ? d_vals + off : nullptr, dflt,
+                    t->counters.p + 1, s);
+    added += read_counter(t, s);
+  }
+  return added;
+}
+
+}  // namespace
+
+// ---------------------------------------------------------------------------------------
+// C ABI
+// ---------------------------------------------------------------------------------------
+extern "C" {
+
+kh_table *kh_create(int device, int map_kind, int key_words, int hash_kind, uint32_t seed, int reducer) {
+  kh_table *t = nullptr;
+  int64_t rc = guarded([&]() -> int64_t {
+    if (key_words < 1 || key_words > 2) { set_error("key_words must be 1 or 2"); return KH_ERR_INVALID; }
+    if (!hash_kind_supported(hash_kind)) { set_error("hash kind %d is not defined for 8/16-byte keys", hash_kind); return KH_ERR_INVALID; }
+    if (reducer < 0 || reducer > 2 || map_kind < 0 || map_kind > 2) { set_error("bad reducer / map kind"); return KH_ERR_INVALID; }
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev <= 0) { set_error("no CUDA device: kmerhash_b200 has no CPU fallback"); return KH_ERR_CUDA; }
+    if (device < 0 || device >= ndev) { set_error("device %d out of range", device); return KH_ERR_INVALID; }
+    DeviceGuard g(device);
+    t = new kh_table();
+    t->device = device; t->map_kind = map_kind; t->W = key_words;
+    t->hash_kind = fold_kind(hash_kind); t->seed = seed; t->reducer = reducer;
+    switch (map_kind) {   // reference defaults
+      case KH_MAP_ROBINHOOD:   t->min_load = 0.4; t->max_load = 0.9; break;
+      case KH_MAP_LINEARPROBE: t->min_load = 0.2; t->max_load = 0.6; break;
+      default:                 t->min_load = 0.2; t->max_load = 0.8; break;
+    }
+    default_geometry(t->W, t->LB, t->G);
+    t->hp = make_hash_params(t->hash_kind, seed, key_words);
+    t->sms = sm_count(device);
+    for (int i = 0; i < 2; ++i) {
+      KH_CUDA(cudaStreamCreateWithFlags(&t->stream[i], cudaStreamNonBlocking));
+      KH_CUDA(cudaEventCreateWithFlags(&t->ev[i], cudaEventDisableTiming));
+    }
+    t->side.alloc(4); t->counters.alloc(2); t->status.alloc(1);
+    KH_CUDA(cudaMemset(t->side.p, 0, 4 * sizeof(uint32_t)));
+    KH_CUDA(cudaHostAlloc((void **)&t->h_counters, 2 * sizeof(unsigned long long), cudaHostAllocDefault));
+    KH_CUDA(cudaHostAlloc((void **)&t->h_status, sizeof(int), cudaHostAllocDefault));
+    rebuild(t, 128);
+    return KH_OK;
+  });
+  if (rc != KH_OK) { if (t) { kh_destroy(t); } return nullptr; }
+  return t;
+}
+
+void kh_destroy(kh_table *t) {
+  if (!t) return;
+  int prev = -1; cudaGetDevice(&prev); cudaSetDevice(t->device);
+  for (int i = 0; i < 2; ++i) { if (t->stream[i]) cudaStreamDestroy(t->stream[i]); if (t->ev[i]) cudaEventDestroy(t->ev[i]); }
+  if (t->h_counters) cudaFreeHost(t->h_counters);
+  if (t->h_status) cudaFreeHost(t->h_status);
+  t->slots.release(); t->side.release(); t->counters.release(); t->status.release();
+  for (int i = 0; i < 2; ++i) { t->d_keys[i].release(); t->d_vals[i].release(); t->d_u8[i].release(); }
+  delete t;
+  if (prev >= 0) cudaSetDevice(prev);
+}
+
+int kh_set_load_factors(kh_table *t, double min_load, double max_load) {
+  if (!t || !(max_load > 0.0 && max_load < 1.0) || !(min_load >= 0.0 && min_load < max_load)) {
+    set_error("load factors must satisfy 0 <= min < max < 1"); return KH_ERR_INVALID;
+  }
+  t->min_load = min_load; t->max_load = max_load;
+  return KH_OK;
+}
+int kh_set_lookahead(kh_table *t, int, int) { return t ? KH_OK : KH_ERR_INVALID; }
+
+int kh_set_geometry(kh_table *t, int lane_bytes, int lanes_per_bucket) {
+  return (int)guarded([&]() -> int64_t {
+    if (!t || !geometry_ok(t->W, lane_bytes, lanes_per_bucket)) { set_error("unsupported geometry"); return KH_ERR_INVALID; }
+    if (t->size != 0) { set_error("geometry can only change on an empty table"); return KH_ERR_INVALID; }
+    DeviceGuard g(t->device);
+    t->LB = lane_bytes; t->G = lanes_per_bucket;
+    return KH_OK;
+  });
+}
+
+int kh_reserve(kh_table *t, uint64_t n) {
+  return (int)guarded([&]() -> int64_t {
+    if (!t) return KH_ERR_INVALID;
+    DeviceGuard g(t->device);
+    const uint64_t want = capacity_for(t, n);
+    if (want > t->capacity) rebuild(t, want);
+    return KH_OK;
+  });
+}
+int kh_rehash(kh_table *t, uint64_t slots) {
+  return (int)guarded([&]() -> int64_t {
+    if (!t) return KH_ERR_INVALID;
+    DeviceGuard g(t->device);
+    uint64_t want = std::max(next_pow2(slots), capacity_for(t, t->size));
+    if (want != t->capacity) rebuild(t, want);
+    return KH_OK;
+  });
+}
+uint64_t kh_capacity(const kh_table *t) { return t ? t->capacity : 0; }
+uint64_t kh_size(const kh_table *t) { return t ? t->size : 0; }
+double kh_load_factor(const kh_table *t) { return (t && t->capacity) ? (double)t->size / (double)t->capacity : 0.0; }
+int kh_device(const kh_table *t) { return t ? t->device : -1; }
+int kh_key_words(const kh_table *t) { return t ? t->W : 0; }
+
+int kh_clear(kh_table *t) {
+  return (int)guarded([&]() -> int64_t {
+    if (!t) return KH_ERR_INVALID;
+    DeviceGuard g(t->device);
+    cudaStream_t s = t->stream[0];
+    const uint64_t units = t->capacity * t->slot_bytes() / 16;
+    KH_LAUNCH(init_slots_kernel, t->grid_for(units, 256 * 4), 256, 0, s, reinterpret_cast<uint4 *>(t->slots.p), units, t->W);
+    KH_CUDA(cudaMemsetAsync(t->side.p, 0, 4 * sizeof(uint32_t), s));
+    KH_CUDA(cudaStreamSynchronize(s));
+    t->size = 0;
+    return KH_OK;
+  });
+}
+
+// ---- HLL ---------------------------------------------------------------------------------
+double kh_estimate_distinct_dev(kh_table *t, const uint64_t *d_keys, uint64_t n, uint8_t *regs_out) {
+  double est = -1.0;
+  guarded([&]() -> int64_t {
+    if (!t) return KH_ERR_INVALID;
+    DeviceGuard g(t->device);
+    est = hll_estimate_dev(t->hash_kind, t->hp, t->W, d_keys, n, regs_out, t->stream[0], t->sms);
+    return KH_OK;
+  });
+  return est;
+}
+
+double kh_estimate_distinct_host(kh_table *t, const uint64_t *keys, uint64_t n, uint8_t *regs_out) {
+  double est = -1.0;
+  guarded([&]() -> int64_t {
+    if (!t) return KH_ERR_INVALID;
+    DeviceGuard g(t->device);
+    DevBuf<uint64_t> d(std::max<uint64_t>(n * t->W, 1));
+    KH_CUDA(cudaMemcpy(d.p, keys, n * t->W * sizeof(uint64_t), cudaMemcpyHostToDevice));
+    est = hll_estimate_dev(t->hash_kind, t->hp, t->W, d.p, n, regs_out, t->stream[0], t->sms);
+    return KH_OK;
+  });
+  return est;
+}
+
+// ---- insert ------------------------------------------------------------------------------
+// Growth policy without an estimate = the reference's insert_no_estimate: fill up to max_load,
+// double, continue (KH/robinhood_offset_hashmap_ptr.hpp:2802-2885).
+static int64_t insert_dev_impl(kh_table *t, const uint64_t *d_keys, const uint32_t *d_vals, uint64_t n,
+                               uint32_t dflt, int estimate) {
+  cudaStream_t s = t->stream[0];
+  if (n == 0) return 0;
+  if (estimate) {
+    // insert_impl: reserve(size + estimate * (1 + error)) then one pass (:2512-2535)
+    const double est = hll_estimate_dev(t->hash_kind, t->hp, t->W, d_keys, n, nullptr, s, t->sms);
+    const uint64_t want = (uint64_t)std::ceil(std::min((double)n, est * (1.0 + hll_error_rate())));
+    ensure_room(t, want);
+  }
+  // A piece may overshoot max_load (duplicates usually keep it far below); it never fills the table:
+  // the hard limit is halfway between max_load and 1.  Afterwards double until the load is legal again.
+  const double hard = 0.5 * (t->max_load + 1.0);
+  uint64_t added = 0, off = 0;
+  while (off < n) {
+    uint64_t room = (uint64_t)std::floor(hard * (double)t->capacity);
+    room = room > t->size ? room - t->size : 0;
+    if (room == 0 || (double)t->size >= t->max_load * (double)t->capacity) { rebuild(t, t->capacity * 2); continue; }
+    const uint64_t m = std::min(n - off, room);
+    const uint64_t got = insert_resident(t, d_keys + off * t->W, d_vals ? d_vals + off : nullptr, m, dflt, s);
+    t->size += got; added += got; off += m;
+  }
+  while ((double)t->size > t->max_load * (double)t->capacity) rebuild(t, t->capacity * 2);
+  return (int64_t)added;
+}
+
+int64_t kh_insert_dev(kh_table *t, const uint64_t *d_keys, const uint32_t *d_vals, uint64_t n,
+                      uint32_t default_val, int estimate) {
+  return guarded([&]() -> int64_t {
+    if (!t || (!d_keys && n)) { set_error("null table or keys"); return KH_ERR_INVALID; }
+    DeviceGuard g(t->device);
+    return insert_dev_impl(t, d_keys, d_vals, n, default_val, estimate);
+  });
+}
+
+static bool is_pinned(const void *p) {
+  cudaPointerAttributes at;
+  if (cudaPointerGetAttributes(&at, p) != cudaSuccess) { cudaGetLastError(); return false; }
+  return at.type == cudaMemoryTypeHost;
+}
+
+int64_t kh_insert_host(kh_table *t, const uint64_t *keys, const uint32_t *vals, uint64_t n,
+                       uint32_t default_val, int estimate) {
+  return guarded([&]() -> int64_t {
+    if (!t || (!keys && n)) { set_error("null table or keys"); return KH_ERR_INVALID; }
+    DeviceGuard g(t->device);
+    if (n == 0) return 0;
+    const int W = t->W;
+    if (estimate || t->reducer != KH_REDUCE_COUNT) {
+      // whole batch resident: HLL needs a full pass before the first insert, and the ordered
+      // reducers need stable batch positions
+      DevBuf<uint64_t> dk(n * W);
+      DevBuf<uint32_t> dv(vals ? n : 0);
+      for (uint64_t off = 0; off < n; off += HOST_CHUNK) {
+        const uint64_t m = std::min(HOST_CHUNK, n - off);
+        KH_CUDA(cudaMemcpyAsync(dk.p + off * W, keys + off * W, m * W * 8, cudaMemcpyHostToDevice, t->stream[0]));
+        if (vals) KH_CUDA(cudaMemcpyAsync(dv.p + off, vals + off, m * 4, cudaMemcpyHostToDevice, t->stream[0]));
+      }
+      return insert_dev_impl(t, dk.p, vals ? dv.p : nullptr, n, default_val, estimate);
+    }
+    // COUNT without estimate: stream chunks; chunk i+1 is copied while chunk i is inserted
+    uint64_t added = 0;
+    const bool pinned = is_pinned(keys) && (!vals || is_pinned(vals));
+    (void)pinned;   // pageable sources still work (the driver stages them); pinned ones overlap
+    for (int b = 0; b < 2; ++b) { t->d_keys[b].ensure(HOST_CHUNK * W); if (vals) t->d_vals[b].ensure(HOST_CHUNK); }
+    uint64_t off = 0; int buf = 0;
+    uint64_t pending_m[2] = {0, 0};
+    auto issue_copy = [&](int b, uint64_t o, uint64_t m) {
+      KH_CUDA(cudaMemcpyAsync(t->d_keys[b].p, keys + o * W, m * W * 8, cudaMemcpyHostToDevice, t->stream[1]));
+      if (vals) KH_CUDA(cudaMemcpyAsync(t->d_vals[b].p, vals + o, m * 4, cudaMemcpyHostToDevice, t->stream[1]));
+      KH_CUDA(cudaEventRecord(t->ev[b], t->stream[1]));
+      pending_m[b] = m;
+    };
+    issue_copy(0, 0, std::min(HOST_CHUNK, n));
+    while (off < n) {
+      const uint64_t m = pending_m[buf];
+      const uint64_t next_off = off + m;
+      // the other buffer is free: its insert was synchronised in the previous iteration
+      if (next_off < n) issue_copy(buf ^ 1, next_off, std::min(HOST_CHUNK, n - next_off));
+      KH_CUDA(cudaStreamWaitEvent(t->stream[0], t->ev[buf], 0));
+      const int64_t got = insert_dev_impl(t, t->d_keys[buf].p, vals ? t->d_vals[buf].p : nullptr, m, default_val, 0);
+      if (got < 0) return got;
+      added += (uint64_t)got;
+      off = next_off; buf ^= 1;
+    }
+    return (int64_t)added;
+  });
+}
+
+}  // extern "C"
+
+// ---- queries -----------------------------------------------------------------------------
+template <typename OutT, typename Launch>
+static int64_t query_host(kh_table *t, const uint64_t *keys, uint64_t n, OutT *out, DevBuf<OutT> *dout, Launch launch) {
+  // double-buffered: H2D(keys i+1) | kernel(i) | D2H(results i-1)
+  const int W = t->W;
+  if (n == 0) return 0;
+  for (int b = 0; b < 2; ++b) { t->d_keys[b].ensure(HOST_CHUNK * W); dout[b].ensure(HOST_CHUNK); }
+  zero_counter(t, t->stream[0]);
+  KH_CUDA(cudaStreamSynchronize(t->stream[0]));
+  cudaStream_t s2[2] = {t->stream[0], t->stream[1]};
+  int buf = 0;
+  for (uint64_t off = 0; off < n; off += HOST_CHUNK, buf ^= 1) {
+    const uint64_t m = std::min(HOST_CHUNK, n - off);
+    cudaStream_t s = s2[buf];   // each buffer has its own stream: copy-in, kernel, copy-out in order
+    KH_CUDA(cudaMemcpyAsync(t->d_keys[buf].p, keys + off * W, m * W * 8, cudaMemcpyHostToDevice, s));
+    launch(t->d_keys[buf].p, m, dout[buf].p, s);
+    KH_CUDA(cudaMemcpyAsync(out + off, dout[buf].p, m * sizeof(OutT), cudaMemcpyDeviceToHost, s));
+  }
+  KH_CUDA(cudaStreamSynchronize(t->stream[1]));
+  return (int64_t)read_counter(t, t->stream[0]);
+}
+
+extern "C" {
+
+int64_t kh_count_dev(kh_table *t, const uint64_t *d_keys, uint64_t n, uint8_t *d_out) {
+  return guarded([&]() -> int64_t {
+    if (!t || (n && (!d_keys || !d_out))) { set_error("null argument"); return KH_ERR_INVALID; }
+    DeviceGuard g(t->device);
+    cudaStream_t s = t->stream[0];
+    zero_counter(t, s);
+    launch_lookup(t, OP_COUNT, d_keys, n, nullptr, d_out, nullptr, 0, t->counters.p, s);
+    return (int64_t)read_counter(t, s);
+  });
+}
+int64_t kh_count_host(kh_table *t, const uint64_t *keys, uint64_t n, uint8_t *out) {
+  return guarded([&]() -> int64_t {
+    if (!t || (n && (!keys || !out))) { set_error("null argument"); return KH_ERR_INVALID; }
+    DeviceGuard g(t->device);
+    return query_host<uint8_t>(t, keys, n, out, t->d_u8, [&](const uint64_t *dk, uint64_t m, uint8_t *dout, cudaStream_t s) {
+      launch_lookup(t, OP_COUNT, dk, m, nullptr, dout, nullptr, 0, t->counters.p, s);
+    });
+  });
+}
+int64_t kh_find_dev(kh_table *t, const uint64_t *d_keys, uint64_t n, uint32_t *d_out, uint32_t nonexistent) {
+  return guarded([&]() -> int64_t {
+    if (!t || (n && (!d_keys || !d_out))) { set_error("null argument"); return KH_ERR_INVALID; }
+    DeviceGuard g(t->device);
+    cudaStream_t s = t->stream[0];
+    zero_counter(t, s);
+    launch_lookup(t, OP_FIND, d_keys, n, d_out, nullptr, nullptr, nonexistent, t->counters.p, s);
+    return (int64_t)read_counter(t, s);
+  });
+}
+int64_t kh_find_host(kh_table *t, const uint64_t *keys, uint64_t n, uint32_t *out, uint32_t nonexistent) {
+  return guarded([&]() -> int64_t {
+    if (!t || (n && (!keys || !out))) { set_error("null argument"); return KH_ERR_INVALID; }
+    DeviceGuard g(t->device);
+    return query_host<uint32_t>(t, keys, n, out, t->d_vals, [&](const uint64_t *dk, uint64_t m, uint32_t *dout, cudaStream_t s) {
+      launch_lookup(t, OP_FIND, dk, m, dout, nullptr, nullptr, nonexistent, t->counters.p, s);
+    });
+  });
+}
+
+int64_t kh_find_existing_dev(kh_table *t, const uint64_t *d_keys, uint64_t n, uint64_t *d_out_keys, uint32_t *d_out_vals) {
+  return guarded([&]() -> int64_t {
+    if (!t || (n && (!d_keys || !d_out_keys || !d_out_vals))) { set_error("null argument"); return KH_ERR_INVALID; }
+    if (n == 0) return 0;
+    DeviceGuard g(t->device);
+    cudaStream_t s = t->stream[0];
+    DevBuf<uint32_t> vals(n);
+    DevBuf<uint8_t> flags(n);
+    DevBuf<uint64_t> pos(n), wide(n);
+    zero_counter(t, s);
+    launch_lookup(t, OP_FIND, d_keys, n, vals.p, nullptr, nullptr, 0, t->counters.p, s);
+    launch_lookup(t, OP_COUNT, d_keys, n, nullptr, flags.p, nullptr, 0, t->counters.p, s);
+    KH_LAUNCH(widen_flags_kernel, t->grid_for(n, 1024), 256, 0, s, flags.p, n, wide.p);
+    size_t tmp_bytes = 0;
+    KH_CUDA(cub::DeviceScan::ExclusiveSum(nullptr, tmp_bytes, wide.p, pos.p, n, s));
+    DevBuf<unsigned char> tmp(tmp_bytes);
+    KH_CUDA(cub::DeviceScan::ExclusiveSum(tmp.p, tmp_bytes, wide.p, pos.p, n, s));
+    g_launches.fetch_add(1, std::memory_order_relaxed);
+    if (t->W == 1) KH_LAUNCH((scatter_hits_kernel<1>), t->grid_for(n, 1024), 256, 0, s, d_keys, vals.p, flags.p, pos.p, n, d_out_keys, d_out_vals);
+    else KH_LAUNCH((scatter_hits_kernel<2>), t->grid_for(n, 1024), 256, 0, s, d_keys, vals.p, flags.p, pos.p, n, d_out_keys, d_out_vals);
+    return (int64_t)(read_counter(t, s) / 2);   // both lookups counted the hits
+  });
+}
+int64_t kh_find_existing_host(kh_table *t, const uint64_t *keys, uint64_t n, uint64_t *out_keys, uint32_t *out_vals) {
+  return guarded([&]() -> int64_t {
+    if (!t || (n && (!keys || !out_keys || !out_vals))) { set_error("null argument"); return KH_ERR_INVALID; }
+    if (n == 0) return 0;
+    DeviceGuard g(t->device);
+    DevBuf<uint64_t> dk(n * t->W), ok(n * t->W);
+    DevBuf<uint32_t> ov(n);
+    KH_CUDA(cudaMemcpy(dk.p, keys, n * t->W * 8, cudaMemcpyHostToDevice));
+    const int64_t hits = kh_find_existing_dev(t, dk.p, n, ok.p, ov.p);
+    if (hits > 0) {
+      KH_CUDA(cudaMemcpy(out_keys, ok.p, (uint64_t)hits * t->W * 8, cudaMemcpyDeviceToHost));
+      KH_CUDA(cudaMemcpy(out_vals, ov.p, (uint64_t)hits * 4, cudaMemcpyDeviceToHost));
+    }
+    return hits;
+  });
+}
+
+int64_t kh_update_dev(kh_table *t, const uint64_t *d_keys, const uint32_t *d_vals, uint64_t n) {
+  return guarded([&]() -> int64_t {
+    if (!t || (n && (!d_keys || !d_vals))) { set_error("null argument"); return KH_ERR_INVALID; }
+    DeviceGuard g(t->device);
+    cudaStream_t s = t->stream[0];
+    zero_counter(t, s);
+    launch_lookup(t, OP_UPDATE, d_keys, n, nullptr, nullptr, d_vals, 0, t->counters.p, s);
+    return (int64_t)read_counter(t, s);
+  });
+}
+int64_t kh_update_host(kh_table *t, const uint64_t *keys, const uint32_t *vals, uint64_t n) {
+  return guarded([&]() -> int64_t {
+    if (!t || (n && (!keys || !vals))) { set_error("null argument"); return KH_ERR_INVALID; }
+    if (n == 0) return 0;
+    DeviceGuard g(t->device);
+    DevBuf<uint64_t> dk(n * t->W); DevBuf<uint32_t> dv(n);
+    KH_CUDA(cudaMemcpy(dk.p, keys, n * t->W * 8, cudaMemcpyHostToDevice));
+    KH_CUDA(cudaMemcpy(dv.p, vals, n * 4, cudaMemcpyHostToDevice));
+    return kh_update_dev(t, dk.p, dv.p, n);
+  });
+}
+
+// ---- erase -------------------------------------------------------------------------------
+static void maybe_shrink(kh_table *t) {
+  // the reference reserves for the surviving size once the load drops below min_load (:3787)
+  if ((double)t->size < t->min_load * (double)t->capacity) {
+    const uint64_t want = capacity_for(t, t->size);
+    if (want < t->capacity) rebuild(t, want);
+  }
+}
+int64_t kh_erase_dev(kh_table *t, const uint64_t *d_keys, uint64_t n) {
+  return guarded([&]() -> int64_t {
+    if (!t || (n && !d_keys)) { set_error("null argument"); return KH_ERR_INVALID; }
+    DeviceGuard g(t->device);
+    cudaStream_t s = t->stream[0];
+    zero_counter(t, s);
+    launch_lookup(t, OP_ERASE, d_keys, n, nullptr, nullptr, nullptr, 0, t->counters.p, s);
+    const uint64_t erased = read_counter(t, s);
+    t->size -= erased;
+    maybe_shrink(t);
+    return (int64_t)erased;
+  });
+}
+int64_t kh_erase_host(kh_table *t, const uint64_t *keys, uint64_t n) {
+  return guarded([&]() -> int64_t {
+    if (!t || (n && !keys)) { set_error("null argument"); return KH_ERR_INVALID; }
+    if (n == 0) return 0;
+    DeviceGuard g(t->device);
+    const int W = t->W;
+    for (int b = 0; b < 2; ++b) t->d_keys[b].ensure(HOST_CHUNK * W);
+    zero_counter(t, t->stream[0]);
+    KH_CUDA(cudaStreamSynchronize(t->stream[0]));
+    int buf = 0;
+    for (uint64_t off = 0; off < n; off += HOST_CHUNK, buf ^= 1) {
+      const uint64_t m = std::min(HOST_CHUNK, n - off);
+      cudaStream_t s = t->stream[buf];
+      KH_CUDA(cudaMemcpyAsync(t->d_keys[buf].p, keys + off * W, m * W * 8, cudaMemcpyHostToDevice, s));
+      launch_lookup(t, OP_ERASE, t->d_keys[buf].p, m, nullptr, nullptr, nullptr, 0, t->counters.p, s);
+    }
+    KH_CUDA(cudaStreamSynchronize(t->stream[1]));
+    const uint64_t erased = read_counter(t, t->stream[0]);
+    t->size -= erased;
+    maybe_shrink(t);
+    return (int64_t)erased;
+  });
+}
+
+// ---- export ------------------------------------------------------------------------------
+int64_t kh_export_dev(kh_table *t, uint64_t *d_out_keys, uint32_t *d_out_vals, uint64_t cap) {
+  return guarded([&]() -> int64_t {
+    if (!t || (cap && !d_out_keys)) { set_error("null argument"); return KH_ERR_INVALID; }
+    DeviceGuard g(t->device);
+    return (int64_t)dump_entries(t, d_out_keys, d_out_vals, cap, t->stream[0]);
+  });
+}
+int64_t kh_export_host(kh_table *t, uint64_t *out_keys, uint32_t *out_vals, uint64_t cap) {
+  return guarded([&]() -> int64_t {
+    if (!t || (cap && !out_keys)) { set_error("null argument"); return KH_ERR_INVALID; }
+    DeviceGuard g(t->device);
+    const uint64_t m = std::min<uint64_t>(cap, t->size);
+    DevBuf<uint64_t> dk(std::max<uint64_t>(m * t->W, 1)); DevBuf<uint32_t> dv(std::max<uint64_t>(m, 1));
+    const uint64_t n = dump_entries(t, dk.p, dv.p, m, t->stream[0]);
+    const uint64_t c = std::min(n, m);
+    if (c) {
+      KH_CUDA(cudaMemcpy(out_keys, dk.p, c * t->W * 8, cudaMemcpyDeviceToHost));
+      if (out_vals) KH_CUDA(cudaMemcpy(out_vals, dv.p, c * 4, cudaMemcpyDeviceToHost));
+    }
+    return (int64_t)n;
+  });
+}
+
+}  // extern "C"
