@@ -114,6 +114,8 @@ double kh_load_factor(const kh_table *t);
 int kh_clear(kh_table *t);
 int kh_device(const kh_table *t);
 int kh_key_words(const kh_table *t);
+/* probe geometry (experiments; empty table only): lane_bytes 16|32, lanes_per_bucket 1|2|4|8 -- see DESIGN.md */
+int kh_set_geometry(kh_table *t, int lane_bytes, int lanes_per_bucket);
 
 /* HyperLogLog distinct estimate of a key batch over the table's store hash, precision 12
  * (replaces get_hll().update(keys,n) + estimate(), KH/hyperloglog64.hpp:176-239; driver
@@ -208,6 +210,8 @@ typedef struct khd_map khd_map;
 khd_map *khd_create(int n_gpus, int key_words, int store_hash, int dist_hash, int reducer, int canonical_k);
 void khd_destroy(khd_map *m);
 int khd_n_gpus(const khd_map *m);
+/* 1 when partition+exchange run as one kernel storing into peer GPUs' buffers (peer access available) */
+int khd_uses_peer_stores(const khd_map *m);
 int64_t khd_insert_host(khd_map *m, const uint64_t *keys, uint64_t n, uint32_t default_val);
 int64_t khd_count_host(khd_map *m, const uint64_t *keys, uint64_t n, uint8_t *out);
 int64_t khd_find_host(khd_map *m, const uint64_t *keys, uint64_t n, uint32_t *out, uint32_t nonexistent);

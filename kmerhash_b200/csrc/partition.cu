@@ -16,6 +16,7 @@
 #include <cub/device/device_scan.cuh>
 #include "kh_common.h"
 #include "kh_table.cuh"
+#include "kh_partition.h"
 
 namespace kh {
 
@@ -60,11 +61,6 @@ __global__ void __launch_bounds__(PART_BLOCK) part_hist_kernel(const uint64_t *k
   for (uint32_t r = threadIdx.x; r < p; r += blockDim.x) hist[(uint64_t)r * gridDim.x + blockIdx.x] = sh[r];
 }
 
-struct PartDst {
-  // destination segment r starts at base[r] (device pointers, possibly on peer GPUs), keys land at
-  // base[r] + (global position - seg_start[r]) * W.  With one contiguous output: base[r] = out + seg_start[r] * W.
-  uint64_t *base[8];
-};
 
 template <int W, bool MULTI_DST>
 __global__ void __launch_bounds__(PART_BLOCK) part_scatter_kernel(const uint64_t *keys, uint64_t n, uint64_t per_block,
@@ -125,21 +121,26 @@ __global__ void unpermute_kernel(const T *in, const uint32_t *perm, uint64_t n, 
   for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) out[perm[i]] = in[i];
 }
 
-// Shared by kh_partition_dev and dist.cu.  counts_host[p] receives the per-rank totals.
-// When dst != nullptr the keys are written through dst->base[] (p <= 8) instead of d_out_keys.
-void partition_dev(int device, int kind, const HashParams &hp, int W, uint32_t p, const uint64_t *d_keys, uint64_t n,
-                   uint64_t *d_out_keys, uint32_t *d_out_perm, uint64_t *counts_host, const PartDst *dst,
-                   cudaStream_t s) {
-  for (uint32_t r = 0; r < p; ++r) counts_host[r] = 0;
+// ---- PartitionPlan: count() = histogram + scan (per-rank totals known on the host),
+//      scatter() = stable scatter, optionally through per-destination base pointers -----------
+void PartitionPlan::init(int device_, int kind_, const HashParams &hp_, int W_, uint32_t p_, const uint64_t *d_keys_,
+                         uint64_t n_) {
+  device = device_; kind = kind_; hp = hp_; W = W_; p = p_; d_keys = d_keys_; n = n_;
+  seg_h.assign(p + 1, 0);
+  blocks = per_block = 0;
   if (n == 0) return;
-  const int sms = sm_count(device);
-  const uint64_t max_blocks = (uint64_t)sms * 8;
-  uint64_t blocks = std::min<uint64_t>(max_blocks, (n + PART_BLOCK - 1) / PART_BLOCK);
-  uint64_t per_block = (n + blocks - 1) / blocks;
+  const uint64_t max_blocks = (uint64_t)sm_count(device) * 8;
+  blocks = std::min<uint64_t>(max_blocks, (n + PART_BLOCK - 1) / PART_BLOCK);
+  per_block = (n + blocks - 1) / blocks;
   per_block = (per_block + PART_BLOCK - 1) / PART_BLOCK * PART_BLOCK;
   blocks = (n + per_block - 1) / per_block;
+}
+
+void PartitionPlan::count(cudaStream_t s, uint64_t *counts_host) {
+  for (uint32_t r = 0; r < p; ++r) counts_host[r] = 0;
+  if (n == 0) return;
   const uint64_t cells = (uint64_t)p * blocks;
-  DevBuf<uint64_t> hist(cells + 1), offs(cells + 1), seg(p + 1);
+  hist.alloc(cells + 1); offs.alloc(cells + 1); seg.alloc(p + 1);
   KH_CUDA(cudaMemsetAsync(hist.p + cells, 0, sizeof(uint64_t), s));
   if (W == 1) KH_LAUNCH((part_hist_kernel<1>), (int)blocks, PART_BLOCK, 0, s, d_keys, n, per_block, kind, hp, p, hist.p);
   else KH_LAUNCH((part_hist_kernel<2>), (int)blocks, PART_BLOCK, 0, s, d_keys, n, per_block, kind, hp, p, hist.p);
@@ -148,23 +149,35 @@ void partition_dev(int device, int kind, const HashParams &hp, int W, uint32_t p
   DevBuf<unsigned char> tmp(tmp_bytes);
   KH_CUDA(cub::DeviceScan::ExclusiveSum(tmp.p, tmp_bytes, hist.p, offs.p, cells + 1, s));
   g_launches.fetch_add(1, std::memory_order_relaxed);
-  // segment starts = offsets[r][0], total at [cells]
-  std::vector<uint64_t> seg_h(p + 1);
+  // segment start of rank r = offsets[r][block 0]
   KH_CUDA(cudaMemcpy2DAsync(seg_h.data(), sizeof(uint64_t), offs.p, blocks * sizeof(uint64_t), sizeof(uint64_t), p,
                             cudaMemcpyDeviceToHost, s));
-  KH_CUDA(cudaStreamSynchronize(s));
+  KH_CUDA(cudaStreamSynchronize(s));   // also keeps `tmp` alive until the scan is done
   seg_h[p] = n;
   for (uint32_t r = 0; r < p; ++r) counts_host[r] = seg_h[r + 1] - seg_h[r];
+  KH_CUDA(cudaMemcpyAsync(seg.p, seg_h.data(), (p + 1) * sizeof(uint64_t), cudaMemcpyHostToDevice, s));
+}
+
+void PartitionPlan::scatter(cudaStream_t s, uint64_t *d_out_keys, uint32_t *d_out_perm, const PartDst *dst) {
+  if (n == 0) return;
   PartDst d{};
   if (dst) {
     d = *dst;
-    KH_CUDA(cudaMemcpyAsync(seg.p, seg_h.data(), (p + 1) * sizeof(uint64_t), cudaMemcpyHostToDevice, s));
     if (W == 1) KH_LAUNCH((part_scatter_kernel<1, true>), (int)blocks, PART_BLOCK, 0, s, d_keys, n, per_block, kind, hp, p, offs.p, d_out_keys, d_out_perm, d, seg.p);
     else KH_LAUNCH((part_scatter_kernel<2, true>), (int)blocks, PART_BLOCK, 0, s, d_keys, n, per_block, kind, hp, p, offs.p, d_out_keys, d_out_perm, d, seg.p);
   } else {
     if (W == 1) KH_LAUNCH((part_scatter_kernel<1, false>), (int)blocks, PART_BLOCK, 0, s, d_keys, n, per_block, kind, hp, p, offs.p, d_out_keys, d_out_perm, d, nullptr);
     else KH_LAUNCH((part_scatter_kernel<2, false>), (int)blocks, PART_BLOCK, 0, s, d_keys, n, per_block, kind, hp, p, offs.p, d_out_keys, d_out_perm, d, nullptr);
   }
+}
+
+void partition_dev(int device, int kind, const HashParams &hp, int W, uint32_t p, const uint64_t *d_keys, uint64_t n,
+                   uint64_t *d_out_keys, uint32_t *d_out_perm, uint64_t *counts_host, const PartDst *dst,
+                   cudaStream_t s) {
+  PartitionPlan plan;
+  plan.init(device, kind, hp, W, p, d_keys, n);
+  plan.count(s, counts_host);
+  plan.scatter(s, d_out_keys, d_out_perm, dst);
   KH_CUDA(cudaStreamSynchronize(s));
 }
 

@@ -1,0 +1,223 @@
+"""Host-side mirror of the reference's container interface over the C ABI.
+
+Class / method names follow the reference (paths relative to the reference tree):
+  hashmap_robinhood_offsets_count / hashmap_robinhood_offsets / ..._reduction
+      include/kmerhash/robinhood_offset_hashmap_ptr.hpp:196-202,4094,4099
+  hashmap_robinhood_doubling      include/kmerhash/hashmap_robinhood.hpp:126
+  hashmap_linearprobe_doubling    include/kmerhash/hashmap_linearprobe.hpp:98
+Batch methods take either numpy arrays (HOST memory; the library moves the data) or torch CUDA
+tensors (DEVICE memory on the table's GPU; zero copy).  Keys are uint64 words: shape (n,) for
+k <= 32, (n, 2) for k <= 64 -- the memory layout of bliss::common::Kmer<K, DNA, uint64_t>.
+"""
+import ctypes as C
+
+import numpy as np
+
+from ._lib import lib, check, HASH_KINDS, REDUCERS, MAP_KINDS, DEFAULT_SEED, DEFAULT_CRC_SEED
+
+try:  # torch is plumbing only (device buffers); the table itself never needs it
+    import torch
+except Exception:  # pragma: no cover
+    torch = None
+
+
+def _is_torch(x):
+    return torch is not None and isinstance(x, torch.Tensor)
+
+
+def _host_keys(keys, W):
+    a = np.ascontiguousarray(keys, dtype=np.uint64)
+    if W == 1:
+        if a.ndim == 2 and a.shape[1] == 1:
+            a = a[:, 0].copy()
+        if a.ndim != 1:
+            raise ValueError("expected keys of shape (n,) for 1-word keys")
+    else:
+        if a.ndim != 2 or a.shape[1] != W:
+            raise ValueError("expected keys of shape (n, %d)" % W)
+    return a, a.shape[0]
+
+
+def _dev_keys(keys, W, device):
+    if not keys.is_cuda or keys.device.index != device:
+        raise ValueError("device keys must live on cuda:%d" % device)
+    if keys.dtype not in (torch.int64, torch.uint64):
+        raise ValueError("device keys must be int64/uint64 words")
+    if not keys.is_contiguous():
+        keys = keys.contiguous()
+    n = keys.shape[0]
+    if W == 2 and (keys.dim() != 2 or keys.shape[1] != 2):
+        raise ValueError("expected keys of shape (n, 2)")
+    if W == 1 and keys.dim() != 1:
+        raise ValueError("expected keys of shape (n,)")
+    torch.cuda.current_stream(device).synchronize()   # the library works on its own streams
+    return keys, n
+
+
+class HashMap:
+    """One table on one GPU.  `reducer` selects COUNT (std::plus), FIRST (Discard) or LAST (Replace)."""
+
+    def __init__(self, key_words=1, hash_kind="MURMUR64avx", reducer="COUNT", map_kind="ROBINHOOD_OFFSETS",
+                 device=0, seed=None, min_load=None, max_load=None):
+        if seed is None:
+            seed = DEFAULT_CRC_SEED if hash_kind == "CRC32C" else DEFAULT_SEED
+        self.W, self.device = int(key_words), int(device)
+        self.hash_kind, self.reducer, self.map_kind = hash_kind, reducer, map_kind
+        self._h = lib.kh_create(self.device, MAP_KINDS[map_kind], self.W, HASH_KINDS[hash_kind], seed, REDUCERS[reducer])
+        if not self._h:
+            check(-3 if lib.kh_device_count() <= 0 else -1, "kh_create")
+        if min_load is not None or max_load is not None:
+            self.set_load_factors(min_load if min_load is not None else 0.2, max_load if max_load is not None else 0.8)
+
+    def __del__(self):
+        h, self._h = getattr(self, "_h", None), None
+        if h:
+            lib.kh_destroy(h)
+
+    # ---- sizing (reference: set_max/min_load_factor, reserve, rehash, capacity, size, clear) ----
+    def set_load_factors(self, min_load, max_load):
+        check(lib.kh_set_load_factors(self._h, min_load, max_load), "set_load_factors")
+
+    def set_insert_lookahead(self, n):
+        lib.kh_set_lookahead(self._h, int(n), 0)
+
+    def set_query_lookahead(self, n):
+        lib.kh_set_lookahead(self._h, 0, int(n))
+
+    def set_geometry(self, lane_bytes, lanes_per_bucket):
+        check(lib.kh_set_geometry(self._h, lane_bytes, lanes_per_bucket), "set_geometry")
+
+    def reserve(self, n):
+        check(lib.kh_reserve(self._h, int(n)), "reserve")
+
+    def rehash(self, slots):
+        check(lib.kh_rehash(self._h, int(slots)), "rehash")
+
+    def capacity(self):
+        return lib.kh_capacity(self._h)
+
+    def size(self):
+        return lib.kh_size(self._h)
+
+    __len__ = size
+
+    def get_load_factor(self):
+        return lib.kh_load_factor(self._h)
+
+    def clear(self):
+        check(lib.kh_clear(self._h), "clear")
+
+    # ---- estimate (reference: get_hll().update + estimate) ----
+    def estimate_distinct(self, keys, return_registers=False):
+        regs = np.zeros(4096, dtype=np.uint8)
+        if _is_torch(keys):
+            k, n = _dev_keys(keys, self.W, self.device)
+            est = lib.kh_estimate_distinct_dev(self._h, k.data_ptr(), n, regs.ctypes.data)
+        else:
+            k, n = _host_keys(keys, self.W)
+            est = lib.kh_estimate_distinct_host(self._h, k.ctypes.data, n, regs.ctypes.data)
+        if est < 0:
+            check(-3, "estimate_distinct")
+        return (est, regs) if return_registers else est
+
+    # ---- insert (reference: insert / insert_no_estimate) ----
+    def insert(self, keys, vals=None, default=1, estimate=True):
+        """Returns the number of keys that were new."""
+        if _is_torch(keys):
+            k, n = _dev_keys(keys, self.W, self.device)
+            vp = None
+            if vals is not None:
+                vals = vals.contiguous()
+                assert vals.is_cuda and vals.dtype in (torch.int32, torch.uint32) and vals.shape[0] == n
+                vp = vals.data_ptr()
+            return check(lib.kh_insert_dev(self._h, k.data_ptr(), vp, n, default, int(estimate)), "insert")
+        k, n = _host_keys(keys, self.W)
+        vp = None
+        if vals is not None:
+            vals = np.ascontiguousarray(vals, dtype=np.uint32)
+            assert vals.shape[0] == n
+            vp = vals.ctypes.data
+        return check(lib.kh_insert_host(self._h, k.ctypes.data, vp, n, default, int(estimate)), "insert")
+
+    def insert_no_estimate(self, keys, vals=None, default=1):
+        return self.insert(keys, vals, default, estimate=False)
+
+    # ---- queries ----
+    def count(self, keys):
+        """0/1 per key (reference: count(out, b, e) / exists)."""
+        if _is_torch(keys):
+            k, n = _dev_keys(keys, self.W, self.device)
+            out = torch.empty(n, dtype=torch.uint8, device=k.device)
+            check(lib.kh_count_dev(self._h, k.data_ptr(), n, out.data_ptr()), "count")
+            return out
+        k, n = _host_keys(keys, self.W)
+        out = np.empty(n, dtype=np.uint8)
+        check(lib.kh_count_host(self._h, k.ctypes.data, n, out.ctypes.data), "count")
+        return out
+
+    exists = count
+
+    def find(self, keys, nonexistent=0):
+        """value per key, `nonexistent` where absent (reference: find<OT>(out, b, e, nonexistent))."""
+        if _is_torch(keys):
+            k, n = _dev_keys(keys, self.W, self.device)
+            out = torch.empty(n, dtype=torch.int32, device=k.device)
+            check(lib.kh_find_dev(self._h, k.data_ptr(), n, out.data_ptr(), nonexistent), "find")
+            return out
+        k, n = _host_keys(keys, self.W)
+        out = np.empty(n, dtype=np.uint32)
+        check(lib.kh_find_host(self._h, k.ctypes.data, n, out.ctypes.data, nonexistent), "find")
+        return out
+
+    def find_existing(self, keys):
+        """(keys, vals) of the hits only, in query order (reference: find_existing)."""
+        k, n = _host_keys(keys, self.W)
+        ok = np.empty((max(n, 1), self.W), dtype=np.uint64)
+        ov = np.empty(max(n, 1), dtype=np.uint32)
+        c = check(lib.kh_find_existing_host(self._h, k.ctypes.data, n, ok.ctypes.data, ov.ctypes.data), "find_existing")
+        return (ok[:c] if self.W > 1 else ok[:c, 0].copy()), ov[:c]
+
+    def update(self, keys, vals):
+        k, n = _host_keys(keys, self.W)
+        vals = np.ascontiguousarray(vals, dtype=np.uint32)
+        return check(lib.kh_update_host(self._h, k.ctypes.data, vals.ctypes.data, n), "update")
+
+    def erase(self, keys):
+        if _is_torch(keys):
+            k, n = _dev_keys(keys, self.W, self.device)
+            return check(lib.kh_erase_dev(self._h, k.data_ptr(), n), "erase")
+        k, n = _host_keys(keys, self.W)
+        return check(lib.kh_erase_host(self._h, k.ctypes.data, n), "erase")
+
+    def to_vector(self):
+        """(keys, vals), unordered (reference: to_vector)."""
+        n = self.size()
+        ok = np.empty((max(n, 1), self.W), dtype=np.uint64)
+        ov = np.empty(max(n, 1), dtype=np.uint32)
+        c = check(lib.kh_export_host(self._h, ok.ctypes.data, ov.ctypes.data, n), "to_vector")
+        c = min(c, n)
+        return (ok[:c] if self.W > 1 else ok[:c, 0].copy()), ov[:c]
+
+    def keys(self):
+        return self.to_vector()[0]
+
+
+# ---- the reference's container names --------------------------------------------------------
+def hashmap_robinhood_offsets_count(key_words=1, hash_kind="MURMUR64avx", device=0, **kw):
+    return HashMap(key_words, hash_kind, "COUNT", "ROBINHOOD_OFFSETS", device, **kw)
+
+
+def hashmap_robinhood_offsets(key_words=1, hash_kind="MURMUR64avx", device=0, **kw):
+    return HashMap(key_words, hash_kind, "FIRST", "ROBINHOOD_OFFSETS", device, **kw)
+
+
+def hashmap_robinhood_offsets_reduction(key_words=1, hash_kind="MURMUR64avx", reducer="LAST", device=0, **kw):
+    return HashMap(key_words, hash_kind, reducer, "ROBINHOOD_OFFSETS", device, **kw)
+
+
+def hashmap_robinhood_doubling(key_words=1, hash_kind="MURMUR64", device=0, **kw):
+    return HashMap(key_words, hash_kind, "FIRST", "ROBINHOOD", device, **kw)
+
+
+def hashmap_linearprobe_doubling(key_words=1, hash_kind="MURMUR64", device=0, **kw):
+    return HashMap(key_words, hash_kind, "FIRST", "LINEARPROBE", device, **kw)
