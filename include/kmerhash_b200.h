@@ -114,6 +114,12 @@ double kh_load_factor(const kh_table *t);
 int kh_clear(kh_table *t);
 int kh_device(const kh_table *t);
 int kh_key_words(const kh_table *t);
+/* the CUDA stream the *_dev entry points of this table launch on (a cudaStream_t), for event timing */
+void *kh_stream(kh_table *t);
+/* CUDA-event timing of the probe kernels on their launching stream: enable, run operations, then read
+ * the accumulated milliseconds and launch count of which = 0 (insert kernels) / 1 (lookup kernels) */
+int kh_kernel_timing(kh_table *t, int enable);
+int kh_kernel_time(kh_table *t, int which, double *sum_ms, uint64_t *launches);
 /* probe geometry (experiments; empty table only): lane_bytes 16|32, lanes_per_bucket 1|2|4|8 -- see DESIGN.md */
 int kh_set_geometry(kh_table *t, int lane_bytes, int lanes_per_bucket);
 

@@ -60,6 +60,9 @@ SIGNATURES = {
     "kh_set_load_factors": (_int, [_vp, _dbl, _dbl]),
     "kh_set_lookahead": (_int, [_vp, _int, _int]),
     "kh_set_geometry": (_int, [_vp, _int, _int]),
+    "kh_stream": (_vp, [_vp]),
+    "kh_kernel_timing": (_int, [_vp, _int]),
+    "kh_kernel_time": (_int, [_vp, _int, _vp, _vp]),
     "kh_reserve": (_int, [_vp, _u64]),
     "kh_rehash": (_int, [_vp, _u64]),
     "kh_capacity": (_u64, [_vp]),

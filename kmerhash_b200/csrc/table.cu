@@ -134,6 +134,13 @@ struct kh_table {
   DevBuf<uint32_t> d_vals[2];
   DevBuf<uint8_t> d_u8[2];
   int sms = 148;
+  // CUDA-event pairs around every probe-kernel launch (bench.py's roofline: measured on the launching stream)
+  std::vector<std::pair<cudaEvent_t, cudaEvent_t>> kev;
+  size_t kev_used = 0;
+  double kev_ms[2] = {0.0, 0.0};        // accumulated [insert kernels, lookup kernels]
+  uint64_t kev_n[2] = {0, 0};
+  std::vector<int> kev_kind;
+  bool kev_on = false;
 
   int slot_bytes() const { return 16 * W; }
   int bucket_slots() const { return G * (LB / slot_bytes()); }
@@ -196,6 +203,32 @@ uint64_t capacity_for(const kh_table *t, uint64_t n) {
   return std::max<uint64_t>(cap, 128);
 }
 
+void kev_begin(kh_table *t, int kind, cudaStream_t s) {
+  if (!t->kev_on) return;
+  if (t->kev_used == t->kev.size()) {
+    cudaEvent_t a, b;
+    KH_CUDA(cudaEventCreate(&a)); KH_CUDA(cudaEventCreate(&b));
+    t->kev.emplace_back(a, b); t->kev_kind.push_back(kind);
+  }
+  t->kev_kind[t->kev_used] = kind;
+  KH_CUDA(cudaEventRecord(t->kev[t->kev_used].first, s));
+}
+void kev_end(kh_table *t, cudaStream_t s) {
+  if (!t->kev_on) return;
+  KH_CUDA(cudaEventRecord(t->kev[t->kev_used].second, s));
+  ++t->kev_used;
+}
+void kev_resolve(kh_table *t) {
+  for (size_t i = 0; i < t->kev_used; ++i) {
+    float ms = 0;
+    if (cudaEventSynchronize(t->kev[i].second) == cudaSuccess &&
+        cudaEventElapsedTime(&ms, t->kev[i].first, t->kev[i].second) == cudaSuccess) {
+      t->kev_ms[t->kev_kind[i]] += ms; t->kev_n[t->kev_kind[i]] += 1;
+    }
+  }
+  t->kev_used = 0;
+}
+
 void launch_insert(kh_table *t, const uint64_t *d_keys, const uint32_t *d_vals, uint64_t n, uint32_t dflt,
                    int mode, cudaStream_t s) {
   if (n == 0) return;
@@ -204,11 +237,13 @@ void launch_insert(kh_table *t, const uint64_t *d_keys, const uint32_t *d_vals, 
   a.hash_kind = t->hash_kind; a.hp = t->hp; a.idx_base = 0;
   a.n_new = t->counters.p; a.status = t->status.p;
   const int grid = t->grid_for(n, 256);
+  kev_begin(t, 0, s);
   KH_GEOM_SWITCH(t, {
     if (mode == INS_COUNT) KH_LAUNCH((insert_kernel<W, LB, G, INS_COUNT>), grid, 256, 0, s, a);
     else if (mode == INS_FIRST) KH_LAUNCH((insert_kernel<W, LB, G, INS_FIRST>), grid, 256, 0, s, a);
     else KH_LAUNCH((insert_kernel<W, LB, G, INS_LAST>), grid, 256, 0, s, a);
   });
+  kev_end(t, s);
 }
 
 void launch_lookup(kh_table *t, int op, const uint64_t *d_keys, uint64_t n, uint32_t *out_u32, uint8_t *out_u8,
@@ -219,6 +254,7 @@ void launch_lookup(kh_table *t, int op, const uint64_t *d_keys, uint64_t n, uint
   a.out_u32 = out_u32; a.out_u8 = out_u8; a.vals = vals; a.nonexistent = nonexistent;
   a.ins_mode = (uint32_t)t->reducer; a.idx_base = 0; a.n_hit = counter;
   const int grid = t->grid_for(n, 256);
+  kev_begin(t, 1, s);
   KH_GEOM_SWITCH(t, {
     switch (op) {
       case OP_FIND:     KH_LAUNCH((lookup_kernel<W, LB, G, OP_FIND>), grid, 256, 0, s, a); break;
@@ -228,6 +264,7 @@ void launch_lookup(kh_table *t, int op, const uint64_t *d_keys, uint64_t n, uint
       default:          KH_LAUNCH((lookup_kernel<W, LB, G, OP_FINALIZE>), grid, 256, 0, s, a); break;
     }
   });
+  kev_end(t, s);
 }
 
 void zero_counter(kh_table *t, cudaStream_t s) {
@@ -360,6 +397,7 @@ void kh_destroy(kh_table *t) {
   if (!t) return;
   int prev = -1; cudaGetDevice(&prev); cudaSetDevice(t->device);
   for (int i = 0; i < 2; ++i) { if (t->stream[i]) cudaStreamDestroy(t->stream[i]); if (t->ev[i]) cudaEventDestroy(t->ev[i]); }
+  for (auto &e : t->kev) { cudaEventDestroy(e.first); cudaEventDestroy(e.second); }
   if (t->h_counters) cudaFreeHost(t->h_counters);
   if (t->h_status) cudaFreeHost(t->h_status);
   t->slots.release(); t->side.release(); t->counters.release(); t->status.release();
@@ -376,6 +414,24 @@ int kh_set_load_factors(kh_table *t, double min_load, double max_load) {
   return KH_OK;
 }
 int kh_set_lookahead(kh_table *t, int, int) { return t ? KH_OK : KH_ERR_INVALID; }
+
+void *kh_stream(kh_table *t) { return t ? (void *)t->stream[0] : nullptr; }
+
+int kh_kernel_timing(kh_table *t, int enable) {
+  if (!t) return KH_ERR_INVALID;
+  t->kev_on = enable != 0; t->kev_used = 0;
+  t->kev_ms[0] = t->kev_ms[1] = 0.0; t->kev_n[0] = t->kev_n[1] = 0;
+  return KH_OK;
+}
+int kh_kernel_time(kh_table *t, int which, double *sum_ms, uint64_t *launches) {
+  if (!t || which < 0 || which > 1) return KH_ERR_INVALID;
+  int prev = -1; cudaGetDevice(&prev); cudaSetDevice(t->device);
+  kev_resolve(t);
+  if (prev >= 0) cudaSetDevice(prev);
+  if (sum_ms) *sum_ms = t->kev_ms[which];
+  if (launches) *launches = t->kev_n[which];
+  return KH_OK;
+}
 
 int kh_set_geometry(kh_table *t, int lane_bytes, int lanes_per_bucket) {
   return (int)guarded([&]() -> int64_t {

@@ -87,6 +87,19 @@ class HashMap:
     def set_geometry(self, lane_bytes, lanes_per_bucket):
         check(lib.kh_set_geometry(self._h, lane_bytes, lanes_per_bucket), "set_geometry")
 
+    def stream_ptr(self):
+        """cudaStream_t (as int) the device-pointer calls of this table launch on"""
+        return lib.kh_stream(self._h)
+
+    def kernel_timing(self, enable=True):
+        check(lib.kh_kernel_timing(self._h, int(enable)), "kernel_timing")
+
+    def kernel_time(self, which="insert"):
+        """(sum of ms, launches) of the insert / lookup probe kernels since kernel_timing(True)"""
+        ms, n = C.c_double(0), C.c_uint64(0)
+        check(lib.kh_kernel_time(self._h, 0 if which == "insert" else 1, C.byref(ms), C.byref(n)), "kernel_time")
+        return ms.value, n.value
+
     def reserve(self, n):
         check(lib.kh_reserve(self._h, int(n)), "reserve")
 

@@ -1,0 +1,115 @@
+"""CPU tier: the C-ABI library loads, exports every symbol include/kmerhash_b200.h declares, fails loudly
+without a GPU (no CPU fallback), and the arithmetic the kernels inline (compiled for the host from the very
+same headers, tests/host_check.cu) is bit-exact to the oracle and the golden vectors."""
+import ctypes as C
+import os
+import re
+import subprocess
+
+import numpy as np
+import pytest
+
+from conftest import ROOT
+
+HEADER = os.path.join(ROOT, "include", "kmerhash_b200.h")
+
+
+def declared_functions():
+    src = open(HEADER).read()
+    src = re.sub(r"/\*.*?\*/", "", src, flags=re.S)
+    return sorted(set(re.findall(r"\b(khd?_[a-z0-9_]+)\s*\(", src)))
+
+
+def test_header_symbols_exported(kh):
+    names = declared_functions()
+    assert len(names) >= 50
+    lib = C.CDLL(kh.LIB_PATH)
+    missing = [n for n in names if not hasattr(lib, n)]
+    assert not missing, missing
+    # and the python binding covers every one of them
+    from kmerhash_b200._lib import SIGNATURES
+    assert sorted(SIGNATURES) == names
+
+
+def test_product_never_touches_the_oracle():
+    for dirpath, _, files in os.walk(os.path.join(ROOT, "kmerhash_b200")):
+        for f in files:
+            if f.endswith((".py", ".cu", ".cuh", ".h", ".hpp")):
+                text = open(os.path.join(dirpath, f)).read()
+                assert "import oracle" not in text and "from oracle" not in text, f
+                assert "libkmerhash_oracle" not in text and "libkmerhash_ref" not in text, f
+
+
+def test_no_gpu_fails_loudly(kh):
+    if kh.device_count() > 0:
+        pytest.skip("a GPU is visible")
+    with pytest.raises(kh.KmerHashError):
+        kh.HashMap()
+    with pytest.raises(kh.KmerHashError):
+        kh.hash_batch(np.arange(8, dtype=np.uint64))
+    with pytest.raises(kh.KmerHashError):
+        kh.kmers_from_reads(b"ACGTACGT", np.array([0, 8], dtype=np.uint64), 3)
+    with pytest.raises(kh.KmerHashError):
+        kh.MultiGpuMap(1)
+    assert "no CPU fallback" in kh.last_error() or "CUDA" in kh.last_error()
+
+
+@pytest.fixture(scope="module")
+def hostlib():
+    path = os.path.join(ROOT, "tests", "libkh_host_check.so")
+    if not os.path.exists(path):
+        import __graft_entry__
+        __graft_entry__.build_host_check()
+    L = C.CDLL(path)
+    u64p = np.ctypeslib.ndpointer(dtype=np.uint64, flags="C_CONTIGUOUS")
+    L.khtest_hash.argtypes = [C.c_int, C.c_uint32, C.c_int, u64p, C.c_size_t, u64p]
+    L.khtest_kmer.argtypes = [C.c_int, C.c_int, u64p, C.c_size_t, u64p]
+    return L
+
+
+def test_kernel_arithmetic_on_host_vs_golden(hostlib, golden, oracle_mod):
+    k1, k2 = golden["hash_keys1"], golden["hash_keys2"]
+    for name, kid in oracle_mod.HASH_KINDS.items():
+        if name == "MURMUR32FINALIZER":
+            continue
+        for seed in (43, 37, 9876543):
+            for W, keys in ((1, k1), (2, k2)):
+                out = np.empty(keys.shape[0], dtype=np.uint64)
+                assert hostlib.khtest_hash(kid, seed, W, np.ascontiguousarray(keys), keys.shape[0], out) == 0
+                assert np.array_equal(out, golden["hash_%s_%d_w%d" % (name, seed, W)]), (name, seed, W)
+    for k in (5, 15, 21, 31, 33, 47, 63):
+        w = np.ascontiguousarray(golden["kmer_windows_k%d" % k])
+        for mode, key in ((0, "kmer_canon_k%d"), (1, "kmer_revcomp_k%d")):
+            out = np.empty_like(w)
+            hostlib.khtest_kmer(k, mode, w, w.shape[0], out)
+            assert np.array_equal(out, golden[key % k]), (k, mode)
+
+
+def test_kernel_arithmetic_on_host_vs_oracle_random(hostlib, oracle_mod):
+    rng = np.random.default_rng(99)
+    port = oracle_mod.port
+    for W in (1, 2):
+        keys = rng.integers(0, 2**64, size=(20000, W), dtype=np.uint64)
+        kk = keys if W == 2 else keys[:, 0].copy()
+        for name, kid in oracle_mod.HASH_KINDS.items():
+            if name == "MURMUR32FINALIZER":
+                continue
+            out = np.empty(20000, dtype=np.uint64)
+            hostlib.khtest_hash(kid, 9876543, W, keys, 20000, out)
+            assert np.array_equal(out, port.hash(name, kk, 9876543)), name
+    for k in (1, 2, 16, 31, 32, 33, 48, 63, 64):
+        W = (2 * k + 63) // 64
+        km = rng.integers(0, 2**64, size=(5000, W), dtype=np.uint64)
+        top = 2 * k - 64 * (W - 1)
+        if top < 64:
+            km[:, W - 1] &= np.uint64((1 << top) - 1)
+        out = np.empty_like(km)
+        hostlib.khtest_kmer(k, 0, km, 5000, out)
+        exp = port.canonical(k, km if W == 2 else km[:, 0].copy())
+        assert np.array_equal(out.reshape(exp.shape), exp), k
+
+
+def test_murmur32fin_rejected(kh):
+    # murmur3finalizer_avx32 is defined for keys <= 4 bytes only (murmurhash3finalizer_32_avx.hpp:527)
+    with pytest.raises((ValueError, kh.KmerHashError)):
+        kh.hash_batch(np.arange(4, dtype=np.uint64), "MURMUR32FINALIZER")

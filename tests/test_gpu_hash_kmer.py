@@ -1,0 +1,112 @@
+"""GPU tier: batched hashes, k-mer generation, canonicalisation and rank partitioning through the C ABI,
+bit-exact against the oracle and the committed golden vectors."""
+import numpy as np
+import pytest
+
+from conftest import READ78, make_reads
+
+pytestmark = pytest.mark.gpu
+
+HASHES = ["IDEN", "MURMUR64", "MURMUR64avx", "MURMUR32", "MURMUR32avx", "MURMUR32sse", "FARM", "FARM32",
+          "CLHASH", "CRC32C", "MURMUR_X86"]
+
+
+@pytest.mark.parametrize("name", HASHES)
+def test_hash_golden(kh, golden, name):
+    for seed in (43, 37, 9876543):
+        assert np.array_equal(kh.hash_batch(golden["hash_keys1"], name, seed), golden["hash_%s_%d_w1" % (name, seed)])
+        assert np.array_equal(kh.hash_batch(golden["hash_keys2"], name, seed), golden["hash_%s_%d_w2" % (name, seed)])
+
+
+@pytest.mark.parametrize("W", [1, 2])
+def test_hash_random_vs_oracle(kh, oracle_mod, W):
+    rng = np.random.default_rng(3 + W)
+    for n in (0, 1, 31, 1000, 200003):          # empty, tiny, ragged tails
+        keys = rng.integers(0, 2**64, size=(n, W), dtype=np.uint64)
+        kk = keys if W == 2 else keys[:, 0].copy()
+        for name in HASHES:
+            got = kh.hash_batch(kk, name, 9876543)
+            assert np.array_equal(got, oracle_mod.port.hash(name, kk, 9876543)), (name, n)
+
+
+def test_seed_changes_hash(kh):
+    """the reference's own hash tests check seed sensitivity (test/unit/test_kmer_hash.cpp:291-424)"""
+    keys = np.arange(1, 2000, dtype=np.uint64)
+    for name in ("MURMUR64", "MURMUR64avx", "MURMUR32", "FARM", "CLHASH", "CRC32C"):
+        a, b = kh.hash_batch(keys, name, 43), kh.hash_batch(keys, name, 44)
+        assert not np.array_equal(a, b), name
+        assert len(np.unique(a)) == len(a), name     # no collisions among adjacent keys
+
+
+@pytest.mark.parametrize("k", [5, 15, 21, 31, 33, 47, 63])
+def test_kmer_golden(kh, golden, k):
+    bases = np.frombuffer(READ78.encode(), dtype=np.uint8)
+    offs = np.array([0, len(READ78)], dtype=np.uint64)
+    assert np.array_equal(kh.kmers_from_reads(bases, offs, k, False), golden["kmer_windows_k%d" % k])
+    assert np.array_equal(kh.kmers_from_reads(bases, offs, k, True), golden["kmer_canon_k%d" % k])
+    w = golden["kmer_windows_k%d" % k]
+    assert np.array_equal(kh.revcomp(w, k), golden["kmer_revcomp_k%d" % k])
+    assert np.array_equal(kh.canonicalize(w, k), golden["kmer_canon_k%d" % k])
+
+
+@pytest.mark.parametrize("k", [1, 2, 16, 31, 32, 33, 48, 63, 64])
+@pytest.mark.parametrize("canonical", [False, True])
+def test_kmers_from_reads_vs_oracle(kh, oracle_mod, k, canonical):
+    rng = np.random.default_rng(100 + k)
+    cases = [
+        make_reads(rng, 300, 20, 260),                                  # ragged, some shorter than k
+        make_reads(rng, 200, 100, 300, n_rate=0.02),                    # N splitting
+        make_reads(rng, 200, 100, 300, n_rate=0.01, eol=True, lower=True),   # CR/LF inside reads, lower case
+        make_reads(rng, 3, 5000, 9000, n_rate=0.001, eol=True),         # long sequences
+        make_reads(rng, 50, 0, 3),                                      # empty / tiny reads
+    ]
+    for bases, offs in cases:
+        exp = oracle_mod.port.kmers_from_reads(bases, offs, k, canonical)
+        got = kh.kmers_from_reads(bases, offs, k, canonical)
+        assert got.shape == exp.shape, (k, got.shape, exp.shape)
+        assert np.array_equal(got, exp), k
+
+
+def test_kmers_from_reads_other_bytes_map_to_A(kh, oracle_mod):
+    read = b"ACGTRYKMACGTXXACGTACGT-ACGT.ACGT"
+    offs = np.array([0, len(read)], dtype=np.uint64)
+    for k in (3, 7):
+        assert np.array_equal(kh.kmers_from_reads(read, offs, k), oracle_mod.port.kmers_from_reads(read, offs, k, False))
+
+
+def test_kmers_no_reads(kh):
+    out = kh.kmers_from_reads(b"", np.array([0], dtype=np.uint64), 31)
+    assert out.shape == (0,)
+
+
+@pytest.mark.parametrize("p", [1, 2, 3, 8, 13])
+@pytest.mark.parametrize("W", [1, 2])
+def test_rank_golden_and_partition(kh, golden, oracle_mod, p, W):
+    keys = golden["hash_keys%d" % W]
+    if p > 1:
+        for name in ("MURMUR64avx", "MURMUR64", "MURMUR32", "FARM", "CLHASH", "CRC32C", "IDEN"):
+            assert np.array_equal(kh.rank_of(keys, p, name), golden["rank_%s_p%d_w%d" % (name, p, W)]), name
+    rng = np.random.default_rng(p * 10 + W)
+    for n in (0, 1, 255, 256, 257, 100000, 700001):
+        k = rng.integers(0, 2**64, size=(n, W), dtype=np.uint64)
+        kk = k if W == 2 else k[:, 0].copy()
+        ranks = oracle_mod.port.rank("MURMUR64avx", kk, p)
+        out, perm, counts = kh.partition(kk, p, "MURMUR64avx")
+        assert counts == np.bincount(ranks, minlength=p).tolist()
+        # stable: each destination segment holds its keys in input order (permute_by_bucketid semantics)
+        exp_perm = np.argsort(ranks, kind="stable").astype(np.uint32)
+        assert np.array_equal(perm, exp_perm), (n, p)
+        assert np.array_equal(out.reshape(k.shape), k[exp_perm])
+
+
+def test_unpermute(kh):
+    import torch
+    rng = np.random.default_rng(1)
+    n = 100001
+    perm = torch.from_numpy(rng.permutation(n).astype(np.int32)).cuda()
+    for dt in (torch.uint8, torch.int32):
+        v = torch.from_numpy(rng.integers(0, 200, size=n).astype(np.int32)).to(dt).cuda()
+        out = kh.unpermute_dev(v, perm)
+        exp = torch.empty_like(v)
+        exp[perm.long()] = v
+        assert torch.equal(out, exp)

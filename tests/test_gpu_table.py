@@ -1,0 +1,274 @@
+"""GPU tier: the table through the C ABI -- differential tests in the style of the reference's own
+(test/unit/test_hashmap_robinhood_offsets.cpp:96-171,261-336,401-451: compare sorted contents and per-key
+answers with a gold map), against the golden vectors of the compiled reference and against the oracle."""
+import numpy as np
+import pytest
+
+from conftest import sort_pairs
+
+pytestmark = pytest.mark.gpu
+
+GEOMS_W1 = [(32, 1), (32, 2), (32, 4), (16, 2), (16, 4), (16, 8)]
+GEOMS_W2 = [(32, 1), (32, 2), (32, 4)]
+
+
+def all_geoms():
+    return [(1, lb, g) for lb, g in GEOMS_W1] + [(2, lb, g) for lb, g in GEOMS_W2]
+
+
+def check_against(m, om):
+    gk, gv = sort_pairs(*m.to_vector())
+    ok, ov = sort_pairs(*om.to_vector())
+    assert m.size() == om.size()
+    assert np.array_equal(gk, ok)
+    assert np.array_equal(gv, ov)
+
+
+@pytest.mark.parametrize("W,lb,g", all_geoms())
+@pytest.mark.parametrize("red", ["count", "first", "last"])
+def test_golden_benchmark_sequence(kh, golden, W, lb, g, red):
+    """insert -> find -> count -> erase -> count2 (benchmark/BenchmarkHashTables.cpp:1191-1364) on the
+    reference's own generate_input data; every answer compared with what the compiled reference returned."""
+    tag = "k31" if W == 1 else "k63"
+    keys, vals = golden["gen_keys_" + tag], golden["gen_vals_" + tag]
+    m = kh.HashMap(W, "MURMUR64avx", red.upper())
+    m.set_geometry(lb, g)
+    if red == "count":
+        new = m.insert(keys, default=1)
+    else:
+        new = m.insert(keys, vals)
+    tk, tv = sort_pairs(*m.to_vector())
+    assert new == len(tk) == m.size()
+    assert np.array_equal(tk, golden["table_%s_keys_%s" % (red, tag)])
+    assert np.array_equal(tv, golden["table_%s_vals_%s" % (red, tag)])
+    q = np.ascontiguousarray(keys[:600])
+    miss = np.ascontiguousarray(keys[:50] ^ np.uint64(5))
+    assert np.array_equal(m.find(q, 0xFFFFFFFF), golden["find_%s_%s" % (red, tag)])
+    assert np.array_equal(m.count(q), golden["count_%s_%s" % (red, tag)])
+    assert np.array_equal(m.count(miss), golden["count_miss_%s_%s" % (red, tag)])
+    assert m.erase(q) == int(golden["erased_%s_%s" % (red, tag)][0])
+    assert np.array_equal(m.count(q), golden["count2_%s_%s" % (red, tag)])
+    assert m.size() == int(golden["size_after_%s_%s" % (red, tag)][0])
+
+
+@pytest.mark.parametrize("hash_kind", ["IDEN", "MURMUR64", "MURMUR64avx", "MURMUR32", "FARM", "FARM32", "CLHASH", "CRC32C"])
+@pytest.mark.parametrize("W", [1, 2])
+def test_every_store_hash(kh, oracle_mod, hash_kind, W):
+    rng = np.random.default_rng(11)
+    base = rng.integers(0, 2**62, size=(4000, W), dtype=np.uint64)
+    keys = base[rng.integers(0, 4000, size=30000)]
+    kk = keys if W == 2 else keys[:, 0].copy()
+    m = kh.HashMap(W, hash_kind, "COUNT")
+    om = oracle_mod.port.Map(W, "COUNT")
+    assert m.insert(kk, default=1) == om.insert(kk, default=1)
+    check_against(m, om)
+
+
+@pytest.mark.parametrize("W,lb,g", all_geoms())
+def test_growth_from_128_and_load_factors(kh, oracle_mod, W, lb, g):
+    """insert_no_estimate: starts at capacity 128 and doubles (config 2: load-factor sweep incl. rehash)."""
+    rng = np.random.default_rng(5)
+    keys = rng.integers(0, 2**62, size=(60000, W), dtype=np.uint64)
+    keys = np.concatenate([keys, keys[:20000]])
+    kk = keys if W == 2 else keys[:, 0].copy()
+    for max_load in (0.5, 0.6, 0.7, 0.8, 0.9):
+        m = kh.HashMap(W, "MURMUR64", "COUNT", "LINEARPROBE")
+        m.set_geometry(lb, g)
+        m.set_load_factors(0.35 if max_load > 0.35 else 0.1, max_load)
+        assert m.capacity() == 128
+        om = oracle_mod.port.Map(W, "COUNT")
+        assert m.insert_no_estimate(kk) == om.insert(kk)
+        assert m.size() <= max_load * m.capacity() + 1
+        assert m.capacity() >= 128 and (m.capacity() & (m.capacity() - 1)) == 0
+        check_against(m, om)
+        q = kk[::7]
+        assert np.array_equal(m.find(q, 0), om.find(q, 0))
+
+
+@pytest.mark.parametrize("W", [1, 2])
+@pytest.mark.parametrize("red", ["COUNT", "FIRST", "LAST"])
+def test_multi_batch_and_values(kh, oracle_mod, W, red):
+    """several batches with explicit values; FIRST keeps the first value ever seen, LAST the last, COUNT adds"""
+    rng = np.random.default_rng(17)
+    pool = rng.integers(0, 2**62, size=(3000, W), dtype=np.uint64)
+    m = kh.HashMap(W, "MURMUR64avx", red)
+    om = oracle_mod.port.Map(W, red)
+    for b in range(4):
+        keys = pool[rng.integers(0, 3000, size=20000)]
+        kk = keys if W == 2 else keys[:, 0].copy()
+        vals = rng.integers(1, 1000, size=20000).astype(np.uint32)
+        assert m.insert(kk, vals, estimate=bool(b & 1)) == om.insert(kk, vals)
+        check_against(m, om)
+
+
+@pytest.mark.parametrize("W,lb,g", all_geoms())
+def test_erase_is_tombstone_free_and_chains_survive(kh, oracle_mod, W, lb, g):
+    """fill close to max load so probe chains cross buckets, erase half, then every survivor must still be
+    found, erased keys must be absent, and re-inserting reuses the freed slots without duplicates."""
+    rng = np.random.default_rng(23)
+    n = 50000
+    keys = rng.integers(0, 2**62, size=(n, W), dtype=np.uint64)
+    kk = keys if W == 2 else keys[:, 0].copy()
+    m = kh.HashMap(W, "MURMUR64avx", "COUNT", max_load=0.9, min_load=0.01)
+    m.set_geometry(lb, g)
+    m.reserve(int(n * 0.99))                   # 2^16 slots -> load ~0.76
+    om = oracle_mod.port.Map(W, "COUNT")
+    m.insert_no_estimate(kk); om.insert(kk)
+    cap = m.capacity()
+    for rnd in range(3):
+        victims = kk[rng.permutation(n)[: n // 2]]
+        victims = np.concatenate([victims, victims[:1000]])       # duplicates inside the erase batch
+        assert m.erase(victims) == om.erase(victims)
+        assert m.capacity() == cap
+        assert np.array_equal(m.count(kk), om.count(kk))
+        assert np.array_equal(m.find(kk, 77), om.find(kk, 77))
+        check_against(m, om)
+        assert m.insert_no_estimate(kk) == om.insert(kk)
+        check_against(m, om)
+    # a rebuild (rehash) clears the sticky bits and keeps the contents
+    m.rehash(cap * 2)
+    check_against(m, om)
+
+
+def test_shrink_after_erase(kh, oracle_mod):
+    rng = np.random.default_rng(29)
+    keys = rng.integers(0, 2**62, size=100000, dtype=np.uint64)
+    m = kh.HashMap(1, "MURMUR64avx", "COUNT", min_load=0.35, max_load=0.8)
+    om = oracle_mod.port.Map(1, "COUNT")
+    m.insert(keys); om.insert(keys)
+    cap = m.capacity()
+    assert m.erase(keys[:90000]) == om.erase(keys[:90000])
+    assert m.capacity() < cap                   # reserve(lsize) after the load fell below min_load
+    check_against(m, om)
+
+
+@pytest.mark.parametrize("W", [1, 2])
+def test_find_existing_update_clear(kh, oracle_mod, W):
+    rng = np.random.default_rng(31)
+    keys = rng.integers(0, 2**62, size=(20000, W), dtype=np.uint64)
+    kk = keys if W == 2 else keys[:, 0].copy()
+    m = kh.HashMap(W, "FARM", "COUNT")
+    om = oracle_mod.port.Map(W, "COUNT")
+    m.insert(kk[:10000]); om.insert(kk[:10000])
+    q = kk[rng.permutation(20000)[:8000]]
+    gk, gv = m.find_existing(q)
+    ek, ev = om.find_existing(q)
+    assert np.array_equal(gk, ek) and np.array_equal(gv, ev)          # hits only, in query order
+    upd = np.unique(q, axis=0)
+    newv = rng.integers(5, 500, size=len(upd)).astype(np.uint32)
+    n_upd = m.update(upd, newv)
+    assert n_upd == int(om.count(upd).sum())
+    got = m.find(upd, 0)
+    present = om.count(upd).astype(bool)
+    assert np.array_equal(got[present], newv[present]) and not got[~present].any()
+    m.clear()
+    assert m.size() == 0 and not m.count(kk).any()
+    assert m.insert(kk[:10]) == 10
+
+
+def test_empty_batches_and_edge_keys(kh, oracle_mod):
+    m = kh.HashMap(1, "MURMUR64avx", "COUNT")
+    e = np.zeros(0, dtype=np.uint64)
+    assert m.insert(e) == 0 and m.erase(e) == 0 and m.size() == 0
+    assert m.count(e).shape == (0,) and m.find(e).shape == (0,)
+    assert m.to_vector()[0].shape == (0,)
+    # key 0 (poly-A), the largest 31-mer, and the all-ones word (not a 31-mer but a legal uint64 key,
+    # BenchmarkDistHashTables uses raw uint64 keys) all behave like any other key
+    edge = np.array([0, (1 << 62) - 1, 0xFFFFFFFFFFFFFFFF, 0xFFFFFFFFFFFFFFFE, 0, 0xFFFFFFFFFFFFFFFF], dtype=np.uint64)
+    assert m.insert(edge) == 4
+    assert m.find(edge, 9).tolist() == [2, 1, 2, 1, 2, 2]
+    k, v = sort_pairs(*m.to_vector())
+    assert k.tolist() == [0, (1 << 62) - 1, 0xFFFFFFFFFFFFFFFE, 0xFFFFFFFFFFFFFFFF] and v.tolist() == [2, 1, 1, 2]
+    assert m.erase(edge[2:3]) == 1 and m.size() == 3
+    assert m.count(edge).tolist() == [1, 1, 0, 1, 1, 0]
+    m2 = kh.HashMap(2, "MURMUR64avx", "COUNT")
+    edge2 = np.array([[0, 0], [0xFFFFFFFFFFFFFFFF, 0xFFFFFFFFFFFFFFFF], [0xFFFFFFFFFFFFFFFF, 0], [0, 0xFFFFFFFFFFFFFFFF],
+                      [0xFFFFFFFFFFFFFFFF, 0xFFFFFFFFFFFFFFFF]], dtype=np.uint64)
+    assert m2.insert(edge2) == 4
+    assert m2.find(edge2, 0).tolist() == [1, 2, 1, 1, 2]
+
+
+def test_bad_arguments(kh):
+    with pytest.raises(ValueError):
+        kh.HashMap(3)
+    m = kh.HashMap(1)
+    with pytest.raises(ValueError):
+        m.set_load_factors(0.9, 0.5)
+    with pytest.raises(ValueError):
+        m.insert(np.zeros((4, 2), dtype=np.uint64))
+
+
+@pytest.mark.parametrize("W", [1, 2])
+def test_hll_estimate(kh, oracle_mod, golden, W):
+    tag = "k31" if W == 1 else "k63"
+    keys = golden["gen_keys_" + tag]
+    m = kh.HashMap(W, "MURMUR64avx", "COUNT")
+    est, regs = m.estimate_distinct(keys, return_registers=True)
+    pest, pregs = oracle_mod.port.hll_estimate(oracle_mod.port.hash("MURMUR64avx", keys, 43), 64)
+    assert np.array_equal(regs, pregs)                     # registers bit-identical
+    assert est == pytest.approx(float(golden["hll_est_" + tag][0]), rel=1e-12)
+    m32 = kh.HashMap(W, "MURMUR32", "COUNT")
+    est32, regs32 = m32.estimate_distinct(keys, return_registers=True)
+    _, pregs32 = oracle_mod.port.hll_estimate(oracle_mod.port.hash("MURMUR32", keys, 43), 32)
+    assert np.array_equal(regs32, pregs32)
+
+
+def test_device_pointer_path(kh, oracle_mod):
+    import torch
+    rng = np.random.default_rng(41)
+    keys = rng.integers(0, 2**62, size=300000, dtype=np.uint64)
+    keys = np.concatenate([keys, keys[:100000]])
+    d = torch.from_numpy(keys.view(np.int64)).cuda()
+    m = kh.HashMap(1, "MURMUR64avx", "COUNT")
+    om = oracle_mod.port.Map(1, "COUNT")
+    assert m.insert(d) == om.insert(keys)
+    assert np.array_equal(m.find(d, 0).cpu().numpy().view(np.uint32), om.find(keys, 0))
+    assert np.array_equal(m.count(d).cpu().numpy(), om.count(keys))
+    assert m.erase(d[:1000]) == om.erase(keys[:1000])
+    check_against(m, om)
+
+
+def test_large_batch_properties(kh):
+    """size-independent properties at a scale the oracle is too slow for: 20M keys with 5x repeats"""
+    rng = np.random.default_rng(43)
+    uniq = rng.integers(0, 2**62, size=4_000_000, dtype=np.uint64)
+    uniq = np.unique(uniq)
+    reps = rng.integers(1, 10, size=len(uniq))
+    keys = np.repeat(uniq, reps)
+    rng.shuffle(keys)
+    m = kh.HashMap(1, "MURMUR64avx", "COUNT")
+    assert m.insert(keys) == len(uniq) == m.size()
+    tk, tv = sort_pairs(*m.to_vector())
+    assert np.array_equal(tk, uniq)                         # identical key set
+    assert int(tv.sum()) == len(keys)                       # counts add up to the input size
+    assert np.array_equal(tv, reps)                         # and equal the true multiplicities
+    assert m.count(keys[:1_000_000]).all()
+    assert m.erase(keys[:1_000_000]) == len(np.unique(keys[:1_000_000]))
+    assert not m.count(keys[:1_000_000]).any()
+    assert m.erase(keys[:1_000_000]) == 0                   # idempotent
+
+
+@pytest.mark.parametrize("n_gpus", [1, 2])
+def test_multi_gpu_map(kh, oracle_mod, n_gpus):
+    if kh.device_count() < n_gpus:
+        pytest.skip("needs %d GPUs" % n_gpus)
+    rng = np.random.default_rng(47)
+    raw = rng.integers(0, 2**62, size=60000, dtype=np.uint64)
+    raw = np.concatenate([raw, raw[:30000]])
+    canon = oracle_mod.port.canonical(31, raw)
+    m = kh.MultiGpuMap(n_gpus, 1, "MURMUR64avx", "MURMUR64avx", "COUNT", canonical_k=31)
+    om = oracle_mod.port.Map(1, "COUNT")
+    assert m.insert(raw) == om.insert(canon) == m.size()
+    ranks = oracle_mod.port.rank("MURMUR64avx", canon, n_gpus)
+    for r in range(n_gpus):      # per-rank partition contents identical to the reference's rule
+        gk, gv = sort_pairs(*m.to_vector_rank(r))
+        mine = np.unique(canon[ranks == r])
+        assert np.array_equal(gk, mine)
+        assert np.array_equal(gv, om.find(mine, 0))
+    q = raw[rng.permutation(len(raw))[:20000]]
+    q = np.concatenate([q, q[:100] ^ np.uint64(3)])
+    cq = oracle_mod.port.canonical(31, q)
+    assert np.array_equal(m.count(q), om.count(cq))         # answers in INPUT order
+    assert np.array_equal(m.find(q, 0), om.find(cq, 0))
+    assert m.erase(q) == om.erase(cq)
+    assert m.size() == om.size()
