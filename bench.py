@@ -1,0 +1,424 @@
+#!/usr/bin/env python
+"""bench.py -- BenchmarkHashTables-shaped measurement of the hot path (BASELINE.json metric:
+k-mer inserts/s & finds/s, k=31, 100M keys, ~5x repeats, then 10M find/count/erase/count).
+
+One step = the reference driver's phase sequence (benchmark/BenchmarkHashTables.cpp:1191-1364) on a
+default-constructed count table:  insert (HLL estimate -> reserve -> batch insert, the reference's
+insert()) -> find -> count -> erase -> count2.
+  value      inserts/s of the insert phase with the keys already resident in HBM (whole job, all GPUs)
+  e2e        the same through the host API: pinned HOST buffers in, HOST results out, copies inside the timing
+  roofline   insert kernel: algorithmic bytes (72 B/key) / CUDA-event kernel time vs measured HBM peak
+  cpu_baseline  the reference's own CPU table (oracle/_ref, compiled from the reference headers) on a bounded
+                sample of the same workload, 1 thread (BenchmarkHashTables is single-process)
+  --impl reference   the reference's CPU implementation alone, all host threads (key-space sharded like
+                BenchmarkDistHashTables, MPI exchange excluded: no MPI on this box)
+N > 1 (torchrun): one process per GPU, each rank brings its own 100M keys (weak scaling); owner rank =
+DistHash_9876543(key) & (p-1); NCCL all-to-all; local insert; queries return along the reverse all-to-all.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+N_KEYS_DEFAULT = 100_000_000
+N_QUERY_DEFAULT = 10_000_000
+REPEATS = 10
+BYTES_PER_INSERT = 72     # 8 B key read + one 32-B sector read + one 32-B sector written back
+BYTES_PER_FIND = 44       # 8 + 32 + 4
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--n-keys", type=int, default=N_KEYS_DEFAULT)
+    ap.add_argument("--n-query", type=int, default=N_QUERY_DEFAULT)
+    ap.add_argument("--hash", default="MURMUR64avx")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true")
+    return ap.parse_args()
+
+
+def generate_workload(n, nq, seed):
+    """synthetic data of the reference generator's shape (generate_input, BenchmarkHashTables.cpp:181-227):
+    random 62-bit 31-mers (bits 31 and 63 clear, as rand() is 31-bit), each unique key 1 + U{0..9} times,
+    shuffled; queries = the first nq input keys."""
+    rng = np.random.default_rng(seed)
+    n_uniq = int(n / ((REPEATS + 1) / 2.0)) + 1
+    uniq = rng.integers(0, 2**63, size=n_uniq, dtype=np.uint64) & np.uint64(0x7FFFFFFF7FFFFFFF)
+    uniq &= np.uint64((1 << 62) - 1)
+    reps = rng.integers(1, REPEATS + 1, size=n_uniq)
+    keys = np.repeat(uniq, reps)[:n]
+    if len(keys) < n:
+        keys = np.concatenate([keys, keys[: n - len(keys)]])
+    keys = keys[rng.permutation(n)]
+    return np.ascontiguousarray(keys), np.ascontiguousarray(keys[:nq])
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md clocks line)"""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index=0):
+        self.lines, self.proc, self.gpu = [], None, gpu_index
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.gpu), "--query-gpu=" + self.Q,
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.th = threading.Thread(target=self._read, daemon=True)
+            self.th.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        for ln in self.lines:
+            f = [x.strip() for x in ln.split(",")]
+            if len(f) < 9:
+                continue
+            try:
+                sm.append(float(f[1])); mx.append(float(f[2]))
+            except ValueError:
+                continue
+            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), f[5:9]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        if not sm:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["no samples"]}
+        busy = sorted(sm)[len(sm) // 2:]          # upper half = samples under load
+        return {"sm_mhz": float(np.median(busy)), "sm_max_mhz": max(mx), "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def host_cores():
+    try:
+        return len(os.sched_getaffinity(0))
+    except Exception:
+        return os.cpu_count() or 1
+
+
+# ---------------------------------------------------------------------------------------------------
+# CPU side: the reference's own implementation (oracle/_ref, else the C port).  Only these two functions
+# touch oracle/ -- as the timed baseline, never on the product path.
+# ---------------------------------------------------------------------------------------------------
+def run_reference_phases(keys, queries, threads, hash_kind):
+    """replays estimate -> insert -> find -> count -> erase -> count2 on the reference's
+    hashmap_robinhood_offsets_count; returns (seconds per phase, counts, kind)"""
+    import oracle
+    if oracle.ref is not None:
+        secs, cnts = oracle.ref.baseline_run(keys, queries, "OFFSETS_COUNT", hash_kind, threads=threads,
+                                             min_load=0.35, max_load=0.8)
+        return secs, cnts, "reference"
+    # the reference did not compile here: time the plain-C port (single thread)
+    m = oracle.port.Map(1, "COUNT")
+    secs = {"partition": 0.0, "estimate": 0.0}
+    t = time.perf_counter(); m.insert(keys); secs["insert"] = time.perf_counter() - t
+    t = time.perf_counter(); f = m.find(queries, 0); secs["find"] = time.perf_counter() - t
+    t = time.perf_counter(); c = m.count(queries); secs["count"] = time.perf_counter() - t
+    t = time.perf_counter(); e = m.erase(queries); secs["erase"] = time.perf_counter() - t
+    t = time.perf_counter(); c2 = m.count(queries); secs["count2"] = time.perf_counter() - t
+    return secs, {"distinct": m.size() + e, "found": int((f != 0).sum()), "counted": int(c.sum()), "erased": e,
+                  "counted2": int(c2.sum())}, "port"
+
+
+def cpu_baseline(keys, queries, hash_kind, n_sample=20_000_000):
+    """bounded sample of the same workload on ONE host core (BenchmarkHashTables is single-process)"""
+    ns = min(n_sample, len(keys))
+    nq = max(1, ns // 10)
+    secs, cnts, kind = run_reference_phases(np.ascontiguousarray(keys[:ns]), np.ascontiguousarray(queries[:nq]), 1, hash_kind)
+    t_ins = secs["estimate"] + secs["insert"]
+    return {"value": ns / t_ins, "unit": "inserts/s", "cores": 1, "kind": kind,
+            "sample": "first %d of the %d keys, %d queries; hashmap_robinhood_offsets_count<Kmer31,u32,%s>, "
+                      "HLL estimate + reserve + insert timed together" % (ns, len(keys), nq, hash_kind),
+            "finds_per_s": nq / secs["find"], "counts_per_s": nq / secs["count"], "erases_per_s": nq / secs["erase"],
+            "seconds": {k: round(v, 4) for k, v in secs.items()}, "distinct": cnts["distinct"]}
+
+
+def reference_arm(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    cores = host_cores()
+    threads = cores
+    ns = min(args.n_keys, 25_000_000)            # bounded sample: a quarter of the workload per step
+    nq = max(1, ns // 10)
+    keys, queries = generate_workload(ns, nq, seed=23)
+    ins, fnd, tot = [], [], []
+    kind = "reference"
+    for it in range(args.warmup + args.steps):
+        t0 = time.perf_counter()
+        secs, cnts, kind = run_reference_phases(keys, queries, threads, args.hash)
+        t1 = time.perf_counter()
+        if it >= args.warmup:
+            ins.append(secs["partition"] + secs["estimate"] + secs["insert"])
+            fnd.append(secs["find"])
+            tot.append(t1 - t0)
+    t_ins, t_find = float(np.mean(ins)), float(np.mean(fnd))
+    value = ns / t_ins
+    line = {
+        "impl": "reference", "metric": "k-mer inserts/s (k=31, count table)", "value": value, "unit": "inserts/s",
+        "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * float(np.mean(tot)),
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u64", "data": "synthetic",
+        "config": {"workload": "BenchmarkHashTables default: random 31-mer uint64 keys, ~5.5x repeats, insert then "
+                               "find/count/erase/count of n/10 keys, hashmap_robinhood_offsets_count",
+                   "n_keys": ns, "n_query": nq, "hash": args.hash,
+                   "note": "bounded sample of the 100M/10M workload; %d threads, one reference table per thread, "
+                           "keys sharded by the reference's rank rule (MPI all-to-all excluded: no MPI here)" % threads},
+        "finds_per_s": nq / t_find,
+        "cpu_baseline": {"value": value, "unit": "inserts/s", "cores": threads, "kind": kind,
+                         "sample": "%d keys / %d queries per step" % (ns, nq)},
+        "e2e": {"value": value, "unit": "inserts/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+# ---------------------------------------------------------------------------------------------------
+# our arm
+# ---------------------------------------------------------------------------------------------------
+def measured_peaks():
+    try:
+        pk = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+        return float(pk["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    except Exception:
+        return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+def pinned_u64(arr):
+    import torch
+    t = torch.empty(arr.shape, dtype=torch.int64).pin_memory()
+    t.numpy().view(np.uint64)[...] = arr
+    return t
+
+
+def ours_single(args):
+    import torch
+    import kmerhash_b200 as kh
+    assert torch.cuda.is_available() and kh.device_count() > 0, "bench.py needs a CUDA device (no CPU fallback)"
+    torch.cuda.set_device(0)
+    n, nq = args.n_keys, args.n_query
+    keys, queries = generate_workload(n, nq, seed=23)
+    d_keys = torch.from_numpy(keys.view(np.int64)).cuda()
+    d_q = torch.from_numpy(queries.view(np.int64)).cuda()
+    m = kh.HashMap(1, args.hash, "COUNT", "ROBINHOOD_OFFSETS", device=0, min_load=0.35, max_load=0.8)
+
+    def ev():
+        e = torch.cuda.Event(enable_timing=True); e.record(); return e
+
+    def step_resident():
+        m.clear(); m.rehash(128)                      # default-constructed table, as the driver starts with
+        e0 = ev(); new = m.insert(d_keys, estimate=True)
+        e1 = ev(); f = m.find(d_q, 0)
+        e2 = ev(); c = m.count(d_q)
+        e3 = ev(); er = m.erase(d_q)
+        e4 = ev(); c2 = m.count(d_q)
+        e5 = ev(); torch.cuda.synchronize()
+        t = [a.elapsed_time(b) for a, b in ((e0, e1), (e1, e2), (e2, e3), (e3, e4), (e4, e5))]
+        return t, (new, int((f != 0).sum().item()), int(c.sum().item()), er, int(c2.sum().item()))
+
+    for _ in range(args.warmup):
+        step_resident()
+    sampler = ClockSampler(0); sampler.start()
+    kh.reset_launch_count()
+    m.kernel_timing(True)
+    torch.cuda.synchronize()
+    times, checks = [], None
+    for _ in range(args.steps):
+        t, checks = step_resident()
+        times.append(t)
+    torch.cuda.synchronize()
+    launches = kh.launch_count()
+    ins_ms, ins_launches = m.kernel_time("insert")
+    look_ms, look_launches = m.kernel_time("lookup")
+    m.kernel_timing(False)
+    clocks = sampler.stop()
+    times = np.array(times)
+    ph = times.mean(axis=0)
+    # sanity: all queries are present, erased ones are gone, distinct count as generated
+    assert checks[1] == nq and checks[2] == nq and checks[4] == 0, checks
+
+    # rebuilds re-insert through the same kernel; the first `steps` launches-by-time split: take the kernel
+    # time per step and charge the algorithmic bytes of the n input keys against it
+    ins_kernel_ms_per_step = ins_ms / args.steps
+    peak, peak_src = measured_peaks()
+    achieved = BYTES_PER_INSERT * n / (ins_kernel_ms_per_step * 1e-3) / 1e9
+    line = {
+        "metric": "k-mer inserts/s (k=31, count table)", "value": n / (ph[0] * 1e-3), "unit": "inserts/s",
+        "n_gpus": 1, "steps": args.steps, "warmup": args.warmup, "ms_per_step": float(ph.sum()),
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u64", "data": "synthetic",
+        "config": {"workload": "BenchmarkHashTables default: %d random 31-mer uint64 keys (~5.5x repeats, %d distinct) "
+                               "insert, then %d find/count/erase/count; robinhood_offsets count map; 1 B200" % (n, checks[0], nq),
+                   "n_keys": n, "n_query": nq, "hash": args.hash, "load_factors": [0.35, 0.8],
+                   "l2": "inputs (800 MB keys, 512 MB table) larger than the 126 MB L2; table rebuilt from capacity 128 every step",
+                   "insert_phase": "HLL estimate + reserve + batch insert (the reference's insert())"},
+        "finds_per_s": nq / (ph[1] * 1e-3), "counts_per_s": nq / (ph[2] * 1e-3),
+        "erases_per_s": nq / (ph[3] * 1e-3), "count2_per_s": nq / (ph[4] * 1e-3),
+        "phase_ms": {"insert": float(ph[0]), "find": float(ph[1]), "count": float(ph[2]), "erase": float(ph[3]), "count2": float(ph[4])},
+        "roofline": {"bound": "hbm", "kernel": "insert_kernel<W=1,LB=32,G=2,COUNT>", "achieved": achieved, "peak": peak,
+                     "unit": "GB/s", "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
+                     "algorithmic_bytes_per_key": BYTES_PER_INSERT,
+                     "kernel_ms_per_step": ins_kernel_ms_per_step, "kernel_launches_per_step": ins_launches / args.steps,
+                     "share_of_step": ins_kernel_ms_per_step / float(ph.sum()),
+                     "lookup_kernels_ms_per_step": look_ms / args.steps},
+        "gpu_launches": int(launches), "clocks": clocks,
+    }
+
+    if not args.no_e2e:
+        hk, hq = pinned_u64(keys), pinned_u64(queries)
+        hk_np, hq_np = hk.numpy().view(np.uint64), hq.numpy().view(np.uint64)
+        out32 = torch.empty(nq, dtype=torch.int32).pin_memory().numpy().view(np.uint32)
+        out8 = torch.empty(nq, dtype=torch.uint8).pin_memory().numpy()
+
+        def step_e2e():
+            m.clear(); m.rehash(128)
+            t0 = time.perf_counter(); m.insert(hk_np, estimate=True)
+            t1 = time.perf_counter(); m.find(hq_np, 0, out=out32)
+            t2 = time.perf_counter(); m.count(hq_np, out=out8)
+            t3 = time.perf_counter(); m.erase(hq_np)
+            t4 = time.perf_counter(); m.count(hq_np, out=out8)
+            t5 = time.perf_counter()
+            return [1e3 * (b - a) for a, b in ((t0, t1), (t1, t2), (t2, t3), (t3, t4), (t4, t5))]
+
+        for _ in range(args.warmup):
+            step_e2e()
+        et = np.array([step_e2e() for _ in range(args.steps)]).mean(axis=0)
+        assert int(out8.sum()) == 0 and int((out32 != 0).sum()) == nq
+        line["e2e"] = {"value": n / (et[0] * 1e-3), "unit": "inserts/s",
+                       "h2d_bytes_per_step": int(8 * n + 4 * 8 * nq), "d2h_bytes_per_step": int(4 * nq + 2 * nq),
+                       "finds_per_s": nq / (et[1] * 1e-3), "ms_per_step": float(et.sum()),
+                       "phase_ms": {k: float(v) for k, v in zip(("insert", "find", "count", "erase", "count2"), et)},
+                       "api": "kh_insert_host / kh_find_host / kh_count_host / kh_erase_host on pinned host buffers"}
+    if not args.no_cpu_baseline:
+        line["cpu_baseline"] = cpu_baseline(keys, queries, args.hash)
+    print(json.dumps(line), flush=True)
+
+
+def ours_multi(args):
+    """N > 1: one process per GPU under torchrun, NCCL all-to-all, weak scaling (each rank brings n keys)."""
+    import torch
+    import torch.distributed as dist
+    import kmerhash_b200 as kh
+    from kmerhash_b200.distributed import DistributedMap
+    rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
+    local = int(os.environ.get("LOCAL_RANK", rank))
+    torch.cuda.set_device(local)
+    dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    n, nq = args.n_keys, args.n_query
+    keys, queries = generate_workload(n, nq, seed=23 + rank)
+    d_keys = torch.from_numpy(keys.view(np.int64)).cuda()
+    d_q = torch.from_numpy(queries.view(np.int64)).cuda()
+    dm = DistributedMap(1, args.hash, args.hash, "COUNT", canonical_k=0, device=local, chunks=4)
+    dm.e.table.set_load_factors(0.35, 0.8)
+
+    def barrier():
+        dist.barrier(); torch.cuda.synchronize()
+
+    def reset():
+        dm.e.table.clear(); dm.e.table.rehash(128)
+
+    def step(k_in, q_in, to_host):
+        reset(); barrier()
+        e0 = torch.cuda.Event(enable_timing=True); e1 = torch.cuda.Event(enable_timing=True); e2 = torch.cuda.Event(enable_timing=True)
+        e0.record(); dm.insert(k_in); xb = dm.last_exchange_bytes
+        barrier(); e1.record(); f = dm.find(q_in, 0)
+        if to_host:
+            f = f.cpu()
+        barrier(); e2.record(); torch.cuda.synchronize()
+        return e0.elapsed_time(e1), e1.elapsed_time(e2), f, xb
+
+    def run(k_in, q_in, to_host):
+        for _ in range(args.warmup):
+            step(k_in, q_in, to_host)
+        ti, tf, xb = [], [], 0
+        for _ in range(args.steps):
+            a, b, f, xb = step(k_in, q_in, to_host)
+            ti.append(a); tf.append(b)
+        t = torch.tensor([float(np.mean(ti)), float(np.mean(tf))], device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)                      # max over ranks
+        assert int((f != 0).sum()) == nq                              # every query key is present
+        return t.tolist(), xb
+
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    kh.reset_launch_count()
+    dm.e.table.kernel_timing(True)
+    (ti, tf), xbytes = run(d_keys, d_q, False)
+    launches = torch.tensor([kh.launch_count()], device="cuda", dtype=torch.int64)
+    dist.all_reduce(launches)
+    ins_ms, _ = dm.e.table.kernel_time("insert")
+    dm.e.table.kernel_timing(False)
+    clocks = sampler.stop() if rank == 0 else None
+    total = torch.tensor([dm.local_size()], device="cuda", dtype=torch.int64)
+    e2e = None
+    if not args.no_e2e:
+        hk, hq = pinned_u64(keys), pinned_u64(queries)
+        (ei, ef), _ = run(hk, hq, True)
+        e2e = {"value": world * n / (ei * 1e-3), "unit": "inserts/s", "h2d_bytes_per_step": int(8 * (n + nq)),
+               "d2h_bytes_per_step": int(4 * nq), "finds_per_s": world * nq / (ef * 1e-3),
+               "api": "DistributedMap.insert / .find on pinned host tensors (per rank)"}
+    if rank == 0:
+        peak, peak_src = measured_peaks()
+        steps_total = args.warmup + args.steps
+        achieved = BYTES_PER_INSERT * n / (ins_ms / max(steps_total, 1) * 1e-3) / 1e9
+        line = {
+            "metric": "k-mer inserts/s (k=31, count table)", "value": world * n / (ti * 1e-3), "unit": "inserts/s",
+            "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ti + tf,
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u64", "data": "synthetic",
+            "config": {"workload": "BenchmarkDistHashTables-shaped: %d random 31-mer uint64 keys per GPU (~5.5x repeats), "
+                                   "hash-partitioned (murmur3 x86_128, seed 9876543) over %d GPUs with NCCL all-to-all, "
+                                   "count map insert, then %d finds per GPU with reply" % (n, world, nq),
+                       "n_keys_per_gpu": n, "n_query_per_gpu": nq, "hash": args.hash, "chunks": dm.chunks,
+                       "l2": "inputs larger than L2; tables rebuilt from capacity 128 every step"},
+            "finds_per_s": world * nq / (tf * 1e-3), "phase_ms": {"insert": ti, "find": tf},
+            "exchange": {"bytes_sent_per_rank_insert": int(xbytes), "GB_per_s_per_rank_if_serial": xbytes / (ti * 1e-3) / 1e9,
+                         "nvlink_peak_GB_per_s_per_direction": 900},
+            "roofline": {"bound": "hbm", "kernel": "insert_kernel<W=1,LB=32,G=2,COUNT> (rank 0)", "achieved": achieved,
+                         "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None, "peak_source": peak_src},
+            "gpu_launches": int(launches.item()), "clocks": clocks,
+        }
+        if e2e:
+            line["e2e"] = e2e
+        print(json.dumps(line), flush=True)
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def main():
+    args = parse_args()
+    if args.impl == "reference":
+        reference_arm(args)
+        return
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    if world > 1:
+        ours_multi(args)
+    else:
+        ours_single(args)
+
+
+if __name__ == "__main__":
+    main()

@@ -118,7 +118,7 @@ struct kh_table {
   int device = 0, map_kind = 0, W = 1, hash_kind = 0, reducer = 0;
   uint32_t seed = KH_DEFAULT_SEED;
   double min_load = 0.2, max_load = 0.8;
-  int LB = 32, G = 1;                 // probe geometry (DESIGN.md "bucket geometry")
+  int LB = 32, G = 2;                 // probe geometry (DESIGN.md "bucket geometry")
   uint64_t capacity = 0, size = 0;
   HashParams hp;
   DevBuf<unsigned char> slots;
@@ -184,7 +184,7 @@ bool geometry_ok(int W, int LB, int G) {
 }
 
 void default_geometry(int W, int &LB, int &G) {
-  LB = 32; G = 1;
+  LB = 32; G = 2;   // 64-byte buckets, two 32-byte lanes: best insert and find rate in profiles/r01_sweep_probes_geometry.jsonl
   if (const char *e = getenv("KH_GEOM")) {   // "LBxG", experiments only
     int lb = 0, g = 0;
     if (sscanf(e, "%dx%d", &lb, &g) == 2 && geometry_ok(W, lb, g)) { LB = lb; G = g; }

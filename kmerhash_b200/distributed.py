@@ -1,0 +1,174 @@
+"""One-process-per-GPU distributed map over torch.distributed (NCCL over NVLink / NVSwitch).
+
+Mirror of the reference's distributed container (paths relative to the reference tree):
+  dsc::counting_batched_robinhood_map / batched_robinhood_map
+      include/kmerhash/distributed_batched_robinhood_map.hpp:748-832 (ctor, sizes), insert :1187 / :2935,
+      count :1535, find :1901, erase :2428; insert_p :910-1179, count_p :1258-1516
+  exchange: mxx::all2all(counts) :1024 + khmxx::distribute_permuted (include/kmerhash/incremental_mxx.hpp:2998)
+            or the overlapped ialltoallv_and_modify (:3437) when chunks > 1
+Every rank calls every method (collective semantics, also with 0 keys, :843,911-917).
+owner = DistHash_{9876543}(canonical key) & (p-1) or % p -- the reference's own rule, so each rank's
+table holds what the reference's rank of the same index holds.  Unlike the reference, query results
+come back in INPUT order (the permutation is undone on the source rank).
+
+The compute engine is the CUDA library (kmerhash_b200.ops / HashMap on torch CUDA tensors).  The
+`engine` argument exists so the host-side exchange logic can be exercised with gloo on CPU tensors in
+the test-suite; the product never passes one.
+"""
+import numpy as np
+import torch
+import torch.distributed as dist
+
+
+class CudaEngine:
+    """partition / canonicalise / table ops on this rank's GPU through the C ABI"""
+
+    def __init__(self, device, key_words, store_hash, dist_hash, reducer, canonical_k):
+        from . import HashMap
+        self.device = torch.device("cuda", device)
+        self.W, self.dist_hash, self.canonical_k = key_words, dist_hash, canonical_k
+        self.table = HashMap(key_words, store_hash, reducer, device=device)
+
+    def as_keys(self, keys):
+        if isinstance(keys, np.ndarray):
+            keys = torch.from_numpy(np.ascontiguousarray(keys, dtype=np.uint64).view(np.int64))
+        return keys.to(self.device, non_blocking=False)
+
+    def canonicalize(self, keys):
+        from . import ops
+        return ops.canonicalize(keys, self.canonical_k) if (self.canonical_k and keys.shape[0]) else keys
+
+    def partition(self, keys, p, want_perm):
+        from . import ops
+        if keys.shape[0] == 0:
+            return keys, torch.empty(0, dtype=torch.int32, device=self.device), [0] * p
+        return ops.partition_dev(keys, p, self.dist_hash, want_perm=want_perm)
+
+    def unpermute(self, vals, perm):
+        from . import ops
+        return ops.unpermute_dev(vals, perm) if vals.shape[0] else vals
+
+    def empty_keys(self, n):
+        shape = (n,) if self.W == 1 else (n, self.W)
+        return torch.empty(shape, dtype=torch.int64, device=self.device)
+
+    def empty_like_result(self, n, dtype):
+        return torch.empty(n, dtype=dtype, device=self.device)
+
+    def insert(self, keys, default):
+        return self.table.insert(keys, default=default) if keys.shape[0] else 0
+
+    def count(self, keys):
+        return self.table.count(keys) if keys.shape[0] else self.empty_like_result(0, torch.uint8)
+
+    def find(self, keys, nonexistent):
+        return self.table.find(keys, nonexistent) if keys.shape[0] else self.empty_like_result(0, torch.int32)
+
+    def erase(self, keys):
+        return self.table.erase(keys) if keys.shape[0] else 0
+
+    def local_size(self):
+        return self.table.size()
+
+    def to_vector(self):
+        return self.table.to_vector()
+
+
+class DistributedMap:
+    def __init__(self, key_words=1, store_hash="MURMUR64avx", dist_hash="MURMUR64avx", reducer="COUNT",
+                 canonical_k=0, device=None, group=None, engine=None, chunks=1):
+        self.group = group
+        self.rank = dist.get_rank(group)
+        self.p = dist.get_world_size(group)
+        if engine is None:
+            if device is None:
+                device = torch.cuda.current_device()
+            engine = CudaEngine(device, key_words, store_hash, dist_hash, reducer, canonical_k)
+        self.e = engine
+        self.W = key_words
+        self.chunks = max(1, int(chunks))
+        self.last_exchange_bytes = 0      # bytes this rank sent to other ranks in the last call
+
+    # ---- the exchange ---------------------------------------------------------------------------
+    def _counts_a2a(self, counts):
+        send = torch.tensor(counts, dtype=torch.int64, device=self.e.device)
+        recv = torch.empty_like(send)
+        dist.all_to_all_single(recv, send, group=self.group)          # mxx::all2all(send_counts)
+        return [int(c) for c in recv.tolist()]
+
+    def _send_keys(self, keys, want_perm, async_op=False):
+        """canonicalise -> partition by owner -> all-to-all.  Returns (recv_keys, perm, send_counts, recv_counts, work)."""
+        keys = self.e.canonicalize(keys)
+        if self.p == 1:                                                # insert_1 / count_1: no exchange
+            return keys, None, [keys.shape[0]], [keys.shape[0]], None
+        permuted, perm, send_counts = self.e.partition(keys, self.p, want_perm)
+        recv_counts = self._counts_a2a(send_counts)
+        recv = self.e.empty_keys(sum(recv_counts))
+        elem = 8 * self.W
+        self.last_exchange_bytes += elem * (sum(send_counts) - send_counts[self.rank])
+        work = dist.all_to_all_single(recv, permuted, output_split_sizes=recv_counts, input_split_sizes=send_counts,
+                                      group=self.group, async_op=async_op)
+        return recv, perm, send_counts, recv_counts, (work, permuted)
+
+    def _reply(self, res, perm, send_counts, recv_counts):
+        """results travel back along the reverse all-to-all and are put into input order"""
+        if self.p == 1:
+            return res
+        back = torch.empty(sum(send_counts), dtype=res.dtype, device=self.e.device)
+        dist.all_to_all_single(back, res, output_split_sizes=send_counts, input_split_sizes=recv_counts, group=self.group)
+        self.last_exchange_bytes += res.element_size() * (sum(recv_counts) - recv_counts[self.rank])
+        return self.e.unpermute(back, perm)
+
+    # ---- batch operations (collective) -------------------------------------------------------------
+    def insert(self, keys, default=1):
+        """returns the number of new keys on THIS rank; chunks > 1 overlaps the all-to-all of chunk i+1
+        with the local insert of chunk i (the reference's ialltoallv_and_modify schedule)."""
+        keys = self.e.as_keys(keys)
+        self.last_exchange_bytes = 0
+        n = keys.shape[0]
+        n_chunks = self.chunks if self.p > 1 else 1
+        bounds = [n * i // n_chunks for i in range(n_chunks + 1)]
+        added, pending = 0, None
+        for i in range(n_chunks):
+            recv, _, _, _, w = self._send_keys(keys[bounds[i]:bounds[i + 1]], False, async_op=n_chunks > 1)
+            if pending is not None:
+                added += self.e.insert(pending, default)               # overlaps the transfer just issued
+            if w is not None and n_chunks > 1:
+                w[0].wait()
+            pending = recv
+        added += self.e.insert(pending, default)
+        return added
+
+    def count(self, keys):
+        keys = self.e.as_keys(keys)
+        self.last_exchange_bytes = 0
+        recv, perm, sc, rc, _ = self._send_keys(keys, True)
+        return self._reply(self.e.count(recv), perm, sc, rc)
+
+    def find(self, keys, nonexistent=0):
+        keys = self.e.as_keys(keys)
+        self.last_exchange_bytes = 0
+        recv, perm, sc, rc, _ = self._send_keys(keys, True)
+        return self._reply(self.e.find(recv, nonexistent), perm, sc, rc)
+
+    def erase(self, keys):
+        keys = self.e.as_keys(keys)
+        self.last_exchange_bytes = 0
+        recv, _, _, _, _ = self._send_keys(keys, False)
+        return self.e.erase(recv)
+
+    # ---- sizes ------------------------------------------------------------------------------------------
+    def local_size(self):
+        return self.e.local_size()
+
+    def size(self):
+        t = torch.tensor([self.local_size()], dtype=torch.int64, device=self.e.device)
+        dist.all_reduce(t, group=self.group)
+        return int(t.item())
+
+    def get_local_container(self):
+        return getattr(self.e, "table", None)
+
+    def to_vector(self):
+        """this rank's (keys, vals)"""
+        return self.e.to_vector()

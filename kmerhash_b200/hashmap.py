@@ -156,21 +156,23 @@ class HashMap:
         return self.insert(keys, vals, default, estimate=False)
 
     # ---- queries ----
-    def count(self, keys):
-        """0/1 per key (reference: count(out, b, e) / exists)."""
+    def count(self, keys, out=None):
+        """0/1 per key (reference: count(out, b, e) / exists).  `out`: optional preallocated (pinned) uint8 array."""
         if _is_torch(keys):
             k, n = _dev_keys(keys, self.W, self.device)
             out = torch.empty(n, dtype=torch.uint8, device=k.device)
             check(lib.kh_count_dev(self._h, k.data_ptr(), n, out.data_ptr()), "count")
             return out
         k, n = _host_keys(keys, self.W)
-        out = np.empty(n, dtype=np.uint8)
+        if out is None:
+            out = np.empty(n, dtype=np.uint8)
+        assert out.dtype == np.uint8 and out.shape[0] >= n and out.flags.c_contiguous
         check(lib.kh_count_host(self._h, k.ctypes.data, n, out.ctypes.data), "count")
         return out
 
     exists = count
 
-    def find(self, keys, nonexistent=0):
+    def find(self, keys, nonexistent=0, out=None):
         """value per key, `nonexistent` where absent (reference: find<OT>(out, b, e, nonexistent))."""
         if _is_torch(keys):
             k, n = _dev_keys(keys, self.W, self.device)
@@ -178,7 +180,9 @@ class HashMap:
             check(lib.kh_find_dev(self._h, k.data_ptr(), n, out.data_ptr(), nonexistent), "find")
             return out
         k, n = _host_keys(keys, self.W)
-        out = np.empty(n, dtype=np.uint32)
+        if out is None:
+            out = np.empty(n, dtype=np.uint32)
+        assert out.dtype == np.uint32 and out.shape[0] >= n and out.flags.c_contiguous
         check(lib.kh_find_host(self._h, k.ctypes.data, n, out.ctypes.data, nonexistent), "find")
         return out
 
