@@ -141,6 +141,13 @@ int64_t kh_insert_host(kh_table *t, const uint64_t *keys, const uint32_t *vals, 
 int64_t kh_insert_dev(kh_table *t, const uint64_t *d_keys, const uint32_t *d_vals, uint64_t n,
                       uint32_t default_val, int estimate);
 
+/* Same, for an array of std::pair<Kmer, T> records as the reference's insert(IT, IT) /
+ * insert(std::vector<value_type> const&) take them (:2783-2796, :2802-2885): `stride_bytes` =
+ * sizeof(value_type) (multiple of 8), key words at offset 0, the T value (`val_bytes` = 1, 2 or 4) at
+ * `val_offset`.  The records are copied as they are and de-interleaved by a kernel. */
+int64_t kh_insert_pairs_host(kh_table *t, const void *pairs, uint64_t n, uint32_t stride_bytes,
+                             uint32_t val_offset, uint32_t val_bytes, int estimate);
+
 /* ---- batch queries -------------------------------------------------------------------
  * kh_count_*: replaces count(out, b, e) / exists (:3251-3328): out[i] = 0/1; returns #present.
  * kh_find_*:  replaces find<OT>(out, b, e, nonexistent) (:3376-3417): out[i] = value or `nonexistent`;

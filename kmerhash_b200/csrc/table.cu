@@ -107,6 +107,20 @@ __global__ void widen_flags_kernel(const uint8_t *flags, uint64_t n, uint64_t *o
   for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) out[i] = flags[i];
 }
 
+// AoS -> SoA: std::pair<Kmer, T> records (stride bytes, key at 0, value at val_off, both 8-byte aligned
+// record starts) de-interleaved on the device, so the host never touches the batch.
+template <int W>
+__global__ void split_pairs_kernel(const uint64_t *recs, uint64_t n, uint32_t stride_w, uint32_t val_off_w,
+                                   uint32_t val_shift, uint32_t val_mask, uint64_t *keys, uint32_t *vals) {
+  const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+  for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+    const uint64_t *r = recs + i * stride_w;
+#pragma unroll
+    for (int q = 0; q < W; ++q) keys[i * W + q] = r[q];
+    vals[i] = (uint32_t)(r[val_off_w] >> val_shift) & val_mask;
+  }
+}
+
 }  // namespace kh
 
 using namespace kh;
@@ -595,6 +609,41 @@ int64_t kh_insert_host(kh_table *t, const uint64_t *keys, const uint32_t *vals, 
       off = next_off; buf ^= 1;
     }
     return (int64_t)added;
+  });
+}
+
+int64_t kh_insert_pairs_host(kh_table *t, const void *pairs, uint64_t n, uint32_t stride_bytes,
+                             uint32_t val_offset, uint32_t val_bytes, int estimate) {
+  return guarded([&]() -> int64_t {
+    if (!t || (!pairs && n)) { set_error("null table or pairs"); return KH_ERR_INVALID; }
+    const int W = t->W;
+    if (stride_bytes % 8 || stride_bytes < (uint32_t)(8 * W) + val_bytes || val_offset < (uint32_t)(8 * W) ||
+        val_offset + val_bytes > stride_bytes || !(val_bytes == 1 || val_bytes == 2 || val_bytes == 4) ||
+        (val_offset % 8) + val_bytes > 8) {
+      set_error("unsupported pair layout: stride %u, value %u bytes at %u", stride_bytes, val_bytes, val_offset);
+      return KH_ERR_INVALID;
+    }
+    DeviceGuard g(t->device);
+    if (n == 0) return 0;
+    const uint32_t stride_w = stride_bytes / 8, val_off_w = val_offset / 8, val_shift = 8 * (val_offset % 8);
+    const uint32_t val_mask = val_bytes == 4 ? 0xffffffffu : ((1u << (8 * val_bytes)) - 1u);
+    DevBuf<uint64_t> dk(n * W);
+    DevBuf<uint32_t> dv(n);
+    DevBuf<uint64_t> stage[2];
+    const uint64_t chunk = HOST_CHUNK / 2;
+    for (int b = 0; b < 2; ++b) stage[b].alloc(std::min(chunk, n) * stride_w);
+    int buf = 0;
+    for (uint64_t off = 0; off < n; off += chunk, buf ^= 1) {
+      const uint64_t m = std::min(chunk, n - off);
+      cudaStream_t s = t->stream[buf];   // copy-in and split of one staging buffer are ordered on its stream
+      KH_CUDA(cudaMemcpyAsync(stage[buf].p, (const unsigned char *)pairs + off * stride_bytes, m * stride_bytes,
+                              cudaMemcpyHostToDevice, s));
+      if (W == 1) KH_LAUNCH((split_pairs_kernel<1>), t->grid_for(m, 1024), 256, 0, s, stage[buf].p, m, stride_w, val_off_w, val_shift, val_mask, dk.p + off, dv.p + off);
+      else KH_LAUNCH((split_pairs_kernel<2>), t->grid_for(m, 1024), 256, 0, s, stage[buf].p, m, stride_w, val_off_w, val_shift, val_mask, dk.p + off * 2, dv.p + off);
+    }
+    KH_CUDA(cudaStreamSynchronize(t->stream[1]));
+    KH_CUDA(cudaStreamSynchronize(t->stream[0]));
+    return insert_dev_impl(t, dk.p, dv.p, n, 0, estimate);
   });
 }
 
