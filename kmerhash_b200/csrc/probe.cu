@@ -39,6 +39,34 @@ __global__ void __launch_bounds__(256) random_access_kernel(unsigned char *buf, 
   if (acc == 0x123456789ULL) atomicAdd(sink, 1ULL);   // keep the loads alive
 }
 
+// same traffic, four independent accesses in flight per thread (does more memory-level parallelism
+// per thread raise the ceiling?)
+template <int BYTES, int MODE>
+__global__ void __launch_bounds__(256) random_access_ilp4_kernel(unsigned char *buf, uint64_t n_pieces_mask, uint64_t n_access,
+                                                                 uint64_t salt, unsigned long long *sink) {
+  const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+  uint64_t acc = 0;
+  for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n_access; i += 4 * stride) {
+    unsigned char *p[4];
+    uint64_t w[4][4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) p[u] = buf + (mix64((i + u * stride) ^ salt) & n_pieces_mask) * BYTES;
+#pragma unroll
+    for (int o = 0; o < BYTES; o += 32) {
+#pragma unroll
+      for (int u = 0; u < 4; ++u)
+        asm volatile("ld.global.cg.v4.u64 {%0,%1,%2,%3}, [%4];" : "=l"(w[u][0]), "=l"(w[u][1]), "=l"(w[u][2]), "=l"(w[u][3]) : "l"(p[u] + o));
+#pragma unroll
+      for (int u = 0; u < 4; ++u) acc += w[u][0] ^ w[u][1] ^ w[u][2] ^ w[u][3];
+    }
+    if (MODE == 1) {
+#pragma unroll
+      for (int u = 0; u < 4; ++u) if (i + u * stride < n_access) atomicAdd(reinterpret_cast<unsigned int *>(p[u] + 8), 1u);
+    }
+  }
+  if (acc == 0x123456789ULL) atomicAdd(sink, 1ULL);
+}
+
 __global__ void stream_copy_kernel(const uint4 *__restrict__ in, uint4 *__restrict__ out, uint64_t n) {
   const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
   for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) out[i] = in[i];
@@ -54,6 +82,9 @@ double kh_probe_random_access(int device, uint64_t buf_bytes, uint64_t n_access,
   double ms_out = -1.0;
   guarded([&]() -> int64_t {
     if (kh_device_count() <= 0) { set_error("no CUDA device"); return KH_ERR_CUDA; }
+    const bool ilp4 = mode >= 2;   // mode 2 = read, 3 = read + atomicAdd, four accesses in flight per thread
+    if (ilp4) mode -= 2;
+    if (ilp4 && bytes_per_access == 16) { set_error("ilp4 probe: 32, 64 or 128 bytes"); return KH_ERR_INVALID; }
     if (bytes_per_access != 16 && bytes_per_access != 32 && bytes_per_access != 64 && bytes_per_access != 128) {
       set_error("bytes_per_access must be 16, 32, 64 or 128"); return KH_ERR_INVALID;
     }
@@ -70,11 +101,17 @@ double kh_probe_random_access(int device, uint64_t buf_bytes, uint64_t n_access,
     for (int it = 0; it < std::max(iters, 1) + 1; ++it) {
       const uint64_t salt = 0x5bd1e995ULL * (it + 1);
       KH_CUDA(cudaEventRecord(e0, 0));
+#define KH_RA4(B)                                                                                             \
+      if (mode == 0) KH_LAUNCH((random_access_ilp4_kernel<B, 0>), grid, 256, 0, 0, buf.p, pieces - 1, n_access, salt, sink.p); \
+      else KH_LAUNCH((random_access_ilp4_kernel<B, 1>), grid, 256, 0, 0, buf.p, pieces - 1, n_access, salt, sink.p);
+      if (ilp4) { switch (bytes_per_access) { case 32: KH_RA4(32) break; case 64: KH_RA4(64) break; default: KH_RA4(128) break; } }
+      else
 #define KH_RA(B)                                                                                              \
       if (mode == 0) KH_LAUNCH((random_access_kernel<B, 0>), grid, 256, 0, 0, buf.p, pieces - 1, n_access, salt, sink.p); \
       else KH_LAUNCH((random_access_kernel<B, 1>), grid, 256, 0, 0, buf.p, pieces - 1, n_access, salt, sink.p);
       switch (bytes_per_access) { case 16: KH_RA(16) break; case 32: KH_RA(32) break; case 64: KH_RA(64) break; default: KH_RA(128) break; }
 #undef KH_RA
+#undef KH_RA4
       KH_CUDA(cudaEventRecord(e1, 0));
       KH_CUDA(cudaEventSynchronize(e1));
       float ms = 0; KH_CUDA(cudaEventElapsedTime(&ms, e0, e1));

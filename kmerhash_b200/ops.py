@@ -177,7 +177,7 @@ class MultiGpuMap:
 
 def probe_random_access(buf_bytes, n_access, bytes_per_access=32, mode="read", iters=3, device=0):
     """milliseconds of the random-access roofline probe."""
-    ms = lib.kh_probe_random_access(device, buf_bytes, n_access, bytes_per_access, 0 if mode == "read" else 1, iters)
+    ms = lib.kh_probe_random_access(device, buf_bytes, n_access, bytes_per_access, {"read": 0, "rmw": 1, "read_ilp4": 2, "rmw_ilp4": 3}[mode], iters)
     if ms < 0:
         check(-3, "probe_random_access")
     return ms

@@ -39,6 +39,17 @@ def probes():
     print(json.dumps({"probe": "stream_copy", "GB_per_s": round(2 * (4 << 30) / ms / 1e6, 1)}), flush=True)
 
 
+def l2probes():
+    """does a table region that fits the 126 MB L2 raise the random-access ceiling? (partitioned-insert question)"""
+    for buf_mb in (16, 32, 64, 96, 128, 256, 512):
+        for mode in ("read", "rmw", "read_ilp4", "rmw_ilp4"):
+            for b in (32, 64):
+                n = 100_000_000
+                ms = kh.probe_random_access(buf_mb << 20, n, b, mode, iters=3)
+                print(json.dumps({"probe": "random", "buf_mb": buf_mb, "mode": mode, "bytes": b, "ms": round(ms, 3),
+                                  "G_access_per_s": round(n / ms / 1e6, 2), "GB_per_s": round(n * b / ms / 1e6, 1)}), flush=True)
+
+
 def geom_sweep(n=100_000_000, nq=10_000_000, words=1):
     keys = gen_keys(n, words=words)
     d = torch.from_numpy(keys.view(np.int64)).cuda()
@@ -75,6 +86,8 @@ if __name__ == "__main__":
     what = sys.argv[1:] or ["probes", "geom"]
     if "probes" in what:
         probes()
+    if "l2probes" in what:
+        l2probes()
     if "geom" in what:
         geom_sweep()
     if "geom2" in what:
