@@ -120,8 +120,13 @@ void *kh_stream(kh_table *t);
  * the accumulated milliseconds and launch count of which = 0 (insert kernels) / 1 (lookup kernels) */
 int kh_kernel_timing(kh_table *t, int enable);
 int kh_kernel_time(kh_table *t, int which, double *sum_ms, uint64_t *launches);
-/* probe geometry (experiments; empty table only): lane_bytes 16|32, lanes_per_bucket 1|2|4|8 -- see DESIGN.md */
+/* probe geometry (experiments; empty table only): lane_bytes 16|32|64, lanes_per_bucket 1|2|4|8 (64: 1 only) -- see DESIGN.md */
 int kh_set_geometry(kh_table *t, int lane_bytes, int lanes_per_bucket);
+
+/* L2-windowed bulk insert: COUNT batches of >= min_keys keys into a table of
+ * >= 4 * window_bytes are first sorted by table region (window_bytes each, power of two) so the probe
+ * kernel works inside the L2.  Default: on, 32 MiB, 4 Mi keys.  Results do not depend on it. */
+int kh_set_insert_window(kh_table *t, int enable, uint64_t window_bytes, uint64_t min_keys);
 
 /* HyperLogLog distinct estimate of a key batch over the table's store hash, precision 12
  * (replaces get_hll().update(keys,n) + estimate(), KH/hyperloglog64.hpp:176-239; driver

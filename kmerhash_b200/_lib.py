@@ -75,6 +75,7 @@ SIGNATURES = {
     "kh_estimate_distinct_dev": (_dbl, [_vp, _vp, _u64, _vp]),
     "kh_insert_host": (_i64, [_vp, _vp, _vp, _u64, _u32, _int]),
     "kh_insert_dev": (_i64, [_vp, _vp, _vp, _u64, _u32, _int]),
+    "kh_set_insert_window": (_int, [_vp, _int, _u64, _u64]),
     "kh_insert_pairs_host": (_i64, [_vp, _vp, _u64, _u32, _u32, _u32, _int]),
     "kh_count_host": (_i64, [_vp, _vp, _u64, _vp]),
     "kh_count_dev": (_i64, [_vp, _vp, _u64, _vp]),

@@ -20,11 +20,19 @@ constexpr int HLL_M = 1 << HLL_P;
 
 inline double hll_error_rate() { return 1.04 / std::sqrt((double)HLL_M); }
 
+// number of fine table regions the fused pass histograms (top REGION_FINE_BITS bits of the spread hash)
+constexpr int REGION_FINE_BITS = 10;
+constexpr int REGION_FINE = 1 << REGION_FINE_BITS;
+
+// g_hist != nullptr: the same pass also counts the keys per fine table region (the windowed bulk insert
+// derives its partition offsets from it, so the keys are hashed and read once for both purposes).
 template <int W>
 __global__ void __launch_bounds__(512) hll_update_kernel(const uint64_t *keys, uint64_t n, int hash_kind, HashParams hp,
-                                                         uint32_t *g_regs) {
+                                                         uint32_t *g_regs, unsigned long long *g_hist) {
   __shared__ uint32_t regs[HLL_M];
+  __shared__ uint32_t fine[REGION_FINE];
   for (int i = threadIdx.x; i < HLL_M; i += blockDim.x) regs[i] = 0;
+  for (int i = threadIdx.x; i < REGION_FINE; i += blockDim.x) fine[i] = 0;
   __syncthreads();
   const bool h32 = hash_bits(hash_kind) == 32;
   const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
@@ -42,10 +50,14 @@ __global__ void __launch_bounds__(512) hll_update_kernel(const uint64_t *keys, u
       rank = __clzll((long long)((h << HLL_P) | 0xFFFULL)) + 1;
     }
     if (regs[idx] < rank) atomicMax(&regs[idx], rank);
+    if (g_hist) atomicAdd(&fine[(uint32_t)(spread_hash(h) >> (64 - REGION_FINE_BITS))], 1u);
   }
   __syncthreads();
   for (int i = threadIdx.x; i < HLL_M; i += blockDim.x)
     if (regs[i]) atomicMax(&g_regs[i], regs[i]);
+  if (g_hist)
+    for (int i = threadIdx.x; i < REGION_FINE; i += blockDim.x)
+      if (fine[i]) atomicAdd(&g_hist[i], (unsigned long long)fine[i]);
 }
 
 // estimate() of the reference (hyperloglog64.hpp:203-239): raw harmonic estimate, linear counting
@@ -66,22 +78,37 @@ inline double hll_estimate_from_regs(const uint8_t *regs, int bits) {
   return est;
 }
 
-inline double hll_estimate_dev(int hash_kind, const HashParams &hp, int W, const uint64_t *d_keys, uint64_t n,
-                               uint8_t *regs_out, cudaStream_t s, int sms) {
-  DevBuf<uint32_t> g(HLL_M);
-  KH_CUDA(cudaMemsetAsync(g.p, 0, HLL_M * sizeof(uint32_t), s));
-  if (n) {
-    const int grid = (int)std::max<uint64_t>(1, std::min<uint64_t>((n + 2047) / 2048, (uint64_t)sms * 4));
-    if (W == 1) KH_LAUNCH((hll_update_kernel<1>), grid, 512, 0, s, d_keys, n, hash_kind, hp, g.p);
-    else KH_LAUNCH((hll_update_kernel<2>), grid, 512, 0, s, d_keys, n, hash_kind, hp, g.p);
-  }
+// Accumulating form: registers (HLL_M x u32) and the optional fine region histogram live on the device
+// and are updated batch by batch (the host pipeline feeds chunks as they arrive over PCIe).
+inline void hll_reset(uint32_t *d_regs, unsigned long long *d_hist, cudaStream_t s) {
+  KH_CUDA(cudaMemsetAsync(d_regs, 0, HLL_M * sizeof(uint32_t), s));
+  if (d_hist) KH_CUDA(cudaMemsetAsync(d_hist, 0, REGION_FINE * sizeof(unsigned long long), s));
+}
+inline void hll_accumulate(int hash_kind, const HashParams &hp, int W, const uint64_t *d_keys, uint64_t n,
+                           uint32_t *d_regs, unsigned long long *d_hist, cudaStream_t s, int sms) {
+  if (!n) return;
+  const int grid = (int)std::max<uint64_t>(1, std::min<uint64_t>((n + 2047) / 2048, (uint64_t)sms * 4));
+  if (W == 1) KH_LAUNCH((hll_update_kernel<1>), grid, 512, 0, s, d_keys, n, hash_kind, hp, d_regs, d_hist);
+  else KH_LAUNCH((hll_update_kernel<2>), grid, 512, 0, s, d_keys, n, hash_kind, hp, d_regs, d_hist);
+}
+// reads the registers back (synchronises s) and evaluates the estimate
+inline double hll_finish(int hash_kind, const uint32_t *d_regs, uint8_t *regs_out, cudaStream_t s) {
   uint32_t h[HLL_M];
-  KH_CUDA(cudaMemcpyAsync(h, g.p, sizeof(h), cudaMemcpyDeviceToHost, s));
+  KH_CUDA(cudaMemcpyAsync(h, d_regs, sizeof(h), cudaMemcpyDeviceToHost, s));
   KH_CUDA(cudaStreamSynchronize(s));
   uint8_t r8[HLL_M];
   for (int i = 0; i < HLL_M; ++i) r8[i] = (uint8_t)h[i];
   if (regs_out) for (int i = 0; i < HLL_M; ++i) regs_out[i] = r8[i];
   return hll_estimate_from_regs(r8, hash_bits(hash_kind));
+}
+
+// d_hist (device, REGION_FINE entries, may be null): zeroed and filled with the fine region histogram
+inline double hll_estimate_dev(int hash_kind, const HashParams &hp, int W, const uint64_t *d_keys, uint64_t n,
+                               uint8_t *regs_out, cudaStream_t s, int sms, unsigned long long *d_hist = nullptr) {
+  DevBuf<uint32_t> g(HLL_M);
+  hll_reset(g.p, d_hist, s);
+  hll_accumulate(hash_kind, hp, W, d_keys, n, g.p, d_hist, s, sms);
+  return hll_finish(hash_kind, g.p, regs_out, s);
 }
 
 }  // namespace kh

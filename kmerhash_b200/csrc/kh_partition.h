@@ -18,6 +18,7 @@ struct PartitionPlan {
   int device = 0, kind = 0, W = 1;
   HashParams hp;
   uint32_t p = 1;
+  int region_shift = 0;          // > 0: partition by table region (top bits of the spread store hash), p = 2^(64-shift)
   const uint64_t *d_keys = nullptr;
   uint64_t n = 0, blocks = 0, per_block = 0;
   DevBuf<uint64_t> hist, offs, seg;

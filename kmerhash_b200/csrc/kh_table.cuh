@@ -39,6 +39,22 @@ constexpr uint32_t AUX_IDX_MASK = 0x7fffffffu;
 constexpr uint32_t AUX_SEALED_FIRST = 0x7fffffffu;   // pre-existing key under FIRST: never loses
 constexpr uint32_t FULL_MASK = 0xffffffffu;
 
+// Home bucket = the TOP log2(n_buckets) bits of spread(hash).  The multiplicative spread makes the top
+// bits depend on every hash bit (32-bit functors and the identity functor leave the top bits of the raw
+// value empty).  Taking the top bits -- not `hash & mask` as the reference does -- makes the order of
+// the home buckets independent of the capacity: "region" r of P (top log2 P bits) is one contiguous
+// 1/P of the table at ANY capacity, which is what the L2-windowed bulk insert sorts by, and a table
+// dump in slot order is already sorted by region for the rebuilt table.
+__host__ __device__ __forceinline__ uint64_t spread_hash(uint64_t h) { return h * 0x9E3779B97F4A7C15ULL; }
+__host__ __device__ __forceinline__ uint64_t top_bits(uint64_t hm, int shift) { return shift >= 64 ? 0 : (hm >> shift); }
+__host__ __device__ __forceinline__ int log2_u64(uint64_t x) {   // x is a power of two
+#ifdef __CUDA_ARCH__
+  return 63 - __clzll((long long)x);
+#else
+  int l = 0; while ((1ULL << l) < x) ++l; return l;
+#endif
+}
+
 enum : int { OP_FIND = 0, OP_COUNT = 1, OP_ERASE = 2, OP_UPDATE = 3, OP_FINALIZE = 4 };
 enum : int { INS_COUNT = 0, INS_FIRST = 1, INS_LAST = 2 };
 
@@ -61,6 +77,15 @@ template <> struct LdCg<4> {
   static __device__ __forceinline__ void ld(const void *p, uint64_t (&w)[4]) {
     asm volatile("ld.global.cg.v4.u64 {%0,%1,%2,%3}, [%4];"
                  : "=l"(w[0]), "=l"(w[1]), "=l"(w[2]), "=l"(w[3]) : "l"(p) : "memory");
+  }
+};
+
+template <> struct LdCg<8> {   // a whole 64-byte bucket by one thread: two 32-byte loads in flight
+  static __device__ __forceinline__ void ld(const void *p, uint64_t (&w)[8]) {
+    asm volatile("ld.global.cg.v4.u64 {%0,%1,%2,%3}, [%4];"
+                 : "=l"(w[0]), "=l"(w[1]), "=l"(w[2]), "=l"(w[3]) : "l"(p) : "memory");
+    asm volatile("ld.global.cg.v4.u64 {%0,%1,%2,%3}, [%4];"
+                 : "=l"(w[4]), "=l"(w[5]), "=l"(w[6]), "=l"(w[7]) : "l"((const char *)p + 32) : "memory");
   }
 };
 
@@ -131,8 +156,8 @@ __device__ __forceinline__ uint64_t hash_runtime(int kind, const uint64_t (&key)
   return h;
 }
 
-// Geometry: W words per key, LB bytes per lane load (16 or 32), G lanes per bucket.
-//   slots per lane   S = LB / (16 W)        (W=1: 1 or 2; W=2: 1, LB must be 32)
+// Geometry: W words per key, LB bytes per lane load (16, 32 or 64), G lanes per bucket.
+//   slots per lane   S = LB / (16 W)        (W=1: 1, 2 or 4; W=2: 1 or 2, LB >= 32)
 //   slots per bucket  = G * S,  bucket bytes = G * LB
 template <int W, int LB, int G>
 struct Geom {
@@ -215,6 +240,7 @@ __global__ void __launch_bounds__(256) lookup_kernel(LookupArgs a) {
   const int gl = lane & (G - 1);
   const int gbase = lane - gl;
   const uint64_t bmask = a.t.capacity / Ge::BUCKET_SLOTS - 1;
+  const int bshift = 64 - log2_u64(bmask + 1);
   const uint64_t warps_total = (uint64_t)gridDim.x * (blockDim.x >> 5);
   const uint64_t warp_id = (uint64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
   uint32_t hits = 0;
@@ -248,7 +274,7 @@ __global__ void __launch_bounds__(256) lookup_kernel(LookupArgs a) {
         }
       }
     }
-    const uint64_t h = hash_runtime<W>(a.hash_kind, key, a.hp);
+    const uint64_t h = top_bits(spread_hash(hash_runtime<W>(a.hash_kind, key, a.hp)), bshift);   // home bucket
 
 #pragma unroll 1
     for (int r = 0; r < G; ++r) {
@@ -258,10 +284,10 @@ __global__ void __launch_bounds__(256) lookup_kernel(LookupArgs a) {
       if (G == 1) {
 #pragma unroll
         for (int q = 0; q < W; ++q) k[q] = key[q];
-        b = h & bmask; act = probe;
+        b = h; act = probe;
       } else {
         shfl_key<W>(key, gbase + r, k);
-        b = __shfl_sync(FULL_MASK, h, gbase + r) & bmask;
+        b = __shfl_sync(FULL_MASK, h, gbase + r);
         act = __shfl_sync(FULL_MASK, (int)probe, gbase + r) != 0;
       }
       uint64_t probes = 0;
@@ -347,6 +373,11 @@ struct InsertArgs {
   uint64_t idx_base;        // ordered modes: batch position of keys[0]
   unsigned long long *n_new;
   int *status;              // set to 1 when a key found no slot (table full)
+  // COUNT mode only: a key that finds neither itself nor an empty slot within probe_limit buckets is not
+  // placed; its batch index goes to defer_idx (n_new[1] counts them) and the host re-inserts those keys
+  // after growing the table.  defer_idx == nullptr: probe the whole table, then report "full".
+  uint32_t *defer_idx;
+  uint64_t probe_limit;
 };
 
 template <int W, int LB, int G, int MODE>
@@ -356,6 +387,7 @@ __global__ void __launch_bounds__(256) insert_kernel(InsertArgs a) {
   const int gl = lane & (G - 1);
   const int gbase = lane - gl;
   const uint64_t bmask = a.t.capacity / Ge::BUCKET_SLOTS - 1;
+  const int bshift = 64 - log2_u64(bmask + 1);
   const uint64_t warps_total = (uint64_t)gridDim.x * (blockDim.x >> 5);
   const uint64_t warp_id = (uint64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
   constexpr uint64_t NONE = ~0ULL;
@@ -380,7 +412,7 @@ __global__ void __launch_bounds__(256) insert_kernel(InsertArgs a) {
       if (atomicExch(&a.t.side[0], 1u) == 0u) ++fresh;
       if (MODE == INS_COUNT) atomicAdd(&a.t.side[1], myv); else atomicMax(&a.t.side[2], myv);
     }
-    const uint64_t h = hash_runtime<W>(a.hash_kind, key, a.hp);
+    const uint64_t h = top_bits(spread_hash(hash_runtime<W>(a.hash_kind, key, a.hp)), bshift);   // home bucket
 
 #pragma unroll 1
     for (int r = 0; r < G; ++r) {
@@ -391,10 +423,10 @@ __global__ void __launch_bounds__(256) insert_kernel(InsertArgs a) {
       if (G == 1) {
 #pragma unroll
         for (int q = 0; q < W; ++q) k[q] = key[q];
-        home = h & bmask; act = probe; v = myv;
+        home = h; act = probe; v = myv;
       } else {
         shfl_key<W>(key, gbase + r, k);
-        home = __shfl_sync(FULL_MASK, h, gbase + r) & bmask;
+        home = __shfl_sync(FULL_MASK, h, gbase + r);
         act = __shfl_sync(FULL_MASK, (int)probe, gbase + r) != 0;
         v = __shfl_sync(FULL_MASK, myv, gbase + r);
       }
@@ -420,8 +452,11 @@ __global__ void __launch_bounds__(256) insert_kernel(InsertArgs a) {
             act = false;
           } else {
             if (fe == NONE && ge) fe = (b * G + (__ffs(ge) - 1)) * Ge::S + e_local;
-            if ((ge && !gs) || ++probes > bmask) claim = true;
-            else b = (b + 1) & bmask;
+            if (ge && !gs) claim = true;                      // the chain ends here: the key is absent
+            else if (++probes > a.probe_limit) {
+              claim = true;
+              if (a.defer_idx) fe = NONE;                     // short limit: the key may sit further on -> defer
+            } else b = (b + 1) & bmask;
           }
         }
         if (warp_any<G>(claim)) {
@@ -447,7 +482,13 @@ __global__ void __launch_bounds__(256) insert_kernel(InsertArgs a) {
           if (claim) {
             if (outcome == 1) { if (gl == 0) ++fresh; act = false; }
             else if (outcome == 2) act = false;
-            else if (outcome == 4) { if (gl == 0) *a.status = 1; act = false; }
+            else if (outcome == 4) {
+              if (gl == 0) {
+                if (a.defer_idx) a.defer_idx[atomicAdd(a.n_new + 1, 1ULL)] = (uint32_t)(base + gbase + r);
+                else *a.status = 1;
+              }
+              act = false;
+            }
             else { b = home; probes = 0; fe = NONE; }   // lost the race: scan again
           }
         }

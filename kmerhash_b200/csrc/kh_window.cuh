@@ -1,0 +1,115 @@
+// kh_window.cuh -- region sort in front of the L2-windowed bulk insert (table.cu: insert_windowed).
+//
+// The batch is reordered so that keys of the same table region (top `lp` bits of the spread store hash
+// = one contiguous 1/2^lp of the table, kh_table.cuh) are adjacent.  Order inside a region is free
+// (COUNT is commutative), which allows the fast non-stable scheme:
+//   1. fine histogram (1024 bins) -- produced by the HLL pass the insert runs anyway (kh_hll.cuh)
+//   2. window_cursor_kernel: one block folds it into 2^lp region start offsets ("cursors")
+//   3. window_scatter_kernel: a block takes a tile of keys, counts them per region in shared memory,
+//      reserves its output ranges with ONE global atomicAdd per non-empty (tile, region), sorts the
+//      tile by region in shared memory and writes each region's run with coalesced stores.
+// Traffic: 8W B read + 8W B written per key, streaming.  This is the role the reference gives its
+// radix-sort table flavour (KH/hashmap_radixsort.hpp: sort first so that the merge is sequential).
+#pragma once
+#include <cstdint>
+#include <cub/block/block_scan.cuh>
+#include "kh_table.cuh"
+#include "kh_hll.cuh"
+
+namespace kh {
+
+constexpr int WIN_BLOCK = 256;
+constexpr int WIN_TILE_BYTES = 16384;          // keys staged per tile
+constexpr int WIN_MAX_P = REGION_FINE;         // 1024
+
+// cursors[r] = number of keys in regions < r  (P = 2^lp regions, P <= 1024)
+__global__ void __launch_bounds__(REGION_FINE) window_cursor_kernel(const unsigned long long *fine, int lp,
+                                                                    unsigned long long *cursors) {
+  using Scan = cub::BlockScan<unsigned long long, REGION_FINE>;
+  __shared__ typename Scan::TempStorage tmp;
+  const int P = 1 << lp, per = REGION_FINE >> lp;
+  unsigned long long c = 0;
+  if ((int)threadIdx.x < P)
+    for (int j = 0; j < per; ++j) c += fine[threadIdx.x * per + j];
+  unsigned long long start;
+  Scan(tmp).ExclusiveSum(c, start);
+  if ((int)threadIdx.x < P) cursors[threadIdx.x] = start;
+}
+
+template <int W>
+__global__ void __launch_bounds__(WIN_BLOCK) window_scatter_kernel(const uint64_t *keys, uint64_t n, int hash_kind,
+                                                                   HashParams hp, int lp,
+                                                                   unsigned long long *cursors, uint64_t *out) {
+  constexpr int TILE = WIN_TILE_BYTES / (8 * W);      // keys per tile
+  constexpr int KPT = TILE / WIN_BLOCK;               // keys per thread
+  constexpr int RPT = WIN_MAX_P / WIN_BLOCK;          // regions per thread in the scan
+  using Scan = cub::BlockScan<uint32_t, WIN_BLOCK>;
+  __shared__ typename Scan::TempStorage tmp;
+  __shared__ uint64_t skeys[TILE * W];
+  __shared__ uint16_t sreg[TILE];
+  __shared__ uint32_t cnt[WIN_MAX_P];                 // keys of the tile per region
+  __shared__ uint32_t lo[WIN_MAX_P];                  // start of the region's run inside the sorted tile
+  __shared__ unsigned long long gbase[WIN_MAX_P];     // start of the region's run in `out`
+  const int P = 1 << lp;
+  const int shift = 64 - lp;
+  const uint64_t n_tiles = (n + TILE - 1) / TILE;
+
+  for (uint64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+    const uint64_t base = tile * TILE;
+    const int tile_n = (int)min((uint64_t)TILE, n - base);
+    for (int r = threadIdx.x; r < P; r += WIN_BLOCK) cnt[r] = 0;
+    __syncthreads();
+
+    uint64_t k[KPT][W];
+    uint32_t reg[KPT], loc[KPT];
+#pragma unroll
+    for (int j = 0; j < KPT; ++j) {
+      const int e = j * WIN_BLOCK + threadIdx.x;
+      if (e < tile_n) {
+        load_key<W>(keys, base + e, k[j]);
+        reg[j] = (uint32_t)top_bits(spread_hash(hash_runtime<W>(hash_kind, k[j], hp)), shift);
+        loc[j] = atomicAdd(&cnt[reg[j]], 1u);
+      }
+    }
+    __syncthreads();
+
+    // exclusive scan of cnt[0..P) -> lo ; reserve the output ranges
+    uint32_t c[RPT], st[RPT];
+#pragma unroll
+    for (int q = 0; q < RPT; ++q) { const int r = threadIdx.x * RPT + q; c[q] = r < P ? cnt[r] : 0u; }
+    Scan(tmp).ExclusiveSum(c, st);
+#pragma unroll
+    for (int q = 0; q < RPT; ++q) {
+      const int r = threadIdx.x * RPT + q;
+      if (r < P) {
+        lo[r] = st[q];
+        if (c[q]) gbase[r] = atomicAdd(&cursors[r], (unsigned long long)c[q]);
+      }
+    }
+    __syncthreads();
+
+    // sort the tile by region in shared memory
+#pragma unroll
+    for (int j = 0; j < KPT; ++j) {
+      const int e = j * WIN_BLOCK + threadIdx.x;
+      if (e < tile_n) {
+        const uint32_t pos = lo[reg[j]] + loc[j];
+#pragma unroll
+        for (int q = 0; q < W; ++q) skeys[pos * W + q] = k[j][q];
+        sreg[pos] = (uint16_t)reg[j];
+      }
+    }
+    __syncthreads();
+
+    // coalesced runs out
+    for (int e = threadIdx.x; e < tile_n; e += WIN_BLOCK) {
+      const uint32_t r = sreg[e];
+      uint64_t *o = out + (gbase[r] + (uint32_t)(e - lo[r])) * W;
+#pragma unroll
+      for (int q = 0; q < W; ++q) o[q] = skeys[e * W + q];
+    }
+    __syncthreads();
+  }
+}
+
+}  // namespace kh

@@ -23,6 +23,21 @@ int sm_count(int device) {
   return n;
 }
 
+void pool_setup(int device) {
+  static std::mutex mu;
+  static bool done[64] = {false};
+  if (device < 0 || device >= 64) return;
+  std::lock_guard<std::mutex> lk(mu);
+  if (done[device]) return;
+  cudaMemPool_t pool;
+  if (cudaDeviceGetDefaultMemPool(&pool, device) == cudaSuccess) {
+    uint64_t keep = ~0ULL;   // never trim: freed scratch stays with the pool for the next batch
+    cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &keep);
+  }
+  cudaGetLastError();
+  done[device] = true;
+}
+
 bool hash_kind_supported(int kind) {
   // murmur3finalizer_avx32 static_asserts sizeof(T) <= 4 (KH/murmurhash3finalizer_32_avx.hpp:527):
   // it cannot be instantiated for 8/16-byte k-mers in the reference either.

@@ -24,7 +24,10 @@ constexpr int PART_MAX_P = 1024;
 constexpr int PART_BLOCK = 256;
 constexpr int PART_WARPS = PART_BLOCK / 32;
 
-__device__ __forceinline__ uint32_t rank_of(uint64_t h, uint32_t p, bool pow2) {
+// region_shift == 0: owner rank of the exchange (the reference's rule).  region_shift > 0: table region =
+// top bits of the spread store hash (kh_table.cuh), used by the L2-windowed bulk insert.
+__device__ __forceinline__ uint32_t rank_of(uint64_t h, uint32_t p, bool pow2, int region_shift = 0) {
+  if (region_shift) return (uint32_t)top_bits(spread_hash(h), region_shift);
   return pow2 ? (uint32_t)(h & (uint64_t)(p - 1)) : (uint32_t)(h % (uint64_t)p);
 }
 
@@ -42,7 +45,8 @@ __global__ void rank_kernel(const uint64_t *keys, uint64_t n, int kind, HashPara
 // block b owns keys [b * per_block, (b+1) * per_block); hist layout [rank][block]
 template <int W>
 __global__ void __launch_bounds__(PART_BLOCK) part_hist_kernel(const uint64_t *keys, uint64_t n, uint64_t per_block,
-                                                               int kind, HashParams hp, uint32_t p, uint64_t *hist) {
+                                                               int kind, HashParams hp, uint32_t p, int region_shift,
+                                                               uint64_t *hist) {
   __shared__ uint32_t sh[PART_MAX_P];
   for (uint32_t r = threadIdx.x; r < p; r += blockDim.x) sh[r] = 0;
   __syncthreads();
@@ -52,7 +56,7 @@ __global__ void __launch_bounds__(PART_BLOCK) part_hist_kernel(const uint64_t *k
   for (uint64_t i = beg + threadIdx.x; i < end; i += blockDim.x) {
     uint64_t key[W];
     load_key<W>(keys, i, key);
-    const uint32_t r = rank_of(hash_runtime<W>(kind, key, hp), p, pow2);
+    const uint32_t r = rank_of(hash_runtime<W>(kind, key, hp), p, pow2, region_shift);
     // warp-aggregated shared atomic
     const uint32_t m = __match_any_sync(__activemask(), r);
     if ((int)(__ffs(m) - 1) == (int)(threadIdx.x & 31)) atomicAdd(&sh[r], (uint32_t)__popc(m));
@@ -64,7 +68,7 @@ __global__ void __launch_bounds__(PART_BLOCK) part_hist_kernel(const uint64_t *k
 
 template <int W, bool MULTI_DST>
 __global__ void __launch_bounds__(PART_BLOCK) part_scatter_kernel(const uint64_t *keys, uint64_t n, uint64_t per_block,
-                                                                  int kind, HashParams hp, uint32_t p,
+                                                                  int kind, HashParams hp, uint32_t p, int region_shift,
                                                                   const uint64_t *offsets /*[rank][block] exclusive*/,
                                                                   uint64_t *out_keys, uint32_t *out_perm, PartDst dst,
                                                                   const uint64_t *seg_start /*[p+1], MULTI_DST only*/) {
@@ -88,7 +92,7 @@ __global__ void __launch_bounds__(PART_BLOCK) part_scatter_kernel(const uint64_t
 #pragma unroll
     for (int q = 0; q < W; ++q) key[q] = 0;
     uint32_t r = p;                                          // invalid lanes form their own group
-    if (valid) { load_key<W>(keys, i, key); r = rank_of(hash_runtime<W>(kind, key, hp), p, pow2); }
+    if (valid) { load_key<W>(keys, i, key); r = rank_of(hash_runtime<W>(kind, key, hp), p, pow2, region_shift); }
     const uint32_t m = __match_any_sync(FULL_MASK, r);
     const bool leader = valid && ((__ffs(m) - 1) == lane);
     const uint32_t in_warp = __popc(m & lt);
@@ -142,8 +146,8 @@ void PartitionPlan::count(cudaStream_t s, uint64_t *counts_host) {
   const uint64_t cells = (uint64_t)p * blocks;
   hist.alloc(cells + 1); offs.alloc(cells + 1); seg.alloc(p + 1);
   KH_CUDA(cudaMemsetAsync(hist.p + cells, 0, sizeof(uint64_t), s));
-  if (W == 1) KH_LAUNCH((part_hist_kernel<1>), (int)blocks, PART_BLOCK, 0, s, d_keys, n, per_block, kind, hp, p, hist.p);
-  else KH_LAUNCH((part_hist_kernel<2>), (int)blocks, PART_BLOCK, 0, s, d_keys, n, per_block, kind, hp, p, hist.p);
+  if (W == 1) KH_LAUNCH((part_hist_kernel<1>), (int)blocks, PART_BLOCK, 0, s, d_keys, n, per_block, kind, hp, p, region_shift, hist.p);
+  else KH_LAUNCH((part_hist_kernel<2>), (int)blocks, PART_BLOCK, 0, s, d_keys, n, per_block, kind, hp, p, region_shift, hist.p);
   size_t tmp_bytes = 0;
   KH_CUDA(cub::DeviceScan::ExclusiveSum(nullptr, tmp_bytes, hist.p, offs.p, cells + 1, s));
   DevBuf<unsigned char> tmp(tmp_bytes);
@@ -163,11 +167,11 @@ void PartitionPlan::scatter(cudaStream_t s, uint64_t *d_out_keys, uint32_t *d_ou
   PartDst d{};
   if (dst) {
     d = *dst;
-    if (W == 1) KH_LAUNCH((part_scatter_kernel<1, true>), (int)blocks, PART_BLOCK, 0, s, d_keys, n, per_block, kind, hp, p, offs.p, d_out_keys, d_out_perm, d, seg.p);
-    else KH_LAUNCH((part_scatter_kernel<2, true>), (int)blocks, PART_BLOCK, 0, s, d_keys, n, per_block, kind, hp, p, offs.p, d_out_keys, d_out_perm, d, seg.p);
+    if (W == 1) KH_LAUNCH((part_scatter_kernel<1, true>), (int)blocks, PART_BLOCK, 0, s, d_keys, n, per_block, kind, hp, p, region_shift, offs.p, d_out_keys, d_out_perm, d, seg.p);
+    else KH_LAUNCH((part_scatter_kernel<2, true>), (int)blocks, PART_BLOCK, 0, s, d_keys, n, per_block, kind, hp, p, region_shift, offs.p, d_out_keys, d_out_perm, d, seg.p);
   } else {
-    if (W == 1) KH_LAUNCH((part_scatter_kernel<1, false>), (int)blocks, PART_BLOCK, 0, s, d_keys, n, per_block, kind, hp, p, offs.p, d_out_keys, d_out_perm, d, nullptr);
-    else KH_LAUNCH((part_scatter_kernel<2, false>), (int)blocks, PART_BLOCK, 0, s, d_keys, n, per_block, kind, hp, p, offs.p, d_out_keys, d_out_perm, d, nullptr);
+    if (W == 1) KH_LAUNCH((part_scatter_kernel<1, false>), (int)blocks, PART_BLOCK, 0, s, d_keys, n, per_block, kind, hp, p, region_shift, offs.p, d_out_keys, d_out_perm, d, nullptr);
+    else KH_LAUNCH((part_scatter_kernel<2, false>), (int)blocks, PART_BLOCK, 0, s, d_keys, n, per_block, kind, hp, p, region_shift, offs.p, d_out_keys, d_out_perm, d, nullptr);
   }
 }
 

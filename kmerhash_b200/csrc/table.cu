@@ -7,16 +7,20 @@
 //   shrink   after erase, when size < min_load * capacity                 :3768-3790
 // but every data-touching step is a kernel (kh_table.cuh) and a resize is a bulk GPU rebuild.
 #include <algorithm>
+#include <chrono>
 #include <cmath>
 #include <cstdlib>
 #include <cstring>
 #include <mutex>
 #include <vector>
 #include <cub/device/device_scan.cuh>
+#include <cub/block/block_scan.cuh>
 
 #include "kh_common.h"
 #include "kh_table.cuh"
 #include "kh_hll.cuh"
+#include "kh_partition.h"
+#include "kh_window.cuh"
 
 namespace kh {
 
@@ -34,33 +38,54 @@ __global__ void init_slots_kernel(uint4 *slots, uint64_t n_units, int words_per_
   }
 }
 
+// Compacting dump of the live entries.  A block takes 1024 consecutive slots per step (4 per thread,
+// coalesced), ranks the occupied ones with a block scan and reserves its output range with ONE atomicAdd,
+// so the output keeps slot order inside a step and steps of the table stay roughly in order (= region
+// order, which the rebuild's re-insert relies on for L2 locality).
+constexpr int EXPORT_ITEMS = 4;
 template <int W>
-__global__ void export_kernel(TableView t, uint64_t *out_keys, uint32_t *out_vals, uint64_t cap,
-                              unsigned long long *counter, int include_side) {
+__global__ void __launch_bounds__(256) export_kernel(TableView t, uint64_t *out_keys, uint32_t *out_vals, uint64_t cap,
+                                                     unsigned long long *counter, int include_side) {
   constexpr int SLOT = 16 * W;
-  const int lane = threadIdx.x & 31;
-  const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
-  const uint64_t n_round = (t.capacity + 31) & ~31ULL;
-  for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n_round; i += stride) {
-    uint64_t w[2 * W];
-    bool occ = false;
-    if (i < t.capacity) {
-      LdCg<2 * W>::ld(t.slots + i * SLOT, w);
-      occ = !key_is_empty<W>(w);
-    }
-    const uint32_t m = __ballot_sync(FULL_MASK, occ);
-    if (m == 0) continue;
-    unsigned long long basepos = 0;
-    if (lane == 0) basepos = atomicAdd(counter, (unsigned long long)__popc(m));
-    basepos = __shfl_sync(FULL_MASK, basepos, 0);
-    if (occ) {
-      const uint64_t pos = basepos + __popc(m & ((1u << lane) - 1u));
-      if (pos < cap) {
+  using Scan = cub::BlockScan<uint32_t, 256>;
+  __shared__ typename Scan::TempStorage tmp;
+  __shared__ unsigned long long block_base;
+  const uint64_t step = 256ULL * EXPORT_ITEMS;
+  const uint64_t n_steps = (t.capacity + step - 1) / step;
+  for (uint64_t st = blockIdx.x; st < n_steps; st += gridDim.x) {
+    uint64_t w[EXPORT_ITEMS][2 * W];
+    bool occ[EXPORT_ITEMS];
 #pragma unroll
-        for (int q = 0; q < W; ++q) out_keys[pos * W + q] = w[q];
-        if (out_vals) out_vals[pos] = (uint32_t)w[W];
+    for (int j = 0; j < EXPORT_ITEMS; ++j) {
+      const uint64_t i = st * step + (uint64_t)j * 256 + threadIdx.x;
+      occ[j] = false;
+      if (i < t.capacity) { LdCg<2 * W>::ld(t.slots + i * SLOT, w[j]); occ[j] = !key_is_empty<W>(w[j]); }
+    }
+    // rank: items are laid out j-major (item j of all threads precedes item j+1), so scan per item row
+    uint32_t before[EXPORT_ITEMS], total_rows = 0;
+#pragma unroll
+    for (int j = 0; j < EXPORT_ITEMS; ++j) {
+      uint32_t excl, row_total;
+      Scan(tmp).ExclusiveSum(occ[j] ? 1u : 0u, excl, row_total);
+      __syncthreads();
+      before[j] = total_rows + excl;
+      total_rows += row_total;
+    }
+    if (threadIdx.x == 0) block_base = total_rows ? atomicAdd(counter, (unsigned long long)total_rows) : 0ULL;
+    __syncthreads();
+    const unsigned long long basepos = block_base;
+#pragma unroll
+    for (int j = 0; j < EXPORT_ITEMS; ++j) {
+      if (occ[j]) {
+        const uint64_t pos = basepos + before[j];
+        if (pos < cap) {
+#pragma unroll
+          for (int q = 0; q < W; ++q) out_keys[pos * W + q] = w[j][q];
+          if (out_vals) out_vals[pos] = (uint32_t)w[j][W];
+        }
       }
     }
+    __syncthreads();
   }
   // side slot (all-ones key)
   if (include_side && blockIdx.x == 0 && threadIdx.x == 0 && t.side[0] == 1u) {
@@ -133,6 +158,8 @@ struct kh_table {
   uint32_t seed = KH_DEFAULT_SEED;
   double min_load = 0.2, max_load = 0.8;
   int LB = 32, G = 2;                 // probe geometry (DESIGN.md "bucket geometry")
+  bool window_on = true;              // L2-windowed bulk insert (KH_WINDOW=0 switches it off for A/B runs)
+  uint64_t window_bytes = 32ULL << 20, window_min_keys = 1ULL << 22;
   uint64_t capacity = 0, size = 0;
   HashParams hp;
   DevBuf<unsigned char> slots;
@@ -168,15 +195,32 @@ struct kh_table {
 
 namespace {
 
+// KH_TRACE=1: host-side wall time of the stages of an insert / rebuild on stderr (the stream is
+// synchronised at every stage boundary while tracing, so the stages do not overlap in the printout)
+struct Trace {
+  static bool enabled() { static const bool on = getenv("KH_TRACE") && atoi(getenv("KH_TRACE")) != 0; return on; }
+  const char *name; cudaStream_t s; std::chrono::steady_clock::time_point t0;
+  Trace(const char *name_, cudaStream_t s_) : name(name_), s(s_) {
+    if (enabled()) { cudaStreamSynchronize(s); t0 = std::chrono::steady_clock::now(); }
+  }
+  ~Trace() {
+    if (enabled()) {
+      cudaStreamSynchronize(s);
+      fprintf(stderr, "[kh-trace] %-18s %8.3f ms\n", name, std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count());
+    }
+  }
+};
+
 // chunk size (keys) of the host<->device pipeline
 constexpr uint64_t HOST_CHUNK = 1ULL << 23;
 constexpr uint64_t ORDERED_CHUNK = 1ULL << 30;
 
 #define KH_GEOM_CASE_(Wv, LBv, Gv, ...) \
   { constexpr int W = Wv; constexpr int LB = LBv; constexpr int G = Gv; __VA_ARGS__; }
-#define KH_GEOM_SWITCH(t, ...)                                                                \
+#define KH_GEOM_SWITCH(t, ...) KH_GEOM_SWITCH3(t, (t)->LB, (t)->G, __VA_ARGS__)
+#define KH_GEOM_SWITCH3(t, LBx, Gx, ...)                                                      \
   do {                                                                                        \
-    const int _code = (t)->W * 10000 + (t)->LB * 100 + (t)->G;                                \
+    const int _code = (t)->W * 10000 + (LBx) * 100 + (Gx);                                    \
     switch (_code) {                                                                          \
       case 11602: KH_GEOM_CASE_(1, 16, 2, __VA_ARGS__) break;                                 \
       case 11604: KH_GEOM_CASE_(1, 16, 4, __VA_ARGS__) break;                                 \
@@ -184,6 +228,8 @@ constexpr uint64_t ORDERED_CHUNK = 1ULL << 30;
       case 13201: KH_GEOM_CASE_(1, 32, 1, __VA_ARGS__) break;                                 \
       case 13202: KH_GEOM_CASE_(1, 32, 2, __VA_ARGS__) break;                                 \
       case 13204: KH_GEOM_CASE_(1, 32, 4, __VA_ARGS__) break;                                 \
+      case 16401: KH_GEOM_CASE_(1, 64, 1, __VA_ARGS__) break;                                 \
+      case 26401: KH_GEOM_CASE_(2, 64, 1, __VA_ARGS__) break;                                 \
       case 23201: KH_GEOM_CASE_(2, 32, 1, __VA_ARGS__) break;                                 \
       case 23202: KH_GEOM_CASE_(2, 32, 2, __VA_ARGS__) break;                                 \
       case 23204: KH_GEOM_CASE_(2, 32, 4, __VA_ARGS__) break;                                 \
@@ -193,6 +239,7 @@ constexpr uint64_t ORDERED_CHUNK = 1ULL << 30;
   } while (0)
 
 bool geometry_ok(int W, int LB, int G) {
+  if (LB == 64) return G == 1;
   if (W == 1) return (LB == 16 && (G == 2 || G == 4 || G == 8)) || (LB == 32 && (G == 1 || G == 2 || G == 4));
   return LB == 32 && (G == 1 || G == 2 || G == 4);
 }
@@ -244,15 +291,24 @@ void kev_resolve(kh_table *t) {
 }
 
 void launch_insert(kh_table *t, const uint64_t *d_keys, const uint32_t *d_vals, uint64_t n, uint32_t dflt,
-                   int mode, cudaStream_t s) {
+                   int mode, cudaStream_t s, uint32_t *defer_idx = nullptr, bool l2_local = false) {
   if (n == 0) return;
   InsertArgs a;
   a.t = t->view(); a.keys = d_keys; a.vals = d_vals; a.n = n; a.dflt = dflt;
   a.hash_kind = t->hash_kind; a.hp = t->hp; a.idx_base = 0;
   a.n_new = t->counters.p; a.status = t->status.p;
+  const uint64_t n_buckets = t->capacity / t->bucket_slots();
+  a.defer_idx = defer_idx;
+  a.probe_limit = defer_idx ? std::min<uint64_t>(n_buckets - 1, 127) : n_buckets - 1;
   const int grid = t->grid_for(n, 256);
+  // The table layout is fixed by the BUCKET size (G x LB bytes), not by how a kernel reads a bucket, so a
+  // 64-byte-bucket table can be probed 2 lanes x 32 B (best when probes miss the L2: fewer bytes in flight
+  // per key, profiles/r01_sweep_*) or 1 thread x 64 B (half the instructions per key: best when the batch
+  // is region-sorted and the probes hit the L2).
+  int LBk = t->LB, Gk = t->G;
+  if (l2_local && t->LB * t->G == 64 && getenv("KH_NO_64x1") == nullptr) { LBk = 64; Gk = 1; }
   kev_begin(t, 0, s);
-  KH_GEOM_SWITCH(t, {
+  KH_GEOM_SWITCH3(t, LBk, Gk, {
     if (mode == INS_COUNT) KH_LAUNCH((insert_kernel<W, LB, G, INS_COUNT>), grid, 256, 0, s, a);
     else if (mode == INS_FIRST) KH_LAUNCH((insert_kernel<W, LB, G, INS_FIRST>), grid, 256, 0, s, a);
     else KH_LAUNCH((insert_kernel<W, LB, G, INS_LAST>), grid, 256, 0, s, a);
@@ -317,6 +373,7 @@ void seal(kh_table *t, cudaStream_t s) {
 // so the COUNT-mode add is a plain copy for every reducer).  The side slot is not touched.
 void rebuild(kh_table *t, uint64_t new_cap) {
   cudaStream_t s = t->stream[0];
+  Trace tr_all("rebuild", s);
   new_cap = std::max<uint64_t>(next_pow2(new_cap), 128);
   if (t->capacity == 0 || t->size == 0) {
     t->slots.release();
@@ -327,13 +384,17 @@ void rebuild(kh_table *t, uint64_t new_cap) {
   }
   DevBuf<uint64_t> keys(t->size * t->W);
   DevBuf<uint32_t> vals(t->size);
-  const uint64_t n = dump_entries(t, keys.p, vals.p, t->size, s, 0);
-  t->slots.release();
-  alloc_slots(t, new_cap, t->slots, s);
-  t->capacity = new_cap;
-  zero_counter(t, s);
-  launch_insert(t, keys.p, vals.p, n, 0, INS_COUNT, s);
-  const uint64_t placed = read_counter(t, s);
+  uint64_t n;
+  { Trace tr("rebuild.dump", s); n = dump_entries(t, keys.p, vals.p, t->size, s, 0); }
+  { Trace tr("rebuild.alloc+init", s);
+    t->slots.release();
+    alloc_slots(t, new_cap, t->slots, s);
+    t->capacity = new_cap; }
+  uint64_t placed;
+  { Trace tr("rebuild.insert", s);
+    zero_counter(t, s);
+    launch_insert(t, keys.p, vals.p, n, 0, INS_COUNT, s, nullptr, true);   // dump order = region order
+    placed = read_counter(t, s); }
   if (placed != n) {
     set_error("rebuild lost entries: %llu of %llu", (unsigned long long)placed, (unsigned long long)n);
     throw CudaError{KH_ERR_CUDA};
@@ -346,22 +407,98 @@ void ensure_room(kh_table *t, uint64_t n_more) {
   if (want > t->capacity) rebuild(t, want);
 }
 
-// one device-resident piece, any reducer.  Returns #new keys.
+bool window_candidate(const kh_table *t, const uint32_t *d_vals, uint64_t n) {
+  return t->window_on && t->reducer == KH_REDUCE_COUNT && !d_vals && n >= t->window_min_keys && n < (1ULL << 32);
+}
+
+// gather the deferred keys (and their addends) of a COUNT launch into fresh arrays
+template <int W>
+__global__ void gather_deferred_kernel(const uint64_t *keys, const uint32_t *vals, const uint32_t *idx, uint64_t n,
+                                       uint64_t *out_keys, uint32_t *out_vals) {
+  const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+  for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+    const uint64_t j = idx[i];
+#pragma unroll
+    for (int q = 0; q < W; ++q) out_keys[i * W + q] = keys[j * W + q];
+    if (vals) out_vals[i] = vals[j];
+  }
+}
+
+// One device-resident piece, any reducer.  Updates t->size and returns #new keys.
+// COUNT: a key that finds no slot near its home bucket (table fuller than planned, e.g. a wrong HLL
+// estimate) is deferred by the kernel; the table is doubled and the deferred keys are inserted again.
 uint64_t insert_resident(kh_table *t, const uint64_t *d_keys, const uint32_t *d_vals, uint64_t n, uint32_t dflt,
-                         cudaStream_t s) {
+                         cudaStream_t s, bool l2_local = false) {
   uint64_t added = 0;
   const int mode = t->reducer == KH_REDUCE_COUNT ? INS_COUNT : (t->reducer == KH_REDUCE_FIRST ? INS_FIRST : INS_LAST);
-  const uint64_t step = (mode == INS_COUNT) ? std::max<uint64_t>(n, 1) : ORDERED_CHUNK;
-  for (uint64_t off = 0; off < n; off += step) {
-    const uint64_t m = std::min(step, n - off);
-    zero_counter(t, s);
-    launch_insert(t, d_keys + off * t->W, d_vals ? d_vals + off : nullptr, m, dflt, mode, s);
-    if (mode != INS_COUNT)   // phase B: the winning batch position stores its value (hits go to counters[1])
+  if (mode != INS_COUNT) {
+    for (uint64_t off = 0; off < n; off += ORDERED_CHUNK) {
+      const uint64_t m = std::min(ORDERED_CHUNK, n - off);
+      zero_counter(t, s);
+      launch_insert(t, d_keys + off * t->W, d_vals ? d_vals + off : nullptr, m, dflt, mode, s);
+      // phase B: the winning batch position stores its value (hits go to counters[1])
       launch_lookup(t, OP_FINALIZE, d_keys + off * t->W, m, nullptr, nullptr, d_vals ? d_vals + off : nullptr, dflt,
                     t->counters.p + 1, s);
-    added += read_counter(t, s);
+      const uint64_t got = read_counter(t, s);
+      added += got; t->size += got;
+    }
+    return added;
+  }
+  constexpr uint64_t COUNT_CHUNK = 1ULL << 31;     // deferred indices are 32-bit
+  for (uint64_t off = 0; off < n; off += COUNT_CHUNK) {
+    uint64_t m = std::min(COUNT_CHUNK, n - off);
+    const uint64_t *ck = d_keys + off * t->W;
+    const uint32_t *cv = d_vals ? d_vals + off : nullptr;
+    DevBuf<uint64_t> rk;          // deferred keys / addends of the previous round
+    DevBuf<uint32_t> rv;
+    while (m) {
+      DevBuf<uint32_t> defer(m);
+      zero_counter(t, s);
+      launch_insert(t, ck, cv, m, dflt, INS_COUNT, s, defer.p, l2_local);
+      const uint64_t got = read_counter(t, s);
+      const uint64_t n_def = t->h_counters[1];
+      added += got; t->size += got;
+      if (n_def == 0) break;
+      DevBuf<uint64_t> nk(n_def * t->W);
+      DevBuf<uint32_t> nv(cv ? n_def : 0);
+      if (t->W == 1) KH_LAUNCH((gather_deferred_kernel<1>), t->grid_for(n_def, 256), 256, 0, s, ck, cv, defer.p, n_def, nk.p, nv.p);
+      else KH_LAUNCH((gather_deferred_kernel<2>), t->grid_for(n_def, 256), 256, 0, s, ck, cv, defer.p, n_def, nk.p, nv.p);
+      KH_CUDA(cudaStreamSynchronize(s));
+      rk = std::move(nk); rv = std::move(nv);
+      ck = rk.p; cv = cv ? rv.p : nullptr; m = n_def;
+      rebuild(t, t->capacity * 2);
+    }
   }
   return added;
+}
+
+// L2-windowed bulk insert.  Random probes into a table much larger than the 126 MB L2 run at the DRAM
+// random-access rate (~13 G read+atomic/s measured, profiles/r01_probes_l2_resident.jsonl); into a region
+// that stays resident in L2 they run at ~55 G/s.  So a large COUNT batch is first sorted by table region
+// (kh_window.cuh: top bits of the spread store hash = a contiguous 1/P of the table, window_bytes each),
+// and the probe kernel then walks the sorted batch: at any moment all resident warps work on one or two
+// regions.  Costs one extra streaming pass (16 B/key), saves the DRAM-latency-bound random traffic.
+// `d_fine`: the fine region histogram of this batch if the HLL pass already produced it, else nullptr.
+uint64_t insert_windowed(kh_table *t, const uint64_t *d_keys, const uint32_t *d_vals, uint64_t n, uint32_t dflt,
+                         const unsigned long long *d_fine, cudaStream_t s) {
+  const uint64_t table_bytes = t->capacity * (uint64_t)t->slot_bytes();
+  const bool windowed = window_candidate(t, d_vals, n) && table_bytes >= 4 * t->window_bytes;
+  if (!windowed) return insert_resident(t, d_keys, d_vals, n, dflt, s);
+  const int lp = std::min(log2_u64(next_pow2(table_bytes / t->window_bytes)), REGION_FINE_BITS);
+  DevBuf<unsigned long long> fine_own, cursors(1u << lp);
+  if (!d_fine) {
+    fine_own.alloc(REGION_FINE);
+    hll_estimate_dev(t->hash_kind, t->hp, t->W, d_keys, n, nullptr, s, t->sms, fine_own.p);
+    d_fine = fine_own.p;
+  }
+  KH_LAUNCH(window_cursor_kernel, 1, REGION_FINE, 0, s, d_fine, lp, cursors.p);
+  DevBuf<uint64_t> sorted(n * t->W);
+  const int grid = t->sms * 4;
+  { Trace tr("window.scatter", s);
+    if (t->W == 1) KH_LAUNCH((window_scatter_kernel<1>), grid, WIN_BLOCK, 0, s, d_keys, n, t->hash_kind, t->hp, lp, cursors.p, sorted.p);
+    else KH_LAUNCH((window_scatter_kernel<2>), grid, WIN_BLOCK, 0, s, d_keys, n, t->hash_kind, t->hp, lp, cursors.p, sorted.p); }
+  Trace tr("window.insert", s);
+  return insert_resident(t, sorted.p, nullptr, n, dflt, s, true);   // synchronises s before the scratch is released
 }
 
 }  // namespace
@@ -390,6 +527,7 @@ kh_table *kh_create(int device, int map_kind, int key_words, int hash_kind, uint
       default:                 t->min_load = 0.2; t->max_load = 0.8; break;
     }
     default_geometry(t->W, t->LB, t->G);
+    if (const char *e = getenv("KH_WINDOW")) t->window_on = atoi(e) != 0;
     t->hp = make_hash_params(t->hash_kind, seed, key_words);
     t->sms = sm_count(device);
     for (int i = 0; i < 2; ++i) {
@@ -444,6 +582,15 @@ int kh_kernel_time(kh_table *t, int which, double *sum_ms, uint64_t *launches) {
   if (prev >= 0) cudaSetDevice(prev);
   if (sum_ms) *sum_ms = t->kev_ms[which];
   if (launches) *launches = t->kev_n[which];
+  return KH_OK;
+}
+
+int kh_set_insert_window(kh_table *t, int enable, uint64_t window_bytes, uint64_t min_keys) {
+  if (!t || (enable && (window_bytes < 1024 || (window_bytes & (window_bytes - 1))))) {
+    set_error("window_bytes must be a power of two >= 1024"); return KH_ERR_INVALID;
+  }
+  t->window_on = enable != 0;
+  if (enable) { t->window_bytes = window_bytes; t->window_min_keys = min_keys; }
   return KH_OK;
 }
 
@@ -523,30 +670,61 @@ double kh_estimate_distinct_host(kh_table *t, const uint64_t *keys, uint64_t n, 
 // ---- insert ------------------------------------------------------------------------------
 // Growth policy without an estimate = the reference's insert_no_estimate: fill up to max_load,
 // double, continue (KH/robinhood_offset_hashmap_ptr.hpp:2802-2885).
+// estimate + fine region histogram of the batch, when the caller's pipeline already produced them
+struct PreEstimate { double est; const unsigned long long *fine; };
+
 static int64_t insert_dev_impl(kh_table *t, const uint64_t *d_keys, const uint32_t *d_vals, uint64_t n,
-                               uint32_t dflt, int estimate) {
+                               uint32_t dflt, int estimate, const PreEstimate *pre = nullptr) {
   cudaStream_t s = t->stream[0];
   if (n == 0) return 0;
+  const double err = 1.0 + hll_error_rate();
+  const uint64_t size0 = t->size;
+  // the HLL pass also histograms the batch by table region when the windowed insert may follow
+  DevBuf<unsigned long long> fine;
+  bool have_fine = false;
+  auto estimate_batch = [&]() -> double {
+    if (pre) return pre->est;
+    Trace tr("hll+hist", s);
+    if (window_candidate(t, d_vals, n)) { fine.alloc(REGION_FINE); have_fine = true; }
+    return hll_estimate_dev(t->hash_kind, t->hp, t->W, d_keys, n, nullptr, s, t->sms, have_fine ? fine.p : nullptr);
+  };
+  // Can the whole batch go in as ONE piece?  Yes when even its distinct keys (an HLL bound) keep the load legal.
+  // (COUNT tolerates a wrong bound: keys that find no slot are deferred and re-inserted after growing.)
+  bool single = false;
+  const bool count_mode = t->reducer == KH_REDUCE_COUNT;
   if (estimate) {
     // insert_impl: reserve(size + estimate * (1 + error)) then one pass (:2512-2535)
-    const double est = hll_estimate_dev(t->hash_kind, t->hp, t->W, d_keys, n, nullptr, s, t->sms);
-    const uint64_t want = (uint64_t)std::ceil(std::min((double)n, est * (1.0 + hll_error_rate())));
-    ensure_room(t, want);
+    const double est = estimate_batch();
+    ensure_room(t, (uint64_t)std::ceil(std::min((double)n, est * err)));
+    single = count_mode;
   }
-  // A piece may overshoot max_load (duplicates usually keep it far below); it never fills the table:
-  // the hard limit is halfway between max_load and 1.  Afterwards double until the load is legal again.
-  const double hard = 0.5 * (t->max_load + 1.0);
-  uint64_t added = 0, off = 0;
-  while (off < n) {
-    uint64_t room = (uint64_t)std::floor(hard * (double)t->capacity);
-    room = room > t->size ? room - t->size : 0;
-    if (room == 0 || (double)t->size >= t->max_load * (double)t->capacity) { rebuild(t, t->capacity * 2); continue; }
-    const uint64_t m = std::min(n - off, room);
-    const uint64_t got = insert_resident(t, d_keys + off * t->W, d_vals ? d_vals + off : nullptr, m, dflt, s);
-    t->size += got; added += got; off += m;
+  if (!single && (double)(t->size + n) <= t->max_load * (double)t->capacity) single = true;
+  if (!single && !estimate && count_mode && n >= (1ULL << 16)) {
+    // insert_no_estimate on a table the caller reserved (the drivers: estimate -> reserve -> insert_no_estimate):
+    // the HLL pass costs one streaming read and saves the piecewise schedule below
+    const double est = estimate_batch();
+    single = (double)t->size + std::min((double)n, est * err) <= t->max_load * (double)t->capacity;
+  }
+  Trace tr_ins("insert.total", s);
+  if (single) {
+    insert_windowed(t, d_keys, d_vals, n, dflt, pre ? pre->fine : (have_fine ? fine.p : nullptr), s);
+  } else {
+    // Growth without an estimate = the reference's insert_no_estimate: fill up to max_load, double, continue.
+    // A piece may overshoot max_load (duplicates usually keep it far below); it never fills the table:
+    // the hard limit is halfway between max_load and 1.
+    const double hard = 0.5 * (t->max_load + 1.0);
+    uint64_t off = 0;
+    while (off < n) {
+      uint64_t room = (uint64_t)std::floor(hard * (double)t->capacity);
+      room = room > t->size ? room - t->size : 0;
+      if (room == 0 || (double)t->size >= t->max_load * (double)t->capacity) { rebuild(t, t->capacity * 2); continue; }
+      const uint64_t m = std::min(n - off, room);
+      insert_resident(t, d_keys + off * t->W, d_vals ? d_vals + off : nullptr, m, dflt, s);
+      off += m;
+    }
   }
   while ((double)t->size > t->max_load * (double)t->capacity) rebuild(t, t->capacity * 2);
-  return (int64_t)added;
+  return (int64_t)(t->size - size0);
 }
 
 int64_t kh_insert_dev(kh_table *t, const uint64_t *d_keys, const uint32_t *d_vals, uint64_t n,
@@ -572,16 +750,30 @@ int64_t kh_insert_host(kh_table *t, const uint64_t *keys, const uint32_t *vals, 
     if (n == 0) return 0;
     const int W = t->W;
     if (estimate || t->reducer != KH_REDUCE_COUNT) {
-      // whole batch resident: HLL needs a full pass before the first insert, and the ordered
-      // reducers need stable batch positions
+      // Whole batch resident (the ordered reducers need stable batch positions, and presizing needs the
+      // estimate before the first insert).  The HLL registers and the region histogram are accumulated
+      // chunk by chunk BEHIND the PCIe copy, so the estimate is ready when the last chunk lands.
       DevBuf<uint64_t> dk(n * W);
       DevBuf<uint32_t> dv(vals ? n : 0);
-      for (uint64_t off = 0; off < n; off += HOST_CHUNK) {
+      const bool pipe_hll = estimate != 0;
+      DevBuf<uint32_t> regs(pipe_hll ? HLL_M : 0);
+      DevBuf<unsigned long long> fine(pipe_hll && window_candidate(t, vals ? dv.p : nullptr, n) ? REGION_FINE : 0);
+      if (pipe_hll) hll_reset(regs.p, fine.p, t->stream[0]);
+      int b = 0;
+      for (uint64_t off = 0; off < n; off += HOST_CHUNK, b ^= 1) {
         const uint64_t m = std::min(HOST_CHUNK, n - off);
-        KH_CUDA(cudaMemcpyAsync(dk.p + off * W, keys + off * W, m * W * 8, cudaMemcpyHostToDevice, t->stream[0]));
-        if (vals) KH_CUDA(cudaMemcpyAsync(dv.p + off, vals + off, m * 4, cudaMemcpyHostToDevice, t->stream[0]));
+        KH_CUDA(cudaMemcpyAsync(dk.p + off * W, keys + off * W, m * W * 8, cudaMemcpyHostToDevice, t->stream[1]));
+        if (vals) KH_CUDA(cudaMemcpyAsync(dv.p + off, vals + off, m * 4, cudaMemcpyHostToDevice, t->stream[1]));
+        if (pipe_hll) {
+          KH_CUDA(cudaEventRecord(t->ev[b], t->stream[1]));
+          KH_CUDA(cudaStreamWaitEvent(t->stream[0], t->ev[b], 0));
+          hll_accumulate(t->hash_kind, t->hp, W, dk.p + off * W, m, regs.p, fine.p, t->stream[0], t->sms);
+        }
       }
-      return insert_dev_impl(t, dk.p, vals ? dv.p : nullptr, n, default_val, estimate);
+      KH_CUDA(cudaStreamSynchronize(t->stream[1]));
+      if (!pipe_hll) return insert_dev_impl(t, dk.p, vals ? dv.p : nullptr, n, default_val, 0);
+      PreEstimate pre{hll_finish(t->hash_kind, regs.p, nullptr, t->stream[0]), fine.p};
+      return insert_dev_impl(t, dk.p, vals ? dv.p : nullptr, n, default_val, estimate, &pre);
     }
     // COUNT without estimate: stream chunks; chunk i+1 is copied while chunk i is inserted
     uint64_t added = 0;
@@ -787,9 +979,11 @@ int64_t kh_erase_dev(kh_table *t, const uint64_t *d_keys, uint64_t n) {
     if (!t || (n && !d_keys)) { set_error("null argument"); return KH_ERR_INVALID; }
     DeviceGuard g(t->device);
     cudaStream_t s = t->stream[0];
-    zero_counter(t, s);
-    launch_lookup(t, OP_ERASE, d_keys, n, nullptr, nullptr, nullptr, 0, t->counters.p, s);
-    const uint64_t erased = read_counter(t, s);
+    uint64_t erased;
+    { Trace tr("erase.kernel", s);
+      zero_counter(t, s);
+      launch_lookup(t, OP_ERASE, d_keys, n, nullptr, nullptr, nullptr, 0, t->counters.p, s);
+      erased = read_counter(t, s); }
     t->size -= erased;
     maybe_shrink(t);
     return (int64_t)erased;

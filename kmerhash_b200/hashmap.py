@@ -87,6 +87,10 @@ class HashMap:
     def set_geometry(self, lane_bytes, lanes_per_bucket):
         check(lib.kh_set_geometry(self._h, lane_bytes, lanes_per_bucket), "set_geometry")
 
+    def set_insert_window(self, enable=True, window_bytes=32 << 20, min_keys=1 << 22):
+        """L2-windowed bulk insert switch / thresholds (results do not depend on it)"""
+        check(lib.kh_set_insert_window(self._h, int(enable), int(window_bytes), int(min_keys)), "set_insert_window")
+
     def stream_ptr(self):
         """cudaStream_t (as int) the device-pointer calls of this table launch on"""
         return lib.kh_stream(self._h)

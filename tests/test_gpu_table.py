@@ -8,8 +8,8 @@ from conftest import sort_pairs
 
 pytestmark = pytest.mark.gpu
 
-GEOMS_W1 = [(32, 1), (32, 2), (32, 4), (16, 2), (16, 4), (16, 8)]
-GEOMS_W2 = [(32, 1), (32, 2), (32, 4)]
+GEOMS_W1 = [(64, 1), (32, 1), (32, 2), (32, 4), (16, 2), (16, 4), (16, 8)]
+GEOMS_W2 = [(64, 1), (32, 1), (32, 2), (32, 4)]
 
 
 def all_geoms():
@@ -272,3 +272,45 @@ def test_multi_gpu_map(kh, oracle_mod, n_gpus):
     assert np.array_equal(m.find(q, 0), om.find(cq, 0))
     assert m.erase(q) == om.erase(cq)
     assert m.size() == om.size()
+
+
+@pytest.mark.parametrize("W", [1, 2])
+@pytest.mark.parametrize("hash_kind", ["MURMUR64avx", "MURMUR32", "IDEN"])
+@pytest.mark.parametrize("window_bytes", [1 << 12, 1 << 16])
+def test_windowed_bulk_insert_matches_oracle(kh, oracle_mod, W, hash_kind, window_bytes):
+    """L2-windowed insert (batch sorted by table region first) forced on at test sizes: same contents, same answers,
+    also for 32-bit and identity store hashes (top bits of the spread hash pick the region)."""
+    rng = np.random.default_rng(17)
+    base = rng.integers(0, 2**62, size=(40000, W), dtype=np.uint64)
+    keys = base[rng.integers(0, 40000, size=300000)]
+    kk = np.ascontiguousarray(keys if W == 2 else keys[:, 0])
+    m = kh.HashMap(W, hash_kind, "COUNT")
+    m.set_insert_window(True, window_bytes, 1)
+    om = oracle_mod.port.Map(W, "COUNT")
+    assert m.insert(kk, default=1) == om.insert(kk, default=1)          # HLL presize + windowed single piece
+    check_against(m, om)
+    more = np.ascontiguousarray(np.concatenate([kk[:50000], kk[:1000] ^ np.uint64(3)]))
+    assert m.insert_no_estimate(more, default=2) == om.insert(more, default=2)   # second batch into a live table
+    check_against(m, om)
+    q = np.ascontiguousarray(kk[:5000])
+    assert np.array_equal(m.find(q, 0), om.find(q, 0))
+    assert m.erase(q) == om.erase(q)
+    check_against(m, om)
+
+
+def test_windowed_and_plain_insert_agree_at_scale(kh):
+    """20 M keys (large enough for the default window thresholds): identical table either way, and the
+    size-independent invariant sum(counts) == n."""
+    rng = np.random.default_rng(3)
+    uniq = rng.integers(0, 2**62, size=4_000_000, dtype=np.uint64)
+    keys = np.ascontiguousarray(uniq[rng.integers(0, len(uniq), size=20_000_000)])
+    out = []
+    for on in (True, False):
+        m = kh.HashMap(1, "MURMUR64avx", "COUNT", min_load=0.35, max_load=0.8)
+        m.set_insert_window(on, 4 << 20, 1 << 20)
+        new = m.insert(keys, default=1)
+        k, v = sort_pairs(*m.to_vector())
+        assert new == len(k) and int(v.astype(np.uint64).sum()) == len(keys)
+        out.append((k, v))
+    assert np.array_equal(out[0][0], out[1][0]) and np.array_equal(out[0][1], out[1][1])
+    assert np.array_equal(out[0][0], np.unique(keys))

@@ -54,7 +54,7 @@ def geom_sweep(n=100_000_000, nq=10_000_000, words=1):
     keys = gen_keys(n, words=words)
     d = torch.from_numpy(keys.view(np.int64)).cuda()
     q = d[:nq].contiguous()
-    geoms = [(32, 1), (32, 2), (32, 4)] + ([(16, 2), (16, 4), (16, 8)] if words == 1 else [])
+    geoms = [(64, 1), (32, 1), (32, 2), (32, 4)] + ([(16, 2), (16, 4), (16, 8)] if words == 1 else [])
     for lb, g in geoms:
         m = kh.HashMap(words, "MURMUR64avx", "COUNT", max_load=0.8, min_load=0.35)
         m.set_geometry(lb, g)
