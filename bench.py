@@ -326,12 +326,14 @@ def ours_multi(args):
     rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
     local = int(os.environ.get("LOCAL_RANK", rank))
     torch.cuda.set_device(local)
+    if os.environ.get("NCCL_DEBUG", "").upper() in ("VERSION", ""):
+        os.environ["NCCL_DEBUG"] = "WARN"          # keep NCCL's version banner out of stdout (one JSON line)
     dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     n, nq = args.n_keys, args.n_query
     keys, queries = generate_workload(n, nq, seed=23 + rank)
     d_keys = torch.from_numpy(keys.view(np.int64)).cuda()
     d_q = torch.from_numpy(queries.view(np.int64)).cuda()
-    dm = DistributedMap(1, args.hash, args.hash, "COUNT", canonical_k=0, device=local, chunks=4)
+    dm = DistributedMap(1, args.hash, args.hash, "COUNT", canonical_k=0, device=local, chunks=1)
     dm.e.table.set_load_factors(0.35, 0.8)
 
     def barrier():

@@ -214,6 +214,13 @@ int kh_revcomp_host(int device, int k, const uint64_t *in, uint64_t n, uint64_t 
 int kh_partition_dev(int device, int hash_kind, uint32_t seed, int key_words, uint32_t p,
                      const uint64_t *d_keys, uint64_t n, uint64_t *d_out_keys, uint32_t *d_out_perm,
                      uint64_t *counts);
+/* Same partition for callers that do not need the reference's STABLE order (the insert path: COUNT is
+ * commutative; the query path: d_out_perm restores input order): each destination's keys are contiguous,
+ * order inside a destination unspecified.  One histogram pass + one tile-sorting scatter pass
+ * (16 B/key of streaming traffic), p <= 1024. */
+int kh_partition_fast_dev(int device, int hash_kind, uint32_t seed, int key_words, uint32_t p,
+                          const uint64_t *d_keys, uint64_t n, uint64_t *d_out_keys, uint32_t *d_out_perm,
+                          uint64_t *counts);
 int kh_rank_host(int device, int hash_kind, uint32_t seed, int key_words, uint32_t p,
                  const uint64_t *keys, uint64_t n, uint32_t *out_rank);
 /* out[perm[i]] = in[i] for 1- or 4-byte elements (results of a permuted query back to input order) */

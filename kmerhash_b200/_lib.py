@@ -97,6 +97,7 @@ SIGNATURES = {
     "kh_canonicalize_host": (_int, [_int, _int, _vp, _u64, _vp]),
     "kh_revcomp_host": (_int, [_int, _int, _vp, _u64, _vp]),
     "kh_partition_dev": (_int, [_int, _int, _u32, _int, _u32, _vp, _u64, _vp, _vp, _vp]),
+    "kh_partition_fast_dev": (_int, [_int, _int, _u32, _int, _u32, _vp, _u64, _vp, _vp, _vp]),
     "kh_rank_host": (_int, [_int, _int, _u32, _int, _u32, _vp, _u64, _vp]),
     "kh_unpermute_dev": (_int, [_int, _int, _vp, _vp, _u64, _vp]),
     "khd_create": (_vp, [_int, _int, _int, _int, _int, _int]),

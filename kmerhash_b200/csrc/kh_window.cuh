@@ -18,12 +18,27 @@
 
 namespace kh {
 
+// what a key is binned by: mode 0 = table region (top `lp` bits of the spread STORE hash), mode 1 = owner rank
+// of the multi-GPU exchange (DIST hash & (p-1) or % p, KH/distributed_batched_robinhood_map.hpp:164-178)
+struct BinSpec {
+  int mode, lp;
+  uint32_t p;
+  int hash_kind;
+  HashParams hp;
+};
+template <int W>
+__device__ __forceinline__ uint32_t bin_of(const BinSpec &b, const uint64_t (&k)[W]) {
+  const uint64_t h = hash_runtime<W>(b.hash_kind, k, b.hp);
+  if (b.mode == 0) return (uint32_t)top_bits(spread_hash(h), 64 - b.lp);
+  return (b.p & (b.p - 1)) == 0 ? (uint32_t)(h & (uint64_t)(b.p - 1)) : (uint32_t)(h % (uint64_t)b.p);
+}
+
 constexpr int WIN_BLOCK = 256;
 constexpr int WIN_TILE_BYTES = 16384;          // keys staged per tile
 constexpr int WIN_MAX_P = REGION_FINE;         // 1024
 
 // cursors[r] = number of keys in regions < r  (P = 2^lp regions, P <= 1024)
-__global__ void __launch_bounds__(REGION_FINE) window_cursor_kernel(const unsigned long long *fine, int lp,
+static __global__ void __launch_bounds__(REGION_FINE) window_cursor_kernel(const unsigned long long *fine, int lp,
                                                                     unsigned long long *cursors) {
   using Scan = cub::BlockScan<unsigned long long, REGION_FINE>;
   __shared__ typename Scan::TempStorage tmp;
@@ -36,10 +51,40 @@ __global__ void __launch_bounds__(REGION_FINE) window_cursor_kernel(const unsign
   if ((int)threadIdx.x < P) cursors[threadIdx.x] = start;
 }
 
+// keys per bin (n_bins <= 1024): shared-memory histogram per block, one global atomic per non-empty bin
 template <int W>
-__global__ void __launch_bounds__(WIN_BLOCK) window_scatter_kernel(const uint64_t *keys, uint64_t n, int hash_kind,
-                                                                   HashParams hp, int lp,
-                                                                   unsigned long long *cursors, uint64_t *out) {
+__global__ void __launch_bounds__(512) bin_hist_kernel(const uint64_t *keys, uint64_t n, BinSpec spec, int n_bins,
+                                                       unsigned long long *g_hist) {
+  __shared__ uint32_t sh[WIN_MAX_P];
+  for (int i = threadIdx.x; i < n_bins; i += blockDim.x) sh[i] = 0;
+  __syncthreads();
+  const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+  for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+    uint64_t k[W];
+    load_key<W>(keys, i, k);
+    atomicAdd(&sh[bin_of<W>(spec, k)], 1u);
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < n_bins; i += blockDim.x)
+    if (sh[i]) atomicAdd(&g_hist[i], (unsigned long long)sh[i]);
+}
+
+// cursors[b] = number of keys in bins < b; totals[b] (may be null) = keys in bin b
+static __global__ void __launch_bounds__(REGION_FINE) bin_cursor_kernel(const unsigned long long *hist, int n_bins,
+                                                                 unsigned long long *cursors, unsigned long long *totals) {
+  using Scan = cub::BlockScan<unsigned long long, REGION_FINE>;
+  __shared__ typename Scan::TempStorage tmp;
+  const unsigned long long c = (int)threadIdx.x < n_bins ? hist[threadIdx.x] : 0ULL;
+  unsigned long long start;
+  Scan(tmp).ExclusiveSum(c, start);
+  if ((int)threadIdx.x < n_bins) { cursors[threadIdx.x] = start; if (totals) totals[threadIdx.x] = c; }
+}
+
+// PERM: out_perm receives the original index of every output position (32-bit: n < 2^32)
+template <int W, bool PERM>
+__global__ void __launch_bounds__(WIN_BLOCK, 4) window_scatter_kernel(const uint64_t *keys, uint64_t n, BinSpec spec,
+                                                                      unsigned long long *cursors, uint64_t *out,
+                                                                      uint32_t *out_perm) {
   constexpr int TILE = WIN_TILE_BYTES / (8 * W);      // keys per tile
   constexpr int KPT = TILE / WIN_BLOCK;               // keys per thread
   constexpr int RPT = WIN_MAX_P / WIN_BLOCK;          // regions per thread in the scan
@@ -47,11 +92,11 @@ __global__ void __launch_bounds__(WIN_BLOCK) window_scatter_kernel(const uint64_
   __shared__ typename Scan::TempStorage tmp;
   __shared__ uint64_t skeys[TILE * W];
   __shared__ uint16_t sreg[TILE];
+  __shared__ uint16_t ssrc[PERM ? TILE : 1];          // position of the key inside the tile before sorting
   __shared__ uint32_t cnt[WIN_MAX_P];                 // keys of the tile per region
   __shared__ uint32_t lo[WIN_MAX_P];                  // start of the region's run inside the sorted tile
   __shared__ unsigned long long gbase[WIN_MAX_P];     // start of the region's run in `out`
-  const int P = 1 << lp;
-  const int shift = 64 - lp;
+  const int P = spec.mode == 0 ? (1 << spec.lp) : (int)spec.p;
   const uint64_t n_tiles = (n + TILE - 1) / TILE;
 
   for (uint64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
@@ -67,7 +112,7 @@ __global__ void __launch_bounds__(WIN_BLOCK) window_scatter_kernel(const uint64_
       const int e = j * WIN_BLOCK + threadIdx.x;
       if (e < tile_n) {
         load_key<W>(keys, base + e, k[j]);
-        reg[j] = (uint32_t)top_bits(spread_hash(hash_runtime<W>(hash_kind, k[j], hp)), shift);
+        reg[j] = bin_of<W>(spec, k[j]);
         loc[j] = atomicAdd(&cnt[reg[j]], 1u);
       }
     }
@@ -97,6 +142,7 @@ __global__ void __launch_bounds__(WIN_BLOCK) window_scatter_kernel(const uint64_
 #pragma unroll
         for (int q = 0; q < W; ++q) skeys[pos * W + q] = k[j][q];
         sreg[pos] = (uint16_t)reg[j];
+        if (PERM) ssrc[pos] = (uint16_t)e;
       }
     }
     __syncthreads();
@@ -104,9 +150,11 @@ __global__ void __launch_bounds__(WIN_BLOCK) window_scatter_kernel(const uint64_
     // coalesced runs out
     for (int e = threadIdx.x; e < tile_n; e += WIN_BLOCK) {
       const uint32_t r = sreg[e];
-      uint64_t *o = out + (gbase[r] + (uint32_t)(e - lo[r])) * W;
+      const unsigned long long gpos = gbase[r] + (uint32_t)(e - lo[r]);
+      uint64_t *o = out + gpos * W;
 #pragma unroll
       for (int q = 0; q < W; ++q) o[q] = skeys[e * W + q];
+      if (PERM) out_perm[gpos] = (uint32_t)(base + ssrc[e]);
     }
     __syncthreads();
   }

@@ -17,6 +17,7 @@
 #include "kh_common.h"
 #include "kh_table.cuh"
 #include "kh_partition.h"
+#include "kh_window.cuh"
 
 namespace kh {
 
@@ -204,6 +205,43 @@ int kh_partition_dev(int device, int hash_kind, uint32_t seed, int key_words, ui
     const int kind = fold_kind(hash_kind);
     const HashParams hp = make_hash_params(kind, seed, key_words);
     partition_dev(device, kind, hp, key_words, p, d_keys, n, d_out_keys, d_out_perm, counts, nullptr, 0);
+    return KH_OK;
+  });
+}
+
+int kh_partition_fast_dev(int device, int hash_kind, uint32_t seed, int key_words, uint32_t p,
+                          const uint64_t *d_keys, uint64_t n, uint64_t *d_out_keys, uint32_t *d_out_perm,
+                          uint64_t *counts) {
+  return (int)guarded([&]() -> int64_t {
+    if (kh_device_count() <= 0) { set_error("no CUDA device: kmerhash_b200 has no CPU fallback"); return KH_ERR_CUDA; }
+    if (key_words < 1 || key_words > 2 || !hash_kind_supported(hash_kind) || p == 0 || p > (uint32_t)WIN_MAX_P || !counts) {
+      set_error("bad partition arguments (1 <= p <= %d)", WIN_MAX_P); return KH_ERR_INVALID;
+    }
+    if (n >= (1ULL << 32)) { set_error("partition batch must be < 2^32 keys"); return KH_ERR_INVALID; }
+    for (uint32_t r = 0; r < p; ++r) counts[r] = 0;
+    if (n == 0) return KH_OK;
+    DeviceGuard g(device);
+    const int kind = fold_kind(hash_kind);
+    const BinSpec spec{1, 0, p, kind, make_hash_params(kind, seed, key_words)};
+    const int sms = sm_count(device);
+    cudaStream_t s = cudaStreamPerThread;
+    DevBuf<unsigned long long> hist(p), cursors(p), totals(p);
+    KH_CUDA(cudaMemsetAsync(hist.p, 0, p * sizeof(unsigned long long), s));
+    const int hgrid = (int)std::max<uint64_t>(1, std::min<uint64_t>((n + 2047) / 2048, (uint64_t)sms * 4));
+    if (key_words == 1) KH_LAUNCH((bin_hist_kernel<1>), hgrid, 512, 0, s, d_keys, n, spec, (int)p, hist.p);
+    else KH_LAUNCH((bin_hist_kernel<2>), hgrid, 512, 0, s, d_keys, n, spec, (int)p, hist.p);
+    KH_LAUNCH(bin_cursor_kernel, 1, REGION_FINE, 0, s, hist.p, (int)p, cursors.p, totals.p);
+    std::vector<unsigned long long> h(p);
+    KH_CUDA(cudaMemcpyAsync(h.data(), totals.p, p * sizeof(unsigned long long), cudaMemcpyDeviceToHost, s));
+    if (key_words == 1) {
+      if (d_out_perm) KH_LAUNCH((window_scatter_kernel<1, true>), sms * 4, WIN_BLOCK, 0, s, d_keys, n, spec, cursors.p, d_out_keys, d_out_perm);
+      else KH_LAUNCH((window_scatter_kernel<1, false>), sms * 4, WIN_BLOCK, 0, s, d_keys, n, spec, cursors.p, d_out_keys, d_out_perm);
+    } else {
+      if (d_out_perm) KH_LAUNCH((window_scatter_kernel<2, true>), sms * 4, WIN_BLOCK, 0, s, d_keys, n, spec, cursors.p, d_out_keys, d_out_perm);
+      else KH_LAUNCH((window_scatter_kernel<2, false>), sms * 4, WIN_BLOCK, 0, s, d_keys, n, spec, cursors.p, d_out_keys, d_out_perm);
+    }
+    KH_CUDA(cudaStreamSynchronize(s));
+    for (uint32_t r = 0; r < p; ++r) counts[r] = h[r];
     return KH_OK;
   });
 }

@@ -495,8 +495,9 @@ uint64_t insert_windowed(kh_table *t, const uint64_t *d_keys, const uint32_t *d_
   DevBuf<uint64_t> sorted(n * t->W);
   const int grid = t->sms * 4;
   { Trace tr("window.scatter", s);
-    if (t->W == 1) KH_LAUNCH((window_scatter_kernel<1>), grid, WIN_BLOCK, 0, s, d_keys, n, t->hash_kind, t->hp, lp, cursors.p, sorted.p);
-    else KH_LAUNCH((window_scatter_kernel<2>), grid, WIN_BLOCK, 0, s, d_keys, n, t->hash_kind, t->hp, lp, cursors.p, sorted.p); }
+    const BinSpec spec{0, lp, 0u, t->hash_kind, t->hp};
+    if (t->W == 1) KH_LAUNCH((window_scatter_kernel<1, false>), grid, WIN_BLOCK, 0, s, d_keys, n, spec, cursors.p, sorted.p, nullptr);
+    else KH_LAUNCH((window_scatter_kernel<2, false>), grid, WIN_BLOCK, 0, s, d_keys, n, spec, cursors.p, sorted.p, nullptr); }
   Trace tr("window.insert", s);
   return insert_resident(t, sorted.p, nullptr, n, dflt, s, true);   // synchronises s before the scratch is released
 }

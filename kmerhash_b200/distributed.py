@@ -15,9 +15,32 @@ The compute engine is the CUDA library (kmerhash_b200.ops / HashMap on torch CUD
 `engine` argument exists so the host-side exchange logic can be exercised with gloo on CPU tensors in
 the test-suite; the product never passes one.
 """
+import os
+import sys
+import time
+
 import numpy as np
 import torch
 import torch.distributed as dist
+
+_TRACE = os.environ.get("KH_TRACE", "0") not in ("", "0")
+
+
+class _Stage:
+    """KH_TRACE=1: wall time of one stage of a distributed call on rank 0 (device synchronised at both ends)"""
+
+    def __init__(self, name):
+        self.name = name
+
+    def __enter__(self):
+        if _TRACE:
+            torch.cuda.synchronize(); self.t0 = time.perf_counter()
+
+    def __exit__(self, *a):
+        if _TRACE:
+            torch.cuda.synchronize()
+            if dist.get_rank() == 0:
+                sys.stderr.write("[kh-trace] dist.%-14s %8.3f ms\n" % (self.name, 1e3 * (time.perf_counter() - self.t0)))
 
 
 class CudaEngine:
@@ -42,7 +65,8 @@ class CudaEngine:
         from . import ops
         if keys.shape[0] == 0:
             return keys, torch.empty(0, dtype=torch.int32, device=self.device), [0] * p
-        return ops.partition_dev(keys, p, self.dist_hash, want_perm=want_perm)
+        # order inside a destination is irrelevant here (COUNT commutes; queries carry their permutation)
+        return ops.partition_dev(keys, p, self.dist_hash, want_perm=want_perm, stable=False)
 
     def unpermute(self, vals, perm):
         from . import ops
@@ -101,13 +125,16 @@ class DistributedMap:
         keys = self.e.canonicalize(keys)
         if self.p == 1:                                                # insert_1 / count_1: no exchange
             return keys, None, [keys.shape[0]], [keys.shape[0]], None
-        permuted, perm, send_counts = self.e.partition(keys, self.p, want_perm)
-        recv_counts = self._counts_a2a(send_counts)
+        with _Stage("partition"):
+            permuted, perm, send_counts = self.e.partition(keys, self.p, want_perm)
+        with _Stage("counts a2a"):
+            recv_counts = self._counts_a2a(send_counts)
         recv = self.e.empty_keys(sum(recv_counts))
         elem = 8 * self.W
         self.last_exchange_bytes += elem * (sum(send_counts) - send_counts[self.rank])
-        work = dist.all_to_all_single(recv, permuted, output_split_sizes=recv_counts, input_split_sizes=send_counts,
-                                      group=self.group, async_op=async_op)
+        with _Stage("keys a2a"):
+            work = dist.all_to_all_single(recv, permuted, output_split_sizes=recv_counts, input_split_sizes=send_counts,
+                                          group=self.group, async_op=async_op)
         return recv, perm, send_counts, recv_counts, (work, permuted)
 
     def _reply(self, res, perm, send_counts, recv_counts):
@@ -136,7 +163,8 @@ class DistributedMap:
             if w is not None and n_chunks > 1:
                 w[0].wait()
             pending = recv
-        added += self.e.insert(pending, default)
+        with _Stage("local insert"):
+            added += self.e.insert(pending, default)
         return added
 
     def count(self, keys):

@@ -88,8 +88,10 @@ def rank_of(keys, p, hash_kind="MURMUR64avx", seed=DIST_SEED, device=0):
     return out
 
 
-def partition_dev(keys, p, hash_kind="MURMUR64avx", seed=DIST_SEED, want_perm=True):
-    """Stable partition of a CUDA key tensor by owner rank (assign_count_permute + permute_by_bucketid).
+def partition_dev(keys, p, hash_kind="MURMUR64avx", seed=DIST_SEED, want_perm=True, stable=True):
+    """Partition of a CUDA key tensor by owner rank (assign_count_permute + permute_by_bucketid).
+    stable=True keeps input order inside every destination (the reference's permuted order); stable=False is the
+    faster tile-sorting scatter whose order inside a destination is unspecified (perm still gives the origin).
     Returns (permuted keys, perm or None, counts[p] as a python list)."""
     dev = keys.device.index
     W = 1 if keys.dim() == 1 else keys.shape[1]
@@ -97,8 +99,9 @@ def partition_dev(keys, p, hash_kind="MURMUR64avx", seed=DIST_SEED, want_perm=Tr
     out = torch.empty_like(a)
     perm = torch.empty(n, dtype=torch.int32, device=a.device) if want_perm else None
     counts = np.zeros(p, dtype=np.uint64)
-    check(lib.kh_partition_dev(dev, HASH_KINDS[hash_kind], seed, W, p, a.data_ptr(), n, out.data_ptr(),
-                               perm.data_ptr() if want_perm else None, counts.ctypes.data), "partition")
+    fn = lib.kh_partition_dev if stable else lib.kh_partition_fast_dev
+    check(fn(dev, HASH_KINDS[hash_kind], seed, W, p, a.data_ptr(), n, out.data_ptr(),
+             perm.data_ptr() if want_perm else None, counts.ctypes.data), "partition")
     return out, perm, [int(c) for c in counts]
 
 

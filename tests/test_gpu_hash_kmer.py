@@ -99,6 +99,27 @@ def test_rank_golden_and_partition(kh, golden, oracle_mod, p, W):
         assert np.array_equal(out.reshape(k.shape), k[exp_perm])
 
 
+@pytest.mark.parametrize("p", [1, 2, 3, 8, 64, 1000])
+@pytest.mark.parametrize("W", [1, 2])
+def test_fast_partition_segments(kh, oracle_mod, p, W):
+    """tile-sorting scatter: same per-destination counts and the same SET of keys per destination as the reference's
+    rule; order inside a destination is free, perm maps every output position to its input index."""
+    import torch
+    rng = np.random.default_rng(p + W)
+    for n in (0, 1, 2047, 2048, 2049, 300001):
+        k = rng.integers(0, 2**64, size=(n, W), dtype=np.uint64)
+        kk = k if W == 2 else k[:, 0].copy()
+        ranks = oracle_mod.port.rank("MURMUR64avx", kk, p)
+        t = torch.from_numpy(np.ascontiguousarray(kk).view(np.int64)).cuda()
+        out, perm, counts = kh.partition_dev(t, p, "MURMUR64avx", want_perm=True, stable=False)
+        assert counts == np.bincount(ranks, minlength=p).tolist()
+        perm = perm.cpu().numpy().view(np.uint32)
+        out = out.cpu().numpy().view(np.uint64).reshape(k.shape)
+        assert np.array_equal(np.sort(perm), np.arange(n, dtype=np.uint32))
+        assert np.array_equal(out, k[perm])
+        assert np.array_equal(ranks[perm], np.repeat(np.arange(p), counts))
+
+
 def test_unpermute(kh):
     import torch
     rng = np.random.default_rng(1)
