@@ -226,6 +226,43 @@ int kh_rank_host(int device, int hash_kind, uint32_t seed, int key_words, uint32
 /* out[perm[i]] = in[i] for 1- or 4-byte elements (results of a permuted query back to input order) */
 int kh_unpermute_dev(int device, int elem_bytes, const void *d_in, const uint32_t *d_perm, uint64_t n, void *d_out);
 
+/* ---- one rank of a multi-process (one process per GPU) distributed insert ---------------
+ * replaces assign_count_estimate_permute (KH/distributed_batched_robinhood_map.hpp:398-625: rank per key,
+ * per-rank counts, PER-DESTINATION HyperLogLog registers, permute) and the receiving half of insert_p
+ * (:910-1179: merge the estimates, reserve, insert).  `t` is this rank's table (store hash, key width).
+ * Sender:   khx_plan_scatter_dev partitions d_keys by owner (p <= 8) into d_out_keys (destination segments
+ *           contiguous, order inside unspecified), fills counts[p] (HOST) and d_meta = p x khx_meta_words()
+ *           uint64 (DEVICE): for every destination its key count, its keys' histogram over table regions and
+ *           their HLL registers.  Keys and metadata travel by all-to-all (NCCL; not done here).
+ * Receiver: khx_insert_recv_dev takes the n received keys and the p received metadata blocks, merges them
+ *           (registers: max, histograms: sum), presizes the table from the merged estimate and inserts with
+ *           value default_val under the table's reducer (COUNT).  Returns #new keys. */
+int khx_meta_words(void);
+int khx_plan_scatter_dev(kh_table *t, int dist_hash, uint32_t dist_seed, uint32_t p, const uint64_t *d_keys, uint64_t n,
+                         uint64_t *d_meta, uint64_t *d_out_keys, uint64_t *counts);
+int64_t khx_insert_recv_dev(kh_table *t, const uint64_t *d_keys, uint64_t n, const uint64_t *d_recv_meta, uint32_t p,
+                            uint32_t default_val);
+
+/* Fused partition + exchange over peer memory (NVLink): instead of permuting into a send buffer and calling an
+ * all-to-all, the rank scatter stores every key straight into the receive buffer of its owner GPU.  The
+ * receive buffers are cudaMalloc'ed per rank and mapped into the other processes of the box with CUDA IPC
+ * (khx_peer_handle -> exchange the 64 bytes -> khx_peer_open); khx_peer_set maps a plain device pointer
+ * (same-process peers).  khx_plan_dev = the metadata pass of khx_plan_scatter_dev alone.  dst_offsets[r] /
+ * dst_counts[r] (HOST, p entries): where this rank's segment starts in rank r's buffer and how long it is
+ * (from the p x p count matrix every rank gathers).  Ordering between ranks is the caller's (see distributed.py). */
+typedef struct khx_peer khx_peer;
+khx_peer *khx_peer_create(int device, uint32_t rank, uint32_t p, uint64_t capacity_keys, int key_words);
+void khx_peer_destroy(khx_peer *x);
+uint64_t khx_peer_capacity(const khx_peer *x);
+uint64_t *khx_peer_recv_ptr(khx_peer *x);
+int khx_peer_handle(khx_peer *x, void *out64);
+int khx_peer_open(khx_peer *x, uint32_t r, const void *handle64);
+int khx_peer_set(khx_peer *x, uint32_t r, uint64_t *d_ptr);
+int khx_plan_dev(kh_table *t, int dist_hash, uint32_t dist_seed, uint32_t p, const uint64_t *d_keys, uint64_t n,
+                 uint64_t *d_meta);
+int khx_scatter_peers_dev(kh_table *t, int dist_hash, uint32_t dist_seed, const uint64_t *d_keys, uint64_t n,
+                          khx_peer *x, const uint64_t *dst_offsets, const uint64_t *dst_counts);
+
 /* ---- single-process multi-GPU map ------------------------------------------------------
  * replaces dsc::counting_batched_robinhood_map / batched_robinhood_map
  * (KH/distributed_batched_robinhood_map.hpp:748-832,1187,1535,1901,2428,2542-2649): one table per

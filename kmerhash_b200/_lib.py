@@ -97,6 +97,18 @@ SIGNATURES = {
     "kh_canonicalize_host": (_int, [_int, _int, _vp, _u64, _vp]),
     "kh_revcomp_host": (_int, [_int, _int, _vp, _u64, _vp]),
     "kh_partition_dev": (_int, [_int, _int, _u32, _int, _u32, _vp, _u64, _vp, _vp, _vp]),
+    "khx_meta_words": (_int, []),
+    "khx_peer_create": (_vp, [_int, _u32, _u32, _u64, _int]),
+    "khx_peer_destroy": (None, [_vp]),
+    "khx_peer_capacity": (_u64, [_vp]),
+    "khx_peer_recv_ptr": (_vp, [_vp]),
+    "khx_peer_handle": (_int, [_vp, _vp]),
+    "khx_peer_open": (_int, [_vp, _u32, _vp]),
+    "khx_peer_set": (_int, [_vp, _u32, _vp]),
+    "khx_plan_dev": (_int, [_vp, _int, _u32, _u32, _vp, _u64, _vp]),
+    "khx_scatter_peers_dev": (_int, [_vp, _int, _u32, _vp, _u64, _vp, _vp, _vp]),
+    "khx_plan_scatter_dev": (_int, [_vp, _int, _u32, _u32, _vp, _u64, _vp, _vp, _vp]),
+    "khx_insert_recv_dev": (_i64, [_vp, _vp, _u64, _vp, _u32, _u32]),
     "kh_partition_fast_dev": (_int, [_int, _int, _u32, _int, _u32, _vp, _u64, _vp, _vp, _vp]),
     "kh_rank_host": (_int, [_int, _int, _u32, _int, _u32, _vp, _u64, _vp]),
     "kh_unpermute_dev": (_int, [_int, _int, _vp, _vp, _u64, _vp]),

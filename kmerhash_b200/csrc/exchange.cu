@@ -1,0 +1,292 @@
+// exchange.cu -- sender / receiver halves of the multi-GPU insert for one rank (one process per GPU).
+//
+// Replaces, for one rank of the reference's distributed map:
+//   assign_count_estimate_permute   KH/distributed_batched_robinhood_map.hpp:398-625
+//       rank id per key + per-rank counts + PER-DESTINATION HyperLogLog registers + permute
+//   insert_p (the receiving half)   :910-1179   merge of the estimates, reserve, local insert
+// The reference already ships the HLL registers with the counts so the receiver can presize its table
+// without a pass over the received keys (:1024-1060).  Here the sender's single metadata pass also
+// histograms every destination's keys by TABLE REGION (top bits of the spread store hash), so the
+// receiver's L2-windowed insert (table.cu) needs no pass of its own before its region sort either:
+//   sender   khx_plan_scatter_dev : meta pass (hash x2, 8 B/key read)  ->  rank scatter (16 B/key)
+//   (keys and the p x KHX_META_WORDS metadata travel by all-to-all)
+//   receiver khx_insert_recv_dev  : merge registers (max) + histograms (sum) -> estimate -> reserve ->
+//                                    region sort -> insert
+#include <algorithm>
+#include <cstring>
+#include <vector>
+#include "kh_common.h"
+#include "kh_table_host.h"
+#include "kh_hll.cuh"
+#include "kh_window.cuh"
+
+namespace kh {
+
+// metadata a sender produces per destination rank, as u64 words (so it travels as an int64 tensor):
+//   [0] key count   [1 .. 1+REGION_FINE) region histogram   [1+REGION_FINE .. +HLL_M) HLL registers
+constexpr int META_HIST = 1;
+constexpr int META_REGS = 1 + REGION_FINE;
+constexpr int META_WORDS = 1 + REGION_FINE + HLL_M;
+constexpr int PLAN_MAX_P = 8;    // shared-memory histogram: p x 1024 x u32 = 32 KB
+
+template <int W>
+__global__ void __launch_bounds__(512) plan_kernel(const uint64_t *keys, uint64_t n, BinSpec dist, int store_kind,
+                                                   HashParams store_hp, unsigned long long *meta) {
+  extern __shared__ uint32_t sh[];                  // [p][REGION_FINE]
+  const uint32_t p = dist.p;
+  for (uint32_t i = threadIdx.x; i < p * REGION_FINE; i += blockDim.x) sh[i] = 0;
+  __syncthreads();
+  const bool h32 = hash_bits(store_kind) == 32;
+  const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+  for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+    uint64_t k[W];
+    load_key<W>(keys, i, k);
+    const uint32_t r = bin_of<W>(dist, k);
+    const uint64_t h = hash_runtime<W>(store_kind, k, store_hp);
+    uint32_t idx, rank;
+    if (h32) {
+      const uint32_t x = (uint32_t)h;
+      idx = x >> (32 - HLL_P);
+      rank = __clz((int)((x << HLL_P) | 0xFFFu)) + 1;
+    } else {
+      idx = (uint32_t)(h >> (64 - HLL_P));
+      rank = __clzll((long long)((h << HLL_P) | 0xFFFULL)) + 1;
+    }
+    // registers live in global memory (p x 16 KB of u64 would not fit next to the histograms); the plain
+    // load may be stale, which only costs a redundant atomicMax
+    unsigned long long *reg = meta + (uint64_t)r * META_WORDS + META_REGS + idx;
+    if (*reg < rank) atomicMax(reg, (unsigned long long)rank);
+    atomicAdd(&sh[r * REGION_FINE + (uint32_t)(spread_hash(h) >> (64 - REGION_FINE_BITS))], 1u);
+  }
+  __syncthreads();
+  for (uint32_t i = threadIdx.x; i < p * REGION_FINE; i += blockDim.x)
+    if (sh[i]) atomicAdd(&meta[(uint64_t)(i / REGION_FINE) * META_WORDS + META_HIST + (i % REGION_FINE)], (unsigned long long)sh[i]);
+  // keys per destination = row sums of the histogram (one warp per row)
+  for (uint32_t r = threadIdx.x >> 5; r < p; r += blockDim.x >> 5) {
+    uint32_t c = 0;
+    for (uint32_t j = threadIdx.x & 31; j < (uint32_t)REGION_FINE; j += 32) c += sh[r * REGION_FINE + j];
+    c = warp_sum(c);
+    if ((threadIdx.x & 31) == 0 && c) atomicAdd(&meta[(uint64_t)r * META_WORDS], (unsigned long long)c);
+  }
+}
+
+// cursors[r] = keys of ranks < r, from the metadata counts
+__global__ void plan_cursor_kernel(const unsigned long long *meta, uint32_t p, unsigned long long *cursors) {
+  if (threadIdx.x == 0 && blockIdx.x == 0) {
+    unsigned long long acc = 0;
+    for (uint32_t r = 0; r < p; ++r) { cursors[r] = acc; acc += meta[(uint64_t)r * META_WORDS]; }
+  }
+}
+
+// receiver: fine[b] = sum over sources, regs[i] = max over sources, total = sum of counts
+__global__ void merge_meta_kernel(const unsigned long long *recv_meta, uint32_t p, unsigned long long *fine,
+                                  uint32_t *regs, unsigned long long *total) {
+  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < (uint32_t)REGION_FINE) {
+    unsigned long long s = 0;
+    for (uint32_t g = 0; g < p; ++g) s += recv_meta[(uint64_t)g * META_WORDS + META_HIST + i];
+    fine[i] = s;
+  }
+  if (i < (uint32_t)HLL_M) {
+    unsigned long long m = 0;
+    for (uint32_t g = 0; g < p; ++g) m = max(m, recv_meta[(uint64_t)g * META_WORDS + META_REGS + i]);
+    regs[i] = (uint32_t)m;
+  }
+  if (i == 0) {
+    unsigned long long s = 0;
+    for (uint32_t g = 0; g < p; ++g) s += recv_meta[(uint64_t)g * META_WORDS];
+    *total = s;
+  }
+}
+
+}  // namespace kh
+
+using namespace kh;
+
+extern "C" {
+
+int khx_meta_words(void) { return META_WORDS; }
+
+int khx_plan_scatter_dev(kh_table *t, int dist_hash, uint32_t dist_seed, uint32_t p, const uint64_t *d_keys, uint64_t n,
+                         uint64_t *d_meta, uint64_t *d_out_keys, uint64_t *counts) {
+  return (int)guarded([&]() -> int64_t {
+    if (!t || !d_meta || !counts || (n && (!d_keys || !d_out_keys))) { set_error("null argument"); return KH_ERR_INVALID; }
+    if (p == 0 || p > (uint32_t)PLAN_MAX_P || !hash_kind_supported(dist_hash)) {
+      set_error("khx_plan_scatter_dev: 1 <= p <= %d", PLAN_MAX_P); return KH_ERR_INVALID;
+    }
+    if (n >= (1ULL << 32)) { set_error("batch must be < 2^32 keys"); return KH_ERR_INVALID; }
+    DeviceGuard g(t->device);
+    cudaStream_t s = t->stream[0];
+    const int dk = fold_kind(dist_hash);
+    const BinSpec dist{1, 0, p, dk, make_hash_params(dk, dist_seed, t->W)};
+    unsigned long long *meta = reinterpret_cast<unsigned long long *>(d_meta);
+    KH_CUDA(cudaMemsetAsync(meta, 0, (size_t)p * META_WORDS * sizeof(unsigned long long), s));
+    for (uint32_t r = 0; r < p; ++r) counts[r] = 0;
+    if (n) {
+      const size_t smem = (size_t)p * REGION_FINE * sizeof(uint32_t);
+      const int grid = (int)std::max<uint64_t>(1, std::min<uint64_t>((n + 2047) / 2048, (uint64_t)t->sms * 4));
+      if (t->W == 1) KH_LAUNCH((plan_kernel<1>), grid, 512, smem, s, d_keys, n, dist, t->hash_kind, t->hp, meta);
+      else KH_LAUNCH((plan_kernel<2>), grid, 512, smem, s, d_keys, n, dist, t->hash_kind, t->hp, meta);
+      DevBuf<unsigned long long> cursors(p);
+      KH_LAUNCH(plan_cursor_kernel, 1, 32, 0, s, meta, p, cursors.p);
+      std::vector<unsigned long long> h(p);
+      KH_CUDA(cudaMemcpy2DAsync(h.data(), sizeof(unsigned long long), meta, META_WORDS * sizeof(unsigned long long),
+                                sizeof(unsigned long long), p, cudaMemcpyDeviceToHost, s));
+      if (t->W == 1) KH_LAUNCH((window_scatter_kernel<1, false>), t->sms * 4, WIN_BLOCK, 0, s, d_keys, n, dist, cursors.p, d_out_keys, nullptr);
+      else KH_LAUNCH((window_scatter_kernel<2, false>), t->sms * 4, WIN_BLOCK, 0, s, d_keys, n, dist, cursors.p, d_out_keys, nullptr);
+      KH_CUDA(cudaStreamSynchronize(s));
+      for (uint32_t r = 0; r < p; ++r) counts[r] = h[r];
+    } else {
+      KH_CUDA(cudaStreamSynchronize(s));
+    }
+    return KH_OK;
+  });
+}
+
+// ---- receive buffers shared between the processes of one box (CUDA IPC over NVLink) --------------
+struct khx_peer {
+  int device = 0, W = 1;
+  uint32_t rank = 0, p = 1;
+  uint64_t capacity = 0;                 // keys
+  uint64_t *local = nullptr;             // this rank's receive buffer (cudaMalloc: IPC cannot export pool memory)
+  uint64_t *remote[WIN_MAX_DST] = {nullptr};
+  bool opened[WIN_MAX_DST] = {false};    // mapped with cudaIpcOpenMemHandle (must be closed)
+};
+
+khx_peer *khx_peer_create(int device, uint32_t rank, uint32_t p, uint64_t capacity_keys, int key_words) {
+  khx_peer *x = nullptr;
+  int64_t rc = guarded([&]() -> int64_t {
+    if (p == 0 || p > (uint32_t)WIN_MAX_DST || rank >= p || key_words < 1 || key_words > 2) {
+      set_error("khx_peer_create: 1 <= p <= %d, rank < p", WIN_MAX_DST); return KH_ERR_INVALID;
+    }
+    DeviceGuard g(device);
+    x = new khx_peer();
+    x->device = device; x->W = key_words; x->rank = rank; x->p = p; x->capacity = std::max<uint64_t>(capacity_keys, 1);
+    KH_CUDA(cudaMalloc((void **)&x->local, x->capacity * 8 * key_words));
+    x->remote[rank] = x->local;
+    return KH_OK;
+  });
+  if (rc != KH_OK) { delete x; return nullptr; }
+  return x;
+}
+
+void khx_peer_destroy(khx_peer *x) {
+  if (!x) return;
+  int prev = -1; cudaGetDevice(&prev); cudaSetDevice(x->device);
+  for (uint32_t r = 0; r < x->p; ++r) if (x->opened[r]) cudaIpcCloseMemHandle(x->remote[r]);
+  if (x->local) cudaFree(x->local);
+  if (prev >= 0) cudaSetDevice(prev);
+  delete x;
+}
+
+uint64_t khx_peer_capacity(const khx_peer *x) { return x ? x->capacity : 0; }
+uint64_t *khx_peer_recv_ptr(khx_peer *x) { return x ? x->local : nullptr; }
+
+int khx_peer_handle(khx_peer *x, void *out64) {
+  return (int)guarded([&]() -> int64_t {
+    if (!x || !out64) { set_error("null argument"); return KH_ERR_INVALID; }
+    static_assert(sizeof(cudaIpcMemHandle_t) == 64, "IPC handle is 64 bytes");
+    DeviceGuard g(x->device);
+    cudaIpcMemHandle_t h;
+    KH_CUDA(cudaIpcGetMemHandle(&h, x->local));
+    memcpy(out64, &h, 64);
+    return KH_OK;
+  });
+}
+
+int khx_peer_open(khx_peer *x, uint32_t r, const void *handle64) {
+  return (int)guarded([&]() -> int64_t {
+    if (!x || !handle64 || r >= x->p || r == x->rank) { set_error("bad peer index"); return KH_ERR_INVALID; }
+    DeviceGuard g(x->device);
+    cudaIpcMemHandle_t h;
+    memcpy(&h, handle64, 64);
+    void *ptr = nullptr;
+    KH_CUDA(cudaIpcOpenMemHandle(&ptr, h, cudaIpcMemLazyEnablePeerAccess));
+    x->remote[r] = (uint64_t *)ptr; x->opened[r] = true;
+    return KH_OK;
+  });
+}
+
+// same-process peers (tests; one process driving several GPUs with peer access enabled): a plain device pointer
+int khx_peer_set(khx_peer *x, uint32_t r, uint64_t *d_ptr) {
+  if (!x || r >= x->p || !d_ptr) { set_error("bad peer index"); return KH_ERR_INVALID; }
+  x->remote[r] = d_ptr; x->opened[r] = false;
+  return KH_OK;
+}
+
+// metadata pass only (the first half of khx_plan_scatter_dev)
+int khx_plan_dev(kh_table *t, int dist_hash, uint32_t dist_seed, uint32_t p, const uint64_t *d_keys, uint64_t n,
+                 uint64_t *d_meta) {
+  return (int)guarded([&]() -> int64_t {
+    if (!t || !d_meta || (n && !d_keys)) { set_error("null argument"); return KH_ERR_INVALID; }
+    if (p == 0 || p > (uint32_t)PLAN_MAX_P || !hash_kind_supported(dist_hash)) {
+      set_error("khx_plan_dev: 1 <= p <= %d", PLAN_MAX_P); return KH_ERR_INVALID;
+    }
+    DeviceGuard g(t->device);
+    cudaStream_t s = t->stream[0];
+    const int dk = fold_kind(dist_hash);
+    const BinSpec dist{1, 0, p, dk, make_hash_params(dk, dist_seed, t->W)};
+    unsigned long long *meta = reinterpret_cast<unsigned long long *>(d_meta);
+    KH_CUDA(cudaMemsetAsync(meta, 0, (size_t)p * META_WORDS * sizeof(unsigned long long), s));
+    if (n) {
+      const size_t smem = (size_t)p * REGION_FINE * sizeof(uint32_t);
+      const int grid = (int)std::max<uint64_t>(1, std::min<uint64_t>((n + 2047) / 2048, (uint64_t)t->sms * 4));
+      if (t->W == 1) KH_LAUNCH((plan_kernel<1>), grid, 512, smem, s, d_keys, n, dist, t->hash_kind, t->hp, meta);
+      else KH_LAUNCH((plan_kernel<2>), grid, 512, smem, s, d_keys, n, dist, t->hash_kind, t->hp, meta);
+    }
+    KH_CUDA(cudaStreamSynchronize(s));
+    return KH_OK;
+  });
+}
+
+// Fused partition + exchange: the rank scatter stores every key DIRECTLY into the receive buffer of its owner
+// (peer memory over NVLink), at dst_offsets[r] keys from the start of rank r's buffer -- there is no send
+// buffer and no separate all-to-all.  The caller orders the ranks: every receive buffer must be free before
+// (a collective that follows the previous insert) and a barrier must follow before the owners read.
+int khx_scatter_peers_dev(kh_table *t, int dist_hash, uint32_t dist_seed, const uint64_t *d_keys, uint64_t n,
+                          khx_peer *x, const uint64_t *dst_offsets, const uint64_t *dst_counts) {
+  return (int)guarded([&]() -> int64_t {
+    if (!t || !x || !dst_offsets || !dst_counts || (n && !d_keys)) { set_error("null argument"); return KH_ERR_INVALID; }
+    if (!hash_kind_supported(dist_hash) || n >= (1ULL << 32) || x->W != t->W) { set_error("bad arguments"); return KH_ERR_INVALID; }
+    DeviceGuard g(t->device);
+    cudaStream_t s = t->stream[0];
+    const int dk = fold_kind(dist_hash);
+    const BinSpec dist{1, 0, x->p, dk, make_hash_params(dk, dist_seed, t->W)};
+    BinDst dst{};
+    for (uint32_t r = 0; r < x->p; ++r) {
+      if (!x->remote[r]) { set_error("peer %u not mapped", r); return KH_ERR_INVALID; }
+      if (dst_offsets[r] + dst_counts[r] > x->capacity) { set_error("receive buffer of rank %u too small", r); return KH_ERR_NOMEM; }
+      dst.base[r] = x->remote[r] + dst_offsets[r] * t->W;
+    }
+    if (n) {
+      DevBuf<unsigned long long> cursors(x->p);
+      KH_CUDA(cudaMemsetAsync(cursors.p, 0, x->p * sizeof(unsigned long long), s));
+      if (t->W == 1) KH_LAUNCH((window_scatter_kernel<1, false, true>), t->sms * 4, WIN_BLOCK, 0, s, d_keys, n, dist, cursors.p, nullptr, nullptr, dst);
+      else KH_LAUNCH((window_scatter_kernel<2, false, true>), t->sms * 4, WIN_BLOCK, 0, s, d_keys, n, dist, cursors.p, nullptr, nullptr, dst);
+    }
+    KH_CUDA(cudaStreamSynchronize(s));
+    return KH_OK;
+  });
+}
+
+int64_t khx_insert_recv_dev(kh_table *t, const uint64_t *d_keys, uint64_t n, const uint64_t *d_recv_meta, uint32_t p,
+                            uint32_t default_val) {
+  return guarded([&]() -> int64_t {
+    if (!t || !d_recv_meta || (n && !d_keys) || p == 0) { set_error("null argument"); return KH_ERR_INVALID; }
+    DeviceGuard g(t->device);
+    if (n == 0) return 0;
+    cudaStream_t s = t->stream[0];
+    DevBuf<unsigned long long> fine(REGION_FINE), total(1);
+    DevBuf<uint32_t> regs(HLL_M);
+    KH_LAUNCH(merge_meta_kernel, (HLL_M + 255) / 256, 256, 0, s, reinterpret_cast<const unsigned long long *>(d_recv_meta), p,
+              fine.p, regs.p, total.p);
+    unsigned long long h_total = 0;
+    KH_CUDA(cudaMemcpyAsync(&h_total, total.p, sizeof(h_total), cudaMemcpyDeviceToHost, s));
+    const double est = hll_finish(t->hash_kind, regs.p, nullptr, s);   // synchronises s
+    if (h_total != n) { set_error("received %llu keys but the metadata announces %llu", (unsigned long long)n, h_total); return KH_ERR_INVALID; }
+    PreEstimate pre{est, fine.p};
+    return insert_dev_impl(t, d_keys, nullptr, n, default_val, 1, &pre);
+  });
+}
+
+}  // extern "C"

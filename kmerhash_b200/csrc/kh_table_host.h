@@ -1,0 +1,59 @@
+// kh_table_host.h -- the table object and the internal entry points shared by table.cu and exchange.cu
+#pragma once
+#include <algorithm>
+#include <utility>
+#include <vector>
+#include "kh_common.h"
+#include "kh_table.cuh"
+
+using namespace kh;   // internal header: only table.cu and exchange.cu include it
+
+struct kh_table {
+  int device = 0, map_kind = 0, W = 1, hash_kind = 0, reducer = 0;
+  uint32_t seed = KH_DEFAULT_SEED;
+  double min_load = 0.2, max_load = 0.8;
+  int LB = 32, G = 2;                 // probe geometry (DESIGN.md "bucket geometry")
+  bool window_on = true;              // L2-windowed bulk insert (KH_WINDOW=0 switches it off for A/B runs)
+  uint64_t window_bytes = 32ULL << 20, window_min_keys = 1ULL << 22;
+  uint64_t capacity = 0, size = 0;
+  HashParams hp;
+  DevBuf<unsigned char> slots;
+  DevBuf<uint32_t> side;              // 3 words
+  DevBuf<unsigned long long> counters;  // [0] n_new / n_hit, [1] export counter
+  DevBuf<int> status;
+  unsigned long long *h_counters = nullptr;  // pinned mirror
+  int *h_status = nullptr;
+  cudaStream_t stream[2] = {nullptr, nullptr};
+  cudaEvent_t ev[2] = {nullptr, nullptr};
+  // staging for *_host calls (grown on demand)
+  DevBuf<uint64_t> d_keys[2];
+  DevBuf<uint32_t> d_vals[2];
+  DevBuf<uint8_t> d_u8[2];
+  int sms = 148;
+  // CUDA-event pairs around every probe-kernel launch (bench.py's roofline: measured on the launching stream)
+  std::vector<std::pair<cudaEvent_t, cudaEvent_t>> kev;
+  size_t kev_used = 0;
+  double kev_ms[2] = {0.0, 0.0};        // accumulated [insert kernels, lookup kernels]
+  uint64_t kev_n[2] = {0, 0};
+  std::vector<int> kev_kind;
+  bool kev_on = false;
+
+  int slot_bytes() const { return 16 * W; }
+  int bucket_slots() const { return G * (LB / slot_bytes()); }
+  TableView view() { return TableView{slots.p, capacity, side.p}; }
+  int grid_for(uint64_t n_items, int per_block) const {
+    uint64_t need = (n_items + per_block - 1) / per_block;
+    uint64_t cap = (uint64_t)sms * 8;
+    return (int)std::max<uint64_t>(1, std::min(need, cap));
+  }
+};
+
+
+namespace kh {
+// estimate + fine region histogram (REGION_FINE bins, device) of a batch, when the caller's pipeline already
+// produced them (host pipeline: accumulated behind the PCIe copy; exchange: computed by the senders)
+struct PreEstimate { double est; const unsigned long long *fine; };
+// batch insert of device-resident keys (see table.cu); returns #new keys or a negative status
+int64_t insert_dev_impl(kh_table *t, const uint64_t *d_keys, const uint32_t *d_vals, uint64_t n, uint32_t dflt,
+                        int estimate, const PreEstimate *pre = nullptr);
+}  // namespace kh

@@ -80,11 +80,17 @@ static __global__ void __launch_bounds__(REGION_FINE) bin_cursor_kernel(const un
   if ((int)threadIdx.x < n_bins) { cursors[threadIdx.x] = start; if (totals) totals[threadIdx.x] = c; }
 }
 
+// per-bin destination base pointers (possibly buffers of PEER GPUs mapped over NVLink): bin r's keys go to
+// base[r][cursor ...], cursors counting from zero inside every bin
+constexpr int WIN_MAX_DST = 8;
+struct BinDst { uint64_t *base[WIN_MAX_DST]; };
+
 // PERM: out_perm receives the original index of every output position (32-bit: n < 2^32)
-template <int W, bool PERM>
+// MULTI: write bin r through dst.base[r] instead of `out` (the fused partition + exchange of exchange.cu)
+template <int W, bool PERM, bool MULTI = false>
 __global__ void __launch_bounds__(WIN_BLOCK, 4) window_scatter_kernel(const uint64_t *keys, uint64_t n, BinSpec spec,
                                                                       unsigned long long *cursors, uint64_t *out,
-                                                                      uint32_t *out_perm) {
+                                                                      uint32_t *out_perm, BinDst dst = BinDst{}) {
   constexpr int TILE = WIN_TILE_BYTES / (8 * W);      // keys per tile
   constexpr int KPT = TILE / WIN_BLOCK;               // keys per thread
   constexpr int RPT = WIN_MAX_P / WIN_BLOCK;          // regions per thread in the scan
@@ -151,7 +157,7 @@ __global__ void __launch_bounds__(WIN_BLOCK, 4) window_scatter_kernel(const uint
     for (int e = threadIdx.x; e < tile_n; e += WIN_BLOCK) {
       const uint32_t r = sreg[e];
       const unsigned long long gpos = gbase[r] + (uint32_t)(e - lo[r]);
-      uint64_t *o = out + gpos * W;
+      uint64_t *o = (MULTI ? dst.base[r] : out) + gpos * W;
 #pragma unroll
       for (int q = 0; q < W; ++q) o[q] = skeys[e * W + q];
       if (PERM) out_perm[gpos] = (uint32_t)(base + ssrc[e]);

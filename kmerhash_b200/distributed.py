@@ -43,6 +43,47 @@ class _Stage:
                 sys.stderr.write("[kh-trace] dist.%-14s %8.3f ms\n" % (self.name, 1e3 * (time.perf_counter() - self.t0)))
 
 
+class PeerBuffers:
+    """this rank's receive buffer + the other ranks' buffers mapped through CUDA IPC (csrc/exchange.cu: khx_peer_*).
+    Collective: every rank of the group constructs it at the same time."""
+
+    def __init__(self, device, rank, p, capacity, key_words, group):
+        import ctypes as C
+        from ._lib import lib, check
+        self.lib, self.p, self.rank = lib, p, rank
+        self.h = lib.khx_peer_create(device, rank, p, int(capacity), key_words)
+        ok = 1 if self.h else 0
+        dev = torch.device("cuda", device)
+        handle = (C.c_ubyte * 64)()
+        if ok and lib.khx_peer_handle(self.h, handle) != 0:
+            ok = 0
+        mine = torch.tensor(list(handle), dtype=torch.uint8, device=dev)
+        allh = torch.empty((p, 64), dtype=torch.uint8, device=dev)
+        dist.all_gather_into_tensor(allh, mine, group=group)
+        allh = allh.cpu().numpy()
+        if ok:
+            for r in range(p):
+                if r != rank:
+                    buf = (C.c_ubyte * 64)(*allh[r].tolist())
+                    if lib.khx_peer_open(self.h, r, buf) != 0:
+                        ok = 0
+                        break
+        flag = torch.tensor([ok], dtype=torch.int32, device=dev)
+        dist.all_reduce(flag, op=dist.ReduceOp.MIN, group=group)
+        self.ok = bool(flag.item())
+        self.capacity = lib.khx_peer_capacity(self.h) if self.h else 0
+
+    def recv_ptr(self):
+        return self.lib.khx_peer_recv_ptr(self.h)
+
+    def close(self):
+        h, self.h = getattr(self, "h", None), None
+        if h:
+            self.lib.khx_peer_destroy(h)
+
+    __del__ = close
+
+
 class CudaEngine:
     """partition / canonicalise / table ops on this rank's GPU through the C ABI"""
 
@@ -82,6 +123,25 @@ class CudaEngine:
     def insert(self, keys, default):
         return self.table.insert(keys, default=default) if keys.shape[0] else 0
 
+    # sender / receiver halves with metadata (COUNT tables, p <= 8): see csrc/exchange.cu
+    def can_plan(self, p):
+        return self.table.reducer == "COUNT" and p <= 8
+
+    def plan_scatter(self, keys, p):
+        return self.table.plan_scatter(keys, p, self.dist_hash)
+
+    def insert_recv(self, keys, recv_meta, default):
+        return self.table.insert_recv(keys, recv_meta, default) if keys.shape[0] else 0
+
+    def plan(self, keys, p):
+        return self.table.plan(keys, p, self.dist_hash)
+
+    def scatter_peers(self, keys, peers, dst_off, dst_cnt):
+        self.table.scatter_peers(keys, peers.h, dst_off, dst_cnt, self.dist_hash)
+
+    def insert_recv_ptr(self, ptr, n, recv_meta, default):
+        return self.table.insert_recv_ptr(ptr, n, recv_meta, default) if n else 0
+
     def count(self, keys):
         return self.table.count(keys) if keys.shape[0] else self.empty_like_result(0, torch.uint8)
 
@@ -112,6 +172,9 @@ class DistributedMap:
         self.W = key_words
         self.chunks = max(1, int(chunks))
         self.last_exchange_bytes = 0      # bytes this rank sent to other ranks in the last call
+        # fused partition + exchange over peer memory (NVLink): on when every rank could map every buffer
+        self.peer_stores = os.environ.get("KH_PEER_STORES", "1") not in ("0", "")
+        self.peers = None
 
     # ---- the exchange ---------------------------------------------------------------------------
     def _counts_a2a(self, counts):
@@ -153,6 +216,8 @@ class DistributedMap:
         keys = self.e.as_keys(keys)
         self.last_exchange_bytes = 0
         n = keys.shape[0]
+        if self.p > 1 and self.chunks == 1 and getattr(self.e, "can_plan", lambda p: False)(self.p):
+            return self._insert_planned(keys, default)
         n_chunks = self.chunks if self.p > 1 else 1
         bounds = [n * i // n_chunks for i in range(n_chunks + 1)]
         added, pending = 0, None
@@ -166,6 +231,55 @@ class DistributedMap:
         with _Stage("local insert"):
             added += self.e.insert(pending, default)
         return added
+
+    def _insert_planned(self, keys, default):
+        """assign_count_estimate_permute shape: the sender's metadata pass yields, per destination, the key count,
+        the HLL registers and the table-region histogram; they travel with the keys, so the receiver presizes and
+        region-sorts without a pass of its own over the received keys."""
+        keys = self.e.canonicalize(keys)
+        if self.peer_stores and hasattr(self.e, "scatter_peers"):
+            return self._insert_peer_stores(keys, default)
+        with _Stage("plan+scatter"):
+            permuted, meta, send_counts = self.e.plan_scatter(keys, self.p)
+        with _Stage("meta a2a"):
+            recv_meta = torch.empty_like(meta)
+            dist.all_to_all_single(recv_meta, meta, group=self.group)
+            recv_counts = [int(c) for c in recv_meta[:, 0].tolist()]
+        recv = self.e.empty_keys(sum(recv_counts))
+        self.last_exchange_bytes += 8 * self.W * (sum(send_counts) - send_counts[self.rank]) + 8 * meta.shape[1] * (self.p - 1)
+        with _Stage("keys a2a"):
+            dist.all_to_all_single(recv, permuted, output_split_sizes=recv_counts, input_split_sizes=send_counts, group=self.group)
+        with _Stage("local insert"):
+            return self.e.insert_recv(recv, recv_meta, default)
+
+    def _insert_peer_stores(self, keys, default):
+        """partition and exchange as ONE kernel: the rank scatter stores every key straight into the receive buffer
+        of its owner GPU through CUDA-IPC mapped peer memory (NVLink); NCCL only carries the p x p metadata."""
+        p, rank, dev = self.p, self.rank, self.e.device
+        with _Stage("plan"):
+            meta = self.e.plan(keys, p)
+        with _Stage("meta gather"):
+            allmeta = torch.empty((p,) + tuple(meta.shape), dtype=meta.dtype, device=dev)
+            dist.all_gather_into_tensor(allmeta, meta, group=self.group)   # also orders ranks: previous reads are done
+            C = allmeta[:, :, 0].cpu().numpy().astype(np.uint64)           # C[g][r] = keys g sends to r
+        need = int(C.sum(axis=0).max())
+        if self.peers is None or self.peers.capacity < need:               # same decision on every rank
+            if self.peers is not None:
+                self.peers.close()
+            self.peers = PeerBuffers(dev.index, rank, p, int(need * 1.25) + 1024, self.W, self.group)
+            if not self.peers.ok:                                          # no IPC / no peer access: NCCL path
+                self.peer_stores = False
+                self.peers.close(); self.peers = None
+                return self._insert_planned(keys, default)
+        dst_off = C[:rank, :].sum(axis=0)
+        dst_cnt = C[rank, :]
+        self.last_exchange_bytes += 8 * self.W * int(dst_cnt.sum() - dst_cnt[rank])
+        with _Stage("scatter->peers"):
+            self.e.scatter_peers(keys, self.peers, dst_off, dst_cnt)
+            dist.barrier(group=self.group)                                 # every rank's stores have landed
+        recv_meta = allmeta[:, rank, :].contiguous()
+        with _Stage("local insert"):
+            return self.e.insert_recv_ptr(self.peers.recv_ptr(), int(C[:, rank].sum()), recv_meta, default)
 
     def count(self, keys):
         keys = self.e.as_keys(keys)

@@ -156,6 +156,46 @@ class HashMap:
             vp = vals.ctypes.data
         return check(lib.kh_insert_host(self._h, k.ctypes.data, vp, n, default, int(estimate)), "insert")
 
+    # ---- one rank of a multi-process distributed insert (include/kmerhash_b200.h: khx_*) ----
+    def plan_scatter(self, keys, p, dist_hash="MURMUR64avx", dist_seed=9876543):
+        """sender half: (keys permuted so that every destination's keys are contiguous, metadata tensor
+        [p, khx_meta_words] int64 on the device, counts[p] python list).  CUDA tensors only."""
+        k, n = _dev_keys(keys, self.W, self.device)
+        out = torch.empty_like(k)
+        meta = torch.empty((p, lib.khx_meta_words()), dtype=torch.int64, device=k.device)
+        counts = np.zeros(p, dtype=np.uint64)
+        check(lib.khx_plan_scatter_dev(self._h, HASH_KINDS[dist_hash], dist_seed, p, k.data_ptr(), n, meta.data_ptr(),
+                                       out.data_ptr(), counts.ctypes.data), "plan_scatter")
+        return out, meta, [int(c) for c in counts]
+
+    def plan(self, keys, p, dist_hash="MURMUR64avx", dist_seed=9876543):
+        """metadata pass alone: [p, khx_meta_words] int64 device tensor (count, region histogram, HLL registers per destination)"""
+        k, n = _dev_keys(keys, self.W, self.device)
+        meta = torch.empty((p, lib.khx_meta_words()), dtype=torch.int64, device=k.device)
+        check(lib.khx_plan_dev(self._h, HASH_KINDS[dist_hash], dist_seed, p, k.data_ptr(), n, meta.data_ptr()), "plan")
+        return meta
+
+    def scatter_peers(self, keys, peer_handle, dst_offsets, dst_counts, dist_hash="MURMUR64avx", dist_seed=9876543):
+        """fused partition + exchange: store every key into its owner's receive buffer (peer memory)"""
+        k, n = _dev_keys(keys, self.W, self.device)
+        off = np.ascontiguousarray(dst_offsets, dtype=np.uint64)
+        cnt = np.ascontiguousarray(dst_counts, dtype=np.uint64)
+        check(lib.khx_scatter_peers_dev(self._h, HASH_KINDS[dist_hash], dist_seed, k.data_ptr(), n, peer_handle,
+                                        off.ctypes.data, cnt.ctypes.data), "scatter_peers")
+
+    def insert_recv_ptr(self, ptr, n, recv_meta, default=1):
+        """receiver half on a raw device pointer (the peer receive buffer)"""
+        assert recv_meta.is_cuda and recv_meta.dtype == torch.int64 and recv_meta.is_contiguous()
+        torch.cuda.current_stream(self.device).synchronize()
+        return check(lib.khx_insert_recv_dev(self._h, ptr, n, recv_meta.data_ptr(), recv_meta.shape[0], default), "insert_recv")
+
+    def insert_recv(self, keys, recv_meta, default=1):
+        """receiver half: insert the received keys, presized and region-sorted from the senders' metadata"""
+        k, n = _dev_keys(keys, self.W, self.device)
+        assert recv_meta.is_cuda and recv_meta.dtype == torch.int64 and recv_meta.is_contiguous()
+        return check(lib.khx_insert_recv_dev(self._h, k.data_ptr(), n, recv_meta.data_ptr(), recv_meta.shape[0], default),
+                     "insert_recv")
+
     def insert_no_estimate(self, keys, vals=None, default=1):
         return self.insert(keys, vals, default, estimate=False)
 

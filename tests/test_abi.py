@@ -17,7 +17,7 @@ HEADER = os.path.join(ROOT, "include", "kmerhash_b200.h")
 def declared_functions():
     src = open(HEADER).read()
     src = re.sub(r"/\*.*?\*/", "", src, flags=re.S)
-    return sorted(set(re.findall(r"\b(khd?_[a-z0-9_]+)\s*\(", src)))
+    return sorted(set(re.findall(r"\b(kh[dx]?_[a-z0-9_]+)\s*\(", src)))
 
 
 def test_header_symbols_exported(kh):
