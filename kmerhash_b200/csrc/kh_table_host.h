@@ -15,6 +15,7 @@ struct kh_table {
   int LB = 32, G = 2;                 // probe geometry (DESIGN.md "bucket geometry")
   bool window_on = true;              // L2-windowed bulk insert (KH_WINDOW=0 switches it off for A/B runs)
   uint64_t window_bytes = 32ULL << 20, window_min_keys = 1ULL << 22;
+  bool has_sticky = false;            // an erase may have left sticky bits since the last rebuild / clear (kh_tile.cuh needs none)
   uint64_t capacity = 0, size = 0;
   HashParams hp;
   DevBuf<unsigned char> slots;
@@ -33,8 +34,8 @@ struct kh_table {
   // CUDA-event pairs around every probe-kernel launch (bench.py's roofline: measured on the launching stream)
   std::vector<std::pair<cudaEvent_t, cudaEvent_t>> kev;
   size_t kev_used = 0;
-  double kev_ms[2] = {0.0, 0.0};        // accumulated [insert kernels, lookup kernels]
-  uint64_t kev_n[2] = {0, 0};
+  double kev_ms[4] = {0.0, 0.0, 0.0, 0.0};   // accumulated [insert kernels, lookup kernels, region scatter, HLL + histogram]
+  uint64_t kev_n[4] = {0, 0, 0, 0};
   std::vector<int> kev_kind;
   bool kev_on = false;
 

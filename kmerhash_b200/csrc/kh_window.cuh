@@ -39,7 +39,7 @@ constexpr int WIN_MAX_P = REGION_FINE;         // 1024
 
 // cursors[r] = number of keys in regions < r  (P = 2^lp regions, P <= 1024)
 static __global__ void __launch_bounds__(REGION_FINE) window_cursor_kernel(const unsigned long long *fine, int lp,
-                                                                    unsigned long long *cursors) {
+                                                                    unsigned long long *cursors, int cstride = 1) {
   using Scan = cub::BlockScan<unsigned long long, REGION_FINE>;
   __shared__ typename Scan::TempStorage tmp;
   const int P = 1 << lp, per = REGION_FINE >> lp;
@@ -48,7 +48,7 @@ static __global__ void __launch_bounds__(REGION_FINE) window_cursor_kernel(const
     for (int j = 0; j < per; ++j) c += fine[threadIdx.x * per + j];
   unsigned long long start;
   Scan(tmp).ExclusiveSum(c, start);
-  if ((int)threadIdx.x < P) cursors[threadIdx.x] = start;
+  if ((int)threadIdx.x < P) cursors[threadIdx.x * cstride] = start;
 }
 
 // keys per bin (n_bins <= 1024): shared-memory histogram per block, one global atomic per non-empty bin
@@ -87,10 +87,16 @@ struct BinDst { uint64_t *base[WIN_MAX_DST]; };
 
 // PERM: out_perm receives the original index of every output position (32-bit: n < 2^32)
 // MULTI: write bin r through dst.base[r] instead of `out` (the fused partition + exchange of exchange.cu)
-template <int W, bool PERM, bool MULTI = false>
+// TAGS (mode 0 only): out_tags receives, next to every sorted key, (spread hash >> tag_shift) & tag_mask = the key's
+// home bucket index inside its region (kh_tile.cuh stages table tiles in shared memory and needs no hash of its own)
+// cstride: distance (in elements) between two regions' cursors.  With ~1000 regions every tile reserves ~900 ranges;
+// cursors packed 16 to a 128-byte line serialise those atomics in a few L2 slices, one line per cursor does not.
+struct TagSpec { uint16_t *out; int shift; uint32_t mask; int cstride; };
+template <int W, bool PERM, bool MULTI = false, bool TAGS = false>
 __global__ void __launch_bounds__(WIN_BLOCK, 4) window_scatter_kernel(const uint64_t *keys, uint64_t n, BinSpec spec,
                                                                       unsigned long long *cursors, uint64_t *out,
-                                                                      uint32_t *out_perm, BinDst dst = BinDst{}) {
+                                                                      uint32_t *out_perm, BinDst dst = BinDst{},
+                                                                      TagSpec tags = TagSpec{nullptr, 0, 0u, 1}) {
   constexpr int TILE = WIN_TILE_BYTES / (8 * W);      // keys per tile
   constexpr int KPT = TILE / WIN_BLOCK;               // keys per thread
   constexpr int RPT = WIN_MAX_P / WIN_BLOCK;          // regions per thread in the scan
@@ -99,6 +105,7 @@ __global__ void __launch_bounds__(WIN_BLOCK, 4) window_scatter_kernel(const uint
   __shared__ uint64_t skeys[TILE * W];
   __shared__ uint16_t sreg[TILE];
   __shared__ uint16_t ssrc[PERM ? TILE : 1];          // position of the key inside the tile before sorting
+  __shared__ uint16_t stag[TAGS ? TILE : 1];
   __shared__ uint32_t cnt[WIN_MAX_P];                 // keys of the tile per region
   __shared__ uint32_t lo[WIN_MAX_P];                  // start of the region's run inside the sorted tile
   __shared__ unsigned long long gbase[WIN_MAX_P];     // start of the region's run in `out`
@@ -112,13 +119,19 @@ __global__ void __launch_bounds__(WIN_BLOCK, 4) window_scatter_kernel(const uint
     __syncthreads();
 
     uint64_t k[KPT][W];
-    uint32_t reg[KPT], loc[KPT];
+    uint32_t reg[KPT], loc[KPT], tg[TAGS ? KPT : 1];
 #pragma unroll
     for (int j = 0; j < KPT; ++j) {
       const int e = j * WIN_BLOCK + threadIdx.x;
       if (e < tile_n) {
         load_key<W>(keys, base + e, k[j]);
-        reg[j] = bin_of<W>(spec, k[j]);
+        if constexpr (TAGS) {
+          const uint64_t hm = spread_hash(hash_runtime<W>(spec.hash_kind, k[j], spec.hp));
+          reg[j] = (uint32_t)top_bits(hm, 64 - spec.lp);
+          tg[j] = (uint32_t)(hm >> tags.shift) & tags.mask;
+        } else {
+          reg[j] = bin_of<W>(spec, k[j]);
+        }
         loc[j] = atomicAdd(&cnt[reg[j]], 1u);
       }
     }
@@ -134,7 +147,7 @@ __global__ void __launch_bounds__(WIN_BLOCK, 4) window_scatter_kernel(const uint
       const int r = threadIdx.x * RPT + q;
       if (r < P) {
         lo[r] = st[q];
-        if (c[q]) gbase[r] = atomicAdd(&cursors[r], (unsigned long long)c[q]);
+        if (c[q]) gbase[r] = atomicAdd(&cursors[TAGS ? r * tags.cstride : r], (unsigned long long)c[q]);
       }
     }
     __syncthreads();
@@ -149,6 +162,7 @@ __global__ void __launch_bounds__(WIN_BLOCK, 4) window_scatter_kernel(const uint
         for (int q = 0; q < W; ++q) skeys[pos * W + q] = k[j][q];
         sreg[pos] = (uint16_t)reg[j];
         if (PERM) ssrc[pos] = (uint16_t)e;
+        if constexpr (TAGS) stag[pos] = (uint16_t)tg[j];
       }
     }
     __syncthreads();
@@ -161,6 +175,7 @@ __global__ void __launch_bounds__(WIN_BLOCK, 4) window_scatter_kernel(const uint
 #pragma unroll
       for (int q = 0; q < W; ++q) o[q] = skeys[e * W + q];
       if (PERM) out_perm[gpos] = (uint32_t)(base + ssrc[e]);
+      if constexpr (TAGS) tags.out[gpos] = stag[e];
     }
     __syncthreads();
   }

@@ -21,6 +21,7 @@
 #include "kh_hll.cuh"
 #include "kh_partition.h"
 #include "kh_window.cuh"
+#include "kh_tile.cuh"
 #include "kh_table_host.h"
 
 namespace kh {
@@ -336,6 +337,7 @@ void rebuild(kh_table *t, uint64_t new_cap) {
   cudaStream_t s = t->stream[0];
   Trace tr_all("rebuild", s);
   new_cap = std::max<uint64_t>(next_pow2(new_cap), 128);
+  t->has_sticky = false;               // every path below ends with freshly initialised slots
   if (t->capacity == 0 || t->size == 0) {
     t->slots.release();
     alloc_slots(t, new_cap, t->slots, s);
@@ -440,8 +442,73 @@ uint64_t insert_resident(kh_table *t, const uint64_t *d_keys, const uint32_t *d_
 // and the probe kernel then walks the sorted batch: at any moment all resident warps work on one or two
 // regions.  Costs one extra streaming pass (16 B/key), saves the DRAM-latency-bound random traffic.
 // `d_fine`: the fine region histogram of this batch if the HLL pass already produced it, else nullptr.
+// Shared-memory tile insert (kh_tile.cuh): eligible for COUNT batches with a uniform addend into an 8-byte-key
+// table of 64-byte buckets without sticky bits, when the batch is large against the table (the whole table is
+// streamed through shared memory once) and a coarse region spans at most 8 tiles.
+bool tile_candidate(const kh_table *t, const uint32_t *d_vals, uint64_t n, int &lp, int &subs_log2) {
+  static const bool on = !(getenv("KH_TILE") && atoi(getenv("KH_TILE")) == 0);
+  if (!on || !window_candidate(t, d_vals, n)) return false;
+  if (t->W != 1 || t->LB * t->G != 64 || t->has_sticky || t->capacity < (uint64_t)TI_SLOTS) return false;
+  if (n * 4 < t->capacity) return false;
+  const int lbk = log2_u64(t->capacity / 4);               // bits of a bucket index
+  lp = std::min(REGION_FINE_BITS, lbk - TI_BUCKET_BITS);
+  subs_log2 = lbk - TI_BUCKET_BITS - lp;
+  return subs_log2 <= 3;
+}
+
+uint64_t insert_tiled(kh_table *t, const uint64_t *d_keys, uint64_t n, uint32_t dflt, const unsigned long long *d_fine,
+                      int lp, int subs_log2, cudaStream_t s) {
+  static std::once_flag once;
+  std::call_once(once, [] { cudaFuncSetAttribute(tile_insert_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TI_SMEM); });
+  constexpr int CSTRIDE = 16;          // one 128-byte line per cursor
+  DevBuf<unsigned long long> fine_own, cursors((size_t)CSTRIDE << lp);
+  if (!d_fine) {
+    fine_own.alloc(REGION_FINE);
+    kev_begin(t, 3, s);
+    hll_estimate_dev(t->hash_kind, t->hp, t->W, d_keys, n, nullptr, s, t->sms, fine_own.p);
+    kev_end(t, s);
+    d_fine = fine_own.p;
+  }
+  KH_LAUNCH(window_cursor_kernel, 1, REGION_FINE, 0, s, d_fine, lp, cursors.p, CSTRIDE);
+  DevBuf<uint64_t> sorted(n);
+  DevBuf<uint16_t> tags(((n + TI_CHUNK - 1) / TI_CHUNK + 1) * TI_CHUNK);
+  const int lbk = log2_u64(t->capacity / 4);
+  { Trace tr("tile.scatter", s);
+    const BinSpec spec{0, lp, 0u, t->hash_kind, t->hp};
+    const TagSpec ts{tags.p, 64 - lbk, (1u << (lbk - lp)) - 1u, CSTRIDE};
+    kev_begin(t, 2, s);
+    KH_LAUNCH((window_scatter_kernel<1, false, false, true>), t->sms * 4, WIN_BLOCK, 0, s, d_keys, n, spec, cursors.p, sorted.p,
+              nullptr, BinDst{}, ts);
+    kev_end(t, s); }
+  DevBuf<uint32_t> defer(n);
+  uint64_t added = 0, n_def = 0;
+  { Trace tr("tile.insert", s);
+    zero_counter(t, s);
+    TileArgs a;
+    a.t = t->view(); a.keys = sorted.p; a.tags = tags.p; a.bin_end = cursors.p; a.bin_stride = CSTRIDE; a.subs_log2 = subs_log2;
+    a.fresh = t->size == 0 ? 1 : 0; a.dflt = dflt; a.n_new = t->counters.p; a.defer_idx = defer.p;
+    const uint64_t n_tiles = t->capacity / TI_SLOTS;
+    const int grid = (int)std::min<uint64_t>(n_tiles, (uint64_t)t->sms * 2);
+    kev_begin(t, 0, s);
+    KH_LAUNCH(tile_insert_kernel, grid, TI_THREADS, TI_SMEM, s, a);
+    kev_end(t, s);
+    added = read_counter(t, s);
+    n_def = t->h_counters[1];
+    t->size += added; }
+  if (n_def) {       // chains that leave their tile, the all-ones key: a handful of keys through the global kernel
+    Trace tr("tile.deferred", s);
+    DevBuf<uint64_t> nk(n_def);
+    KH_LAUNCH((gather_deferred_kernel<1>), t->grid_for(n_def, 256), 256, 0, s, sorted.p, (const uint32_t *)nullptr, defer.p, n_def,
+              nk.p, (uint32_t *)nullptr);
+    added += insert_resident(t, nk.p, nullptr, n_def, dflt, s);
+  }
+  return added;
+}
+
 uint64_t insert_windowed(kh_table *t, const uint64_t *d_keys, const uint32_t *d_vals, uint64_t n, uint32_t dflt,
                          const unsigned long long *d_fine, cudaStream_t s) {
+  int tile_lp = 0, tile_subs = 0;
+  if (tile_candidate(t, d_vals, n, tile_lp, tile_subs)) return insert_tiled(t, d_keys, n, dflt, d_fine, tile_lp, tile_subs, s);
   const uint64_t table_bytes = t->capacity * (uint64_t)t->slot_bytes();
   const bool windowed = window_candidate(t, d_vals, n) && table_bytes >= 4 * t->window_bytes;
   if (!windowed) return insert_resident(t, d_keys, d_vals, n, dflt, s);
@@ -534,11 +601,11 @@ void *kh_stream(kh_table *t) { return t ? (void *)t->stream[0] : nullptr; }
 int kh_kernel_timing(kh_table *t, int enable) {
   if (!t) return KH_ERR_INVALID;
   t->kev_on = enable != 0; t->kev_used = 0;
-  t->kev_ms[0] = t->kev_ms[1] = 0.0; t->kev_n[0] = t->kev_n[1] = 0;
+  for (int i = 0; i < 4; ++i) { t->kev_ms[i] = 0.0; t->kev_n[i] = 0; }
   return KH_OK;
 }
 int kh_kernel_time(kh_table *t, int which, double *sum_ms, uint64_t *launches) {
-  if (!t || which < 0 || which > 1) return KH_ERR_INVALID;
+  if (!t || which < 0 || which > 3) return KH_ERR_INVALID;
   int prev = -1; cudaGetDevice(&prev); cudaSetDevice(t->device);
   kev_resolve(t);
   if (prev >= 0) cudaSetDevice(prev);
@@ -600,6 +667,7 @@ int kh_clear(kh_table *t) {
     KH_CUDA(cudaMemsetAsync(t->side.p, 0, 4 * sizeof(uint32_t), s));
     KH_CUDA(cudaStreamSynchronize(s));
     t->size = 0;
+    t->has_sticky = false;
     return KH_OK;
   });
 }
@@ -647,7 +715,10 @@ int64_t kh::insert_dev_impl(kh_table *t, const uint64_t *d_keys, const uint32_t 
     if (pre) return pre->est;
     Trace tr("hll+hist", s);
     if (window_candidate(t, d_vals, n)) { fine.alloc(REGION_FINE); have_fine = true; }
-    return hll_estimate_dev(t->hash_kind, t->hp, t->W, d_keys, n, nullptr, s, t->sms, have_fine ? fine.p : nullptr);
+    kev_begin(t, 3, s);
+    const double e = hll_estimate_dev(t->hash_kind, t->hp, t->W, d_keys, n, nullptr, s, t->sms, have_fine ? fine.p : nullptr);
+    kev_end(t, s);
+    return e;
   };
   // Can the whole batch go in as ONE piece?  Yes when even its distinct keys (an HLL bound) keep the load legal.
   // (COUNT tolerates a wrong bound: keys that find no slot are deferred and re-inserted after growing.)
@@ -948,6 +1019,7 @@ int64_t kh_erase_dev(kh_table *t, const uint64_t *d_keys, uint64_t n) {
       launch_lookup(t, OP_ERASE, d_keys, n, nullptr, nullptr, nullptr, 0, t->counters.p, s);
       erased = read_counter(t, s); }
     t->size -= erased;
+    if (erased) t->has_sticky = true;
     maybe_shrink(t);
     return (int64_t)erased;
   });
@@ -971,6 +1043,7 @@ int64_t kh_erase_host(kh_table *t, const uint64_t *keys, uint64_t n) {
     KH_CUDA(cudaStreamSynchronize(t->stream[1]));
     const uint64_t erased = read_counter(t, t->stream[0]);
     t->size -= erased;
+    if (erased) t->has_sticky = true;
     maybe_shrink(t);
     return (int64_t)erased;
   });

@@ -101,7 +101,7 @@ class HashMap:
     def kernel_time(self, which="insert"):
         """(sum of ms, launches) of the insert / lookup probe kernels since kernel_timing(True)"""
         ms, n = C.c_double(0), C.c_uint64(0)
-        check(lib.kh_kernel_time(self._h, 0 if which == "insert" else 1, C.byref(ms), C.byref(n)), "kernel_time")
+        check(lib.kh_kernel_time(self._h, {"insert": 0, "lookup": 1, "scatter": 2, "hll": 3}[which], C.byref(ms), C.byref(n)), "kernel_time")
         return ms.value, n.value
 
     def reserve(self, n):

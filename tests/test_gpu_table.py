@@ -427,3 +427,30 @@ def test_fused_scatter_into_peer_buffers(kh, oracle_mod, p, W):
         for h in peers:
             if h:
                 lib.khx_peer_destroy(h)
+
+
+@pytest.mark.parametrize("max_load", [0.8, 0.97])
+def test_tile_insert_deferred_chains_and_side_key(kh, oracle_mod, max_load):
+    """shared-memory tile insert (kh_tile.cuh): chains that leave their 8192-slot tile and the all-ones key are
+    deferred to the global kernel; a second large batch goes into the live (non-fresh) table; after an erase
+    (sticky bits) inserts fall back to the global path.  Contents and answers equal the oracle's throughout."""
+    rng = np.random.default_rng(29)
+    n_uniq = int(4 * 8192 * max_load * 0.95)                 # fills 4 tiles close to max_load
+    uniq = rng.integers(0, 2**62, size=n_uniq, dtype=np.uint64)
+    keys = uniq[rng.integers(0, n_uniq, size=6 * n_uniq)]
+    keys = np.ascontiguousarray(np.concatenate([keys, uniq, np.full(7, 2**64 - 1, dtype=np.uint64)]))
+    m = kh.HashMap(1, "MURMUR64avx", "COUNT", min_load=0.1, max_load=max_load)
+    m.set_insert_window(True, 1 << 12, 1)
+    om = oracle_mod.port.Map(1, "COUNT")
+    m.reserve(n_uniq)
+    assert m.capacity() == 4 * 8192
+    assert m.insert_no_estimate(keys, default=1) == om.insert(keys, default=1)     # fresh table
+    check_against(m, om)
+    more = np.ascontiguousarray(np.concatenate([keys[:40000], rng.integers(0, 2**62, size=300, dtype=np.uint64)]))
+    assert m.insert_no_estimate(more, default=3) == om.insert(more, default=3)     # live table
+    check_against(m, om)
+    q = np.ascontiguousarray(keys[:3000])
+    assert m.erase(q) == om.erase(q)
+    assert m.insert_no_estimate(more, default=1) == om.insert(more, default=1)     # sticky bits: global path
+    check_against(m, om)
+    assert np.array_equal(m.find(q, 0), om.find(q, 0))
