@@ -52,23 +52,30 @@ __device__ __forceinline__ void lds_v2(const uint64_t *p, uint64_t &a, uint64_t 
   asm volatile("ld.shared.v2.u64 {%0,%1}, [%2];" : "=l"(a), "=l"(b) : "r"(addr) : "memory");
 }
 
-// one key into the staged tile; returns 1 when the key was new, defers when the chain leaves the tile
+// one key into the staged tile; returns 1 when the key was new, defers when the chain leaves the tile.
+// The slot index is computed with selects so that every lane of a batch reaches the same ATOMS instruction.
 __device__ __forceinline__ uint32_t tile_insert_one(uint64_t *sk, uint32_t *sv, uint64_t key, uint32_t lb, uint32_t v,
                                                     uint32_t pos, const TileArgs &a) {
   if (key == EMPTY_WORD) lb = TI_BUCKETS;       // side-slot key: global path
+  uint32_t is_new = 0;
   while (lb < (uint32_t)TI_BUCKETS) {
     uint64_t k0, k1, k2, k3;
     lds_v2(sk + lb * 4, k0, k1);
     lds_v2(sk + lb * 4 + 2, k2, k3);
-    const int m = k0 == key ? 0 : (k1 == key ? 1 : (k2 == key ? 2 : (k3 == key ? 3 : -1)));
-    if (m >= 0) { atomicAdd(&sv[lb * 4 + m], v); return 0; }
-    const int e = k0 == EMPTY_WORD ? 0 : (k1 == EMPTY_WORD ? 1 : (k2 == EMPTY_WORD ? 2 : (k3 == EMPTY_WORD ? 3 : -1)));
-    if (e < 0) { ++lb; continue; }
-    const uint64_t old = atomicCAS(reinterpret_cast<unsigned long long *>(&sk[lb * 4 + e]), (unsigned long long)EMPTY_WORD,
-                                   (unsigned long long)key);
-    if (old == EMPTY_WORD) { atomicAdd(&sv[lb * 4 + e], v); return 1; }
-    if (old == key) { atomicAdd(&sv[lb * 4 + e], v); return 0; }
-    // another key took the slot: scan the same bucket again
+    int m = k3 == key ? 3 : -1;
+    m = k2 == key ? 2 : m; m = k1 == key ? 1 : m; m = k0 == key ? 0 : m;
+    if (m < 0) {
+      int e = k3 == EMPTY_WORD ? 3 : -1;
+      e = k2 == EMPTY_WORD ? 2 : e; e = k1 == EMPTY_WORD ? 1 : e; e = k0 == EMPTY_WORD ? 0 : e;
+      if (e < 0) { ++lb; continue; }
+      const uint64_t old = atomicCAS(reinterpret_cast<unsigned long long *>(&sk[lb * 4 + e]), (unsigned long long)EMPTY_WORD,
+                                     (unsigned long long)key);
+      if (old != EMPTY_WORD && old != key) continue;      // another key took the slot: scan the same bucket again
+      is_new = old == EMPTY_WORD ? 1u : 0u;
+      m = e;
+    }
+    atomicAdd(&sv[lb * 4 + m], v);
+    return is_new;
   }
   a.defer_idx[atomicAdd(a.n_new + 1, 1ULL)] = pos;
   return 0;
@@ -88,7 +95,8 @@ __global__ void __launch_bounds__(TI_THREADS, 2) tile_insert_kernel(TileArgs a) 
   for (uint64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
     const uint64_t c = tile >> a.subs_log2;
     const uint32_t sub = (uint32_t)tile & subs_mask;
-    const uint64_t begin = c ? a.bin_end[(c - 1) * a.bin_stride] : 0ULL, end = a.bin_end[c * a.bin_stride];
+    // batch positions are 32-bit (the host keeps n < 2^32)
+    const uint32_t begin = c ? (uint32_t)a.bin_end[(c - 1) * a.bin_stride] : 0u, end = (uint32_t)a.bin_end[c * a.bin_stride];
     uint4 *g = reinterpret_cast<uint4 *>(a.t.slots) + tile * TI_SLOTS;
     if (a.fresh && begin == end) continue;          // nothing to add to an empty tile (uniform per CTA)
 
@@ -105,9 +113,13 @@ __global__ void __launch_bounds__(TI_THREADS, 2) tile_insert_kernel(TileArgs a) 
     __syncthreads();
 
     // ---- scan the region's tags, compact the tile's keys, insert them with full warps -----
-    const uint64_t first = begin & ~(uint64_t)(TI_CHUNK - 1);
+    // One batch of 32 keys is always "in flight": its key / tag loads were issued a step earlier, so the gather
+    // latency overlaps the probes of the batch before it.
+    const uint32_t first = begin & ~(uint32_t)(TI_CHUNK - 1);
     uint32_t qn = 0;
-    uint64_t base = first + (uint64_t)warp * TI_CHUNK;
+    bool pending = false;
+    uint64_t pkey = 0; uint32_t ptag = 0, ppos = 0;
+    uint64_t base = (uint64_t)first + (uint64_t)warp * TI_CHUNK;       // 64-bit: may step past 2^32 at the end
     uint2 nxt = make_uint2(0u, 0u);
     if (base < end) nxt = __ldg(reinterpret_cast<const uint2 *>(a.tags + base) + lane);
     for (; base < end; base += (uint64_t)TI_WARPS * TI_CHUNK) {
@@ -115,13 +127,15 @@ __global__ void __launch_bounds__(TI_THREADS, 2) tile_insert_kernel(TileArgs a) 
       const uint64_t nb = base + (uint64_t)TI_WARPS * TI_CHUNK;
       if (nb < end) nxt = __ldg(reinterpret_cast<const uint2 *>(a.tags + nb) + lane);
       const uint32_t tg[4] = {cur.x & 0xffffu, cur.x >> 16, cur.y & 0xffffu, cur.y >> 16};
-      const uint64_t p0 = base + (uint64_t)lane * 4;
+      const uint32_t p0 = (uint32_t)base + (uint32_t)lane * 4;
+      const bool interior = base >= begin && base + TI_CHUNK <= end;   // warp-uniform
 #pragma unroll
       for (int j = 0; j < 4; ++j) {
-        const uint64_t p = p0 + j;
-        const bool mine = p >= begin && p < end && (tg[j] >> TI_BUCKET_BITS) == sub;
+        const uint32_t p = p0 + j;
+        bool mine = (tg[j] >> TI_BUCKET_BITS) == sub;
+        if (!interior) mine = mine && p >= begin && p < end;
         const uint32_t bal = __ballot_sync(FULL_MASK, mine);
-        if (mine) sq[qn + __popc(bal & lt_mask)] = (uint32_t)p;
+        if (mine) sq[qn + __popc(bal & lt_mask)] = p;
         qn += __popc(bal);
       }
       __syncwarp();
@@ -129,8 +143,9 @@ __global__ void __launch_bounds__(TI_THREADS, 2) tile_insert_kernel(TileArgs a) 
       while (qn - h >= 32u) {
         const uint32_t pos = sq[h + lane];
         const uint64_t key = __ldg(a.keys + pos);
-        const uint32_t lb = (uint32_t)__ldg(a.tags + pos) & (uint32_t)(TI_BUCKETS - 1);
-        fresh += tile_insert_one(sk, sv, key, lb, a.dflt, pos, a);
+        const uint32_t tag = (uint32_t)__ldg(a.tags + pos);
+        if (pending) fresh += tile_insert_one(sk, sv, pkey, ptag & (uint32_t)(TI_BUCKETS - 1), a.dflt, ppos, a);
+        pkey = key; ptag = tag; ppos = pos; pending = true;
         h += 32;
       }
       if (h) {                                       // move the remainder (< 32 entries) to the front
@@ -142,6 +157,7 @@ __global__ void __launch_bounds__(TI_THREADS, 2) tile_insert_kernel(TileArgs a) 
       }
       __syncwarp();
     }
+    if (pending) fresh += tile_insert_one(sk, sv, pkey, ptag & (uint32_t)(TI_BUCKETS - 1), a.dflt, ppos, a);
     if (lane < qn) {
       const uint32_t pos = sq[lane];
       const uint64_t key = __ldg(a.keys + pos);

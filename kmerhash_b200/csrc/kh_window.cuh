@@ -112,19 +112,33 @@ __global__ void __launch_bounds__(WIN_BLOCK, 4) window_scatter_kernel(const uint
   const int P = spec.mode == 0 ? (1 << spec.lp) : (int)spec.p;
   const uint64_t n_tiles = (n + TILE - 1) / TILE;
 
+  // keys of the NEXT tile are fetched into k[] as soon as the current tile's keys sit in shared memory, and the
+  // range reservations (global atomics with return) are consumed only after the in-tile sort: both latencies
+  // overlap shared-memory work instead of stalling the block between two barriers.
+  uint64_t k[KPT][W];
+  auto fetch = [&](uint64_t tile) {
+    if (tile >= n_tiles) return;
+    const uint64_t base = tile * TILE;
+    const int tile_n = (int)min((uint64_t)TILE, n - base);
+#pragma unroll
+    for (int j = 0; j < KPT; ++j) {
+      const int e = j * WIN_BLOCK + threadIdx.x;
+      if (e < tile_n) load_key<W>(keys, base + e, k[j]);
+    }
+  };
+  fetch(blockIdx.x);
+
   for (uint64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
     const uint64_t base = tile * TILE;
     const int tile_n = (int)min((uint64_t)TILE, n - base);
     for (int r = threadIdx.x; r < P; r += WIN_BLOCK) cnt[r] = 0;
     __syncthreads();
 
-    uint64_t k[KPT][W];
     uint32_t reg[KPT], loc[KPT], tg[TAGS ? KPT : 1];
 #pragma unroll
     for (int j = 0; j < KPT; ++j) {
       const int e = j * WIN_BLOCK + threadIdx.x;
       if (e < tile_n) {
-        load_key<W>(keys, base + e, k[j]);
         if constexpr (TAGS) {
           const uint64_t hm = spread_hash(hash_runtime<W>(spec.hash_kind, k[j], spec.hp));
           reg[j] = (uint32_t)top_bits(hm, 64 - spec.lp);
@@ -139,15 +153,17 @@ __global__ void __launch_bounds__(WIN_BLOCK, 4) window_scatter_kernel(const uint
 
     // exclusive scan of cnt[0..P) -> lo ; reserve the output ranges
     uint32_t c[RPT], st[RPT];
+    unsigned long long gb[RPT];
 #pragma unroll
     for (int q = 0; q < RPT; ++q) { const int r = threadIdx.x * RPT + q; c[q] = r < P ? cnt[r] : 0u; }
     Scan(tmp).ExclusiveSum(c, st);
 #pragma unroll
     for (int q = 0; q < RPT; ++q) {
       const int r = threadIdx.x * RPT + q;
+      gb[q] = 0;
       if (r < P) {
         lo[r] = st[q];
-        if (c[q]) gbase[r] = atomicAdd(&cursors[TAGS ? r * tags.cstride : r], (unsigned long long)c[q]);
+        if (c[q]) gb[q] = atomicAdd(&cursors[TAGS ? r * tags.cstride : r], (unsigned long long)c[q]);
       }
     }
     __syncthreads();
@@ -164,6 +180,12 @@ __global__ void __launch_bounds__(WIN_BLOCK, 4) window_scatter_kernel(const uint
         if (PERM) ssrc[pos] = (uint16_t)e;
         if constexpr (TAGS) stag[pos] = (uint16_t)tg[j];
       }
+    }
+    fetch(tile + gridDim.x);
+#pragma unroll
+    for (int q = 0; q < RPT; ++q) {
+      const int r = threadIdx.x * RPT + q;
+      if (r < P && c[q]) gbase[r] = gb[q];
     }
     __syncthreads();
 
