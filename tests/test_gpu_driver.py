@@ -64,3 +64,59 @@ def test_driver_is_built():
     assert os.path.exists(DRIVER)
     r = subprocess.run([DRIVER, "--help"], capture_output=True, text=True, timeout=60)
     assert r.returncode == 0 and "BenchmarkHashTables" in r.stdout
+
+
+COUNTER = os.path.join(ROOT, "drivers", "BenchmarkKmerCounter")
+
+
+def _write_fastq(path, reads):
+    with open(path, "w") as f:
+        for i, r in enumerate(reads):
+            f.write("@r%d\n%s\n+\n%s\n" % (i, r, "I" * len(r)))
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("gpus", [1, 2])
+def test_kmercounter_driver_matches_oracle(tmp_path, oracle_mod, gpus):
+    """BenchmarkKmerCounter on a FASTQ file (reads with N runs and short reads): the [Kmer][count] records it writes
+    equal the oracle's canonical 31-mer count map (CountType = uint16_t, benchmark/BenchmarkKmerCounter.cpp:184)."""
+    import kmerhash_b200 as kh
+    if gpus > kh.device_count():
+        pytest.skip("needs %d GPUs" % gpus)
+    rng = np.random.default_rng(11)
+    genome = "".join("ACGT"[c] for c in rng.integers(0, 4, size=20000))
+    reads = []
+    for i in range(3000):
+        ln = int(rng.integers(20, 151))
+        s = int(rng.integers(0, len(genome) - ln))
+        r = genome[s:s + ln]
+        if i % 7 == 0 and ln > 40:
+            p = int(rng.integers(0, ln - 2))
+            r = r[:p] + "NN" + r[p + 2:]
+        reads.append(r)
+    fq = str(tmp_path / "reads.fastq")
+    out = str(tmp_path / "counts.bin")
+    _write_fastq(fq, reads)
+    r = subprocess.run([COUNTER, "-G", str(gpus), "-O", out, "--sample", "5000", fq], capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stdout + r.stderr
+    raw = np.fromfile(out, dtype=np.uint8).reshape(-1, 10)
+    keys = np.ascontiguousarray(raw[:, :8]).view(np.uint64).reshape(-1)
+    cnts = np.ascontiguousarray(raw[:, 8:]).view(np.uint16).reshape(-1)
+
+    bases = np.frombuffer("".join(reads).encode(), dtype=np.uint8)
+    offsets = np.concatenate([[0], np.cumsum([len(x) for x in reads])]).astype(np.uint64)
+    exp = oracle_mod.port.kmers_from_reads(bases, offsets, 31, True)
+    m = oracle_mod.port.Map(1, "COUNT")
+    m.insert(exp, default=1)
+    ek, ev = m.to_vector()
+    a, b = sort_pairs(keys, cnts.astype(np.uint32)), sort_pairs(ek, ev & 0xFFFF)
+    assert np.array_equal(a[0], b[0]) and np.array_equal(a[1], b[1])
+    assert "kmers %d distinct %d" % (len(exp), len(ek)) in r.stdout
+    for phase in ("read", "parse", "insert", "count", "find", "write"):
+        assert phase in r.stdout
+
+
+def test_kmercounter_driver_is_built():
+    assert os.path.exists(COUNTER)
+    r = subprocess.run([COUNTER, "--help"], capture_output=True, text=True, timeout=60)
+    assert r.returncode == 0 and "BenchmarkKmerCounter" in r.stdout
