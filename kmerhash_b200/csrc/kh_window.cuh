@@ -203,4 +203,138 @@ __global__ void __launch_bounds__(WIN_BLOCK, 4) window_scatter_kernel(const uint
   }
 }
 
+// ---- large-tile region scatter ------------------------------------------------------------------------------
+// Same job as window_scatter_kernel<W,false,false,TAGS> (non-stable sort of the batch by table region, optional
+// home-bucket tags), built for ~1000 regions: a CTA sorts RS_TILE_BYTES = 64 KB of keys at a time, so a region's
+// run inside a tile is ~8 keys (64 B) instead of ~2 (16 B) -- 4x fewer, 4x longer global stores and 4x fewer range
+// reservations (global atomics) per key.  Registers hold only the top 32 bits of every key's spread hash between
+// the two sweeps (16 per thread); the key itself is read again from L2 in the second sweep instead of being kept:
+//   sweep 1  load + hash, shared-memory histogram of the tile by region
+//   scan     region starts inside the tile; ONE global atomicAdd per (tile, region) reserves the output range
+//   sweep 2  re-read the key, take the next position of its region, store key / region / tag sorted in shared memory
+//   out      sorted tile -> global memory, consecutive threads = consecutive addresses inside a run
+constexpr int RS_BLOCK = 512;
+constexpr int RS_TILE_BYTES = 65536;
+template <int W> constexpr size_t rs_smem_bytes() {
+  return (size_t)RS_TILE_BYTES + 2 * (size_t)(RS_TILE_BYTES / (8 * W)) * 2 + WIN_MAX_P * 4 + WIN_MAX_P * 8;
+}
+template <int W, bool TAGS>
+__global__ void __launch_bounds__(RS_BLOCK, 2) region_scatter_kernel(const uint64_t *keys, uint64_t n, BinSpec spec,
+                                                                     unsigned long long *cursors, uint64_t *out, TagSpec tags) {
+  constexpr int TILE = RS_TILE_BYTES / (8 * W);
+  constexpr int KPT = TILE / RS_BLOCK;                // 16 (W=1) / 8 (W=2)
+  constexpr int RPT = WIN_MAX_P / RS_BLOCK;           // 2
+  constexpr int B = 8 / W;                            // keys loaded per thread before they are hashed
+  using Scan = cub::BlockScan<uint32_t, RS_BLOCK>;
+  __shared__ typename Scan::TempStorage tmp;
+  extern __shared__ __align__(16) unsigned char rs_smem[];
+  uint64_t *skeys = reinterpret_cast<uint64_t *>(rs_smem);
+  unsigned long long *goff = reinterpret_cast<unsigned long long *>(rs_smem + RS_TILE_BYTES);   // run start in `out` - run start in tile
+  uint32_t *cur = reinterpret_cast<uint32_t *>(goff + WIN_MAX_P);                               // histogram, then running position
+  uint16_t *sreg = reinterpret_cast<uint16_t *>(cur + WIN_MAX_P);
+  uint16_t *stag = sreg + TILE;
+  const int P = 1 << spec.lp;
+  const int rshift = spec.lp ? 32 - spec.lp : 31;     // lp == 0: one region (bit 31 is masked off below)
+  const uint32_t rmask = spec.lp ? 0xffffffffu : 0u;
+  const int tshift = tags.shift - 32;                 // tag = bits of the spread hash from tags.shift up
+  const uint64_t n_tiles = (n + TILE - 1) / TILE;
+
+  for (uint64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+    const uint64_t base = tile * TILE;
+    const int tile_n = (int)min((uint64_t)TILE, n - base);
+    const uint64_t next = tile + gridDim.x;
+    if (next < n_tiles) {                             // pull the next tile into L2 while this one is sorted
+      const char *pf = reinterpret_cast<const char *>(keys + next * TILE * W) + (size_t)threadIdx.x * 128;
+      if (next * TILE + ((size_t)threadIdx.x + 1) * (128 / (8 * W)) <= n) asm volatile("prefetch.global.L2 [%0];" ::"l"(pf));
+    }
+    for (int r = threadIdx.x; r < P; r += RS_BLOCK) cur[r] = 0;
+    __syncthreads();
+
+    uint32_t hm[KPT];
+#pragma unroll
+    for (int j0 = 0; j0 < KPT; j0 += B) {
+      uint64_t k[B][W];
+#pragma unroll
+      for (int j = 0; j < B; ++j) {
+        const int e = (j0 + j) * RS_BLOCK + threadIdx.x;
+        if (e < tile_n) load_key<W>(keys, base + e, k[j]);
+      }
+#pragma unroll
+      for (int j = 0; j < B; ++j) {
+        const int e = (j0 + j) * RS_BLOCK + threadIdx.x;
+        if (e < tile_n) {
+          hm[j0 + j] = (uint32_t)(spread_hash(hash_runtime<W>(spec.hash_kind, k[j], spec.hp)) >> 32);
+          atomicAdd(&cur[(hm[j0 + j] >> rshift) & rmask], 1u);
+        }
+      }
+    }
+    __syncthreads();
+
+    uint32_t c[RPT], st[RPT];
+    unsigned long long gb[RPT];
+#pragma unroll
+    for (int q = 0; q < RPT; ++q) { const int r = threadIdx.x * RPT + q; c[q] = r < P ? cur[r] : 0u; }
+    Scan(tmp).ExclusiveSum(c, st);
+#pragma unroll
+    for (int q = 0; q < RPT; ++q) {
+      const int r = threadIdx.x * RPT + q;
+      gb[q] = 0;
+      if (r < P) {
+        cur[r] = st[q];
+        if (c[q]) gb[q] = atomicAdd(&cursors[(size_t)r * tags.cstride], (unsigned long long)c[q]);
+      }
+    }
+    __syncthreads();
+
+#pragma unroll
+    for (int j0 = 0; j0 < KPT; j0 += B) {
+      uint64_t k[B][W];
+#pragma unroll
+      for (int j = 0; j < B; ++j) {
+        const int e = (j0 + j) * RS_BLOCK + threadIdx.x;
+        if (e < tile_n) load_key<W>(keys, base + e, k[j]);
+      }
+#pragma unroll
+      for (int j = 0; j < B; ++j) {
+        const int e = (j0 + j) * RS_BLOCK + threadIdx.x;
+        if (e < tile_n) {
+          const uint32_t r = (hm[j0 + j] >> rshift) & rmask;
+          const uint32_t pos = atomicAdd(&cur[r], 1u);
+#pragma unroll
+          for (int q = 0; q < W; ++q) skeys[pos * W + q] = k[j][q];
+          sreg[pos] = (uint16_t)r;
+          if constexpr (TAGS) stag[pos] = (uint16_t)((hm[j0 + j] >> tshift) & tags.mask);
+        }
+      }
+    }
+#pragma unroll
+    for (int q = 0; q < RPT; ++q) {
+      const int r = threadIdx.x * RPT + q;
+      if (r < P) goff[r] = gb[q] - st[q];
+    }
+    __syncthreads();
+
+#pragma unroll 4
+    for (int e = threadIdx.x; e < tile_n; e += RS_BLOCK) {
+      const unsigned long long gpos = goff[sreg[e]] + (unsigned long long)e;
+      uint64_t *o = out + gpos * W;
+#pragma unroll
+      for (int q = 0; q < W; ++q) o[q] = skeys[e * W + q];
+      if constexpr (TAGS) tags.out[gpos] = stag[e];
+    }
+    __syncthreads();
+  }
+}
+
+// host side: launch on `grid` CTAs (2 per SM fit)
+template <int W, bool TAGS>
+inline void region_scatter_launch(int sms, cudaStream_t s, const uint64_t *keys, uint64_t n, const BinSpec &spec,
+                                  unsigned long long *cursors, uint64_t *out, const TagSpec &tags) {
+  // per device, so set on every launch (a process may drive several GPUs)
+  KH_CUDA(cudaFuncSetAttribute(region_scatter_kernel<W, TAGS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)rs_smem_bytes<W>()));
+  constexpr uint64_t TILE = RS_TILE_BYTES / (8 * W);
+  const int grid = (int)std::max<uint64_t>(1, std::min<uint64_t>((n + TILE - 1) / TILE, (uint64_t)sms * 2));
+  KH_LAUNCH((region_scatter_kernel<W, TAGS>), grid, RS_BLOCK, rs_smem_bytes<W>(), s, keys, n, spec, cursors, out, tags);
+}
+
 }  // namespace kh

@@ -458,8 +458,8 @@ bool tile_candidate(const kh_table *t, const uint32_t *d_vals, uint64_t n, int &
 
 uint64_t insert_tiled(kh_table *t, const uint64_t *d_keys, uint64_t n, uint32_t dflt, const unsigned long long *d_fine,
                       int lp, int subs_log2, cudaStream_t s) {
-  static std::once_flag once;
-  std::call_once(once, [] { cudaFuncSetAttribute(tile_insert_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TI_SMEM); });
+  KH_CUDA(cudaFuncSetAttribute(tile_insert_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TI_SMEM));   // per device
+  static const bool old_scatter = getenv("KH_SCATTER") && !strcmp(getenv("KH_SCATTER"), "old");
   constexpr int CSTRIDE = 16;          // one 128-byte line per cursor
   DevBuf<unsigned long long> fine_own, cursors((size_t)CSTRIDE << lp);
   if (!d_fine) {
@@ -477,8 +477,9 @@ uint64_t insert_tiled(kh_table *t, const uint64_t *d_keys, uint64_t n, uint32_t 
     const BinSpec spec{0, lp, 0u, t->hash_kind, t->hp};
     const TagSpec ts{tags.p, 64 - lbk, (1u << (lbk - lp)) - 1u, CSTRIDE};
     kev_begin(t, 2, s);
-    KH_LAUNCH((window_scatter_kernel<1, false, false, true>), t->sms * 4, WIN_BLOCK, 0, s, d_keys, n, spec, cursors.p, sorted.p,
-              nullptr, BinDst{}, ts);
+    if (old_scatter) KH_LAUNCH((window_scatter_kernel<1, false, false, true>), t->sms * 4, WIN_BLOCK, 0, s, d_keys, n, spec, cursors.p,
+                               sorted.p, nullptr, BinDst{}, ts);
+    else region_scatter_launch<1, true>(t->sms, s, d_keys, n, spec, cursors.p, sorted.p, ts);
     kev_end(t, s); }
   DevBuf<uint32_t> defer(n);
   uint64_t added = 0, n_def = 0;
@@ -524,8 +525,9 @@ uint64_t insert_windowed(kh_table *t, const uint64_t *d_keys, const uint32_t *d_
   const int grid = t->sms * 4;
   { Trace tr("window.scatter", s);
     const BinSpec spec{0, lp, 0u, t->hash_kind, t->hp};
-    if (t->W == 1) KH_LAUNCH((window_scatter_kernel<1, false>), grid, WIN_BLOCK, 0, s, d_keys, n, spec, cursors.p, sorted.p, nullptr);
-    else KH_LAUNCH((window_scatter_kernel<2, false>), grid, WIN_BLOCK, 0, s, d_keys, n, spec, cursors.p, sorted.p, nullptr); }
+    const TagSpec ts{nullptr, 32, 0u, 1};
+    if (t->W == 1) region_scatter_launch<1, false>(t->sms, s, d_keys, n, spec, cursors.p, sorted.p, ts);
+    else region_scatter_launch<2, false>(t->sms, s, d_keys, n, spec, cursors.p, sorted.p, ts); }
   Trace tr("window.insert", s);
   return insert_resident(t, sorted.p, nullptr, n, dflt, s, true);   // synchronises s before the scratch is released
 }
