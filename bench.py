@@ -297,7 +297,7 @@ def ours_single(args):
                      "lookup_kernels_ms_per_step": look_ms / args.steps,
                      # the two streaming passes in front of the table kernel, same CUDA-event timing
                      "other_kernels": {
-                         "window_scatter_kernel (region sort + tags, 18 B/key algorithmic)": {
+                         "region_scatter_kernel (region sort + tags, 18 B/key algorithmic)": {
                              "ms_per_step": sc_ms / args.steps, "achieved_GBps": 18 * n / max(sc_ms / args.steps, 1e-9) / 1e6,
                              "frac": 18 * n / max(sc_ms / args.steps, 1e-9) / 1e6 / peak},
                          "hll_update_kernel (HLL registers + region histogram, 8 B/key algorithmic)": {

@@ -53,7 +53,9 @@ struct kh_table {
 namespace kh {
 // estimate + fine region histogram (REGION_FINE bins, device) of a batch, when the caller's pipeline already
 // produced them (host pipeline: accumulated behind the PCIe copy; exchange: computed by the senders)
-struct PreEstimate { double est; const unsigned long long *fine; };
+// segs (may be null): the batch lies in several pieces of d_keys (kh_window.cuh: SegSpec)
+struct SegSpec;
+struct PreEstimate { double est; const unsigned long long *fine; const SegSpec *segs = nullptr; };
 // batch insert of device-resident keys (see table.cu); returns #new keys or a negative status
 int64_t insert_dev_impl(kh_table *t, const uint64_t *d_keys, const uint32_t *d_vals, uint64_t n, uint32_t dflt,
                         int estimate, const PreEstimate *pre = nullptr);

@@ -215,12 +215,23 @@ __global__ void __launch_bounds__(WIN_BLOCK, 4) window_scatter_kernel(const uint
 //   out      sorted tile -> global memory, consecutive threads = consecutive addresses inside a run
 constexpr int RS_BLOCK = 512;
 constexpr int RS_TILE_BYTES = 65536;
+// The batch may be handed over in up to WIN_MAX_DST pieces (the per-sender slabs of a peer receive buffer, exchange.cu):
+// logical position i lies in piece s with prefix[s] <= i < prefix[s+1], at keys[base[s] + i - prefix[s]].
+struct SegSpec { int nseg; unsigned long long prefix[WIN_MAX_DST + 1]; unsigned long long base[WIN_MAX_DST]; };
+__device__ __forceinline__ uint64_t seg_phys(const SegSpec &g, uint64_t i) {
+  if (g.nseg <= 1) return i;
+  int s = 0;
+#pragma unroll
+  for (int q = 1; q < WIN_MAX_DST; ++q) s += (q < g.nseg && i >= g.prefix[q]) ? 1 : 0;
+  return g.base[s] + (i - g.prefix[s]);
+}
 template <int W> constexpr size_t rs_smem_bytes() {
   return (size_t)RS_TILE_BYTES + 2 * (size_t)(RS_TILE_BYTES / (8 * W)) * 2 + WIN_MAX_P * 4 + WIN_MAX_P * 8;
 }
 template <int W, bool TAGS>
 __global__ void __launch_bounds__(RS_BLOCK, 2) region_scatter_kernel(const uint64_t *keys, uint64_t n, BinSpec spec,
-                                                                     unsigned long long *cursors, uint64_t *out, TagSpec tags) {
+                                                                     unsigned long long *cursors, uint64_t *out, TagSpec tags,
+                                                                     const __grid_constant__ SegSpec segs) {
   constexpr int TILE = RS_TILE_BYTES / (8 * W);
   constexpr int KPT = TILE / RS_BLOCK;                // 16 (W=1) / 8 (W=2)
   constexpr int RPT = WIN_MAX_P / RS_BLOCK;           // 2
@@ -243,7 +254,7 @@ __global__ void __launch_bounds__(RS_BLOCK, 2) region_scatter_kernel(const uint6
     const uint64_t base = tile * TILE;
     const int tile_n = (int)min((uint64_t)TILE, n - base);
     const uint64_t next = tile + gridDim.x;
-    if (next < n_tiles) {                             // pull the next tile into L2 while this one is sorted
+    if (next < n_tiles && segs.nseg <= 1) {           // pull the next tile into L2 while this one is sorted
       const char *pf = reinterpret_cast<const char *>(keys + next * TILE * W) + (size_t)threadIdx.x * 128;
       if (next * TILE + ((size_t)threadIdx.x + 1) * (128 / (8 * W)) <= n) asm volatile("prefetch.global.L2 [%0];" ::"l"(pf));
     }
@@ -257,7 +268,7 @@ __global__ void __launch_bounds__(RS_BLOCK, 2) region_scatter_kernel(const uint6
 #pragma unroll
       for (int j = 0; j < B; ++j) {
         const int e = (j0 + j) * RS_BLOCK + threadIdx.x;
-        if (e < tile_n) load_key<W>(keys, base + e, k[j]);
+        if (e < tile_n) load_key<W>(keys, seg_phys(segs, base + e), k[j]);
       }
 #pragma unroll
       for (int j = 0; j < B; ++j) {
@@ -292,7 +303,7 @@ __global__ void __launch_bounds__(RS_BLOCK, 2) region_scatter_kernel(const uint6
 #pragma unroll
       for (int j = 0; j < B; ++j) {
         const int e = (j0 + j) * RS_BLOCK + threadIdx.x;
-        if (e < tile_n) load_key<W>(keys, base + e, k[j]);
+        if (e < tile_n) load_key<W>(keys, seg_phys(segs, base + e), k[j]);
       }
 #pragma unroll
       for (int j = 0; j < B; ++j) {
@@ -329,12 +340,14 @@ __global__ void __launch_bounds__(RS_BLOCK, 2) region_scatter_kernel(const uint6
 // host side: launch on `grid` CTAs (2 per SM fit)
 template <int W, bool TAGS>
 inline void region_scatter_launch(int sms, cudaStream_t s, const uint64_t *keys, uint64_t n, const BinSpec &spec,
-                                  unsigned long long *cursors, uint64_t *out, const TagSpec &tags) {
+                                  unsigned long long *cursors, uint64_t *out, const TagSpec &tags, const SegSpec *segs = nullptr) {
   // per device, so set on every launch (a process may drive several GPUs)
   KH_CUDA(cudaFuncSetAttribute(region_scatter_kernel<W, TAGS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)rs_smem_bytes<W>()));
   constexpr uint64_t TILE = RS_TILE_BYTES / (8 * W);
   const int grid = (int)std::max<uint64_t>(1, std::min<uint64_t>((n + TILE - 1) / TILE, (uint64_t)sms * 2));
-  KH_LAUNCH((region_scatter_kernel<W, TAGS>), grid, RS_BLOCK, rs_smem_bytes<W>(), s, keys, n, spec, cursors, out, tags);
+  SegSpec one{};
+  one.nseg = 1;
+  KH_LAUNCH((region_scatter_kernel<W, TAGS>), grid, RS_BLOCK, rs_smem_bytes<W>(), s, keys, n, spec, cursors, out, tags, segs ? *segs : one);
 }
 
 }  // namespace kh

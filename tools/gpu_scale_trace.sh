@@ -1,0 +1,7 @@
+mkdir -p gpurun_out
+N=${1:-2}
+TR="python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29511"
+KH_TRACE=1 timeout 420 $TR bench.py --gpus $N --steps 1 --warmup 2 2>&1 | grep "kh-trace" | tail -n 40
+timeout 420 $TR bench.py --gpus $N --steps 3 --warmup 3 > gpurun_out/bench_${N}gpu.json 2> gpurun_out/bench_${N}gpu.err; echo "bench$N rc=$?"
+python -c "import json; d=json.loads(open('gpurun_out/bench_${N}gpu.json').read().strip().splitlines()[-1]); print(d['value']/1e9, d['phase_ms'], d['e2e'])"
+exit 0
