@@ -263,6 +263,19 @@ int khx_plan_dev(kh_table *t, int dist_hash, uint32_t dist_seed, uint32_t p, con
 int khx_scatter_peers_dev(kh_table *t, int dist_hash, uint32_t dist_seed, const uint64_t *d_keys, uint64_t n,
                           khx_peer *x, const uint64_t *dst_offsets, const uint64_t *dst_counts);
 
+/* Single-pass sender (assign_count_estimate_permute :398-625 and the exchange as ONE kernel): every receive buffer is cut
+ * into 2 halves x p slabs of slab_cap keys; this rank stores its keys for owner r into slab `rank` of half `parity` of
+ * r's buffer while the same pass fills d_meta (counts, region histograms, HLL registers per owner) -- no offset depends
+ * on another rank, so nothing has to be gathered before the stores.  A slab that would overflow is cut off; its true
+ * count is in d_meta[r][0], so after the metadata all-gather every rank sees the overflow and the caller redoes the batch
+ * with khx_plan_dev + khx_scatter_peers_dev.  The halves alternate between batches (the all-gather of batch i+1 orders
+ * batch i+2 behind every rank's reads of batch i).  khx_insert_recv_slabs_dev = khx_insert_recv_dev reading the p slabs
+ * of this rank's own buffer in place (counts[g], HOST: keys sender g stored). */
+int khx_plan_scatter_slabs_dev(kh_table *t, int dist_hash, uint32_t dist_seed, const uint64_t *d_keys, uint64_t n, khx_peer *x,
+                               uint64_t slab_cap, int parity, uint64_t *d_meta);
+int64_t khx_insert_recv_slabs_dev(kh_table *t, khx_peer *x, uint64_t slab_cap, int parity, const uint64_t *counts,
+                                  const uint64_t *d_recv_meta, uint32_t default_val);
+
 /* ---- single-process multi-GPU map ------------------------------------------------------
  * replaces dsc::counting_batched_robinhood_map / batched_robinhood_map
  * (KH/distributed_batched_robinhood_map.hpp:748-832,1187,1535,1901,2428,2542-2649): one table per

@@ -99,6 +99,138 @@ __global__ void merge_meta_kernel(const unsigned long long *recv_meta, uint32_t 
   }
 }
 
+// ---- single-pass sender: metadata + rank scatter into fixed per-sender SLABS of the owners' receive buffers -------
+// khx_plan_dev + khx_scatter_peers_dev read and dist-hash every key twice because the exact receive offsets need every
+// sender's counts first.  With a fixed slab per (owner, sender) pair -- sender g writes its keys for owner r at
+// recv_r[g * slab_cap ...] -- no offset depends on another rank, so ONE pass does it all: dist hash -> owner, store hash ->
+// HLL registers + region histogram of that owner (shared memory), tile sorted by owner in shared memory, runs stored to
+// the owners over NVLink.  A slab that would overflow is cut off (the true count still goes into the metadata, so every
+// rank sees it after the metadata all-gather and all ranks redo the batch through the exact two-pass path).
+constexpr int PS_BLOCK = 512;
+constexpr int PS_TILE_BYTES = 16384;
+template <int W> constexpr size_t ps_smem_bytes(uint32_t p) {
+  return (size_t)PS_TILE_BYTES + (size_t)p * REGION_FINE * 4 + (size_t)p * HLL_M;
+}
+template <int W>
+__global__ void __launch_bounds__(PS_BLOCK, 2) plan_scatter_slabs_kernel(const uint64_t *keys, uint64_t n, BinSpec dist, int store_kind,
+                                                                          HashParams store_hp, const __grid_constant__ BinDst dst, unsigned long long slab_cap,
+                                                                          unsigned long long *cursors, unsigned long long *meta) {
+  constexpr int TILE = PS_TILE_BYTES / (8 * W);
+  constexpr int KPT = TILE / PS_BLOCK;               // 4 (W=1) / 2 (W=2)
+  extern __shared__ __align__(16) unsigned char ps_smem[];
+  uint64_t *skeys = reinterpret_cast<uint64_t *>(ps_smem);
+  uint32_t *hist = reinterpret_cast<uint32_t *>(ps_smem + PS_TILE_BYTES);   // [p][REGION_FINE]
+  uint32_t *regs = hist + dist.p * REGION_FINE;                           // [p][HLL_M] bytes, four to a word
+  __shared__ uint32_t cnt[WIN_MAX_DST], lo[WIN_MAX_DST];
+  __shared__ unsigned long long gbase[WIN_MAX_DST];
+  const uint32_t p = dist.p;
+  const int lane = threadIdx.x & 31;
+  const uint32_t lt_mask = (1u << lane) - 1u;
+  for (uint32_t i = threadIdx.x; i < p * REGION_FINE + p * (HLL_M / 4); i += PS_BLOCK) hist[i] = 0;
+  const bool h32 = hash_bits(store_kind) == 32;
+  const uint64_t n_tiles = (n + TILE - 1) / TILE;
+  unsigned long long my_total = 0;                   // thread r < p: keys of this CTA for owner r
+
+  for (uint64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+    const uint64_t base = tile * TILE;
+    const int tile_n = (int)min((uint64_t)TILE, n - base);
+    const uint64_t next = tile + gridDim.x;
+    if (next < n_tiles && threadIdx.x < PS_TILE_BYTES / 128) {            // next tile -> L2 while this one is sorted
+      const uint64_t e = next * TILE + (uint64_t)threadIdx.x * (128 / (8 * W));
+      if (e < n) asm volatile("prefetch.global.L2 [%0];" ::"l"(keys + e * W));
+    }
+    if (threadIdx.x < WIN_MAX_DST) cnt[threadIdx.x] = 0;
+    __syncthreads();
+
+    uint64_t k[KPT][W];
+    uint32_t own[KPT], loc[KPT];
+#pragma unroll
+    for (int j = 0; j < KPT; ++j) {
+      const int e = j * PS_BLOCK + threadIdx.x;
+      if (e < tile_n) load_key<W>(keys, base + e, k[j]);
+    }
+#pragma unroll
+    for (int j = 0; j < KPT; ++j) {
+      const int e = j * PS_BLOCK + threadIdx.x;
+      own[j] = 0xffu;
+      if (e < tile_n) {
+        own[j] = bin_of<W>(dist, k[j]);
+        const uint64_t h = hash_runtime<W>(store_kind, k[j], store_hp);
+        uint32_t idx, rank;
+        if (h32) {
+          const uint32_t x = (uint32_t)h;
+          idx = x >> (32 - HLL_P);
+          rank = __clz((int)((x << HLL_P) | 0xFFFu)) + 1;
+        } else {
+          idx = (uint32_t)(h >> (64 - HLL_P));
+          rank = __clzll((long long)((h << HLL_P) | 0xFFFULL)) + 1;
+        }
+        // byte-wide max inside a shared-memory word
+        uint32_t *w = regs + (own[j] * HLL_M + idx) / 4;
+        const int sh = (idx & 3) * 8;
+        uint32_t old = *w;
+        while (((old >> sh) & 0xffu) < rank) {
+          const uint32_t seen = atomicCAS(w, old, (old & ~(0xffu << sh)) | (rank << sh));
+          if (seen == old) break;
+          old = seen;
+        }
+        atomicAdd(&hist[own[j] * REGION_FINE + (uint32_t)(spread_hash(h) >> (64 - REGION_FINE_BITS))], 1u);
+      }
+      // position inside the owner's run of this tile: one shared-memory atomic per (warp, owner)
+      const uint32_t peers = __match_any_sync(FULL_MASK, own[j]);
+      uint32_t start = 0;
+      if (own[j] != 0xffu && (peers & lt_mask) == 0) start = atomicAdd(&cnt[own[j]], (uint32_t)__popc(peers));
+      start = __shfl_sync(FULL_MASK, start, __ffs(peers) - 1);
+      loc[j] = start + __popc(peers & lt_mask);
+    }
+    __syncthreads();
+
+    if (threadIdx.x < p) {
+      uint32_t st = 0;
+      for (uint32_t r = 0; r < threadIdx.x; ++r) st += cnt[r];
+      const uint32_t c = cnt[threadIdx.x];
+      lo[threadIdx.x] = st;
+      gbase[threadIdx.x] = c ? atomicAdd(&cursors[threadIdx.x], (unsigned long long)c) : 0ULL;
+      my_total += c;
+    }
+    __syncthreads();
+
+#pragma unroll
+    for (int j = 0; j < KPT; ++j) {
+      const int e = j * PS_BLOCK + threadIdx.x;
+      if (e < tile_n) {
+        const uint32_t pos = lo[own[j]] + loc[j];
+#pragma unroll
+        for (int q = 0; q < W; ++q) skeys[pos * W + q] = k[j][q];
+      }
+    }
+    __syncthreads();
+
+    // sorted tile out: position e belongs to the owner r with lo[r] <= e < lo[r] + cnt[r]
+    for (int e = threadIdx.x; e < tile_n; e += PS_BLOCK) {
+      uint32_t r = 0;
+#pragma unroll
+      for (int q = 1; q < WIN_MAX_DST; ++q) r += (q < (int)p && (uint32_t)e >= lo[q]) ? 1u : 0u;
+      const unsigned long long gpos = gbase[r] + (uint32_t)(e - lo[r]);
+      if (gpos < slab_cap) {
+        uint64_t *o = dst.base[r] + gpos * W;
+#pragma unroll
+        for (int q = 0; q < W; ++q) o[q] = skeys[e * W + q];
+      }
+    }
+    __syncthreads();
+  }
+
+  __syncthreads();
+  for (uint32_t i = threadIdx.x; i < p * REGION_FINE; i += PS_BLOCK)
+    if (hist[i]) atomicAdd(&meta[(uint64_t)(i / REGION_FINE) * META_WORDS + META_HIST + (i % REGION_FINE)], (unsigned long long)hist[i]);
+  for (uint32_t i = threadIdx.x; i < p * HLL_M; i += PS_BLOCK) {
+    const uint32_t v = (regs[i / 4] >> ((i & 3) * 8)) & 0xffu;
+    if (v) atomicMax(&meta[(uint64_t)(i / HLL_M) * META_WORDS + META_REGS + (i % HLL_M)], (unsigned long long)v);
+  }
+  if (threadIdx.x < p && my_total) atomicAdd(&meta[(uint64_t)threadIdx.x * META_WORDS], my_total);
+}
+
 }  // namespace kh
 
 using namespace kh;
@@ -266,6 +398,83 @@ int khx_scatter_peers_dev(kh_table *t, int dist_hash, uint32_t dist_seed, const 
     }
     KH_CUDA(cudaStreamSynchronize(s));
     return KH_OK;
+  });
+}
+
+// Single-pass sender (plan_scatter_slabs_kernel): this rank's keys for owner r go to slab `rank` of half `parity` of
+// r's receive buffer, i.e. to remote[r] + ((parity * p + rank) * slab_cap) keys; d_meta receives the p metadata blocks.
+// The receive buffers hold 2 * p * slab_cap keys: two halves used alternately, so a rank may start batch i+1 while
+// another still reads batch i (the metadata all-gather of batch i+1 orders batch i+2 behind it).
+int khx_plan_scatter_slabs_dev(kh_table *t, int dist_hash, uint32_t dist_seed, const uint64_t *d_keys, uint64_t n, khx_peer *x,
+                               uint64_t slab_cap, int parity, uint64_t *d_meta) {
+  return (int)guarded([&]() -> int64_t {
+    if (!t || !x || !d_meta || (n && !d_keys)) { set_error("null argument"); return KH_ERR_INVALID; }
+    if (!hash_kind_supported(dist_hash) || n >= (1ULL << 32) || x->W != t->W || x->p > (uint32_t)PLAN_MAX_P || parity < 0 || parity > 1) {
+      set_error("khx_plan_scatter_slabs_dev: bad arguments"); return KH_ERR_INVALID;
+    }
+    if (2ULL * x->p * slab_cap > x->capacity) { set_error("receive buffers hold %llu keys, 2 x %u slabs of %llu do not fit",
+                                                          (unsigned long long)x->capacity, x->p, (unsigned long long)slab_cap); return KH_ERR_NOMEM; }
+    DeviceGuard g(t->device);
+    cudaStream_t s = t->stream[0];
+    const uint32_t p = x->p;
+    const int dk = fold_kind(dist_hash);
+    const BinSpec dist{1, 0, p, dk, make_hash_params(dk, dist_seed, t->W)};
+    unsigned long long *meta = reinterpret_cast<unsigned long long *>(d_meta);
+    KH_CUDA(cudaMemsetAsync(meta, 0, (size_t)p * META_WORDS * sizeof(unsigned long long), s));
+    if (n) {
+      BinDst dst{};
+      for (uint32_t r = 0; r < p; ++r) {
+        if (!x->remote[r]) { set_error("peer %u not mapped", r); return KH_ERR_INVALID; }
+        dst.base[r] = x->remote[r] + ((uint64_t)parity * p + x->rank) * slab_cap * t->W;
+      }
+      DevBuf<unsigned long long> cursors(p);
+      KH_CUDA(cudaMemsetAsync(cursors.p, 0, p * sizeof(unsigned long long), s));
+      const uint64_t tile = PS_TILE_BYTES / (8 * t->W);
+      const int grid = (int)std::max<uint64_t>(1, std::min<uint64_t>((n + tile - 1) / tile, (uint64_t)t->sms * 2));
+      if (t->W == 1) {
+        KH_CUDA(cudaFuncSetAttribute(plan_scatter_slabs_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ps_smem_bytes<1>(p)));
+        KH_LAUNCH((plan_scatter_slabs_kernel<1>), grid, PS_BLOCK, ps_smem_bytes<1>(p), s, d_keys, n, dist, t->hash_kind, t->hp, dst,
+                  (unsigned long long)slab_cap, cursors.p, meta);
+      } else {
+        KH_CUDA(cudaFuncSetAttribute(plan_scatter_slabs_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ps_smem_bytes<2>(p)));
+        KH_LAUNCH((plan_scatter_slabs_kernel<2>), grid, PS_BLOCK, ps_smem_bytes<2>(p), s, d_keys, n, dist, t->hash_kind, t->hp, dst,
+                  (unsigned long long)slab_cap, cursors.p, meta);
+      }
+      KH_CUDA(cudaStreamSynchronize(s));     // cursors goes out of scope; the stores have been issued and completed
+    } else {
+      KH_CUDA(cudaStreamSynchronize(s));
+    }
+    return KH_OK;
+  });
+}
+
+// Receiver of the slab exchange: counts[g] (HOST) keys lie in slab g of half `parity` of this rank's receive buffer.
+int64_t khx_insert_recv_slabs_dev(kh_table *t, khx_peer *x, uint64_t slab_cap, int parity, const uint64_t *counts,
+                                  const uint64_t *d_recv_meta, uint32_t default_val) {
+  return guarded([&]() -> int64_t {
+    if (!t || !x || !counts || !d_recv_meta) { set_error("null argument"); return KH_ERR_INVALID; }
+    if (x->W != t->W || parity < 0 || parity > 1 || 2ULL * x->p * slab_cap > x->capacity) { set_error("khx_insert_recv_slabs_dev: bad arguments"); return KH_ERR_INVALID; }
+    DeviceGuard g(t->device);
+    const uint32_t p = x->p;
+    SegSpec segs{};
+    segs.nseg = (int)p;
+    uint64_t n = 0;
+    for (uint32_t q = 0; q < p; ++q) {
+      if (counts[q] > slab_cap) { set_error("slab %u holds %llu keys, more than its capacity", q, (unsigned long long)counts[q]); return KH_ERR_INVALID; }
+      segs.prefix[q] = n;
+      segs.base[q] = ((uint64_t)parity * p + q) * slab_cap;
+      n += counts[q];
+    }
+    segs.prefix[p] = n;
+    if (n == 0) return 0;
+    cudaStream_t s = t->stream[0];
+    DevBuf<unsigned long long> fine(REGION_FINE), total(1);
+    DevBuf<uint32_t> regs(HLL_M);
+    KH_LAUNCH(merge_meta_kernel, (HLL_M + 255) / 256, 256, 0, s, reinterpret_cast<const unsigned long long *>(d_recv_meta), p,
+              fine.p, regs.p, total.p);
+    const double est = hll_finish(t->hash_kind, regs.p, nullptr, s);   // synchronises s
+    PreEstimate pre{est, fine.p, p > 1 ? &segs : nullptr};
+    return insert_dev_impl(t, x->local + (p > 1 ? 0 : segs.base[0] * t->W), nullptr, n, default_val, 1, &pre);
   });
 }
 

@@ -218,11 +218,15 @@ constexpr int RS_TILE_BYTES = 65536;
 // The batch may be handed over in up to WIN_MAX_DST pieces (the per-sender slabs of a peer receive buffer, exchange.cu):
 // logical position i lies in piece s with prefix[s] <= i < prefix[s+1], at keys[base[s] + i - prefix[s]].
 struct SegSpec { int nseg; unsigned long long prefix[WIN_MAX_DST + 1]; unsigned long long base[WIN_MAX_DST]; };
-__device__ __forceinline__ uint64_t seg_phys(const SegSpec &g, uint64_t i) {
-  if (g.nseg <= 1) return i;
+__device__ __forceinline__ int seg_index(const SegSpec &g, uint64_t i) {
   int s = 0;
 #pragma unroll
   for (int q = 1; q < WIN_MAX_DST; ++q) s += (q < g.nseg && i >= g.prefix[q]) ? 1 : 0;
+  return s;
+}
+__device__ __forceinline__ uint64_t seg_phys(const SegSpec &g, uint64_t i) {
+  if (g.nseg <= 1) return i;
+  const int s = seg_index(g, i);
   return g.base[s] + (i - g.prefix[s]);
 }
 template <int W> constexpr size_t rs_smem_bytes() {
@@ -253,10 +257,19 @@ __global__ void __launch_bounds__(RS_BLOCK, 2) region_scatter_kernel(const uint6
   for (uint64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
     const uint64_t base = tile * TILE;
     const int tile_n = (int)min((uint64_t)TILE, n - base);
+    // a tile that lies inside ONE piece (all but nseg-1 tiles) is addressed with a constant shift
+    uint64_t shift = 0;
+    bool one_piece = true;
+    if (segs.nseg > 1) {
+      const int s0 = seg_index(segs, base), s1 = seg_index(segs, base + tile_n - 1);
+      one_piece = s0 == s1;
+      shift = segs.base[s0] - segs.prefix[s0];
+    }
+    auto phys = [&](uint64_t i) -> uint64_t { return one_piece ? i + shift : seg_phys(segs, i); };
     const uint64_t next = tile + gridDim.x;
-    if (next < n_tiles && segs.nseg <= 1) {           // pull the next tile into L2 while this one is sorted
-      const char *pf = reinterpret_cast<const char *>(keys + next * TILE * W) + (size_t)threadIdx.x * 128;
-      if (next * TILE + ((size_t)threadIdx.x + 1) * (128 / (8 * W)) <= n) asm volatile("prefetch.global.L2 [%0];" ::"l"(pf));
+    if (next < n_tiles) {                             // pull the next tile into L2 while this one is sorted
+      const uint64_t pe = next * TILE + (uint64_t)threadIdx.x * (128 / (8 * W));
+      if (pe < n) asm volatile("prefetch.global.L2 [%0];" ::"l"(keys + seg_phys(segs, pe) * W));
     }
     for (int r = threadIdx.x; r < P; r += RS_BLOCK) cur[r] = 0;
     __syncthreads();
@@ -268,7 +281,7 @@ __global__ void __launch_bounds__(RS_BLOCK, 2) region_scatter_kernel(const uint6
 #pragma unroll
       for (int j = 0; j < B; ++j) {
         const int e = (j0 + j) * RS_BLOCK + threadIdx.x;
-        if (e < tile_n) load_key<W>(keys, seg_phys(segs, base + e), k[j]);
+        if (e < tile_n) load_key<W>(keys, phys(base + e), k[j]);
       }
 #pragma unroll
       for (int j = 0; j < B; ++j) {
@@ -303,7 +316,7 @@ __global__ void __launch_bounds__(RS_BLOCK, 2) region_scatter_kernel(const uint6
 #pragma unroll
       for (int j = 0; j < B; ++j) {
         const int e = (j0 + j) * RS_BLOCK + threadIdx.x;
-        if (e < tile_n) load_key<W>(keys, seg_phys(segs, base + e), k[j]);
+        if (e < tile_n) load_key<W>(keys, phys(base + e), k[j]);
       }
 #pragma unroll
       for (int j = 0; j < B; ++j) {

@@ -456,12 +456,25 @@ bool tile_candidate(const kh_table *t, const uint32_t *d_vals, uint64_t n, int &
   return subs_log2 <= 3;
 }
 
+// a batch handed over in pieces (SegSpec) -> one contiguous array, for the paths whose kernels want one
+const uint64_t *flatten_segments(kh_table *t, const uint64_t *d_keys, uint64_t n, const SegSpec *segs, DevBuf<uint64_t> &buf, cudaStream_t s) {
+  if (!segs || segs->nseg <= 1) return d_keys;
+  buf.alloc(n * t->W);
+  for (int q = 0; q < segs->nseg; ++q) {
+    const uint64_t c = segs->prefix[q + 1] - segs->prefix[q];
+    if (c) KH_CUDA(cudaMemcpyAsync(buf.p + segs->prefix[q] * t->W, d_keys + segs->base[q] * t->W, c * 8 * t->W, cudaMemcpyDeviceToDevice, s));
+  }
+  return buf.p;
+}
+
 uint64_t insert_tiled(kh_table *t, const uint64_t *d_keys, uint64_t n, uint32_t dflt, const unsigned long long *d_fine,
-                      int lp, int subs_log2, cudaStream_t s) {
+                      int lp, int subs_log2, cudaStream_t s, const SegSpec *segs = nullptr) {
   KH_CUDA(cudaFuncSetAttribute(tile_insert_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TI_SMEM));   // per device
   static const bool old_scatter = getenv("KH_SCATTER") && !strcmp(getenv("KH_SCATTER"), "old");
   constexpr int CSTRIDE = 16;          // one 128-byte line per cursor
   DevBuf<unsigned long long> fine_own, cursors((size_t)CSTRIDE << lp);
+  DevBuf<uint64_t> flat;
+  if (!d_fine || old_scatter) { d_keys = flatten_segments(t, d_keys, n, segs, flat, s); segs = nullptr; }
   if (!d_fine) {
     fine_own.alloc(REGION_FINE);
     kev_begin(t, 3, s);
@@ -479,7 +492,7 @@ uint64_t insert_tiled(kh_table *t, const uint64_t *d_keys, uint64_t n, uint32_t 
     kev_begin(t, 2, s);
     if (old_scatter) KH_LAUNCH((window_scatter_kernel<1, false, false, true>), t->sms * 4, WIN_BLOCK, 0, s, d_keys, n, spec, cursors.p,
                                sorted.p, nullptr, BinDst{}, ts);
-    else region_scatter_launch<1, true>(t->sms, s, d_keys, n, spec, cursors.p, sorted.p, ts);
+    else region_scatter_launch<1, true>(t->sms, s, d_keys, n, spec, cursors.p, sorted.p, ts, segs);
     kev_end(t, s); }
   DevBuf<uint32_t> defer(n);
   uint64_t added = 0, n_def = 0;
@@ -507,11 +520,13 @@ uint64_t insert_tiled(kh_table *t, const uint64_t *d_keys, uint64_t n, uint32_t 
 }
 
 uint64_t insert_windowed(kh_table *t, const uint64_t *d_keys, const uint32_t *d_vals, uint64_t n, uint32_t dflt,
-                         const unsigned long long *d_fine, cudaStream_t s) {
+                         const unsigned long long *d_fine, cudaStream_t s, const SegSpec *segs = nullptr) {
   int tile_lp = 0, tile_subs = 0;
-  if (tile_candidate(t, d_vals, n, tile_lp, tile_subs)) return insert_tiled(t, d_keys, n, dflt, d_fine, tile_lp, tile_subs, s);
+  if (tile_candidate(t, d_vals, n, tile_lp, tile_subs)) return insert_tiled(t, d_keys, n, dflt, d_fine, tile_lp, tile_subs, s, segs);
   const uint64_t table_bytes = t->capacity * (uint64_t)t->slot_bytes();
   const bool windowed = window_candidate(t, d_vals, n) && table_bytes >= 4 * t->window_bytes;
+  DevBuf<uint64_t> flat;
+  if (!windowed || !d_fine) { d_keys = flatten_segments(t, d_keys, n, segs, flat, s); segs = nullptr; }
   if (!windowed) return insert_resident(t, d_keys, d_vals, n, dflt, s);
   const int lp = std::min(log2_u64(next_pow2(table_bytes / t->window_bytes)), REGION_FINE_BITS);
   DevBuf<unsigned long long> fine_own, cursors(1u << lp);
@@ -526,8 +541,8 @@ uint64_t insert_windowed(kh_table *t, const uint64_t *d_keys, const uint32_t *d_
   { Trace tr("window.scatter", s);
     const BinSpec spec{0, lp, 0u, t->hash_kind, t->hp};
     const TagSpec ts{nullptr, 32, 0u, 1};
-    if (t->W == 1) region_scatter_launch<1, false>(t->sms, s, d_keys, n, spec, cursors.p, sorted.p, ts);
-    else region_scatter_launch<2, false>(t->sms, s, d_keys, n, spec, cursors.p, sorted.p, ts); }
+    if (t->W == 1) region_scatter_launch<1, false>(t->sms, s, d_keys, n, spec, cursors.p, sorted.p, ts, segs);
+    else region_scatter_launch<2, false>(t->sms, s, d_keys, n, spec, cursors.p, sorted.p, ts, segs); }
   Trace tr("window.insert", s);
   return insert_resident(t, sorted.p, nullptr, n, dflt, s, true);   // synchronises s before the scratch is released
 }
@@ -740,9 +755,12 @@ int64_t kh::insert_dev_impl(kh_table *t, const uint64_t *d_keys, const uint32_t 
     single = (double)t->size + std::min((double)n, est * err) <= t->max_load * (double)t->capacity;
   }
   Trace tr_ins("insert.total", s);
+  const SegSpec *segs = pre ? pre->segs : nullptr;
+  DevBuf<uint64_t> flat;
   if (single) {
-    insert_windowed(t, d_keys, d_vals, n, dflt, pre ? pre->fine : (have_fine ? fine.p : nullptr), s);
+    insert_windowed(t, d_keys, d_vals, n, dflt, pre ? pre->fine : (have_fine ? fine.p : nullptr), s, segs);
   } else {
+    d_keys = flatten_segments(t, d_keys, n, segs, flat, s);
     // Growth without an estimate = the reference's insert_no_estimate: fill up to max_load, double, continue.
     // A piece may overshoot max_load (duplicates usually keep it far below); it never fills the table:
     // the hard limit is halfway between max_load and 1.

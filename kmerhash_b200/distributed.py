@@ -142,6 +142,12 @@ class CudaEngine:
     def insert_recv_ptr(self, ptr, n, recv_meta, default):
         return self.table.insert_recv_ptr(ptr, n, recv_meta, default) if n else 0
 
+    def plan_scatter_slabs(self, keys, peers, slab_cap, parity):
+        return self.table.plan_scatter_slabs(keys, peers.h, peers.p, slab_cap, parity, self.dist_hash)
+
+    def insert_recv_slabs(self, peers, slab_cap, parity, counts, recv_meta, default):
+        return self.table.insert_recv_slabs(peers.h, slab_cap, parity, counts, recv_meta, default) if int(counts.sum()) else 0
+
     def count(self, keys):
         return self.table.count(keys) if keys.shape[0] else self.empty_like_result(0, torch.uint8)
 
@@ -175,6 +181,12 @@ class DistributedMap:
         # fused partition + exchange over peer memory (NVLink): on when every rank could map every buffer
         self.peer_stores = os.environ.get("KH_PEER_STORES", "1") not in ("0", "")
         self.peers = None
+        # single-pass sender into per-sender slabs of the receive buffers (csrc/exchange.cu: plan_scatter_slabs_kernel)
+        self.slabs = os.environ.get("KH_SLABS", "1") not in ("0", "")
+        self.slab_cap = 0                 # keys per (owner, sender) slab; the buffers hold 2 halves x p slabs
+        self.parity = 0
+        self.slab_misses = 0              # consecutive batches that overflowed a slab (skewed owners)
+        self._exact_dirty = False         # the last batch went through the exact path: its buffer use overlaps both halves
 
     # ---- the exchange ---------------------------------------------------------------------------
     def _counts_a2a(self, counts):
@@ -256,6 +268,84 @@ class DistributedMap:
         """partition and exchange as ONE kernel: the rank scatter stores every key straight into the receive buffer
         of its owner GPU through CUDA-IPC mapped peer memory (NVLink); NCCL only carries the p x p metadata."""
         p, rank, dev = self.p, self.rank, self.e.device
+        if self.slabs and hasattr(self.e, "plan_scatter_slabs"):
+            r = self._insert_slabs(keys, default)
+            if r is not None:
+                return r
+            return self._insert_exact(keys, default, ordered=True)
+        return self._insert_exact(keys, default, ordered=False)
+
+    def _ensure_peers(self, capacity):
+        """(re)allocate the receive buffers; collective.  False when IPC / peer access is unavailable."""
+        if self.peers is not None:
+            self.peers.close()
+        self.peers = PeerBuffers(self.e.device.index, self.rank, self.p, int(capacity), self.W, self.group)
+        if not self.peers.ok:
+            self.peer_stores = False
+            self.peers.close(); self.peers = None
+            return False
+        return True
+
+    def _insert_slabs(self, keys, default):
+        """ONE pass over the keys on the sender: metadata + stores into this rank's slab of every owner's buffer; the
+        metadata all-gather that follows is also the barrier behind the stores.  Returns None when a slab overflowed
+        (every rank sees the same count matrix, so every rank takes the exact path for this batch)."""
+        p, rank, dev = self.p, self.rank, self.e.device
+        n = int(keys.shape[0])
+        if self.peers is None or self.slab_cap == 0:
+            nmax = torch.tensor([n], dtype=torch.int64, device=dev)
+            dist.all_reduce(nmax, op=dist.ReduceOp.MAX, group=self.group)
+            self.slab_cap = int(int(nmax.item()) / p * 1.25) + 4096
+            if not self._ensure_peers(2 * p * self.slab_cap):
+                return self._insert_planned(keys, default)
+            self.parity, self._exact_dirty = 0, False
+        if self._exact_dirty:                                              # a rank may still read the exact-path buffer
+            dist.barrier(group=self.group)
+            self._exact_dirty = False
+        parity = self.parity
+        with _Stage("plan+scatter"):
+            meta = self.e.plan_scatter_slabs(keys, self.peers, self.slab_cap, parity)
+        with _Stage("meta gather"):
+            allmeta = torch.empty((p,) + tuple(meta.shape), dtype=meta.dtype, device=dev)
+            dist.all_gather_into_tensor(allmeta, meta, group=self.group)   # every rank's stores have landed
+            C = allmeta[:, :, 0].cpu().numpy().astype(np.uint64)           # C[g][r] = keys g sends to r
+        self._allmeta, self._C = allmeta, C
+        if int(C.max()) > self.slab_cap:
+            self.slab_misses += 1
+            return None
+        self.slab_misses = 0
+        self.parity ^= 1
+        self.last_exchange_bytes += 8 * self.W * int(C[rank].sum() - C[rank, rank])
+        recv_meta = allmeta[:, rank, :].contiguous()
+        with _Stage("local insert"):
+            return self.e.insert_recv_slabs(self.peers, self.slab_cap, parity, C[:, rank], recv_meta, default)
+
+    def _insert_exact(self, keys, default, ordered):
+        """two-pass sender: metadata pass -> all-gather -> exact offsets -> rank scatter into the owners' buffers.
+        ordered=True: called after a slab overflow, the metadata of this batch is already gathered."""
+        p, rank, dev = self.p, self.rank, self.e.device
+        if ordered:
+            allmeta, C = self._allmeta, self._C
+            need = int(C.sum(axis=0).max())
+            grow = need > self.peers.capacity
+            if self.slab_misses >= 2:                        # owners stay skewed: keep to the exact path from now on
+                self.slabs = False
+            elif int(C.max()) * p <= 2 * int(C.sum(axis=1).max()):   # balanced owners, larger batches: larger slabs
+                self.slab_cap = int(int(C.max()) * 1.25) + 4096
+                grow = grow or 2 * p * self.slab_cap > self.peers.capacity
+            if grow and not self._ensure_peers(max(int(need * 1.25) + 1024, 2 * p * self.slab_cap)):
+                return self._insert_planned(keys, default)
+            self._exact_dirty = True
+            self.parity = 0
+            dst_off = C[:rank, :].sum(axis=0)
+            dst_cnt = C[rank, :]
+            self.last_exchange_bytes += 8 * self.W * int(dst_cnt.sum() - dst_cnt[rank])
+            with _Stage("scatter->peers"):
+                self.e.scatter_peers(keys, self.peers, dst_off, dst_cnt)
+                dist.barrier(group=self.group)
+            recv_meta = allmeta[:, rank, :].contiguous()
+            with _Stage("local insert"):
+                return self.e.insert_recv_ptr(self.peers.recv_ptr(), int(C[:, rank].sum()), recv_meta, default)
         with _Stage("plan"):
             meta = self.e.plan(keys, p)
         with _Stage("meta gather"):

@@ -183,6 +183,24 @@ class HashMap:
         check(lib.khx_scatter_peers_dev(self._h, HASH_KINDS[dist_hash], dist_seed, k.data_ptr(), n, peer_handle,
                                         off.ctypes.data, cnt.ctypes.data), "scatter_peers")
 
+    def plan_scatter_slabs(self, keys, peer_handle, p, slab_cap, parity, dist_hash="MURMUR64avx", dist_seed=9876543):
+        """single-pass sender: metadata + rank scatter into this rank's slab of every owner's receive buffer
+        (half `parity`); returns the [p, khx_meta_words] metadata tensor"""
+        k, n = _dev_keys(keys, self.W, self.device)
+        meta = torch.empty((p, lib.khx_meta_words()), dtype=torch.int64, device=k.device)
+        check(lib.khx_plan_scatter_slabs_dev(self._h, HASH_KINDS[dist_hash], dist_seed, k.data_ptr(), n, peer_handle,
+                                             int(slab_cap), int(parity), meta.data_ptr()), "plan_scatter_slabs")
+        return meta
+
+    def insert_recv_slabs(self, peer_handle, slab_cap, parity, counts, recv_meta, default=1):
+        """receiver half reading the p slabs of this rank's receive buffer in place; counts[g] = keys sender g stored"""
+        assert recv_meta.is_cuda and recv_meta.dtype == torch.int64 and recv_meta.is_contiguous()
+        cnt = np.ascontiguousarray(counts, dtype=np.uint64)
+        assert cnt.shape[0] == recv_meta.shape[0]
+        torch.cuda.current_stream(self.device).synchronize()
+        return check(lib.khx_insert_recv_slabs_dev(self._h, peer_handle, int(slab_cap), int(parity), cnt.ctypes.data,
+                                                   recv_meta.data_ptr(), default), "insert_recv_slabs")
+
     def insert_recv_ptr(self, ptr, n, recv_meta, default=1):
         """receiver half on a raw device pointer (the peer receive buffer)"""
         assert recv_meta.is_cuda and recv_meta.dtype == torch.int64 and recv_meta.is_contiguous()

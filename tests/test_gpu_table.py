@@ -429,6 +429,87 @@ def test_fused_scatter_into_peer_buffers(kh, oracle_mod, p, W):
                 lib.khx_peer_destroy(h)
 
 
+@pytest.mark.parametrize("p,W,n_per,tiled", [(2, 1, 90000, False), (3, 2, 60000, False), (8, 1, 70000, False), (8, 2, 30000, False),
+                                             (2, 1, 3000000, True), (8, 1, 1500000, True)])
+def test_single_pass_slab_exchange(kh, oracle_mod, p, W, n_per, tiled):
+    """khx_plan_scatter_slabs_dev + khx_insert_recv_slabs_dev (p ranks emulated on one GPU): the one-pass sender must
+    produce the metadata of khx_plan_dev bit for bit and fill slab (owner r, sender g) with exactly the keys the
+    reference's rule sends from g to r; the receiver, reading the slabs in place, must build the reference's per-rank
+    table.  Two batches on alternating halves; then an overflowing slab: nothing may be written past it and the
+    metadata must still carry the true counts."""
+    import ctypes
+    import torch
+    from kmerhash_b200._lib import lib
+    o = oracle_mod.port
+    cudart = ctypes.CDLL("libcudart.so")
+    rng = np.random.default_rng(170 + p + W)
+    n_base = max(20000, n_per // 4)
+    base = rng.integers(0, 2**62, size=(n_base, W), dtype=np.uint64)
+    tables = [kh.HashMap(W, "MURMUR64avx", "COUNT") for _ in range(p)]
+    if tiled:
+        for t in tables:
+            t.set_insert_window(True, 1 << 14, 1)
+    slab_cap = int(n_per / p * 1.5) + 1024
+    cap = 2 * p * slab_cap + 64                                    # 64 guard keys behind the last slab
+    peers = [lib.khx_peer_create(0, r, p, cap, W) for r in range(p)]
+
+    def read_buf(r):
+        buf = torch.empty((cap, W), dtype=torch.int64, device="cuda")
+        torch.cuda.synchronize()
+        assert cudart.cudaMemcpy(ctypes.c_void_p(buf.data_ptr()), ctypes.c_void_p(lib.khx_peer_recv_ptr(peers[r])),
+                                 ctypes.c_size_t(cap * 8 * W), 3) == 0
+        return buf.cpu().numpy().view(np.uint64)
+
+    def srt(a):
+        return np.sort(a[:, 0]) if W == 1 else a[np.lexsort(a.T[::-1])]
+
+    try:
+        assert all(peers)
+        for r in range(p):
+            for q in range(p):
+                if q != r:
+                    assert lib.khx_peer_set(peers[r], q, lib.khx_peer_recv_ptr(peers[q])) == 0
+        gm = o.Map(W, "COUNT")
+        for parity in (0, 1):
+            batches = [np.ascontiguousarray(base[rng.integers(0, n_base, size=n_per + 777 * g)]) for g in range(p)]
+            flat = [b if W == 2 else np.ascontiguousarray(b[:, 0]) for b in batches]
+            dkeys = [torch.from_numpy(b.view(np.int64)).cuda() for b in flat]
+            metas = [tables[g].plan_scatter_slabs(dkeys[g], peers[g], p, slab_cap, parity) for g in range(p)]
+            for g in range(p):
+                assert torch.equal(metas[g], tables[g].plan(dkeys[g], p))
+            allmeta = torch.stack(metas)
+            Cm = allmeta[:, :, 0].cpu().numpy().astype(np.uint64)
+            assert int(Cm.max()) <= slab_cap
+            for r in range(p):
+                got = read_buf(r)
+                for g in range(p):
+                    lo = (parity * p + g) * slab_cap
+                    src = batches[g][o.rank("MURMUR64avx", flat[g], p) == r]
+                    assert int(Cm[g, r]) == len(src)
+                    assert np.array_equal(srt(got[lo:lo + len(src)]), srt(src))
+            gm.insert(np.concatenate(flat), default=1)
+            gk, gv = gm.to_vector()
+            owner = o.rank("MURMUR64avx", gk, p)
+            for r in range(p):
+                tables[r].insert_recv_slabs(peers[r], slab_cap, parity, Cm[:, r], allmeta[:, r, :].contiguous(), 1)
+                ek, ev = sort_pairs(gk[owner == r], gv[owner == r])
+                tk, tv = sort_pairs(*tables[r].to_vector())
+                assert np.array_equal(tk, ek) and np.array_equal(tv, ev)
+        # overflow: slabs far too small.  Guard keys behind each slab region must survive; counts stay true.
+        small = 1000
+        before = [read_buf(r) for r in range(p)]
+        meta = tables[0].plan_scatter_slabs(dkeys[0], peers[0], p, small, 0)
+        assert torch.equal(meta[:, 0], tables[0].plan(dkeys[0], p)[:, 0]) and int(meta[:, 0].max()) > small
+        for r in range(p):
+            after = read_buf(r)
+            changed = np.nonzero((after != before[r]).any(axis=1))[0]
+            assert changed.size == 0 or (changed.min() >= 0 and changed.max() < small)   # sender 0, half 0: slab [0, small)
+    finally:
+        for h in peers:
+            if h:
+                lib.khx_peer_destroy(h)
+
+
 @pytest.mark.parametrize("max_load", [0.8, 0.97])
 def test_tile_insert_deferred_chains_and_side_key(kh, oracle_mod, max_load):
     """shared-memory tile insert (kh_tile.cuh): chains that leave their 8192-slot tile and the all-ones key are

@@ -1,0 +1,77 @@
+"""Parity of DistributedMap on real GPUs (torchrun, NCCL): every rank's table must hold exactly what the reference's rank
+of the same index holds -- { (k, c) in the global count map : DistHash_9876543(k) & (p-1) == rank } -- after a sequence
+of batches that exercises the single-pass slab exchange, its overflow fallback (skewed owners), the growth of the
+slabs (a larger batch) and the return to the slab path.  The oracle (oracle/, CPU) is the checker.
+  python -m torch.distributed.run --nproc-per-node 2 --master-addr 127.0.0.1 tools/dist_parity.py
+Prints one line per rank; exit code 1 on any mismatch."""
+import os
+import sys
+
+ROOT = os.path.join(os.path.dirname(os.path.abspath(__file__)), "..")
+sys.path.insert(0, ROOT)
+import numpy as np
+import torch
+import torch.distributed as dist
+
+import kmerhash_b200 as kh
+from kmerhash_b200.distributed import DistributedMap
+import oracle
+
+rank, local, p = int(os.environ["RANK"]), int(os.environ["LOCAL_RANK"]), int(os.environ["WORLD_SIZE"])
+torch.cuda.set_device(local)
+os.environ.setdefault("NCCL_DEBUG", "WARN")
+dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+o = oracle.port
+
+
+def batch_of(seed, n, skew=False):
+    """every rank can regenerate every rank's batch (the checker needs the global multiset)"""
+    rng = np.random.default_rng(seed)
+    base = rng.integers(0, 2**62, size=max(1000, n // 5), dtype=np.uint64)
+    b = base[rng.integers(0, base.shape[0], size=n)]
+    if skew:                                      # 70 % of the batch is ONE key: its owner's slab overflows
+        b[rng.random(n) < 0.7] = base[0]
+    return np.ascontiguousarray(b)
+
+
+def sort_pairs(k, v):
+    order = np.argsort(k, kind="stable")
+    return k[order], v[order]
+
+
+ok = True
+for n0 in (5_000_000, 200_000):                   # tile-insert sized and small batches
+    m = DistributedMap(1, "MURMUR64avx", "MURMUR64avx", "COUNT", device=local)
+    ref = o.Map(1, "COUNT")
+    plan = [(n0, False), (n0, False), (n0, True), (n0, False), (3 * n0, False), (3 * n0, False), (n0, True), (n0, True), (n0, False)]
+    path = []
+    for step, (n, skew) in enumerate(plan):
+        mine = None
+        for g in range(p):
+            b = batch_of(1000 * step + g + n0 % 97, n + 1234 * g, skew)
+            ref.insert(b, default=1)
+            if g == rank:
+                mine = b
+        m.insert(torch.from_numpy(mine.view(np.int64)).cuda())
+        path.append("slab" if (m.slabs and m.slab_misses == 0) else "exact")
+        gk, gv = ref.to_vector()
+        own = o.rank("MURMUR64avx", gk, p) == rank
+        ek, ev = sort_pairs(gk[own], gv[own])
+        tk, tv = sort_pairs(*m.to_vector())
+        good = np.array_equal(tk, ek) and np.array_equal(tv.astype(np.uint32), ev.astype(np.uint32))
+        ok = ok and good
+        if not good:
+            print("rank %d n0 %d step %d MISMATCH: %d vs %d entries" % (rank, n0, step, len(tk), len(ek)), flush=True)
+    q = batch_of(5, 100000)
+    found = m.find(torch.from_numpy(q.view(np.int64)).cuda(), 0).cpu().numpy().astype(np.uint32)
+    gk, gv = ref.to_vector()
+    d = dict(zip(gk.tolist(), gv.tolist()))
+    exp = np.array([d.get(int(x), 0) for x in q], dtype=np.uint32)
+    ok = ok and np.array_equal(found, exp)
+    print("rank %d n0 %d paths %s size %d %s" % (rank, n0, ",".join(path), m.local_size(), "OK" if ok else "FAIL"), flush=True)
+
+flag = torch.tensor([1 if ok else 0], device="cuda")
+dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+dist.barrier()
+dist.destroy_process_group()
+sys.exit(0 if int(flag.item()) else 1)
