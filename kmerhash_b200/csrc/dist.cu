@@ -183,6 +183,23 @@ khd_map *khd_create(int n_gpus, int key_words, int store_hash, int dist_hash, in
         if (e == cudaErrorPeerAccessAlreadyEnabled) cudaGetLastError();
         else if (e != cudaSuccess) { cudaGetLastError(); m->p2p = false; }
       }
+      // the receive buffers come from this device's stream-ordered pool (DevBuf): cudaDeviceEnablePeerAccess covers
+      // cudaMalloc memory only, pool memory needs its own grant for every peer that stores into it
+      if (n_gpus > 1) {
+        pool_setup(g);
+        cudaMemPool_t pool;
+        KH_CUDA(cudaDeviceGetDefaultMemPool(&pool, g));
+        std::vector<cudaMemAccessDesc> acc;
+        for (int r = 0; r < n_gpus; ++r) if (r != g) {
+          int can = 0;
+          KH_CUDA(cudaDeviceCanAccessPeer(&can, r, g));
+          if (!can) continue;
+          cudaMemAccessDesc d{};
+          d.location.type = cudaMemLocationTypeDevice; d.location.id = r; d.flags = cudaMemAccessFlagsProtReadWrite;
+          acc.push_back(d);
+        }
+        if (!acc.empty() && cudaMemPoolSetAccess(pool, acc.data(), acc.size()) != cudaSuccess) { cudaGetLastError(); m->p2p = false; }
+      }
       const uint32_t seed = (fold_kind(store_hash) == KH_HASH_CRC32C) ? KH_DEFAULT_CRC_SEED : KH_DEFAULT_SEED;
       m->table[g] = kh_create(g, KH_MAP_ROBINHOOD_OFFSETS, key_words, store_hash, seed, reducer);
       if (!m->table[g]) return KH_ERR_CUDA;
@@ -195,10 +212,13 @@ khd_map *khd_create(int n_gpus, int key_words, int store_hash, int dist_hash, in
 
 void khd_destroy(khd_map *m) {
   if (!m) return;
+  int prev = -1;
+  cudaGetDevice(&prev);                 // the caller's current device is not ours to change
   for (int g = 0; g < (int)m->table.size(); ++g) {
     if (m->table[g]) kh_destroy(m->table[g]);
     if (m->stream[g]) { cudaSetDevice(m->dev[g]); cudaStreamDestroy(m->stream[g]); }
   }
+  if (prev >= 0) cudaSetDevice(prev);
   delete m;
 }
 

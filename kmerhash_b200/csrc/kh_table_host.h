@@ -15,6 +15,7 @@ struct kh_table {
   int LB = 32, G = 2;                 // probe geometry (DESIGN.md "bucket geometry")
   bool window_on = true;              // L2-windowed bulk insert (KH_WINDOW=0 switches it off for A/B runs)
   uint64_t window_bytes = 32ULL << 20, window_min_keys = 1ULL << 22;
+  bool uninit = false;                // slots allocated but not yet initialised (insert_dev_impl -> tile insert writes every tile)
   bool has_sticky = false;            // an erase may have left sticky bits since the last rebuild / clear (kh_tile.cuh needs none)
   uint64_t capacity = 0, size = 0;
   HashParams hp;

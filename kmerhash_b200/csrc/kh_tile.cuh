@@ -41,7 +41,7 @@ struct TileArgs {
   const unsigned long long *bin_end;     // end offset of every coarse region in keys/tags (scatter cursors)
   int bin_stride;                        // elements between two regions' cursors
   int subs_log2;                         // tiles per coarse region = 1 << subs_log2
-  int fresh;                             // the table holds no entry: skip reading it
+  int fresh;                             // the table holds no entry: skip reading it (2: slots uninitialised, write every tile)
   uint32_t dflt;                         // addend of every key
   unsigned long long *n_new;             // [0] += new keys, [1] += deferred keys
   uint32_t *defer_idx;                   // positions (in `keys`) of the deferred keys
@@ -98,7 +98,7 @@ __global__ void __launch_bounds__(TI_THREADS, 2) tile_insert_kernel(TileArgs a) 
     // batch positions are 32-bit (the host keeps n < 2^32)
     const uint32_t begin = c ? (uint32_t)a.bin_end[(c - 1) * a.bin_stride] : 0u, end = (uint32_t)a.bin_end[c * a.bin_stride];
     uint4 *g = reinterpret_cast<uint4 *>(a.t.slots) + tile * TI_SLOTS;
-    if (a.fresh && begin == end) continue;          // nothing to add to an empty tile (uniform per CTA)
+    if (a.fresh == 1 && begin == end) continue;     // nothing to add to an empty tile (uniform per CTA)
 
     // ---- stage the tile -------------------------------------------------------------------
     if (a.fresh) {

@@ -214,10 +214,19 @@ void default_geometry(int W, int &LB, int &G) {
   }
 }
 
+void init_slots(kh_table *t, uint64_t cap, unsigned char *p, cudaStream_t s) {
+  const uint64_t units = cap * t->slot_bytes() / 16;
+  KH_LAUNCH(init_slots_kernel, t->grid_for(units, 256 * 4), 256, 0, s, reinterpret_cast<uint4 *>(p), units, t->W);
+}
 void alloc_slots(kh_table *t, uint64_t cap, DevBuf<unsigned char> &buf, cudaStream_t s) {
   buf.alloc(cap * t->slot_bytes());
-  const uint64_t units = cap * t->slot_bytes() / 16;
-  KH_LAUNCH(init_slots_kernel, t->grid_for(units, 256 * 4), 256, 0, s, reinterpret_cast<uint4 *>(buf.p), units, t->W);
+  init_slots(t, cap, buf.p, s);
+}
+// a table whose initialisation was left to the tile insert (rebuild(..., lazy)) and that takes another path after all
+void materialize(kh_table *t, cudaStream_t s) {
+  if (!t->uninit) return;
+  t->uninit = false;
+  init_slots(t, t->capacity, t->slots.p, s);
 }
 
 uint64_t capacity_for(const kh_table *t, uint64_t n) {
@@ -333,18 +342,23 @@ void seal(kh_table *t, cudaStream_t s) {
 
 // bulk rebuild into `new_cap` slots: dump -> fresh table -> insert (keys are unique, fresh vals are 0,
 // so the COUNT-mode add is a plain copy for every reducer).  The side slot is not touched.
-void rebuild(kh_table *t, uint64_t new_cap) {
+// lazy: an EMPTY table's new slots are left uninitialised (t->uninit); the caller guarantees that the tile insert, which
+// writes every tile of a fresh table anyway, or materialize() follows before anything reads the table.
+void rebuild(kh_table *t, uint64_t new_cap, bool lazy = false) {
   cudaStream_t s = t->stream[0];
   Trace tr_all("rebuild", s);
   new_cap = std::max<uint64_t>(next_pow2(new_cap), 128);
   t->has_sticky = false;               // every path below ends with freshly initialised slots
   if (t->capacity == 0 || t->size == 0) {
     t->slots.release();
-    alloc_slots(t, new_cap, t->slots, s);
+    t->uninit = false;
+    if (lazy) { t->slots.alloc(new_cap * t->slot_bytes()); t->uninit = true; }
+    else alloc_slots(t, new_cap, t->slots, s);
     t->capacity = new_cap;
     KH_CUDA(cudaStreamSynchronize(s));
     return;
   }
+  materialize(t, s);
   DevBuf<uint64_t> keys(t->size * t->W);
   DevBuf<uint32_t> vals(t->size);
   uint64_t n;
@@ -365,9 +379,9 @@ void rebuild(kh_table *t, uint64_t new_cap) {
   if (t->reducer == KH_REDUCE_FIRST) { seal(t, s); KH_CUDA(cudaStreamSynchronize(s)); }
 }
 
-void ensure_room(kh_table *t, uint64_t n_more) {
+void ensure_room(kh_table *t, uint64_t n_more, bool lazy = false) {
   const uint64_t want = capacity_for(t, t->size + n_more);
-  if (want > t->capacity) rebuild(t, want);
+  if (want > t->capacity) rebuild(t, want, lazy);
 }
 
 bool window_candidate(const kh_table *t, const uint32_t *d_vals, uint64_t n) {
@@ -500,7 +514,8 @@ uint64_t insert_tiled(kh_table *t, const uint64_t *d_keys, uint64_t n, uint32_t 
     zero_counter(t, s);
     TileArgs a;
     a.t = t->view(); a.keys = sorted.p; a.tags = tags.p; a.bin_end = cursors.p; a.bin_stride = CSTRIDE; a.subs_log2 = subs_log2;
-    a.fresh = t->size == 0 ? 1 : 0; a.dflt = dflt; a.n_new = t->counters.p; a.defer_idx = defer.p;
+    a.fresh = t->uninit ? 2 : (t->size == 0 ? 1 : 0); a.dflt = dflt;   // 2: the slots hold garbage, every tile is written
+    t->uninit = false; a.n_new = t->counters.p; a.defer_idx = defer.p;
     const uint64_t n_tiles = t->capacity / TI_SLOTS;
     const int grid = (int)std::min<uint64_t>(n_tiles, (uint64_t)t->sms * 2);
     kev_begin(t, 0, s);
@@ -523,6 +538,7 @@ uint64_t insert_windowed(kh_table *t, const uint64_t *d_keys, const uint32_t *d_
                          const unsigned long long *d_fine, cudaStream_t s, const SegSpec *segs = nullptr) {
   int tile_lp = 0, tile_subs = 0;
   if (tile_candidate(t, d_vals, n, tile_lp, tile_subs)) return insert_tiled(t, d_keys, n, dflt, d_fine, tile_lp, tile_subs, s, segs);
+  materialize(t, s);
   const uint64_t table_bytes = t->capacity * (uint64_t)t->slot_bytes();
   const bool windowed = window_candidate(t, d_vals, n) && table_bytes >= 4 * t->window_bytes;
   DevBuf<uint64_t> flat;
@@ -744,9 +760,16 @@ int64_t kh::insert_dev_impl(kh_table *t, const uint64_t *d_keys, const uint32_t 
   if (estimate) {
     // insert_impl: reserve(size + estimate * (1 + error)) then one pass (:2512-2535)
     const double est = estimate_batch();
-    ensure_room(t, (uint64_t)std::ceil(std::min((double)n, est * err)));
+    // an empty COUNT table about to take a large uniform batch: the tile insert writes every tile, skip the init pass
+    const bool lazy = t->size == 0 && window_candidate(t, d_vals, n);
+    ensure_room(t, (uint64_t)std::ceil(std::min((double)n, est * err)), lazy);
     single = count_mode;
   }
+  struct Materialize {                  // whatever path follows (or throws): never leave uninitialised slots behind
+    kh_table *t; cudaStream_t s;
+    ~Materialize() { if (t->uninit) { try { materialize(t, s); cudaStreamSynchronize(s); } catch (...) {} } }
+  } mat_guard{t, s};
+  if (!single) materialize(t, s);
   if (!single && (double)(t->size + n) <= t->max_load * (double)t->capacity) single = true;
   if (!single && !estimate && count_mode && n >= (1ULL << 16)) {
     // insert_no_estimate on a table the caller reserved (the drivers: estimate -> reserve -> insert_no_estimate):
