@@ -40,10 +40,14 @@ def sort_pairs(k, v):
 
 
 ok = True
-for n0 in (5_000_000, 200_000):                   # tile-insert sized and small batches
+SIZES = [int(x) for x in os.environ.get("KH_PARITY_N0", "5000000,200000").split(",")]   # tile-insert sized and small batches
+SHORT = os.environ.get("KH_PARITY_SHORT", "0") not in ("", "0")
+for n0 in SIZES:
     m = DistributedMap(1, "MURMUR64avx", "MURMUR64avx", "COUNT", device=local)
     ref = o.Map(1, "COUNT")
     plan = [(n0, False), (n0, False), (n0, True), (n0, False), (3 * n0, False), (3 * n0, False), (n0, True), (n0, True), (n0, False)]
+    if SHORT:
+        plan = [(n0, False), (n0, True), (n0, False), (3 * n0, False), (n0, False)]
     path = []
     for step, (n, skew) in enumerate(plan):
         mine = None
