@@ -276,6 +276,28 @@ int khx_plan_scatter_slabs_dev(kh_table *t, int dist_hash, uint32_t dist_seed, c
 int64_t khx_insert_recv_slabs_dev(kh_table *t, khx_peer *x, uint64_t slab_cap, int parity, const uint64_t *counts,
                                   const uint64_t *d_recv_meta, uint32_t default_val);
 
+/* Query exchange over the slabs: replaces the exchange of count_p / find_p / erase_p
+ * (KH/distributed_batched_robinhood_map.hpp:1258-1516,1619,2169) and the reply of ialltoallv_and_query_one_to_one
+ * (KH/incremental_mxx.hpp:4403).  Buffers come from khx_peer_create_q: p slabs of slab_cap keys followed by a reply region
+ * (4 bytes per key).  Asker: khx_query_scatter_slabs_dev stores its keys for owner r into slab `rank` of r's buffer,
+ * d_perm[r * slab_cap + i] (DEVICE, p * slab_cap u32) = input index of the i-th key sent to r, d_counts[r] (DEVICE) = keys
+ * for r (a slab that would overflow is cut off, the count stays true: the caller sees it in the gathered counts and falls
+ * back).  Owner, once every asker's stores have landed: khx_query_slabs_dev looks the slabs up (op 0 find -> u32, 1 count ->
+ * u8, 2 erase) and stores the answers straight into slab `rank` of asker g's reply region; returns #hits / #erased.
+ * Asker, once every owner's answers have landed: khx_unpermute_slabs_dev puts them into input order in d_out. */
+khx_peer *khx_peer_create_q(int device, uint32_t rank, uint32_t p, uint64_t capacity_keys, int key_words);
+/* Barrier between the ranks over peer memory (flags in a header behind every receive buffer; replaces the MPI_Barrier /
+ * MPI_Waitall points of khmxx, KH/incremental_mxx.hpp:3437-4403): returns once every rank has called it with the same
+ * epoch (1, 2, 3, ... per buffer set); all peer stores a rank issued before its call are then visible to their owners.
+ * d_counts_row (DEVICE, p words or NULL) is published to every rank, counts_matrix (HOST, p x p or NULL) receives the
+ * matrix [sender][owner].  KH_ERR_CUDA when a peer does not arrive within 10 s. */
+int khx_peer_sync_dev(kh_table *t, khx_peer *x, uint64_t epoch, const uint64_t *d_counts_row, uint64_t *counts_matrix);
+int khx_query_scatter_slabs_dev(kh_table *t, int dist_hash, uint32_t dist_seed, const uint64_t *d_keys, uint64_t n, khx_peer *x,
+                                uint64_t slab_cap, uint32_t *d_perm, uint64_t *d_counts);
+int64_t khx_query_slabs_dev(kh_table *t, khx_peer *x, int op, uint64_t slab_cap, const uint64_t *counts, uint32_t nonexistent);
+int khx_unpermute_slabs_dev(kh_table *t, khx_peer *x, int elem_bytes, uint64_t slab_cap, const uint32_t *d_perm,
+                            const uint64_t *d_counts, uint64_t n, void *d_out);
+
 /* ---- single-process multi-GPU map ------------------------------------------------------
  * replaces dsc::counting_batched_robinhood_map / batched_robinhood_map
  * (KH/distributed_batched_robinhood_map.hpp:748-832,1187,1535,1901,2428,2542-2649): one table per

@@ -109,6 +109,11 @@ SIGNATURES = {
     "khx_scatter_peers_dev": (_int, [_vp, _int, _u32, _vp, _u64, _vp, _vp, _vp]),
     "khx_plan_scatter_slabs_dev": (_int, [_vp, _int, _u32, _vp, _u64, _vp, _u64, _int, _vp]),
     "khx_insert_recv_slabs_dev": (_i64, [_vp, _vp, _u64, _int, _vp, _vp, _u32]),
+    "khx_peer_sync_dev": (_int, [_vp, _vp, _u64, _vp, _vp]),
+    "khx_peer_create_q": (_vp, [_int, _u32, _u32, _u64, _int]),
+    "khx_query_scatter_slabs_dev": (_int, [_vp, _int, _u32, _vp, _u64, _vp, _u64, _vp, _vp]),
+    "khx_query_slabs_dev": (_i64, [_vp, _vp, _int, _u64, _vp, _u32]),
+    "khx_unpermute_slabs_dev": (_int, [_vp, _vp, _int, _u64, _vp, _vp, _u64, _vp]),
     "khx_plan_scatter_dev": (_int, [_vp, _int, _u32, _u32, _vp, _u64, _vp, _vp, _vp]),
     "khx_insert_recv_dev": (_i64, [_vp, _vp, _u64, _vp, _u32, _u32]),
     "kh_partition_fast_dev": (_int, [_int, _int, _u32, _int, _u32, _vp, _u64, _vp, _vp, _vp]),

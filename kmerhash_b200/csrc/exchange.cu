@@ -108,25 +108,35 @@ __global__ void merge_meta_kernel(const unsigned long long *recv_meta, uint32_t 
 // rank sees it after the metadata all-gather and all ranks redo the batch through the exact two-pass path).
 constexpr int PS_BLOCK = 512;
 constexpr int PS_TILE_BYTES = 16384;
-template <int W> constexpr size_t ps_smem_bytes(uint32_t p) {
-  return (size_t)PS_TILE_BYTES + (size_t)p * REGION_FINE * 4 + (size_t)p * HLL_M;
+// shared memory: sorted tile | owner of every sorted position | META: [p][1024] histogram + [p][4096] register bytes |
+// PERM: position of every sorted key inside the unsorted tile
+template <int W> constexpr size_t ps_smem_bytes(uint32_t p, bool meta, bool perm) {
+  return (size_t)PS_TILE_BYTES + PS_TILE_BYTES / (8 * W) + (meta ? (size_t)p * REGION_FINE * 4 + (size_t)p * HLL_M : 0) +
+         (perm ? (size_t)2 * (PS_TILE_BYTES / (8 * W)) : 0);
 }
-template <int W>
-__global__ void __launch_bounds__(PS_BLOCK, 2) plan_scatter_slabs_kernel(const uint64_t *keys, uint64_t n, BinSpec dist, int store_kind,
-                                                                          HashParams store_hp, const __grid_constant__ BinDst dst, unsigned long long slab_cap,
-                                                                          unsigned long long *cursors, unsigned long long *meta) {
+// META: the insert sender (metadata per owner into `meta`).  PERM: the query sender -- out_perm[r * slab_cap + i] = index
+// (in `keys`) of the i-th key stored into owner r's slab, so the answers, which come back in slab order, can be put
+// into input order.  cursors[r] ends as the number of keys this rank has for owner r (also beyond slab_cap).
+template <int W, bool META, bool PERM>
+__global__ void __launch_bounds__(PS_BLOCK, 2) scatter_slabs_kernel(const uint64_t *keys, uint64_t n, BinSpec dist, int store_kind,
+                                                                     HashParams store_hp, const __grid_constant__ BinDst dst,
+                                                                     unsigned long long slab_cap, unsigned long long *cursors,
+                                                                     unsigned long long *meta, uint32_t *out_perm) {
   constexpr int TILE = PS_TILE_BYTES / (8 * W);
   constexpr int KPT = TILE / PS_BLOCK;               // 4 (W=1) / 2 (W=2)
   extern __shared__ __align__(16) unsigned char ps_smem[];
   uint64_t *skeys = reinterpret_cast<uint64_t *>(ps_smem);
-  uint32_t *hist = reinterpret_cast<uint32_t *>(ps_smem + PS_TILE_BYTES);   // [p][REGION_FINE]
-  uint32_t *regs = hist + dist.p * REGION_FINE;                           // [p][HLL_M] bytes, four to a word
+  uint8_t *sown = ps_smem + PS_TILE_BYTES;
+  uint32_t *hist = reinterpret_cast<uint32_t *>(sown + TILE);              // [p][REGION_FINE]
+  uint32_t *regs = hist + (META ? dist.p * REGION_FINE : 0);               // [p][HLL_M] bytes, four to a word
+  uint16_t *ssrc = reinterpret_cast<uint16_t *>(regs + (META ? dist.p * (HLL_M / 4) : 0));
   __shared__ uint32_t cnt[WIN_MAX_DST], lo[WIN_MAX_DST];
   __shared__ unsigned long long gbase[WIN_MAX_DST];
   const uint32_t p = dist.p;
   const int lane = threadIdx.x & 31;
   const uint32_t lt_mask = (1u << lane) - 1u;
-  for (uint32_t i = threadIdx.x; i < p * REGION_FINE + p * (HLL_M / 4); i += PS_BLOCK) hist[i] = 0;
+  if constexpr (META)
+    for (uint32_t i = threadIdx.x; i < p * REGION_FINE + p * (HLL_M / 4); i += PS_BLOCK) hist[i] = 0;
   const bool h32 = hash_bits(store_kind) == 32;
   const uint64_t n_tiles = (n + TILE - 1) / TILE;
   unsigned long long my_total = 0;                   // thread r < p: keys of this CTA for owner r
@@ -155,26 +165,28 @@ __global__ void __launch_bounds__(PS_BLOCK, 2) plan_scatter_slabs_kernel(const u
       own[j] = 0xffu;
       if (e < tile_n) {
         own[j] = bin_of<W>(dist, k[j]);
-        const uint64_t h = hash_runtime<W>(store_kind, k[j], store_hp);
-        uint32_t idx, rank;
-        if (h32) {
-          const uint32_t x = (uint32_t)h;
-          idx = x >> (32 - HLL_P);
-          rank = __clz((int)((x << HLL_P) | 0xFFFu)) + 1;
-        } else {
-          idx = (uint32_t)(h >> (64 - HLL_P));
-          rank = __clzll((long long)((h << HLL_P) | 0xFFFULL)) + 1;
+        if constexpr (META) {
+          const uint64_t h = hash_runtime<W>(store_kind, k[j], store_hp);
+          uint32_t idx, rank;
+          if (h32) {
+            const uint32_t x = (uint32_t)h;
+            idx = x >> (32 - HLL_P);
+            rank = __clz((int)((x << HLL_P) | 0xFFFu)) + 1;
+          } else {
+            idx = (uint32_t)(h >> (64 - HLL_P));
+            rank = __clzll((long long)((h << HLL_P) | 0xFFFULL)) + 1;
+          }
+          // byte-wide max inside a shared-memory word
+          uint32_t *w = regs + (own[j] * HLL_M + idx) / 4;
+          const int sh = (idx & 3) * 8;
+          uint32_t old = *w;
+          while (((old >> sh) & 0xffu) < rank) {
+            const uint32_t seen = atomicCAS(w, old, (old & ~(0xffu << sh)) | (rank << sh));
+            if (seen == old) break;
+            old = seen;
+          }
+          atomicAdd(&hist[own[j] * REGION_FINE + (uint32_t)(spread_hash(h) >> (64 - REGION_FINE_BITS))], 1u);
         }
-        // byte-wide max inside a shared-memory word
-        uint32_t *w = regs + (own[j] * HLL_M + idx) / 4;
-        const int sh = (idx & 3) * 8;
-        uint32_t old = *w;
-        while (((old >> sh) & 0xffu) < rank) {
-          const uint32_t seen = atomicCAS(w, old, (old & ~(0xffu << sh)) | (rank << sh));
-          if (seen == old) break;
-          old = seen;
-        }
-        atomicAdd(&hist[own[j] * REGION_FINE + (uint32_t)(spread_hash(h) >> (64 - REGION_FINE_BITS))], 1u);
       }
       // position inside the owner's run of this tile: one shared-memory atomic per (warp, owner)
       const uint32_t peers = __match_any_sync(FULL_MASK, own[j]);
@@ -202,33 +214,76 @@ __global__ void __launch_bounds__(PS_BLOCK, 2) plan_scatter_slabs_kernel(const u
         const uint32_t pos = lo[own[j]] + loc[j];
 #pragma unroll
         for (int q = 0; q < W; ++q) skeys[pos * W + q] = k[j][q];
+        sown[pos] = (uint8_t)own[j];
+        if constexpr (PERM) ssrc[pos] = (uint16_t)e;
       }
     }
     __syncthreads();
 
-    // sorted tile out: position e belongs to the owner r with lo[r] <= e < lo[r] + cnt[r]
+    // sorted tile out: consecutive threads = consecutive addresses inside an owner's run
     for (int e = threadIdx.x; e < tile_n; e += PS_BLOCK) {
-      uint32_t r = 0;
-#pragma unroll
-      for (int q = 1; q < WIN_MAX_DST; ++q) r += (q < (int)p && (uint32_t)e >= lo[q]) ? 1u : 0u;
+      const uint32_t r = sown[e];
       const unsigned long long gpos = gbase[r] + (uint32_t)(e - lo[r]);
       if (gpos < slab_cap) {
         uint64_t *o = dst.base[r] + gpos * W;
 #pragma unroll
         for (int q = 0; q < W; ++q) o[q] = skeys[e * W + q];
+        if constexpr (PERM) out_perm[(unsigned long long)r * slab_cap + gpos] = (uint32_t)(base + ssrc[e]);
       }
     }
     __syncthreads();
   }
 
-  __syncthreads();
-  for (uint32_t i = threadIdx.x; i < p * REGION_FINE; i += PS_BLOCK)
-    if (hist[i]) atomicAdd(&meta[(uint64_t)(i / REGION_FINE) * META_WORDS + META_HIST + (i % REGION_FINE)], (unsigned long long)hist[i]);
-  for (uint32_t i = threadIdx.x; i < p * HLL_M; i += PS_BLOCK) {
-    const uint32_t v = (regs[i / 4] >> ((i & 3) * 8)) & 0xffu;
-    if (v) atomicMax(&meta[(uint64_t)(i / HLL_M) * META_WORDS + META_REGS + (i % HLL_M)], (unsigned long long)v);
+  if constexpr (META) {
+    __syncthreads();
+    for (uint32_t i = threadIdx.x; i < p * REGION_FINE; i += PS_BLOCK)
+      if (hist[i]) atomicAdd(&meta[(uint64_t)(i / REGION_FINE) * META_WORDS + META_HIST + (i % REGION_FINE)], (unsigned long long)hist[i]);
+    for (uint32_t i = threadIdx.x; i < p * HLL_M; i += PS_BLOCK) {
+      const uint32_t v = (regs[i / 4] >> ((i & 3) * 8)) & 0xffu;
+      if (v) atomicMax(&meta[(uint64_t)(i / HLL_M) * META_WORDS + META_REGS + (i % HLL_M)], (unsigned long long)v);
+    }
+    if (threadIdx.x < p && my_total) atomicAdd(&meta[(uint64_t)threadIdx.x * META_WORDS], my_total);
   }
-  if (threadIdx.x < p && my_total) atomicAdd(&meta[(uint64_t)threadIdx.x * META_WORDS], my_total);
+}
+
+// ---- barrier + count exchange over peer memory ------------------------------------------------------------------------
+// Every receive buffer ends in a header { flags[8]; counts[8][8] }.  One tiny kernel per rank: thread r publishes this
+// rank's row of the count matrix in rank r's header, fences, raises flags[my_rank] = epoch there, then waits until rank r's
+// flag in the LOCAL header has reached the epoch.  When the kernel ends, every peer's stores that preceded its flag (the
+// keys / answers of the kernels before it on its stream) are visible here -- a barrier without NCCL's launch latency, and
+// the p x p counts arrive with it.  A peer that never shows up trips the time-out instead of hanging the GPU.
+struct PeerHeader { unsigned long long flags[WIN_MAX_DST]; unsigned long long counts[WIN_MAX_DST][WIN_MAX_DST]; };
+struct PeerHeaders { PeerHeader *h[WIN_MAX_DST]; };
+__global__ void peer_sync_kernel(const __grid_constant__ PeerHeaders hd, uint32_t rank, uint32_t p, unsigned long long epoch,
+                                 const unsigned long long *counts_row, int *timed_out) {
+  const uint32_t r = threadIdx.x;
+  if (r >= p) return;
+  if (counts_row)
+    for (uint32_t c = 0; c < p; ++c) *reinterpret_cast<volatile unsigned long long *>(&hd.h[r]->counts[rank][c]) = counts_row[c];
+  __threadfence_system();
+  *reinterpret_cast<volatile unsigned long long *>(&hd.h[r]->flags[rank]) = epoch;
+  unsigned long long t0;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
+  const volatile unsigned long long *mine = &hd.h[rank]->flags[r];
+  while (*mine < epoch) {
+    unsigned long long t1;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1));
+    if (t1 - t0 > 10000000000ULL) { *timed_out = 1; break; }      // 10 s
+    __nanosleep(200);
+  }
+  __threadfence_system();
+}
+
+// answers of a query, as they came back in slab order, into input order: out[perm[r][i]] = reply[r][i] for i < counts[r]
+template <typename T>
+__global__ void unpermute_slabs_kernel(const T *reply, const uint32_t *perm, const unsigned long long *counts, uint32_t p,
+                                       unsigned long long slab_cap, T *out) {
+  const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+  for (uint32_t r = 0; r < p; ++r) {
+    const unsigned long long c = min(counts[r], slab_cap);
+    for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < c; i += stride)
+      out[perm[(uint64_t)r * slab_cap + i]] = reply[(uint64_t)r * slab_cap + i];
+  }
 }
 
 }  // namespace kh
@@ -281,11 +336,20 @@ struct khx_peer {
   uint32_t rank = 0, p = 1;
   uint64_t capacity = 0;                 // keys
   uint64_t *local = nullptr;             // this rank's receive buffer (cudaMalloc: IPC cannot export pool memory)
+  uint32_t reply_bytes = 0;              // bytes per key of the answer region that follows the keys (query exchange), 0 = none
   uint64_t *remote[WIN_MAX_DST] = {nullptr};
   bool opened[WIN_MAX_DST] = {false};    // mapped with cudaIpcOpenMemHandle (must be closed)
 };
 
+static khx_peer *peer_create(int device, uint32_t rank, uint32_t p, uint64_t capacity_keys, int key_words, uint32_t reply_bytes);
 khx_peer *khx_peer_create(int device, uint32_t rank, uint32_t p, uint64_t capacity_keys, int key_words) {
+  return peer_create(device, rank, p, capacity_keys, key_words, 0);
+}
+// receive buffer of the QUERY exchange: capacity_keys keys followed by 4 answer bytes per key, one allocation / IPC handle
+khx_peer *khx_peer_create_q(int device, uint32_t rank, uint32_t p, uint64_t capacity_keys, int key_words) {
+  return peer_create(device, rank, p, capacity_keys, key_words, 4);
+}
+static khx_peer *peer_create(int device, uint32_t rank, uint32_t p, uint64_t capacity_keys, int key_words, uint32_t reply_bytes) {
   khx_peer *x = nullptr;
   int64_t rc = guarded([&]() -> int64_t {
     if (p == 0 || p > (uint32_t)WIN_MAX_DST || rank >= p || key_words < 1 || key_words > 2) {
@@ -294,7 +358,10 @@ khx_peer *khx_peer_create(int device, uint32_t rank, uint32_t p, uint64_t capaci
     DeviceGuard g(device);
     x = new khx_peer();
     x->device = device; x->W = key_words; x->rank = rank; x->p = p; x->capacity = std::max<uint64_t>(capacity_keys, 1);
-    KH_CUDA(cudaMalloc((void **)&x->local, x->capacity * 8 * key_words));
+    x->reply_bytes = reply_bytes;
+    const size_t body = x->capacity * (8 * key_words + reply_bytes);
+    KH_CUDA(cudaMalloc((void **)&x->local, body + sizeof(PeerHeader)));
+    KH_CUDA(cudaMemset(reinterpret_cast<unsigned char *>(x->local) + body, 0, sizeof(PeerHeader)));
     x->remote[rank] = x->local;
     return KH_OK;
   });
@@ -401,7 +468,7 @@ int khx_scatter_peers_dev(kh_table *t, int dist_hash, uint32_t dist_seed, const 
   });
 }
 
-// Single-pass sender (plan_scatter_slabs_kernel): this rank's keys for owner r go to slab `rank` of half `parity` of
+// Single-pass sender (scatter_slabs_kernel): this rank's keys for owner r go to slab `rank` of half `parity` of
 // r's receive buffer, i.e. to remote[r] + ((parity * p + rank) * slab_cap) keys; d_meta receives the p metadata blocks.
 // The receive buffers hold 2 * p * slab_cap keys: two halves used alternately, so a rank may start batch i+1 while
 // another still reads batch i (the metadata all-gather of batch i+1 orders batch i+2 behind it).
@@ -431,14 +498,15 @@ int khx_plan_scatter_slabs_dev(kh_table *t, int dist_hash, uint32_t dist_seed, c
       KH_CUDA(cudaMemsetAsync(cursors.p, 0, p * sizeof(unsigned long long), s));
       const uint64_t tile = PS_TILE_BYTES / (8 * t->W);
       const int grid = (int)std::max<uint64_t>(1, std::min<uint64_t>((n + tile - 1) / tile, (uint64_t)t->sms * 2));
+      const size_t smem = t->W == 1 ? ps_smem_bytes<1>(p, true, false) : ps_smem_bytes<2>(p, true, false);
       if (t->W == 1) {
-        KH_CUDA(cudaFuncSetAttribute(plan_scatter_slabs_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ps_smem_bytes<1>(p)));
-        KH_LAUNCH((plan_scatter_slabs_kernel<1>), grid, PS_BLOCK, ps_smem_bytes<1>(p), s, d_keys, n, dist, t->hash_kind, t->hp, dst,
-                  (unsigned long long)slab_cap, cursors.p, meta);
+        KH_CUDA(cudaFuncSetAttribute((scatter_slabs_kernel<1, true, false>), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        KH_LAUNCH((scatter_slabs_kernel<1, true, false>), grid, PS_BLOCK, smem, s, d_keys, n, dist, t->hash_kind, t->hp, dst,
+                  (unsigned long long)slab_cap, cursors.p, meta, (uint32_t *)nullptr);
       } else {
-        KH_CUDA(cudaFuncSetAttribute(plan_scatter_slabs_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ps_smem_bytes<2>(p)));
-        KH_LAUNCH((plan_scatter_slabs_kernel<2>), grid, PS_BLOCK, ps_smem_bytes<2>(p), s, d_keys, n, dist, t->hash_kind, t->hp, dst,
-                  (unsigned long long)slab_cap, cursors.p, meta);
+        KH_CUDA(cudaFuncSetAttribute((scatter_slabs_kernel<2, true, false>), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        KH_LAUNCH((scatter_slabs_kernel<2, true, false>), grid, PS_BLOCK, smem, s, d_keys, n, dist, t->hash_kind, t->hp, dst,
+                  (unsigned long long)slab_cap, cursors.p, meta, (uint32_t *)nullptr);
       }
       KH_CUDA(cudaStreamSynchronize(s));     // cursors goes out of scope; the stores have been issued and completed
     } else {
@@ -475,6 +543,141 @@ int64_t khx_insert_recv_slabs_dev(kh_table *t, khx_peer *x, uint64_t slab_cap, i
     const double est = hll_finish(t->hash_kind, regs.p, nullptr, s);   // synchronises s
     PreEstimate pre{est, fine.p, p > 1 ? &segs : nullptr};
     return insert_dev_impl(t, x->local + (p > 1 ? 0 : segs.base[0] * t->W), nullptr, n, default_val, 1, &pre);
+  });
+}
+
+// ---- query exchange (find / count / erase) over the slabs -----------------------------------------------------------
+// replaces count_p / find_p / erase_p's exchange (KH/distributed_batched_robinhood_map.hpp:1258-1516,1619,2169) and the
+// reply of ialltoallv_and_query_one_to_one (KH/incremental_mxx.hpp:4403): keys go out by peer stores (scatter_slabs_kernel
+// with PERM), the owner's lookup kernel stores every answer straight into the asker's reply region, the asker puts the
+// answers into input order.  Between the steps the caller needs: the p x p counts (all-gather of d_counts, which is also
+// the barrier behind the key stores) and a barrier behind the answer stores.
+int khx_query_scatter_slabs_dev(kh_table *t, int dist_hash, uint32_t dist_seed, const uint64_t *d_keys, uint64_t n, khx_peer *x,
+                                uint64_t slab_cap, uint32_t *d_perm, uint64_t *d_counts) {
+  return (int)guarded([&]() -> int64_t {
+    if (!t || !x || !d_counts || (n && (!d_keys || !d_perm))) { set_error("null argument"); return KH_ERR_INVALID; }
+    if (!hash_kind_supported(dist_hash) || n >= (1ULL << 32) || x->W != t->W || x->p > (uint32_t)WIN_MAX_DST || x->reply_bytes == 0) {
+      set_error("khx_query_scatter_slabs_dev: bad arguments (buffers from khx_peer_create_q?)"); return KH_ERR_INVALID;
+    }
+    if ((uint64_t)x->p * slab_cap > x->capacity) { set_error("receive buffers hold %llu keys, %u slabs of %llu do not fit",
+                                                             (unsigned long long)x->capacity, x->p, (unsigned long long)slab_cap); return KH_ERR_NOMEM; }
+    DeviceGuard g(t->device);
+    cudaStream_t s = t->stream[0];
+    const uint32_t p = x->p;
+    const int dk = fold_kind(dist_hash);
+    const BinSpec dist{1, 0, p, dk, make_hash_params(dk, dist_seed, t->W)};
+    unsigned long long *cursors = reinterpret_cast<unsigned long long *>(d_counts);
+    KH_CUDA(cudaMemsetAsync(cursors, 0, p * sizeof(unsigned long long), s));
+    if (n) {
+      BinDst dst{};
+      for (uint32_t r = 0; r < p; ++r) {
+        if (!x->remote[r]) { set_error("peer %u not mapped", r); return KH_ERR_INVALID; }
+        dst.base[r] = x->remote[r] + (uint64_t)x->rank * slab_cap * t->W;
+      }
+      const uint64_t tile = PS_TILE_BYTES / (8 * t->W);
+      const int grid = (int)std::max<uint64_t>(1, std::min<uint64_t>((n + tile - 1) / tile, (uint64_t)t->sms * 2));
+      const size_t smem = t->W == 1 ? ps_smem_bytes<1>(p, false, true) : ps_smem_bytes<2>(p, false, true);
+      if (t->W == 1) KH_LAUNCH((scatter_slabs_kernel<1, false, true>), grid, PS_BLOCK, smem, s, d_keys, n, dist, t->hash_kind, t->hp, dst,
+                               (unsigned long long)slab_cap, cursors, (unsigned long long *)nullptr, d_perm);
+      else KH_LAUNCH((scatter_slabs_kernel<2, false, true>), grid, PS_BLOCK, smem, s, d_keys, n, dist, t->hash_kind, t->hp, dst,
+                     (unsigned long long)slab_cap, cursors, (unsigned long long *)nullptr, d_perm);
+    }
+    KH_CUDA(cudaStreamSynchronize(s));
+    return KH_OK;
+  });
+}
+
+// owner side: counts[g] (HOST) keys of asker g lie in slab g of this rank's buffer.  op 0 = find (u32 answers, `nonexistent`
+// for absent keys), 1 = count (u8 answers), 2 = erase (no answers).  Answers go to slab `rank` of asker g's reply region.
+// Returns the number of hits / erased keys.
+int64_t khx_query_slabs_dev(kh_table *t, khx_peer *x, int op, uint64_t slab_cap, const uint64_t *counts, uint32_t nonexistent) {
+  return guarded([&]() -> int64_t {
+    if (!t || !x || !counts || op < 0 || op > 2) { set_error("bad argument"); return KH_ERR_INVALID; }
+    if (x->W != t->W || x->reply_bytes == 0 || (uint64_t)x->p * slab_cap > x->capacity) { set_error("khx_query_slabs_dev: bad arguments"); return KH_ERR_INVALID; }
+    DeviceGuard g(t->device);
+    const uint32_t p = x->p;
+    const int W = t->W;
+    for (uint32_t q = 0; q < p; ++q)
+      if (counts[q] > slab_cap) { set_error("slab %u holds %llu keys, more than its capacity", q, (unsigned long long)counts[q]); return KH_ERR_INVALID; }
+    int64_t total = 0;
+    if (op == 2) {                       // one erase over all slabs (the shrink rule looks at the table once, as the reference does)
+      uint64_t n = 0;
+      for (uint32_t q = 0; q < p; ++q) n += counts[q];
+      if (!n) return 0;
+      DevBuf<uint64_t> flat(n * W);
+      uint64_t off = 0;
+      for (uint32_t q = 0; q < p; ++q) if (counts[q]) {
+        KH_CUDA(cudaMemcpyAsync(flat.p + off * W, x->local + (uint64_t)q * slab_cap * W, counts[q] * 8 * W, cudaMemcpyDeviceToDevice, t->stream[0]));
+        off += counts[q];
+      }
+      KH_CUDA(cudaStreamSynchronize(t->stream[0]));
+      return kh_erase_dev(t, flat.p, n);
+    }
+    const size_t elem = op == 0 ? 4 : 1;
+    for (uint32_t q = 0; q < p; ++q) {
+      if (!counts[q]) continue;
+      if (!x->remote[q]) { set_error("peer %u not mapped", q); return KH_ERR_INVALID; }
+      const uint64_t *keys = x->local + (uint64_t)q * slab_cap * W;
+      unsigned char *reply = reinterpret_cast<unsigned char *>(x->remote[q]) + x->capacity * 8 * W + (uint64_t)x->rank * slab_cap * elem;
+      const int64_t rc = op == 0 ? kh_find_dev(t, keys, counts[q], reinterpret_cast<uint32_t *>(reply), nonexistent)
+                                 : kh_count_dev(t, keys, counts[q], reply);
+      if (rc < 0) return rc;
+      total += rc;
+    }
+    return total;
+  });
+}
+
+// barrier over peer memory (peer_sync_kernel).  epoch: 1, 2, 3, ... per buffer set, the same on every rank.  d_counts_row
+// (DEVICE, p words, may be null): this rank's row of the count matrix, published to every rank; counts_matrix (HOST, p x p,
+// may be null) receives the matrix [sender][owner] as it stands in the local header after the barrier.
+int khx_peer_sync_dev(kh_table *t, khx_peer *x, uint64_t epoch, const uint64_t *d_counts_row, uint64_t *counts_matrix) {
+  return (int)guarded([&]() -> int64_t {
+    if (!t || !x || epoch == 0) { set_error("bad argument"); return KH_ERR_INVALID; }
+    DeviceGuard g(t->device);
+    cudaStream_t s = t->stream[0];
+    const size_t body = x->capacity * (size_t)(8 * x->W + x->reply_bytes);
+    PeerHeaders hd{};
+    for (uint32_t r = 0; r < x->p; ++r) {
+      if (!x->remote[r]) { set_error("peer %u not mapped", r); return KH_ERR_INVALID; }
+      hd.h[r] = reinterpret_cast<PeerHeader *>(reinterpret_cast<unsigned char *>(x->remote[r]) + body);
+    }
+    DevBuf<int> flag(1);
+    KH_CUDA(cudaMemsetAsync(flag.p, 0, sizeof(int), s));
+    KH_LAUNCH(peer_sync_kernel, 1, 32, 0, s, hd, x->rank, x->p, (unsigned long long)epoch,
+              reinterpret_cast<const unsigned long long *>(d_counts_row), flag.p);
+    int h_flag = 0;
+    PeerHeader h_hdr;
+    KH_CUDA(cudaMemcpyAsync(&h_flag, flag.p, sizeof(int), cudaMemcpyDeviceToHost, s));
+    if (counts_matrix) KH_CUDA(cudaMemcpyAsync(&h_hdr, hd.h[x->rank], sizeof(PeerHeader), cudaMemcpyDeviceToHost, s));
+    KH_CUDA(cudaStreamSynchronize(s));
+    if (h_flag) { set_error("khx_peer_sync_dev: a peer did not reach epoch %llu within 10 s", (unsigned long long)epoch); return KH_ERR_CUDA; }
+    if (counts_matrix)
+      for (uint32_t a = 0; a < x->p; ++a)
+        for (uint32_t b = 0; b < x->p; ++b) counts_matrix[a * x->p + b] = h_hdr.counts[a][b];
+    return KH_OK;
+  });
+}
+
+// asker side, after the barrier behind the answer stores: d_out[perm[r][i]] = reply[r][i]  (elem_bytes 4 or 1)
+int khx_unpermute_slabs_dev(kh_table *t, khx_peer *x, int elem_bytes, uint64_t slab_cap, const uint32_t *d_perm, const uint64_t *d_counts,
+                            uint64_t n, void *d_out) {
+  return (int)guarded([&]() -> int64_t {
+    if (!t || !x || !d_counts || (n && (!d_perm || !d_out)) || (elem_bytes != 1 && elem_bytes != 4)) { set_error("bad argument"); return KH_ERR_INVALID; }
+    if (x->reply_bytes == 0 || (uint64_t)x->p * slab_cap > x->capacity) { set_error("khx_unpermute_slabs_dev: bad arguments"); return KH_ERR_INVALID; }
+    DeviceGuard g(t->device);
+    cudaStream_t s = t->stream[0];
+    if (n) {
+      const unsigned char *reply = reinterpret_cast<const unsigned char *>(x->local) + x->capacity * 8 * x->W;
+      const unsigned long long *cnt = reinterpret_cast<const unsigned long long *>(d_counts);
+      const int grid = t->grid_for(std::max<uint64_t>(n / x->p, 1), 256);
+      if (elem_bytes == 4) KH_LAUNCH((unpermute_slabs_kernel<uint32_t>), grid, 256, 0, s, reinterpret_cast<const uint32_t *>(reply), d_perm, cnt,
+                                     x->p, (unsigned long long)slab_cap, reinterpret_cast<uint32_t *>(d_out));
+      else KH_LAUNCH((unpermute_slabs_kernel<uint8_t>), grid, 256, 0, s, reply, d_perm, cnt, x->p, (unsigned long long)slab_cap,
+                     reinterpret_cast<uint8_t *>(d_out));
+    }
+    KH_CUDA(cudaStreamSynchronize(s));
+    return KH_OK;
   });
 }
 

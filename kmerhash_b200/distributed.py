@@ -47,11 +47,12 @@ class PeerBuffers:
     """this rank's receive buffer + the other ranks' buffers mapped through CUDA IPC (csrc/exchange.cu: khx_peer_*).
     Collective: every rank of the group constructs it at the same time."""
 
-    def __init__(self, device, rank, p, capacity, key_words, group):
+    def __init__(self, device, rank, p, capacity, key_words, group, query=False):
         import ctypes as C
         from ._lib import lib, check
         self.lib, self.p, self.rank = lib, p, rank
-        self.h = lib.khx_peer_create(device, rank, p, int(capacity), key_words)
+        self.epoch = 0                    # barriers passed on this buffer set (khx_peer_sync_dev)
+        self.h = (lib.khx_peer_create_q if query else lib.khx_peer_create)(device, rank, p, int(capacity), key_words)
         ok = 1 if self.h else 0
         dev = torch.device("cuda", device)
         handle = (C.c_ubyte * 64)()
@@ -148,6 +149,19 @@ class CudaEngine:
     def insert_recv_slabs(self, peers, slab_cap, parity, counts, recv_meta, default):
         return self.table.insert_recv_slabs(peers.h, slab_cap, parity, counts, recv_meta, default) if int(counts.sum()) else 0
 
+    def query_scatter_slabs(self, keys, peers, slab_cap, perm, counts):
+        self.table.query_scatter_slabs(keys, peers.h, slab_cap, perm, counts, self.dist_hash)
+
+    def peer_sync(self, peers, counts_row=None):
+        peers.epoch += 1
+        return self.table.peer_sync(peers.h, peers.epoch, counts_row, peers.p)
+
+    def query_slabs(self, peers, op, slab_cap, counts, nonexistent):
+        return self.table.query_slabs(peers.h, op, slab_cap, counts, nonexistent)
+
+    def unpermute_slabs(self, peers, slab_cap, perm, counts, out):
+        self.table.unpermute_slabs(peers.h, slab_cap, perm, counts, out)
+
     def count(self, keys):
         return self.table.count(keys) if keys.shape[0] else self.empty_like_result(0, torch.uint8)
 
@@ -181,12 +195,17 @@ class DistributedMap:
         # fused partition + exchange over peer memory (NVLink): on when every rank could map every buffer
         self.peer_stores = os.environ.get("KH_PEER_STORES", "1") not in ("0", "")
         self.peers = None
-        # single-pass sender into per-sender slabs of the receive buffers (csrc/exchange.cu: plan_scatter_slabs_kernel)
+        # single-pass sender into per-sender slabs of the receive buffers (csrc/exchange.cu: scatter_slabs_kernel)
         self.slabs = os.environ.get("KH_SLABS", "1") not in ("0", "")
         self.slab_cap = 0                 # keys per (owner, sender) slab; the buffers hold 2 halves x p slabs
         self.parity = 0
         self.slab_misses = 0              # consecutive batches that overflowed a slab (skewed owners)
         self._exact_dirty = False         # the last batch went through the exact path: its buffer use overlaps both halves
+        # queries over peer slabs with direct answer stores (csrc/exchange.cu: khx_query_*)
+        self.qslabs = self.slabs
+        self.qpeers = None
+        self.q_slab_cap = 0
+        self.q_misses = 0
 
     # ---- the exchange ---------------------------------------------------------------------------
     def _counts_a2a(self, counts):
@@ -371,21 +390,85 @@ class DistributedMap:
         with _Stage("local insert"):
             return self.e.insert_recv_ptr(self.peers.recv_ptr(), int(C[:, rank].sum()), recv_meta, default)
 
+    def _query_slabs(self, op, keys, nonexistent=0):
+        """find / count / erase without NCCL on the data path: keys go to the owners by peer stores (one kernel), every
+        owner's lookup kernel stores its answers straight into the asker's reply region, the asker un-permutes.  The two
+        barriers (behind the key stores, with the p x p counts; behind the answers) are flag kernels over peer memory.
+        Returns None when this op has to take the NCCL path (no peer access, a slab overflowed)."""
+        self.last_query_path = "nccl"
+        if not (self.p > 1 and self.peer_stores and self.qslabs and hasattr(self.e, "query_scatter_slabs")):
+            return None
+        p, rank, dev = self.p, self.rank, self.e.device
+        keys = self.e.canonicalize(keys)
+        n = int(keys.shape[0])
+        if self.qpeers is None:
+            nmax = torch.tensor([n], dtype=torch.int64, device=dev)
+            dist.all_reduce(nmax, op=dist.ReduceOp.MAX, group=self.group)
+            self.q_slab_cap = int(int(nmax.item()) / p * 1.25) + 4096
+            self.qpeers = PeerBuffers(dev.index, rank, p, p * self.q_slab_cap, self.W, self.group, query=True)
+            if not self.qpeers.ok:
+                self.qslabs = False
+                self.qpeers.close(); self.qpeers = None
+                return None
+        cap = self.q_slab_cap
+        perm = torch.empty(p * cap, dtype=torch.int32, device=dev)
+        counts = torch.zeros(p, dtype=torch.int64, device=dev)
+        with _Stage("q.scatter"):
+            self.e.query_scatter_slabs(keys, self.qpeers, cap, perm, counts)
+        with _Stage("q.sync+counts"):
+            C = self.e.peer_sync(self.qpeers, counts)                         # every rank's key stores have landed; C[g][r]
+        if int(C.max()) > cap:                                                # same decision on every rank
+            if int(C.max()) * p <= 2 * int(C.sum(axis=1).max()):              # balanced owners, larger batches: larger slabs
+                self.q_slab_cap = int(int(C.max()) * 1.25) + 4096
+                self.qpeers.close()
+                self.qpeers = PeerBuffers(dev.index, rank, p, p * self.q_slab_cap, self.W, self.group, query=True)
+                if not self.qpeers.ok:
+                    self.qslabs = False
+                    self.qpeers.close(); self.qpeers = None
+            else:
+                self.q_misses += 1
+                if self.q_misses >= 2:                                        # owners stay skewed: NCCL path from now on
+                    self.qslabs = False
+            return None
+        self.q_misses = 0
+        self.last_query_path = "slab"
+        elem = {"find": 4, "count": 1, "erase": 0}[op]
+        self.last_exchange_bytes += (8 * self.W + elem) * int(C[rank].sum() - C[rank, rank])
+        with _Stage("q.lookup"):
+            hits = self.e.query_slabs(self.qpeers, op, cap, C[:, rank], nonexistent)
+        with _Stage("q.sync"):
+            self.e.peer_sync(self.qpeers)                                     # every owner's answers have landed
+        if op == "erase":
+            return hits
+        out = torch.empty(n, dtype=torch.int32 if op == "find" else torch.uint8, device=dev)
+        with _Stage("q.unpermute"):
+            self.e.unpermute_slabs(self.qpeers, cap, perm, counts, out)
+        return out
+
     def count(self, keys):
         keys = self.e.as_keys(keys)
         self.last_exchange_bytes = 0
+        r = self._query_slabs("count", keys)
+        if r is not None:
+            return r
         recv, perm, sc, rc, _ = self._send_keys(keys, True)
         return self._reply(self.e.count(recv), perm, sc, rc)
 
     def find(self, keys, nonexistent=0):
         keys = self.e.as_keys(keys)
         self.last_exchange_bytes = 0
+        r = self._query_slabs("find", keys, nonexistent)
+        if r is not None:
+            return r
         recv, perm, sc, rc, _ = self._send_keys(keys, True)
         return self._reply(self.e.find(recv, nonexistent), perm, sc, rc)
 
     def erase(self, keys):
         keys = self.e.as_keys(keys)
         self.last_exchange_bytes = 0
+        r = self._query_slabs("erase", keys)
+        if r is not None:
+            return r
         recv, _, _, _, _ = self._send_keys(keys, False)
         return self.e.erase(recv)
 

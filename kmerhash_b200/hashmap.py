@@ -201,6 +201,30 @@ class HashMap:
         return check(lib.khx_insert_recv_slabs_dev(self._h, peer_handle, int(slab_cap), int(parity), cnt.ctypes.data,
                                                    recv_meta.data_ptr(), default), "insert_recv_slabs")
 
+    # query exchange over peer slabs (khx_query_*): see distributed.py
+    def query_scatter_slabs(self, keys, peer_handle, slab_cap, perm, counts, dist_hash="MURMUR64avx", dist_seed=9876543):
+        k, n = _dev_keys(keys, self.W, self.device)
+        assert perm.is_cuda and perm.dtype == torch.int32 and counts.is_cuda and counts.dtype == torch.int64
+        check(lib.khx_query_scatter_slabs_dev(self._h, HASH_KINDS[dist_hash], dist_seed, k.data_ptr(), n, peer_handle, int(slab_cap),
+                                              perm.data_ptr(), counts.data_ptr()), "query_scatter_slabs")
+
+    def peer_sync(self, peer_handle, epoch, counts_row=None, p=0):
+        """barrier over peer memory; with counts_row (int64 CUDA tensor, p entries) returns the p x p matrix [sender][owner]"""
+        mat = np.zeros((p, p), dtype=np.uint64) if counts_row is not None else None
+        check(lib.khx_peer_sync_dev(self._h, peer_handle, int(epoch), counts_row.data_ptr() if counts_row is not None else None,
+                                    mat.ctypes.data if mat is not None else None), "peer_sync")
+        return mat
+
+    def query_slabs(self, peer_handle, op, slab_cap, counts, nonexistent=0):
+        cnt = np.ascontiguousarray(counts, dtype=np.uint64)
+        torch.cuda.current_stream(self.device).synchronize()
+        return check(lib.khx_query_slabs_dev(self._h, peer_handle, {"find": 0, "count": 1, "erase": 2}[op], int(slab_cap),
+                                             cnt.ctypes.data, int(nonexistent) & 0xFFFFFFFF), "query_slabs")
+
+    def unpermute_slabs(self, peer_handle, slab_cap, perm, counts, out):
+        check(lib.khx_unpermute_slabs_dev(self._h, peer_handle, out.element_size(), int(slab_cap), perm.data_ptr(), counts.data_ptr(),
+                                          out.shape[0], out.data_ptr()), "unpermute_slabs")
+
     def insert_recv_ptr(self, ptr, n, recv_meta, default=1):
         """receiver half on a raw device pointer (the peer receive buffer)"""
         assert recv_meta.is_cuda and recv_meta.dtype == torch.int64 and recv_meta.is_contiguous()

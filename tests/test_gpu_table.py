@@ -510,6 +510,107 @@ def test_single_pass_slab_exchange(kh, oracle_mod, p, W, n_per, tiled):
                 lib.khx_peer_destroy(h)
 
 
+def test_peer_memory_barrier(kh):
+    """khx_peer_sync_dev: p ranks emulated on one GPU, one host thread per rank (the flag kernels wait for each other, so
+    they must be able to run concurrently).  Every rank must come back with the same p x p count matrix, row g = what
+    rank g published; a second epoch without counts must pass as well."""
+    import threading
+    import torch
+    from kmerhash_b200._lib import lib
+    p = 4
+    tables = [kh.HashMap(1, "MURMUR64avx", "COUNT") for _ in range(p)]
+    peers = [lib.khx_peer_create(0, r, p, 1024, 1) for r in range(p)]
+    try:
+        assert all(peers)
+        for r in range(p):
+            for q in range(p):
+                if q != r:
+                    assert lib.khx_peer_set(peers[r], q, lib.khx_peer_recv_ptr(peers[q])) == 0
+        rows = [torch.tensor([100 * g + c for c in range(p)], dtype=torch.int64, device="cuda") for g in range(p)]
+        torch.cuda.synchronize()
+        got, errs = [None] * p, []
+
+        def run(r):
+            try:
+                got[r] = tables[r].peer_sync(peers[r], 1, rows[r], p)
+                tables[r].peer_sync(peers[r], 2)
+            except Exception as e:      # noqa: BLE001
+                errs.append(e)
+
+        th = [threading.Thread(target=run, args=(r,)) for r in range(p)]
+        [t.start() for t in th]
+        [t.join(60) for t in th]
+        assert not errs, errs
+        exp = np.array([[100 * g + c for c in range(p)] for g in range(p)], dtype=np.uint64)
+        for r in range(p):
+            assert np.array_equal(got[r], exp)
+    finally:
+        for h in peers:
+            if h:
+                lib.khx_peer_destroy(h)
+
+
+@pytest.mark.parametrize("p,W", [(2, 1), (3, 2), (8, 1), (8, 2)])
+def test_query_slab_exchange(kh, oracle_mod, p, W):
+    """khx_query_scatter_slabs_dev / khx_query_slabs_dev / khx_unpermute_slabs_dev with p ranks emulated on one GPU: every
+    rank's table holds its partition of a count map; every rank asks a batch (present and absent keys); find / count
+    answers must come back in INPUT order and equal the oracle's; erase must remove exactly the asked keys."""
+    import torch
+    from kmerhash_b200._lib import lib
+    o = oracle_mod.port
+    rng = np.random.default_rng(270 + p + W)
+    base = rng.integers(0, 2**62, size=(40000, W), dtype=np.uint64)
+    sq = (lambda a: a if W == 2 else np.ascontiguousarray(a[:, 0]))
+    stored = sq(np.ascontiguousarray(base[rng.integers(0, 30000, size=200000)]))          # last 10000 base keys never stored
+    gm = o.Map(W, "COUNT"); gm.insert(stored, default=1)
+    owner = o.rank("MURMUR64avx", stored, p)
+    tables = [kh.HashMap(W, "MURMUR64avx", "COUNT") for _ in range(p)]
+    for r in range(p):
+        tables[r].insert(stored[owner == r], default=1)
+    n_q = 50000
+    slab_cap = int(n_q / p * 1.5) + 512
+    peers = [lib.khx_peer_create_q(0, r, p, p * slab_cap, W) for r in range(p)]
+    try:
+        assert all(peers)
+        for r in range(p):
+            for q in range(p):
+                if q != r:
+                    assert lib.khx_peer_set(peers[r], q, lib.khx_peer_recv_ptr(peers[q])) == 0
+        for op in ("find", "count", "erase"):
+            asks = [sq(np.ascontiguousarray(base[rng.integers(0, 40000, size=n_q + 111 * g)])) for g in range(p)]
+            dq = [torch.from_numpy(a.view(np.int64)).cuda() for a in asks]
+            perms = [torch.empty(p * slab_cap, dtype=torch.int32, device="cuda") for _ in range(p)]
+            cnts = [torch.zeros(p, dtype=torch.int64, device="cuda") for _ in range(p)]
+            for g in range(p):
+                tables[g].query_scatter_slabs(dq[g], peers[g], slab_cap, perms[g], cnts[g])
+            Cm = torch.stack(cnts).cpu().numpy().astype(np.uint64)                          # [g][r]
+            for g in range(p):
+                assert Cm[g].tolist() == np.bincount(o.rank("MURMUR64avx", asks[g], p), minlength=p).tolist()
+            hits = [tables[r].query_slabs(peers[r], op, slab_cap, Cm[:, r], 77) for r in range(p)]
+            if op == "erase":
+                allq = np.concatenate(asks)
+                assert sum(hits) == gm.erase(allq)
+                gk, gv = gm.to_vector()
+                own = o.rank("MURMUR64avx", gk, p)
+                for r in range(p):
+                    ek, ev = sort_pairs(gk[own == r], gv[own == r])
+                    tk, tv = sort_pairs(*tables[r].to_vector())
+                    assert np.array_equal(tk, ek) and np.array_equal(tv, ev)
+                continue
+            for g in range(p):
+                out = torch.full((asks[g].shape[0],), 0x55, dtype=torch.int32 if op == "find" else torch.uint8, device="cuda")
+                tables[g].unpermute_slabs(peers[g], slab_cap, perms[g], cnts[g], out)
+                got = out.cpu().numpy()
+                exp = gm.find(asks[g], 77) if op == "find" else gm.count(asks[g])
+                assert np.array_equal(got.astype(exp.dtype), exp)
+            exp_hits = sum(int(gm.count(a).sum()) for a in asks)
+            assert sum(hits) == exp_hits
+    finally:
+        for h in peers:
+            if h:
+                lib.khx_peer_destroy(h)
+
+
 @pytest.mark.parametrize("max_load", [0.8, 0.97])
 def test_tile_insert_deferred_chains_and_side_key(kh, oracle_mod, max_load):
     """shared-memory tile insert (kh_tile.cuh): chains that leave their 8192-slot tile and the all-ones key are

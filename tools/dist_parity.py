@@ -66,13 +66,33 @@ for n0 in SIZES:
         ok = ok and good
         if not good:
             print("rank %d n0 %d step %d MISMATCH: %d vs %d entries" % (rank, n0, step, len(tk), len(ek)), flush=True)
-    q = batch_of(5, 100000)
-    found = m.find(torch.from_numpy(q.view(np.int64)).cuda(), 0).cpu().numpy().astype(np.uint32)
+    # queries: per-rank batches (half of the keys absent), a skewed batch (slab overflow -> NCCL path), a larger batch
+    # (slabs grow), erase, then counts again.  Answers must come back in input order.
+    qpath = []
+    for qstep, (nq, skew) in enumerate([(100000, False), (100000, True), (400000, False), (400000, False)]):
+        q = batch_of(7000 + 10 * qstep + rank, nq + 321 * rank, skew)
+        some = batch_of(1000 + rank + n0 % 97, n0 + 1234 * rank)[: nq // 2]      # keys of the second insert batch
+        q[: some.shape[0]] = some
+        dq = torch.from_numpy(q.view(np.int64)).cuda()
+        found = m.find(dq, 0).cpu().numpy().astype(np.uint32)
+        qpath.append(m.last_query_path)
+        cnt = m.count(dq).cpu().numpy()
+        ok = ok and np.array_equal(found, ref.find(q, 0).astype(np.uint32)) and np.array_equal(cnt, ref.count(q).astype(np.uint8))
+    for g in range(p):                           # every rank erases its own batch; the checker erases all of them
+        e = batch_of(9000 + g, 50000 + 17 * g)
+        e[:20000] = batch_of(1000 + g + n0 % 97, n0 + 1234 * g)[:20000]
+        ref.erase(e)
+        if g == rank:
+            m.erase(torch.from_numpy(e.view(np.int64)).cuda())
     gk, gv = ref.to_vector()
-    d = dict(zip(gk.tolist(), gv.tolist()))
-    exp = np.array([d.get(int(x), 0) for x in q], dtype=np.uint32)
-    ok = ok and np.array_equal(found, exp)
-    print("rank %d n0 %d paths %s size %d %s" % (rank, n0, ",".join(path), m.local_size(), "OK" if ok else "FAIL"), flush=True)
+    own = o.rank("MURMUR64avx", gk, p) == rank
+    ek, ev = sort_pairs(gk[own], gv[own])
+    tk, tv = sort_pairs(*m.to_vector())
+    ok = ok and np.array_equal(tk, ek) and np.array_equal(tv.astype(np.uint32), ev.astype(np.uint32))
+    q = batch_of(9000 + rank, 50000 + 17 * rank)
+    ok = ok and np.array_equal(m.count(torch.from_numpy(q.view(np.int64)).cuda()).cpu().numpy(), ref.count(q).astype(np.uint8))
+    print("rank %d n0 %d paths %s queries %s size %d %s" % (rank, n0, ",".join(path), ",".join(qpath), m.local_size(),
+                                                           "OK" if ok else "FAIL"), flush=True)
 
 flag = torch.tensor([1 if ok else 0], device="cuda")
 dist.all_reduce(flag, op=dist.ReduceOp.MIN)
