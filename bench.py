@@ -16,6 +16,7 @@ N > 1 (torchrun): one process per GPU, each rank brings its own 100M keys (weak 
 DistHash_9876543(key) & (p-1); NCCL all-to-all; local insert; queries return along the reverse all-to-all.
 """
 import argparse
+import gc
 import json
 import os
 import subprocess
@@ -81,6 +82,10 @@ class ClockSampler:
                                          stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
             self.th = threading.Thread(target=self._read, daemon=True)
             self.th.start()
+            # nvidia-smi's start-up (NVML init) can stall the driver for tens of ms: let it finish before anything is timed
+            t0 = time.time()
+            while not self.lines and time.time() - t0 < 5.0:
+                time.sleep(0.01)
         except Exception:
             self.proc = None
 
@@ -372,9 +377,12 @@ def ours_multi(args):
         barrier(); e2.record(); torch.cuda.synchronize()
         return e0.elapsed_time(e1), e1.elapsed_time(e2), f, xb
 
+    step_log = []                                                     # rank 0's per-step times (device and e2e runs)
+
     def run(k_in, q_in, to_host):
         for _ in range(args.warmup):
             step(k_in, q_in, to_host)
+        gc.collect(); gc.disable()                                    # no collector pause inside a sub-millisecond phase
         ti, tf, xb = [], [], 0
         for _ in range(args.steps):
             a, b, f, xb = step(k_in, q_in, to_host)
@@ -382,6 +390,8 @@ def ours_multi(args):
         t = torch.tensor([float(np.mean(ti)), float(np.mean(tf))], device="cuda")
         dist.all_reduce(t, op=dist.ReduceOp.MAX)                      # max over ranks
         assert int((f != 0).sum()) == nq                              # every query key is present
+        gc.enable()
+        step_log.append({"insert_ms": [round(x, 3) for x in ti], "find_ms": [round(x, 3) for x in tf]})
         return t.tolist(), xb
 
     sampler = ClockSampler(local)
@@ -416,7 +426,7 @@ def ours_multi(args):
                                    "count map insert, then %d finds per GPU with reply" % (n, world, nq),
                        "n_keys_per_gpu": n, "n_query_per_gpu": nq, "hash": args.hash, "chunks": dm.chunks,
                        "l2": "inputs larger than L2; tables rebuilt from capacity 128 every step"},
-            "finds_per_s": world * nq / (tf * 1e-3), "phase_ms": {"insert": ti, "find": tf},
+            "finds_per_s": world * nq / (tf * 1e-3), "phase_ms": {"insert": ti, "find": tf}, "rank0_steps": step_log[:1],
             "exchange": {"bytes_sent_per_rank_insert": int(xbytes), "GB_per_s_per_rank_if_serial": xbytes / (ti * 1e-3) / 1e9,
                          "nvlink_peak_GB_per_s_per_direction": 900},
             "roofline": {"bound": "hbm", "kernel": "table insert kernels on rank 0 (tile_insert_kernel, kh_tile.cuh; insert_kernel for deferred keys)", "achieved": achieved,

@@ -292,6 +292,12 @@ khx_peer *khx_peer_create_q(int device, uint32_t rank, uint32_t p, uint64_t capa
  * d_counts_row (DEVICE, p words or NULL) is published to every rank, counts_matrix (HOST, p x p or NULL) receives the
  * matrix [sender][owner].  KH_ERR_CUDA when a peer does not arrive within 10 s. */
 int khx_peer_sync_dev(kh_table *t, khx_peer *x, uint64_t epoch, const uint64_t *d_counts_row, uint64_t *counts_matrix);
+/* Insert exchange without NCCL: after khx_plan_scatter_slabs_dev, push metadata block r of d_meta into owner r's metadata
+ * area (half `parity`, slot of this rank) by peer stores and pass the barrier, which also delivers the count matrix
+ * (d_meta[r][0]).  khx_peer_meta_ptr = this rank's area of that half: p blocks of khx_meta_words() words, block g from
+ * sender g -- the d_recv_meta of khx_insert_recv_slabs_dev. */
+int khx_push_meta_sync_dev(kh_table *t, khx_peer *x, int parity, const uint64_t *d_meta, uint64_t epoch, uint64_t *counts_matrix);
+uint64_t *khx_peer_meta_ptr(khx_peer *x, int parity);
 int khx_query_scatter_slabs_dev(kh_table *t, int dist_hash, uint32_t dist_seed, const uint64_t *d_keys, uint64_t n, khx_peer *x,
                                 uint64_t slab_cap, uint32_t *d_perm, uint64_t *d_counts);
 int64_t khx_query_slabs_dev(kh_table *t, khx_peer *x, int op, uint64_t slab_cap, const uint64_t *counts, uint32_t nonexistent);

@@ -252,14 +252,17 @@ __global__ void __launch_bounds__(PS_BLOCK, 2) scatter_slabs_kernel(const uint64
 // flag in the LOCAL header has reached the epoch.  When the kernel ends, every peer's stores that preceded its flag (the
 // keys / answers of the kernels before it on its stream) are visible here -- a barrier without NCCL's launch latency, and
 // the p x p counts arrive with it.  A peer that never shows up trips the time-out instead of hanging the GPU.
-struct PeerHeader { unsigned long long flags[WIN_MAX_DST]; unsigned long long counts[WIN_MAX_DST][WIN_MAX_DST]; };
+struct PeerHeader { unsigned long long flags[WIN_MAX_DST]; unsigned long long counts[2][WIN_MAX_DST][WIN_MAX_DST]; };
 struct PeerHeaders { PeerHeader *h[WIN_MAX_DST]; };
+// slot: which of the two count matrices this call writes (they alternate, so a rank that is one call ahead never
+// overwrites a matrix a slower rank has not copied out yet).  cstride: distance between two entries of counts_row.
 __global__ void peer_sync_kernel(const __grid_constant__ PeerHeaders hd, uint32_t rank, uint32_t p, unsigned long long epoch,
-                                 const unsigned long long *counts_row, int *timed_out) {
+                                 const unsigned long long *counts_row, int cstride, int slot, int *timed_out) {
   const uint32_t r = threadIdx.x;
   if (r >= p) return;
   if (counts_row)
-    for (uint32_t c = 0; c < p; ++c) *reinterpret_cast<volatile unsigned long long *>(&hd.h[r]->counts[rank][c]) = counts_row[c];
+    for (uint32_t c = 0; c < p; ++c)
+      *reinterpret_cast<volatile unsigned long long *>(&hd.h[r]->counts[slot][rank][c]) = counts_row[(size_t)c * cstride];
   __threadfence_system();
   *reinterpret_cast<volatile unsigned long long *>(&hd.h[r]->flags[rank]) = epoch;
   unsigned long long t0;
@@ -272,6 +275,14 @@ __global__ void peer_sync_kernel(const __grid_constant__ PeerHeaders hd, uint32_
     __nanosleep(200);
   }
   __threadfence_system();
+}
+
+// insert sender: metadata block r -> owner r's metadata area (slot of this rank), by peer stores
+struct MetaDst { unsigned long long *d[WIN_MAX_DST]; };
+__global__ void push_meta_kernel(const unsigned long long *meta, const __grid_constant__ MetaDst dst) {
+  const unsigned long long *src = meta + (size_t)blockIdx.x * META_WORDS;
+  unsigned long long *o = dst.d[blockIdx.x];
+  for (int i = threadIdx.x; i < META_WORDS; i += blockDim.x) o[i] = src[i];
 }
 
 // answers of a query, as they came back in slab order, into input order: out[perm[r][i]] = reply[r][i] for i < counts[r]
@@ -336,6 +347,7 @@ struct khx_peer {
   uint32_t rank = 0, p = 1;
   uint64_t capacity = 0;                 // keys
   uint64_t *local = nullptr;             // this rank's receive buffer (cudaMalloc: IPC cannot export pool memory)
+  uint64_t count_syncs = 0;              // barriers that carried a count matrix (selects the matrix slot; same on every rank)
   uint32_t reply_bytes = 0;              // bytes per key of the answer region that follows the keys (query exchange), 0 = none
   uint64_t *remote[WIN_MAX_DST] = {nullptr};
   bool opened[WIN_MAX_DST] = {false};    // mapped with cudaIpcOpenMemHandle (must be closed)
@@ -360,7 +372,8 @@ static khx_peer *peer_create(int device, uint32_t rank, uint32_t p, uint64_t cap
     x->device = device; x->W = key_words; x->rank = rank; x->p = p; x->capacity = std::max<uint64_t>(capacity_keys, 1);
     x->reply_bytes = reply_bytes;
     const size_t body = x->capacity * (8 * key_words + reply_bytes);
-    KH_CUDA(cudaMalloc((void **)&x->local, body + sizeof(PeerHeader)));
+    // keys | answers | header | metadata area: 2 halves x p senders x META_WORDS (insert exchange)
+    KH_CUDA(cudaMalloc((void **)&x->local, body + sizeof(PeerHeader) + (size_t)2 * p * META_WORDS * 8));
     KH_CUDA(cudaMemset(reinterpret_cast<unsigned char *>(x->local) + body, 0, sizeof(PeerHeader)));
     x->remote[rank] = x->local;
     return KH_OK;
@@ -631,7 +644,7 @@ int64_t khx_query_slabs_dev(kh_table *t, khx_peer *x, int op, uint64_t slab_cap,
 // barrier over peer memory (peer_sync_kernel).  epoch: 1, 2, 3, ... per buffer set, the same on every rank.  d_counts_row
 // (DEVICE, p words, may be null): this rank's row of the count matrix, published to every rank; counts_matrix (HOST, p x p,
 // may be null) receives the matrix [sender][owner] as it stands in the local header after the barrier.
-int khx_peer_sync_dev(kh_table *t, khx_peer *x, uint64_t epoch, const uint64_t *d_counts_row, uint64_t *counts_matrix) {
+static int peer_sync(kh_table *t, khx_peer *x, uint64_t epoch, const uint64_t *d_counts_row, int counts_stride, uint64_t *counts_matrix) {
   return (int)guarded([&]() -> int64_t {
     if (!t || !x || epoch == 0) { set_error("bad argument"); return KH_ERR_INVALID; }
     DeviceGuard g(t->device);
@@ -644,8 +657,10 @@ int khx_peer_sync_dev(kh_table *t, khx_peer *x, uint64_t epoch, const uint64_t *
     }
     DevBuf<int> flag(1);
     KH_CUDA(cudaMemsetAsync(flag.p, 0, sizeof(int), s));
+    const int slot = (int)(x->count_syncs & 1);
+    if (d_counts_row) ++x->count_syncs;
     KH_LAUNCH(peer_sync_kernel, 1, 32, 0, s, hd, x->rank, x->p, (unsigned long long)epoch,
-              reinterpret_cast<const unsigned long long *>(d_counts_row), flag.p);
+              reinterpret_cast<const unsigned long long *>(d_counts_row), counts_stride, slot, flag.p);
     int h_flag = 0;
     PeerHeader h_hdr;
     KH_CUDA(cudaMemcpyAsync(&h_flag, flag.p, sizeof(int), cudaMemcpyDeviceToHost, s));
@@ -654,9 +669,38 @@ int khx_peer_sync_dev(kh_table *t, khx_peer *x, uint64_t epoch, const uint64_t *
     if (h_flag) { set_error("khx_peer_sync_dev: a peer did not reach epoch %llu within 10 s", (unsigned long long)epoch); return KH_ERR_CUDA; }
     if (counts_matrix)
       for (uint32_t a = 0; a < x->p; ++a)
-        for (uint32_t b = 0; b < x->p; ++b) counts_matrix[a * x->p + b] = h_hdr.counts[a][b];
+        for (uint32_t b = 0; b < x->p; ++b) counts_matrix[a * x->p + b] = h_hdr.counts[slot][a][b];
     return KH_OK;
   });
+}
+int khx_peer_sync_dev(kh_table *t, khx_peer *x, uint64_t epoch, const uint64_t *d_counts_row, uint64_t *counts_matrix) {
+  return peer_sync(t, x, epoch, d_counts_row, 1, counts_matrix);
+}
+
+// insert exchange without NCCL: push metadata block r (of d_meta, as khx_plan_scatter_slabs_dev filled it) into owner r's
+// metadata area of half `parity`, then the barrier, publishing the counts d_meta[r][0] on the way.
+int khx_push_meta_sync_dev(kh_table *t, khx_peer *x, int parity, const uint64_t *d_meta, uint64_t epoch, uint64_t *counts_matrix) {
+  const int64_t rc = guarded([&]() -> int64_t {
+    if (!t || !x || !d_meta || parity < 0 || parity > 1) { set_error("bad argument"); return KH_ERR_INVALID; }
+    DeviceGuard g(t->device);
+    const size_t body = x->capacity * (size_t)(8 * x->W + x->reply_bytes) + sizeof(PeerHeader);
+    MetaDst dst{};
+    for (uint32_t r = 0; r < x->p; ++r) {
+      if (!x->remote[r]) { set_error("peer %u not mapped", r); return KH_ERR_INVALID; }
+      dst.d[r] = reinterpret_cast<unsigned long long *>(reinterpret_cast<unsigned char *>(x->remote[r]) + body) +
+                 ((size_t)parity * x->p + x->rank) * META_WORDS;
+    }
+    KH_LAUNCH(push_meta_kernel, x->p, 256, 0, t->stream[0], reinterpret_cast<const unsigned long long *>(d_meta), dst);
+    return KH_OK;
+  });
+  if (rc != KH_OK) return (int)rc;
+  return peer_sync(t, x, epoch, d_meta, META_WORDS, counts_matrix);
+}
+// this rank's metadata area of half `parity`: p blocks of khx_meta_words() words, block g from sender g
+uint64_t *khx_peer_meta_ptr(khx_peer *x, int parity) {
+  if (!x || parity < 0 || parity > 1) return nullptr;
+  const size_t body = x->capacity * (size_t)(8 * x->W + x->reply_bytes) + sizeof(PeerHeader);
+  return reinterpret_cast<uint64_t *>(reinterpret_cast<unsigned char *>(x->local) + body) + (size_t)parity * x->p * META_WORDS;
 }
 
 // asker side, after the barrier behind the answer stores: d_out[perm[r][i]] = reply[r][i]  (elem_bytes 4 or 1)

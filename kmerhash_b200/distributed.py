@@ -149,6 +149,10 @@ class CudaEngine:
     def insert_recv_slabs(self, peers, slab_cap, parity, counts, recv_meta, default):
         return self.table.insert_recv_slabs(peers.h, slab_cap, parity, counts, recv_meta, default) if int(counts.sum()) else 0
 
+    def push_meta_sync(self, peers, parity, meta):
+        peers.epoch += 1
+        return self.table.push_meta_sync(peers.h, parity, meta, peers.epoch, peers.p)
+
     def query_scatter_slabs(self, keys, peers, slab_cap, perm, counts):
         self.table.query_scatter_slabs(keys, peers.h, slab_cap, perm, counts, self.dist_hash)
 
@@ -324,20 +328,21 @@ class DistributedMap:
         parity = self.parity
         with _Stage("plan+scatter"):
             meta = self.e.plan_scatter_slabs(keys, self.peers, self.slab_cap, parity)
-        with _Stage("meta gather"):
-            allmeta = torch.empty((p,) + tuple(meta.shape), dtype=meta.dtype, device=dev)
-            dist.all_gather_into_tensor(allmeta, meta, group=self.group)   # every rank's stores have landed
-            C = allmeta[:, :, 0].cpu().numpy().astype(np.uint64)           # C[g][r] = keys g sends to r
-        self._allmeta, self._C = allmeta, C
-        if int(C.max()) > self.slab_cap:
+        with _Stage("meta push+sync"):
+            # metadata block r -> owner r by peer stores, then the flag barrier: every rank's stores have landed and
+            # every rank holds the count matrix C[g][r] = keys g sends to r
+            C = self.e.push_meta_sync(self.peers, parity, meta)
+        if int(C.max()) > self.slab_cap:                                   # same decision on every rank
             self.slab_misses += 1
+            allmeta = torch.empty((p,) + tuple(meta.shape), dtype=meta.dtype, device=dev)
+            dist.all_gather_into_tensor(allmeta, meta, group=self.group)   # the exact path wants every block
+            self._allmeta, self._C = allmeta, C
             return None
         self.slab_misses = 0
         self.parity ^= 1
         self.last_exchange_bytes += 8 * self.W * int(C[rank].sum() - C[rank, rank])
-        recv_meta = allmeta[:, rank, :].contiguous()
         with _Stage("local insert"):
-            return self.e.insert_recv_slabs(self.peers, self.slab_cap, parity, C[:, rank], recv_meta, default)
+            return self.e.insert_recv_slabs(self.peers, self.slab_cap, parity, C[:, rank], None, default)
 
     def _insert_exact(self, keys, default, ordered):
         """two-pass sender: metadata pass -> all-gather -> exact offsets -> rank scatter into the owners' buffers.

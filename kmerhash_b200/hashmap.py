@@ -192,14 +192,27 @@ class HashMap:
                                              int(slab_cap), int(parity), meta.data_ptr()), "plan_scatter_slabs")
         return meta
 
-    def insert_recv_slabs(self, peer_handle, slab_cap, parity, counts, recv_meta, default=1):
-        """receiver half reading the p slabs of this rank's receive buffer in place; counts[g] = keys sender g stored"""
-        assert recv_meta.is_cuda and recv_meta.dtype == torch.int64 and recv_meta.is_contiguous()
+    def insert_recv_slabs(self, peer_handle, slab_cap, parity, counts, recv_meta=None, default=1):
+        """receiver half reading the p slabs of this rank's receive buffer in place; counts[g] = keys sender g stored.
+        recv_meta: [p, khx_meta_words] int64 CUDA tensor, or None = the buffer's own metadata area (khx_push_meta_sync_dev)"""
         cnt = np.ascontiguousarray(counts, dtype=np.uint64)
-        assert cnt.shape[0] == recv_meta.shape[0]
+        if recv_meta is None:
+            mp = lib.khx_peer_meta_ptr(peer_handle, int(parity))
+        else:
+            assert recv_meta.is_cuda and recv_meta.dtype == torch.int64 and recv_meta.is_contiguous()
+            assert cnt.shape[0] == recv_meta.shape[0]
+            mp = recv_meta.data_ptr()
         torch.cuda.current_stream(self.device).synchronize()
-        return check(lib.khx_insert_recv_slabs_dev(self._h, peer_handle, int(slab_cap), int(parity), cnt.ctypes.data,
-                                                   recv_meta.data_ptr(), default), "insert_recv_slabs")
+        return check(lib.khx_insert_recv_slabs_dev(self._h, peer_handle, int(slab_cap), int(parity), cnt.ctypes.data, mp, default),
+                     "insert_recv_slabs")
+
+    def push_meta_sync(self, peer_handle, parity, meta, epoch, p):
+        """metadata blocks to their owners by peer stores + barrier; returns the p x p count matrix [sender][owner]"""
+        assert meta.is_cuda and meta.dtype == torch.int64 and meta.is_contiguous()
+        mat = np.zeros((p, p), dtype=np.uint64)
+        torch.cuda.current_stream(self.device).synchronize()
+        check(lib.khx_push_meta_sync_dev(self._h, peer_handle, int(parity), meta.data_ptr(), int(epoch), mat.ctypes.data), "push_meta_sync")
+        return mat
 
     # query exchange over peer slabs (khx_query_*): see distributed.py
     def query_scatter_slabs(self, keys, peer_handle, slab_cap, perm, counts, dist_hash="MURMUR64avx", dist_seed=9876543):
