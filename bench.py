@@ -74,8 +74,35 @@ class ClockSampler:
 
     def __init__(self, gpu_index=0):
         self.lines, self.proc, self.gpu = [], None, gpu_index
+        self.nvml = None
+
+    def _nvml_loop(self):
+        nv, h = self.nvml
+        masks = {"hw_slowdown": 0x8, "hw_thermal_slowdown": 0x40, "sw_thermal_slowdown": 0x20, "sw_power_cap": 0x4}
+        get_reasons = getattr(nv, "nvmlDeviceGetCurrentClocksEventReasons", None) or getattr(nv, "nvmlDeviceGetCurrentClocksThrottleReasons")
+        while not self._stop:
+            try:
+                sm = nv.nvmlDeviceGetClockInfo(h, nv.NVML_CLOCK_SM)
+                r = int(get_reasons(h))
+                self.samples.append((float(sm), [k for k, m in masks.items() if r & m]))
+            except Exception:
+                pass
+            time.sleep(0.01)
 
     def start(self):
+        # in-process NVML (same counters nvidia-smi prints, without a second process querying the GPU every few ms,
+        # which stalls sub-millisecond phases); nvidia-smi -lms only when the NVML binding is missing
+        try:
+            import pynvml as nv
+            nv.nvmlInit()
+            h = nv.nvmlDeviceGetHandleByIndex(self.gpu)
+            self.max_mhz = float(nv.nvmlDeviceGetMaxClockInfo(h, nv.NVML_CLOCK_SM))
+            self.nvml, self.samples, self._stop = (nv, h), [], False
+            self.th = threading.Thread(target=self._nvml_loop, daemon=True)
+            self.th.start()
+            return
+        except Exception:
+            self.nvml = None
         try:
             self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.gpu), "--query-gpu=" + self.Q,
                                           "--format=csv,noheader,nounits", "-lms", "20"],
@@ -94,6 +121,15 @@ class ClockSampler:
             self.lines.append(line.strip())
 
     def stop(self):
+        if self.nvml:
+            self._stop = True
+            self.th.join(1.0)
+            if not self.samples:
+                return {"sm_mhz": None, "sm_max_mhz": self.max_mhz, "reasons": ["no samples"]}
+            sm = sorted(x[0] for x in self.samples)
+            busy = sm[len(sm) // 2:]
+            reasons = sorted({r for x in self.samples for r in x[1]})
+            return {"sm_mhz": float(np.median(busy)), "sm_max_mhz": self.max_mhz, "reasons": reasons, "samples": len(sm), "source": "nvml"}
         if not self.proc:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
         self.proc.terminate()
