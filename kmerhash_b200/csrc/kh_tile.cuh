@@ -45,6 +45,11 @@ struct TileArgs {
   uint32_t dflt;                         // addend of every key
   unsigned long long *n_new;             // [0] += new keys, [1] += deferred keys
   uint32_t *defer_idx;                   // positions (in `keys`) of the deferred keys
+  // SLAB layout (region_scatter_kernel<.., SLAB>): fine region f of 1024 owns positions [f * slab, bin_end[f]) and every
+  // position carries the top 32 bits of its key's spread hash instead of a 16-bit tag
+  const uint32_t *tags32;
+  unsigned long long slab;
+  int lbk;                               // log2(number of buckets of the table)
 };
 
 __device__ __forceinline__ void lds_v2(const uint64_t *p, uint64_t &a, uint64_t &b) {
@@ -81,6 +86,7 @@ __device__ __forceinline__ uint32_t tile_insert_one(uint64_t *sk, uint32_t *sv, 
   return 0;
 }
 
+template <bool SLAB>
 __global__ void __launch_bounds__(TI_THREADS, 2) tile_insert_kernel(TileArgs a) {
   extern __shared__ __align__(16) unsigned char ti_smem[];
   uint64_t *sk = reinterpret_cast<uint64_t *>(ti_smem);
@@ -96,9 +102,18 @@ __global__ void __launch_bounds__(TI_THREADS, 2) tile_insert_kernel(TileArgs a) 
     const uint64_t c = tile >> a.subs_log2;
     const uint32_t sub = (uint32_t)tile & subs_mask;
     // batch positions are 32-bit (the host keeps n < 2^32)
-    const uint32_t begin = c ? (uint32_t)a.bin_end[(c - 1) * a.bin_stride] : 0u, end = (uint32_t)a.bin_end[c * a.bin_stride];
+    uint32_t begin = 0, end = 0;
+    // SLAB: the tile's keys lie in `pieces` consecutive fine regions starting at f0 (one region when the table has at
+    // least 1024 tiles, else 1024 / n_tiles regions per tile); a key is the tile's when the top bits of its hash say so
+    const int tile_bits = a.lbk - TI_BUCKET_BITS;                  // bits of a tile index
+    const uint32_t pieces = SLAB ? (tile_bits >= 10 ? 1u : (1u << (10 - tile_bits))) : 1u;
+    const uint32_t f0 = SLAB ? (tile_bits >= 10 ? (uint32_t)(tile >> (tile_bits - 10)) : (uint32_t)tile << (10 - tile_bits)) : 0u;
+    if constexpr (!SLAB) {
+      begin = c ? (uint32_t)a.bin_end[(c - 1) * a.bin_stride] : 0u;
+      end = (uint32_t)a.bin_end[c * a.bin_stride];
+      if (a.fresh == 1 && begin == end) continue;   // nothing to add to an empty tile (uniform per CTA)
+    }
     uint4 *g = reinterpret_cast<uint4 *>(a.t.slots) + tile * TI_SLOTS;
-    if (a.fresh == 1 && begin == end) continue;     // nothing to add to an empty tile (uniform per CTA)
 
     // ---- stage the tile -------------------------------------------------------------------
     if (a.fresh) {
@@ -115,24 +130,37 @@ __global__ void __launch_bounds__(TI_THREADS, 2) tile_insert_kernel(TileArgs a) 
     // ---- scan the region's tags, compact the tile's keys, insert them with full warps -----
     // One batch of 32 keys is always "in flight": its key / tag loads were issued a step earlier, so the gather
     // latency overlaps the probes of the batch before it.
-    const uint32_t first = begin & ~(uint32_t)(TI_CHUNK - 1);
     uint32_t qn = 0;
     bool pending = false;
     uint64_t pkey = 0; uint32_t ptag = 0, ppos = 0;
+    const int lb_shift = SLAB ? 32 - a.lbk : 0;                        // SLAB: bucket index = hash top half >> lb_shift
+    for (uint32_t piece = 0; piece < pieces; ++piece) {
+    if constexpr (SLAB) {
+      const uint32_t f = f0 + piece;
+      begin = (uint32_t)(f * a.slab);
+      end = (uint32_t)min((unsigned long long)a.bin_end[(size_t)f * a.bin_stride], (unsigned long long)(f + 1) * a.slab);
+    }
+    const uint32_t first = begin & ~(uint32_t)(TI_CHUNK - 1);
     uint64_t base = (uint64_t)first + (uint64_t)warp * TI_CHUNK;       // 64-bit: may step past 2^32 at the end
-    uint2 nxt = make_uint2(0u, 0u);
-    if (base < end) nxt = __ldg(reinterpret_cast<const uint2 *>(a.tags + base) + lane);
+    uint4 nxt = make_uint4(0u, 0u, 0u, 0u);
+    auto load_tags = [&](uint64_t at) -> uint4 {
+      if constexpr (SLAB) return __ldg(reinterpret_cast<const uint4 *>(a.tags32 + at) + lane);
+      const uint2 v = __ldg(reinterpret_cast<const uint2 *>(a.tags + at) + lane);
+      return make_uint4(v.x & 0xffffu, v.x >> 16, v.y & 0xffffu, v.y >> 16);
+    };
+    if (base < end) nxt = load_tags(base);
     for (; base < end; base += (uint64_t)TI_WARPS * TI_CHUNK) {
-      const uint2 cur = nxt;
+      const uint4 cur = nxt;
       const uint64_t nb = base + (uint64_t)TI_WARPS * TI_CHUNK;
-      if (nb < end) nxt = __ldg(reinterpret_cast<const uint2 *>(a.tags + nb) + lane);
-      const uint32_t tg[4] = {cur.x & 0xffffu, cur.x >> 16, cur.y & 0xffffu, cur.y >> 16};
+      if (nb < end) nxt = load_tags(nb);
+      const uint32_t tg[4] = {cur.x, cur.y, cur.z, cur.w};
       const uint32_t p0 = (uint32_t)base + (uint32_t)lane * 4;
       const bool interior = base >= begin && base + TI_CHUNK <= end;   // warp-uniform
 #pragma unroll
       for (int j = 0; j < 4; ++j) {
         const uint32_t p = p0 + j;
-        bool mine = (tg[j] >> TI_BUCKET_BITS) == sub;
+        bool mine = SLAB ? (uint32_t)((uint64_t)tg[j] >> (lb_shift + TI_BUCKET_BITS)) == (uint32_t)tile
+                         : (tg[j] >> TI_BUCKET_BITS) == sub;
         if (!interior) mine = mine && p >= begin && p < end;
         const uint32_t bal = __ballot_sync(FULL_MASK, mine);
         if (mine) sq[qn + __popc(bal & lt_mask)] = p;
@@ -143,7 +171,7 @@ __global__ void __launch_bounds__(TI_THREADS, 2) tile_insert_kernel(TileArgs a) 
       while (qn - h >= 32u) {
         const uint32_t pos = sq[h + lane];
         const uint64_t key = __ldg(a.keys + pos);
-        const uint32_t tag = (uint32_t)__ldg(a.tags + pos);
+        const uint32_t tag = SLAB ? (__ldg(a.tags32 + pos) >> lb_shift) : (uint32_t)__ldg(a.tags + pos);
         if (pending) fresh += tile_insert_one(sk, sv, pkey, ptag & (uint32_t)(TI_BUCKETS - 1), a.dflt, ppos, a);
         pkey = key; ptag = tag; ppos = pos; pending = true;
         h += 32;
@@ -157,11 +185,12 @@ __global__ void __launch_bounds__(TI_THREADS, 2) tile_insert_kernel(TileArgs a) 
       }
       __syncwarp();
     }
+    }   // pieces
     if (pending) fresh += tile_insert_one(sk, sv, pkey, ptag & (uint32_t)(TI_BUCKETS - 1), a.dflt, ppos, a);
     if (lane < qn) {
       const uint32_t pos = sq[lane];
       const uint64_t key = __ldg(a.keys + pos);
-      const uint32_t lb = (uint32_t)__ldg(a.tags + pos) & (uint32_t)(TI_BUCKETS - 1);
+      const uint32_t lb = (SLAB ? (__ldg(a.tags32 + pos) >> lb_shift) : (uint32_t)__ldg(a.tags + pos)) & (uint32_t)(TI_BUCKETS - 1);
       fresh += tile_insert_one(sk, sv, key, lb, a.dflt, pos, a);
     }
     __syncthreads();

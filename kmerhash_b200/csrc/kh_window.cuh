@@ -229,13 +229,27 @@ __device__ __forceinline__ uint64_t seg_phys(const SegSpec &g, uint64_t i) {
   const int s = seg_index(g, i);
   return g.base[s] + (i - g.prefix[s]);
 }
-template <int W> constexpr size_t rs_smem_bytes() {
-  return (size_t)RS_TILE_BYTES + 2 * (size_t)(RS_TILE_BYTES / (8 * W)) * 2 + WIN_MAX_P * 4 + WIN_MAX_P * 8;
+// sorted tile | per position: region (u16) + tag (u16), or one u32 (SLAB) | cur | goff (u32: positions stay < 2^32) |
+// SLAB: 4096 HLL register bytes
+template <int W> constexpr size_t rs_smem_bytes(bool slab = false) {
+  return (size_t)RS_TILE_BYTES + 2 * (size_t)(RS_TILE_BYTES / (8 * W)) * 2 + WIN_MAX_P * 4 + WIN_MAX_P * 4 + (slab ? HLL_M : 0);
 }
-template <int W, bool TAGS>
+// SLAB mode: no histogram of the batch exists yet.  Region r owns the fixed range [r * slab, (r + 1) * slab) of `out` (the
+// cursors start at r * slab), keys that do not fit go to an overflow list, and the SAME pass computes the HyperLogLog
+// registers -- estimate, histogram and region sort in one read of the batch.  The tag is 32 bits wide: the top half of
+// the spread hash (region = its top 10 bits), so the consumer can cut any table geometry out of it.
+struct SlabSpec {
+  unsigned long long slab;            // positions per region
+  uint64_t *ovf_keys;                 // keys whose region was full
+  unsigned long long *ovf_count, ovf_cap;
+  uint32_t *g_regs;                   // HLL_M registers, merged with atomicMax
+  uint32_t *tags32;                   // per output position
+  int h32;                            // the store hash is 32 bits wide
+};
+template <int W, bool TAGS, bool SLAB = false>
 __global__ void __launch_bounds__(RS_BLOCK, 2) region_scatter_kernel(const uint64_t *keys, uint64_t n, BinSpec spec,
                                                                      unsigned long long *cursors, uint64_t *out, TagSpec tags,
-                                                                     const __grid_constant__ SegSpec segs) {
+                                                                     const __grid_constant__ SegSpec segs, SlabSpec sl = SlabSpec{}) {
   constexpr int TILE = RS_TILE_BYTES / (8 * W);
   constexpr int KPT = TILE / RS_BLOCK;                // 16 (W=1) / 8 (W=2)
   constexpr int RPT = WIN_MAX_P / RS_BLOCK;           // 2
@@ -244,10 +258,15 @@ __global__ void __launch_bounds__(RS_BLOCK, 2) region_scatter_kernel(const uint6
   __shared__ typename Scan::TempStorage tmp;
   extern __shared__ __align__(16) unsigned char rs_smem[];
   uint64_t *skeys = reinterpret_cast<uint64_t *>(rs_smem);
-  unsigned long long *goff = reinterpret_cast<unsigned long long *>(rs_smem + RS_TILE_BYTES);   // run start in `out` - run start in tile
-  uint32_t *cur = reinterpret_cast<uint32_t *>(goff + WIN_MAX_P);                               // histogram, then running position
+  uint32_t *goff = reinterpret_cast<uint32_t *>(rs_smem + RS_TILE_BYTES);      // run start in `out` - run start in tile (mod 2^32)
+  uint32_t *cur = goff + WIN_MAX_P;                                            // histogram, then running position
   uint16_t *sreg = reinterpret_cast<uint16_t *>(cur + WIN_MAX_P);
   uint16_t *stag = sreg + TILE;
+  uint32_t *shm = reinterpret_cast<uint32_t *>(sreg);                          // SLAB: hash top half per sorted position (replaces sreg + stag)
+  uint32_t *regs = reinterpret_cast<uint32_t *>(sreg + 2 * TILE);              // SLAB: HLL register bytes, four to a word
+  if constexpr (SLAB) {
+    for (int i = threadIdx.x; i < HLL_M / 4; i += RS_BLOCK) regs[i] = 0;
+  }
   const int P = 1 << spec.lp;
   const int rshift = spec.lp ? 32 - spec.lp : 31;     // lp == 0: one region (bit 31 is masked off below)
   const uint32_t rmask = spec.lp ? 0xffffffffu : 0u;
@@ -287,8 +306,28 @@ __global__ void __launch_bounds__(RS_BLOCK, 2) region_scatter_kernel(const uint6
       for (int j = 0; j < B; ++j) {
         const int e = (j0 + j) * RS_BLOCK + threadIdx.x;
         if (e < tile_n) {
-          hm[j0 + j] = (uint32_t)(spread_hash(hash_runtime<W>(spec.hash_kind, k[j], spec.hp)) >> 32);
+          const uint64_t h = hash_runtime<W>(spec.hash_kind, k[j], spec.hp);
+          hm[j0 + j] = (uint32_t)(spread_hash(h) >> 32);
           atomicAdd(&cur[(hm[j0 + j] >> rshift) & rmask], 1u);
+          if constexpr (SLAB) {                       // hyperloglog64::update (KH/hyperloglog64.hpp:145-201), byte-wide max in a word
+            uint32_t idx, rank;
+            if (sl.h32) {
+              const uint32_t x = (uint32_t)h;
+              idx = x >> (32 - HLL_P);
+              rank = __clz((int)((x << HLL_P) | 0xFFFu)) + 1;
+            } else {
+              idx = (uint32_t)(h >> (64 - HLL_P));
+              rank = __clzll((long long)((h << HLL_P) | 0xFFFULL)) + 1;
+            }
+            uint32_t *w = regs + idx / 4;
+            const int sh = (idx & 3) * 8;
+            uint32_t old = *w;
+            while (((old >> sh) & 0xffu) < rank) {
+              const uint32_t seen = atomicCAS(w, old, (old & ~(0xffu << sh)) | (rank << sh));
+              if (seen == old) break;
+              old = seen;
+            }
+          }
         }
       }
     }
@@ -326,28 +365,60 @@ __global__ void __launch_bounds__(RS_BLOCK, 2) region_scatter_kernel(const uint6
           const uint32_t pos = atomicAdd(&cur[r], 1u);
 #pragma unroll
           for (int q = 0; q < W; ++q) skeys[pos * W + q] = k[j][q];
-          sreg[pos] = (uint16_t)r;
-          if constexpr (TAGS) stag[pos] = (uint16_t)((hm[j0 + j] >> tshift) & tags.mask);
+          if constexpr (SLAB) {
+            shm[pos] = hm[j0 + j];
+          } else {
+            sreg[pos] = (uint16_t)r;
+            if constexpr (TAGS) stag[pos] = (uint16_t)((hm[j0 + j] >> tshift) & tags.mask);
+          }
         }
       }
     }
 #pragma unroll
     for (int q = 0; q < RPT; ++q) {
       const int r = threadIdx.x * RPT + q;
-      if (r < P) goff[r] = gb[q] - st[q];
+      if (r < P) goff[r] = (uint32_t)gb[q] - st[q];
     }
     __syncthreads();
 
 #pragma unroll 4
     for (int e = threadIdx.x; e < tile_n; e += RS_BLOCK) {
-      const unsigned long long gpos = goff[sreg[e]] + (unsigned long long)e;
-      uint64_t *o = out + gpos * W;
+      if constexpr (SLAB) {
+        const uint32_t t32 = shm[e], r = (t32 >> rshift) & rmask;
+        const uint32_t gpos = goff[r] + (uint32_t)e;
+        if ((unsigned long long)gpos < (unsigned long long)(r + 1) * sl.slab) {
+          uint64_t *o = out + (size_t)gpos * W;
 #pragma unroll
-      for (int q = 0; q < W; ++q) o[q] = skeys[e * W + q];
-      if constexpr (TAGS) tags.out[gpos] = stag[e];
+          for (int q = 0; q < W; ++q) o[q] = skeys[e * W + q];
+          sl.tags32[gpos] = t32;
+        } else {                                      // the region's slab is full
+          const unsigned long long at = atomicAdd(sl.ovf_count, 1ULL);
+          if (at < sl.ovf_cap)
+#pragma unroll
+            for (int q = 0; q < W; ++q) sl.ovf_keys[at * W + q] = skeys[e * W + q];
+        }
+      } else {
+        const size_t gpos = goff[sreg[e]] + (uint32_t)e;
+        uint64_t *o = out + gpos * W;
+#pragma unroll
+        for (int q = 0; q < W; ++q) o[q] = skeys[e * W + q];
+        if constexpr (TAGS) tags.out[gpos] = stag[e];
+      }
     }
     __syncthreads();
   }
+  if constexpr (SLAB) {
+    for (int i = threadIdx.x; i < HLL_M; i += RS_BLOCK) {
+      const uint32_t v = (regs[i / 4] >> ((i & 3) * 8)) & 0xffu;
+      if (v) atomicMax(&sl.g_regs[i], v);
+    }
+  }
+}
+
+// SLAB mode: region r's cursor starts at r * slab
+static __global__ void slab_cursor_kernel(unsigned long long *cursors, int cstride, unsigned long long slab) {
+  const int r = blockIdx.x * blockDim.x + threadIdx.x;
+  if (r < WIN_MAX_P) cursors[(size_t)r * cstride] = (unsigned long long)r * slab;
 }
 
 // host side: launch on `grid` CTAs (2 per SM fit)
@@ -361,6 +432,18 @@ inline void region_scatter_launch(int sms, cudaStream_t s, const uint64_t *keys,
   SegSpec one{};
   one.nseg = 1;
   KH_LAUNCH((region_scatter_kernel<W, TAGS>), grid, RS_BLOCK, rs_smem_bytes<W>(), s, keys, n, spec, cursors, out, tags, segs ? *segs : one);
+}
+
+// the cursors must have been set by slab_cursor_kernel; they persist over the launches of one batch (chunked feeding)
+inline void region_scatter_slab_launch(int sms, cudaStream_t s, const uint64_t *keys, uint64_t n, const BinSpec &spec,
+                                       unsigned long long *cursors, int cstride, uint64_t *out, const SlabSpec &sl) {
+  KH_CUDA(cudaFuncSetAttribute(region_scatter_kernel<1, true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)rs_smem_bytes<1>(true)));
+  constexpr uint64_t TILE = RS_TILE_BYTES / 8;
+  const int grid = (int)std::max<uint64_t>(1, std::min<uint64_t>((n + TILE - 1) / TILE, (uint64_t)sms * 2));
+  SegSpec one{};
+  one.nseg = 1;
+  const TagSpec ts{nullptr, 32, 0u, cstride};
+  KH_LAUNCH((region_scatter_kernel<1, true, true>), grid, RS_BLOCK, rs_smem_bytes<1>(true), s, keys, n, spec, cursors, out, ts, one, sl);
 }
 
 }  // namespace kh

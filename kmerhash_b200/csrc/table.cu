@@ -483,7 +483,7 @@ const uint64_t *flatten_segments(kh_table *t, const uint64_t *d_keys, uint64_t n
 
 uint64_t insert_tiled(kh_table *t, const uint64_t *d_keys, uint64_t n, uint32_t dflt, const unsigned long long *d_fine,
                       int lp, int subs_log2, cudaStream_t s, const SegSpec *segs = nullptr) {
-  KH_CUDA(cudaFuncSetAttribute(tile_insert_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TI_SMEM));   // per device
+  KH_CUDA(cudaFuncSetAttribute(tile_insert_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TI_SMEM));   // per device
   static const bool old_scatter = getenv("KH_SCATTER") && !strcmp(getenv("KH_SCATTER"), "old");
   constexpr int CSTRIDE = 16;          // one 128-byte line per cursor
   DevBuf<unsigned long long> fine_own, cursors((size_t)CSTRIDE << lp);
@@ -515,11 +515,12 @@ uint64_t insert_tiled(kh_table *t, const uint64_t *d_keys, uint64_t n, uint32_t 
     TileArgs a;
     a.t = t->view(); a.keys = sorted.p; a.tags = tags.p; a.bin_end = cursors.p; a.bin_stride = CSTRIDE; a.subs_log2 = subs_log2;
     a.fresh = t->uninit ? 2 : (t->size == 0 ? 1 : 0); a.dflt = dflt;   // 2: the slots hold garbage, every tile is written
+    a.tags32 = nullptr; a.slab = 0; a.lbk = lbk;
     t->uninit = false; a.n_new = t->counters.p; a.defer_idx = defer.p;
     const uint64_t n_tiles = t->capacity / TI_SLOTS;
     const int grid = (int)std::min<uint64_t>(n_tiles, (uint64_t)t->sms * 2);
     kev_begin(t, 0, s);
-    KH_LAUNCH(tile_insert_kernel, grid, TI_THREADS, TI_SMEM, s, a);
+    KH_LAUNCH(tile_insert_kernel<false>, grid, TI_THREADS, TI_SMEM, s, a);
     kev_end(t, s);
     added = read_counter(t, s);
     n_def = t->h_counters[1];
@@ -535,7 +536,118 @@ uint64_t insert_tiled(kh_table *t, const uint64_t *d_keys, uint64_t n, uint32_t 
 }
 
 uint64_t insert_windowed(kh_table *t, const uint64_t *d_keys, const uint32_t *d_vals, uint64_t n, uint32_t dflt,
-                         const unsigned long long *d_fine, cudaStream_t s, const SegSpec *segs = nullptr) {
+                         const unsigned long long *d_fine, cudaStream_t s, const SegSpec *segs = nullptr);
+
+// One-read bulk insert of a batch whose distinct count is not known yet (the reference's insert(): estimate -> reserve ->
+// insert, KH/robinhood_offset_hashmap_ptr.hpp:2512-2535).  The region scatter runs FIRST, in SLAB mode: it needs no
+// histogram (every one of the 1024 regions owns a fixed range sized for a uniform hash, the rare overflow goes to a side
+// list), so the same pass that sorts the batch also computes the HyperLogLog registers.  Then: estimate -> reserve (slots
+// left uninitialised) -> tile insert cutting its keys out of the 32-bit hash tags -> deferred and overflow keys through the
+// global kernel.  Returns false without touching the table when the batch does not qualify (the caller takes the
+// two-pass route); when only the table turns out unsuitable after the estimate, the region counts serve as the histogram
+// of the two-pass route, so nothing is computed twice but the sort.
+bool fused_candidate(const kh_table *t, const uint32_t *d_vals, uint64_t n) {
+  static const bool on = !(getenv("KH_FUSED") && atoi(getenv("KH_FUSED")) == 0);
+  static const bool tile_on = !(getenv("KH_TILE") && atoi(getenv("KH_TILE")) == 0);
+  if (!on || !tile_on || !window_candidate(t, d_vals, n)) return false;
+  if (t->W != 1 || t->LB * t->G != 64 || t->has_sticky || n >= (1ULL << 31) || n < (1ULL << 20)) return false;
+  return t->capacity <= (1ULL << 26);          // a larger table has more than 8 tiles per region: no tile insert anyway
+}
+
+// state of one fused batch: begin -> feed (once, or chunk by chunk as the keys arrive over PCIe) -> finish
+struct FusedBatch {
+  static constexpr int CSTRIDE = 16;
+  uint64_t n = 0, slab = 0, ovf_cap = 0;
+  DevBuf<unsigned long long> cursors, ovf_count;
+  DevBuf<uint64_t> sorted, ovf;
+  DevBuf<uint32_t> tags32, regs;
+};
+void fused_begin(FusedBatch &f, kh_table *t, uint64_t n, cudaStream_t s) {
+  f.n = n;
+  f.slab = ((uint64_t)((double)n / REGION_FINE * 1.125) + 2048 + 127) & ~127ULL;
+  f.ovf_cap = n / 16 + 4096;
+  f.cursors.alloc((size_t)FusedBatch::CSTRIDE * REGION_FINE); f.ovf_count.alloc(1);
+  f.sorted.alloc(f.slab * REGION_FINE); f.ovf.alloc(f.ovf_cap);
+  f.tags32.alloc(f.slab * REGION_FINE + 2 * TI_CHUNK); f.regs.alloc(HLL_M);
+  KH_CUDA(cudaMemsetAsync(f.regs.p, 0, HLL_M * sizeof(uint32_t), s));
+  KH_CUDA(cudaMemsetAsync(f.ovf_count.p, 0, sizeof(unsigned long long), s));
+  KH_LAUNCH(slab_cursor_kernel, (WIN_MAX_P + 255) / 256, 256, 0, s, f.cursors.p, FusedBatch::CSTRIDE, (unsigned long long)f.slab);
+}
+void fused_feed(FusedBatch &f, kh_table *t, const uint64_t *d_keys, uint64_t m, cudaStream_t s) {
+  if (!m) return;
+  const BinSpec spec{0, REGION_FINE_BITS, 0u, t->hash_kind, t->hp};
+  SlabSpec sl{};
+  sl.slab = f.slab; sl.ovf_keys = f.ovf.p; sl.ovf_count = f.ovf_count.p; sl.ovf_cap = f.ovf_cap; sl.g_regs = f.regs.p; sl.tags32 = f.tags32.p;
+  sl.h32 = hash_bits(t->hash_kind) == 32 ? 1 : 0;
+  kev_begin(t, 2, s);
+  region_scatter_slab_launch(t->sms, s, d_keys, m, spec, f.cursors.p, FusedBatch::CSTRIDE, f.sorted.p, sl);
+  kev_end(t, s);
+}
+
+// d_keys: the whole batch (only read again when the two-pass route has to take over)
+int64_t fused_finish(FusedBatch &f, kh_table *t, const uint64_t *d_keys, uint32_t dflt, cudaStream_t s) {
+  constexpr int CSTRIDE = FusedBatch::CSTRIDE;
+  const double err = 1.0 + hll_error_rate();
+  const uint64_t size0 = t->size, n = f.n, slab = f.slab, ovf_cap = f.ovf_cap;
+  DevBuf<unsigned long long> &cursors = f.cursors, &ovf_count = f.ovf_count;
+  DevBuf<uint64_t> &sorted = f.sorted, &ovf = f.ovf;
+  DevBuf<uint32_t> &tags32 = f.tags32, &regs = f.regs;
+  unsigned long long n_ovf = 0;
+  KH_CUDA(cudaMemcpyAsync(&n_ovf, ovf_count.p, sizeof(n_ovf), cudaMemcpyDeviceToHost, s));
+  const double est = hll_finish(t->hash_kind, regs.p, nullptr, s);       // synchronises s
+  const bool lazy = t->size == 0;
+  ensure_room(t, (uint64_t)std::ceil(std::min((double)n, est * err)), lazy);
+  int lp = 0, subs = 0;
+  if (n_ovf > ovf_cap || !tile_candidate(t, nullptr, n, lp, subs)) {
+    // the table does not suit the tile insert (or the batch is heavily skewed): two-pass route, histogram = region counts
+    std::vector<unsigned long long> h((size_t)CSTRIDE * REGION_FINE), fine_h(REGION_FINE);
+    KH_CUDA(cudaMemcpyAsync(h.data(), cursors.p, h.size() * sizeof(unsigned long long), cudaMemcpyDeviceToHost, s));
+    KH_CUDA(cudaStreamSynchronize(s));
+    for (int r = 0; r < REGION_FINE; ++r) fine_h[r] = h[(size_t)r * CSTRIDE] - (unsigned long long)r * slab;
+    DevBuf<unsigned long long> fine(REGION_FINE);
+    KH_CUDA(cudaMemcpyAsync(fine.p, fine_h.data(), REGION_FINE * sizeof(unsigned long long), cudaMemcpyHostToDevice, s));
+    sorted.release(); tags32.release(); ovf.release();
+    insert_windowed(t, d_keys, nullptr, n, dflt, fine.p, s);
+    return (int64_t)(t->size - size0);
+  }
+  KH_CUDA(cudaFuncSetAttribute(tile_insert_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TI_SMEM));   // per device
+  DevBuf<uint32_t> defer(n);
+  uint64_t n_def = 0;
+  { Trace tr("tile.insert", s);
+    zero_counter(t, s);
+    TileArgs a;
+    a.t = t->view(); a.keys = sorted.p; a.tags = nullptr; a.bin_end = cursors.p; a.bin_stride = CSTRIDE; a.subs_log2 = 0;
+    a.fresh = t->uninit ? 2 : (t->size == 0 ? 1 : 0); a.dflt = dflt; a.n_new = t->counters.p; a.defer_idx = defer.p;
+    a.tags32 = tags32.p; a.slab = slab; a.lbk = log2_u64(t->capacity / 4);
+    t->uninit = false;
+    const uint64_t n_tiles = t->capacity / TI_SLOTS;
+    const int grid = (int)std::min<uint64_t>(n_tiles, (uint64_t)t->sms * 2);
+    kev_begin(t, 0, s);
+    KH_LAUNCH(tile_insert_kernel<true>, grid, TI_THREADS, TI_SMEM, s, a);
+    kev_end(t, s);
+    t->size += read_counter(t, s);
+    n_def = t->h_counters[1]; }
+  if (n_def) {
+    Trace tr("tile.deferred", s);
+    DevBuf<uint64_t> nk(n_def);
+    KH_LAUNCH((gather_deferred_kernel<1>), t->grid_for(n_def, 256), 256, 0, s, sorted.p, (const uint32_t *)nullptr, defer.p, n_def,
+              nk.p, (uint32_t *)nullptr);
+    insert_resident(t, nk.p, nullptr, n_def, dflt, s);
+  }
+  if (n_ovf) insert_resident(t, ovf.p, nullptr, n_ovf, dflt, s);
+  KH_CUDA(cudaStreamSynchronize(s));
+  return (int64_t)(t->size - size0);
+}
+
+int64_t insert_fused(kh_table *t, const uint64_t *d_keys, uint64_t n, uint32_t dflt, cudaStream_t s) {
+  FusedBatch f;
+  fused_begin(f, t, n, s);
+  { Trace tr("fused.hll+scatter", s); fused_feed(f, t, d_keys, n, s); }
+  return fused_finish(f, t, d_keys, dflt, s);
+}
+
+uint64_t insert_windowed(kh_table *t, const uint64_t *d_keys, const uint32_t *d_vals, uint64_t n, uint32_t dflt,
+                         const unsigned long long *d_fine, cudaStream_t s, const SegSpec *segs) {
   int tile_lp = 0, tile_subs = 0;
   if (tile_candidate(t, d_vals, n, tile_lp, tile_subs)) return insert_tiled(t, d_keys, n, dflt, d_fine, tile_lp, tile_subs, s, segs);
   materialize(t, s);
@@ -757,6 +869,16 @@ int64_t kh::insert_dev_impl(kh_table *t, const uint64_t *d_keys, const uint32_t 
   // (COUNT tolerates a wrong bound: keys that find no slot are deferred and re-inserted after growing.)
   bool single = false;
   const bool count_mode = t->reducer == KH_REDUCE_COUNT;
+  if (estimate && !pre && fused_candidate(t, d_vals, n)) {
+    Trace tr_ins("insert.total(fused)", s);
+    struct Materialize {
+      kh_table *t; cudaStream_t s;
+      ~Materialize() { if (t->uninit) { try { materialize(t, s); cudaStreamSynchronize(s); } catch (...) {} } }
+    } guard{t, s};
+    insert_fused(t, d_keys, n, dflt, s);
+    while ((double)t->size > t->max_load * (double)t->capacity) rebuild(t, t->capacity * 2);
+    return (int64_t)(t->size - size0);
+  }
   if (estimate) {
     // insert_impl: reserve(size + estimate * (1 + error)) then one pass (:2512-2535)
     const double est = estimate_batch();
@@ -826,6 +948,30 @@ int64_t kh_insert_host(kh_table *t, const uint64_t *keys, const uint32_t *vals, 
     DeviceGuard g(t->device);
     if (n == 0) return 0;
     const int W = t->W;
+    if (estimate && !vals && fused_candidate(t, nullptr, n)) {
+      // One-read route, fed chunk by chunk BEHIND the PCIe copy: when the last chunk lands, the batch is already sorted by
+      // table region and its HLL registers are complete; only the estimate, the reserve and the tile insert remain.
+      DevBuf<uint64_t> dk(n * W);
+      FusedBatch f;
+      fused_begin(f, t, n, t->stream[0]);
+      int b = 0;
+      for (uint64_t off = 0; off < n; off += HOST_CHUNK, b ^= 1) {
+        const uint64_t m = std::min(HOST_CHUNK, n - off);
+        KH_CUDA(cudaMemcpyAsync(dk.p + off * W, keys + off * W, m * W * 8, cudaMemcpyHostToDevice, t->stream[1]));
+        KH_CUDA(cudaEventRecord(t->ev[b], t->stream[1]));
+        KH_CUDA(cudaStreamWaitEvent(t->stream[0], t->ev[b], 0));
+        fused_feed(f, t, dk.p + off * W, m, t->stream[0]);
+      }
+      KH_CUDA(cudaStreamSynchronize(t->stream[1]));
+      const uint64_t size0 = t->size;
+      struct Materialize {
+        kh_table *t; cudaStream_t s;
+        ~Materialize() { if (t->uninit) { try { materialize(t, s); cudaStreamSynchronize(s); } catch (...) {} } }
+      } guard{t, t->stream[0]};
+      fused_finish(f, t, dk.p, default_val, t->stream[0]);
+      while ((double)t->size > t->max_load * (double)t->capacity) rebuild(t, t->capacity * 2);
+      return (int64_t)(t->size - size0);
+    }
     if (estimate || t->reducer != KH_REDUCE_COUNT) {
       // Whole batch resident (the ordered reducers need stable batch positions, and presizing needs the
       // estimate before the first insert).  The HLL registers and the region histogram are accumulated

@@ -510,6 +510,43 @@ def test_single_pass_slab_exchange(kh, oracle_mod, p, W, n_per, tiled):
                 lib.khx_peer_destroy(h)
 
 
+@pytest.mark.parametrize("n,distinct,skew", [(3_000_000, 40_000, 0.0), (3_000_000, 1_500_000, 0.0), (6_000_000, 5_000_000, 0.0),
+                                             (3_000_000, 1_000_000, 0.5), (2_000_000, 1_900_000, 0.97)])
+def test_fused_one_read_bulk_insert(kh, oracle_mod, n, distinct, skew):
+    """insert() of a large COUNT batch takes the one-read route (region scatter in SLAB mode computing the HLL registers,
+    then the tile insert on 32-bit hash tags): contents must equal the oracle's, the capacity must equal the one the
+    classic estimate -> reserve -> insert route reaches (same HLL registers => same reserve), for tables with fewer and
+    more tiles than regions, for a second batch into the filled table, and for skewed batches (region overflow list;
+    at 97 % one key the whole batch falls back to the two-pass route)."""
+    o = oracle_mod.port
+    rng = np.random.default_rng(int(n + distinct + 100 * skew))
+    base = rng.integers(0, 2**62, size=distinct, dtype=np.uint64)
+    base[0] = np.uint64(0xFFFFFFFFFFFFFFFF)                              # the side-slot key rides along
+    m = kh.HashMap(1, "MURMUR64avx", "COUNT")
+    m.set_insert_window(True, 32 << 20, 1 << 20)
+    c = kh.HashMap(1, "MURMUR64avx", "COUNT")
+    c.set_insert_window(False, 32 << 20, 1 << 20)
+    gm = o.Map(1, "COUNT")
+    for batch in range(2):
+        keys = base[rng.integers(0, distinct, size=n)]
+        if skew:
+            keys[rng.random(n) < skew] = base[1]
+        keys = np.ascontiguousarray(keys)
+        import torch
+        d = torch.from_numpy(keys.view(np.int64)).cuda()
+        new_m = m.insert(d, default=1)
+        new_c = c.insert(d, default=1)
+        before = gm.size()
+        gm.insert(keys, default=1)
+        assert new_m == new_c == gm.size() - before
+        assert m.capacity() == c.capacity() and m.size() == gm.size()
+        ek, ev = sort_pairs(*gm.to_vector())
+        tk, tv = sort_pairs(*m.to_vector())
+        assert np.array_equal(tk, ek) and np.array_equal(tv, ev)
+    q = np.ascontiguousarray(np.concatenate([base[:1000], rng.integers(0, 2**62, size=1000, dtype=np.uint64)]))
+    assert np.array_equal(m.find(q, 0), gm.find(q, 0))
+
+
 def test_peer_memory_barrier(kh):
     """khx_peer_sync_dev: p ranks emulated on one GPU, one host thread per rank (the flag kernels wait for each other, so
     they must be able to run concurrently).  Every rank must come back with the same p x p count matrix, row g = what
