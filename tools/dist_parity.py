@@ -27,6 +27,8 @@ o = oracle.port
 def batch_of(seed, n, skew=False):
     """every rank can regenerate every rank's batch (the checker needs the global multiset)"""
     rng = np.random.default_rng(seed)
+    if n == 0:
+        return np.empty(0, dtype=np.uint64)
     base = rng.integers(0, 2**62, size=max(1000, n // 5), dtype=np.uint64)
     b = base[rng.integers(0, base.shape[0], size=n)]
     if skew:                                      # 70 % of the batch is ONE key: its owner's slab overflows
@@ -66,6 +68,21 @@ for n0 in SIZES:
         ok = ok and good
         if not good:
             print("rank %d n0 %d step %d MISMATCH: %d vs %d entries" % (rank, n0, step, len(tk), len(ek)), flush=True)
+    # collective calls with nothing to contribute (the reference: every rank calls, also with 0 elements,
+    # KH/distributed_batched_robinhood_map.hpp:843,911-917): rank 0 inserts nothing, the last rank asks nothing
+    for g in range(p):
+        b = batch_of(555 + g, 300000 if g else 0)
+        if b.shape[0]:
+            ref.insert(b, default=1)
+        if g == rank:
+            m.insert(torch.from_numpy(b.view(np.int64)).cuda())
+    q0 = batch_of(556 + rank, 0 if rank == p - 1 else 70000)
+    r0 = m.find(torch.from_numpy(q0.view(np.int64)).cuda(), 0).cpu().numpy().astype(np.uint32)
+    ok = ok and r0.shape[0] == q0.shape[0] and (q0.shape[0] == 0 or np.array_equal(r0, ref.find(q0, 0).astype(np.uint32)))
+    c0 = m.count(torch.from_numpy(q0.view(np.int64)).cuda()).cpu().numpy()
+    ok = ok and c0.shape[0] == q0.shape[0] and (q0.shape[0] == 0 or np.array_equal(c0, ref.count(q0).astype(np.uint8)))
+    if not ok:
+        print("rank %d n0 %d empty-batch step FAILED" % (rank, n0), flush=True)
     # queries: per-rank batches (half of the keys absent), a skewed batch (slab overflow -> NCCL path), a larger batch
     # (slabs grow), erase, then counts again.  Answers must come back in input order.
     qpath = []
