@@ -118,7 +118,7 @@ template <int W> constexpr size_t ps_smem_bytes(uint32_t p, bool meta, bool perm
 // (in `keys`) of the i-th key stored into owner r's slab, so the answers, which come back in slab order, can be put
 // into input order.  cursors[r] ends as the number of keys this rank has for owner r (also beyond slab_cap).
 template <int W, bool META, bool PERM>
-__global__ void __launch_bounds__(PS_BLOCK, 2) scatter_slabs_kernel(const uint64_t *keys, uint64_t n, BinSpec dist, int store_kind,
+__global__ void __launch_bounds__(PS_BLOCK, 3) scatter_slabs_kernel(const uint64_t *keys, uint64_t n, BinSpec dist, int store_kind,
                                                                      HashParams store_hp, const __grid_constant__ BinDst dst,
                                                                      unsigned long long slab_cap, unsigned long long *cursors,
                                                                      unsigned long long *meta, uint32_t *out_perm) {
@@ -510,8 +510,9 @@ int khx_plan_scatter_slabs_dev(kh_table *t, int dist_hash, uint32_t dist_seed, c
       DevBuf<unsigned long long> cursors(p);
       KH_CUDA(cudaMemsetAsync(cursors.p, 0, p * sizeof(unsigned long long), s));
       const uint64_t tile = PS_TILE_BYTES / (8 * t->W);
-      const int grid = (int)std::max<uint64_t>(1, std::min<uint64_t>((n + tile - 1) / tile, (uint64_t)t->sms * 2));
       const size_t smem = t->W == 1 ? ps_smem_bytes<1>(p, true, false) : ps_smem_bytes<2>(p, true, false);
+      const int per_sm = 3 * (smem + 1024) <= 227 * 1024 ? 3 : 2;       // resident CTAs (40 registers x 512 threads allow 3)
+      const int grid = (int)std::max<uint64_t>(1, std::min<uint64_t>((n + tile - 1) / tile, (uint64_t)t->sms * per_sm));
       if (t->W == 1) {
         KH_CUDA(cudaFuncSetAttribute((scatter_slabs_kernel<1, true, false>), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         KH_LAUNCH((scatter_slabs_kernel<1, true, false>), grid, PS_BLOCK, smem, s, d_keys, n, dist, t->hash_kind, t->hp, dst,
@@ -588,7 +589,7 @@ int khx_query_scatter_slabs_dev(kh_table *t, int dist_hash, uint32_t dist_seed, 
         dst.base[r] = x->remote[r] + (uint64_t)x->rank * slab_cap * t->W;
       }
       const uint64_t tile = PS_TILE_BYTES / (8 * t->W);
-      const int grid = (int)std::max<uint64_t>(1, std::min<uint64_t>((n + tile - 1) / tile, (uint64_t)t->sms * 2));
+      const int grid = (int)std::max<uint64_t>(1, std::min<uint64_t>((n + tile - 1) / tile, (uint64_t)t->sms * 3));
       const size_t smem = t->W == 1 ? ps_smem_bytes<1>(p, false, true) : ps_smem_bytes<2>(p, false, true);
       if (t->W == 1) KH_LAUNCH((scatter_slabs_kernel<1, false, true>), grid, PS_BLOCK, smem, s, d_keys, n, dist, t->hash_kind, t->hp, dst,
                                (unsigned long long)slab_cap, cursors, (unsigned long long *)nullptr, d_perm);
