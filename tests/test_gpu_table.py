@@ -547,6 +547,29 @@ def test_fused_one_read_bulk_insert(kh, oracle_mod, n, distinct, skew):
     assert np.array_equal(m.find(q, 0), gm.find(q, 0))
 
 
+@pytest.mark.parametrize("hash_kind", ["MURMUR32", "CRC32C", "FARM", "FARM32", "CLHASH", "MURMUR64", "IDEN"])
+def test_fused_one_read_bulk_insert_hash_kinds(kh, oracle_mod, hash_kind):
+    """the one-read route under every store hash (32-bit hashes take the 32-bit HLL branch): same contents as the
+    oracle, same capacity as the classic estimate -> reserve -> insert route"""
+    import torch
+    o = oracle_mod.port
+    rng = np.random.default_rng(len(hash_kind) + 5)
+    base = rng.integers(0, 2**62, size=1_200_000, dtype=np.uint64)
+    keys = np.ascontiguousarray(base[rng.integers(0, base.shape[0], size=2_500_000)])
+    d = torch.from_numpy(keys.view(np.int64)).cuda()
+    m = kh.HashMap(1, hash_kind, "COUNT")
+    m.set_insert_window(True, 32 << 20, 1 << 20)
+    c = kh.HashMap(1, hash_kind, "COUNT")
+    c.set_insert_window(False, 32 << 20, 1 << 20)
+    gm = o.Map(1, "COUNT")
+    gm.insert(keys, default=1)
+    assert m.insert(d, default=1) == c.insert(d, default=1) == gm.size()
+    assert m.capacity() == c.capacity()
+    ek, ev = sort_pairs(*gm.to_vector())
+    tk, tv = sort_pairs(*m.to_vector())
+    assert np.array_equal(tk, ek) and np.array_equal(tv, ev)
+
+
 def test_peer_memory_barrier(kh):
     """khx_peer_sync_dev: p ranks emulated on one GPU, one host thread per rank (the flag kernels wait for each other, so
     they must be able to run concurrently).  Every rank must come back with the same p x p count matrix, row g = what
