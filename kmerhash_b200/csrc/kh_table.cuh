@@ -141,6 +141,10 @@ __device__ __forceinline__ void shfl_key(const uint64_t (&k)[W], int src, uint64
 
 template <int W>
 __device__ __forceinline__ uint64_t hash_runtime(int kind, const uint64_t (&key)[W], const HashParams &hp) {
+  // The default store / rank hash first, as a plain uniform branch: with only the switch in the way the compiler keeps
+  // every key's hash in its own basic block and the unrolled per-thread batches (8 keys in the region scatter) lose their
+  // instruction-level parallelism -- the scatter ran 1.45 ms with the switch alone, 1.21 ms with this line.
+  if (kind == KH_HASH_MURMUR64AVX) return hash_key<KH_HASH_MURMUR64AVX, W>(key, hp);
   uint64_t h = 0;
   switch (kind) {
     case KH_HASH_IDEN:        h = hash_key<KH_HASH_IDEN, W>(key, hp); break;

@@ -279,12 +279,15 @@ __global__ void __launch_bounds__(RS_BLOCK, 2) region_scatter_kernel(const uint6
     // a tile that lies inside ONE piece (all but nseg-1 tiles) is addressed with a constant shift
     uint64_t shift = 0;
     bool one_piece = true;
-    if (segs.nseg > 1) {
+    if (!SLAB && segs.nseg > 1) {
       const int s0 = seg_index(segs, base), s1 = seg_index(segs, base + tile_n - 1);
       one_piece = s0 == s1;
       shift = segs.base[s0] - segs.prefix[s0];
     }
-    auto phys = [&](uint64_t i) -> uint64_t { return one_piece ? i + shift : seg_phys(segs, i); };
+    auto phys = [&](uint64_t i) -> uint64_t {
+      if constexpr (SLAB) return i;                   // the one-read route is fed contiguous chunks
+      return one_piece ? i + shift : seg_phys(segs, i);
+    };
     const uint64_t next = tile + gridDim.x;
     if (next < n_tiles) {                             // pull the next tile into L2 while this one is sorted
       const uint64_t pe = next * TILE + (uint64_t)threadIdx.x * (128 / (8 * W));
@@ -306,7 +309,9 @@ __global__ void __launch_bounds__(RS_BLOCK, 2) region_scatter_kernel(const uint6
       for (int j = 0; j < B; ++j) {
         const int e = (j0 + j) * RS_BLOCK + threadIdx.x;
         if (e < tile_n) {
-          const uint64_t h = hash_runtime<W>(spec.hash_kind, k[j], spec.hp);
+          // the default store hash without the run-time dispatch
+          const uint64_t h = spec.hash_kind == KH_HASH_MURMUR64AVX ? hash_key<KH_HASH_MURMUR64AVX, W>(k[j], spec.hp)
+                                                                    : hash_runtime<W>(spec.hash_kind, k[j], spec.hp);
           hm[j0 + j] = (uint32_t)(spread_hash(h) >> 32);
           atomicAdd(&cur[(hm[j0 + j] >> rshift) & rmask], 1u);
           if constexpr (SLAB) {                       // hyperloglog64::update (KH/hyperloglog64.hpp:145-201), byte-wide max in a word
