@@ -217,7 +217,12 @@ constexpr int RS_BLOCK = 512;
 constexpr int RS_TILE_BYTES = 65536;
 // The batch may be handed over in up to WIN_MAX_DST pieces (the per-sender slabs of a peer receive buffer, exchange.cu):
 // logical position i lies in piece s with prefix[s] <= i < prefix[s+1], at keys[base[s] + i - prefix[s]].
-struct SegSpec { int nseg; unsigned long long prefix[WIN_MAX_DST + 1]; unsigned long long base[WIN_MAX_DST]; };
+// tprefix[s] (filled by region_scatter_launch): kernel tiles in front of piece s -- every piece is cut into its own tiles,
+// so a tile never straddles two pieces and no per-key address arithmetic is needed.
+struct SegSpec {
+  int nseg;
+  unsigned long long prefix[WIN_MAX_DST + 1], base[WIN_MAX_DST], tprefix[WIN_MAX_DST + 1];
+};
 __device__ __forceinline__ int seg_index(const SegSpec &g, uint64_t i) {
   int s = 0;
 #pragma unroll
@@ -271,27 +276,30 @@ __global__ void __launch_bounds__(RS_BLOCK, 2) region_scatter_kernel(const uint6
   const int rshift = spec.lp ? 32 - spec.lp : 31;     // lp == 0: one region (bit 31 is masked off below)
   const uint32_t rmask = spec.lp ? 0xffffffffu : 0u;
   const int tshift = tags.shift - 32;                 // tag = bits of the spread hash from tags.shift up
-  const uint64_t n_tiles = (n + TILE - 1) / TILE;
+  const bool pieces = !SLAB && segs.nseg > 1;         // the one-read route is fed contiguous chunks
+  const uint64_t n_tiles = pieces ? segs.tprefix[segs.nseg] : (n + TILE - 1) / TILE;
+  // where tile t starts in `keys` and how many keys it holds (tile-uniform; a handful of compares per tile)
+  auto locate = [&](uint64_t t, uint64_t &start, int &cnt) {
+    if (!pieces) { start = t * TILE; cnt = (int)min((uint64_t)TILE, n - start); return; }
+    int sg = 0;
+#pragma unroll
+    for (int q = 1; q < WIN_MAX_DST; ++q) sg += (q < segs.nseg && t >= segs.tprefix[q]) ? 1 : 0;
+    const uint64_t off = (t - segs.tprefix[sg]) * TILE;
+    start = segs.base[sg] + off;
+    cnt = (int)min((uint64_t)TILE, (uint64_t)(segs.prefix[sg + 1] - segs.prefix[sg] - off));
+  };
 
   for (uint64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
-    const uint64_t base = tile * TILE;
-    const int tile_n = (int)min((uint64_t)TILE, n - base);
-    // a tile that lies inside ONE piece (all but nseg-1 tiles) is addressed with a constant shift
-    uint64_t shift = 0;
-    bool one_piece = true;
-    if (!SLAB && segs.nseg > 1) {
-      const int s0 = seg_index(segs, base), s1 = seg_index(segs, base + tile_n - 1);
-      one_piece = s0 == s1;
-      shift = segs.base[s0] - segs.prefix[s0];
-    }
-    auto phys = [&](uint64_t i) -> uint64_t {
-      if constexpr (SLAB) return i;                   // the one-read route is fed contiguous chunks
-      return one_piece ? i + shift : seg_phys(segs, i);
-    };
+    uint64_t base;                                    // first key of the tile in `keys`
+    int tile_n;
+    locate(tile, base, tile_n);
+    auto phys = [&](uint64_t i) -> uint64_t { return i; };
     const uint64_t next = tile + gridDim.x;
     if (next < n_tiles) {                             // pull the next tile into L2 while this one is sorted
-      const uint64_t pe = next * TILE + (uint64_t)threadIdx.x * (128 / (8 * W));
-      if (pe < n) asm volatile("prefetch.global.L2 [%0];" ::"l"(keys + seg_phys(segs, pe) * W));
+      uint64_t nb; int nn;
+      locate(next, nb, nn);
+      const int pe = (int)threadIdx.x * (128 / (8 * W));
+      if (pe < nn) asm volatile("prefetch.global.L2 [%0];" ::"l"(keys + (nb + pe) * W));
     }
     for (int r = threadIdx.x; r < P; r += RS_BLOCK) cur[r] = 0;
     __syncthreads();
@@ -433,10 +441,17 @@ inline void region_scatter_launch(int sms, cudaStream_t s, const uint64_t *keys,
   // per device, so set on every launch (a process may drive several GPUs)
   KH_CUDA(cudaFuncSetAttribute(region_scatter_kernel<W, TAGS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)rs_smem_bytes<W>()));
   constexpr uint64_t TILE = RS_TILE_BYTES / (8 * W);
-  const int grid = (int)std::max<uint64_t>(1, std::min<uint64_t>((n + TILE - 1) / TILE, (uint64_t)sms * 2));
-  SegSpec one{};
-  one.nseg = 1;
-  KH_LAUNCH((region_scatter_kernel<W, TAGS>), grid, RS_BLOCK, rs_smem_bytes<W>(), s, keys, n, spec, cursors, out, tags, segs ? *segs : one);
+  SegSpec sg{};
+  sg.nseg = 1;
+  uint64_t n_tiles = (n + TILE - 1) / TILE;
+  if (segs && segs->nseg > 1) {
+    sg = *segs;
+    sg.tprefix[0] = 0;
+    for (int q = 0; q < sg.nseg; ++q) sg.tprefix[q + 1] = sg.tprefix[q] + (sg.prefix[q + 1] - sg.prefix[q] + TILE - 1) / TILE;
+    n_tiles = sg.tprefix[sg.nseg];
+  }
+  const int grid = (int)std::max<uint64_t>(1, std::min<uint64_t>(n_tiles, (uint64_t)sms * 2));
+  KH_LAUNCH((region_scatter_kernel<W, TAGS>), grid, RS_BLOCK, rs_smem_bytes<W>(), s, keys, n, spec, cursors, out, tags, sg);
 }
 
 // the cursors must have been set by slab_cursor_kernel; they persist over the launches of one batch (chunked feeding)
