@@ -223,17 +223,6 @@ struct SegSpec {
   int nseg;
   unsigned long long prefix[WIN_MAX_DST + 1], base[WIN_MAX_DST], tprefix[WIN_MAX_DST + 1];
 };
-__device__ __forceinline__ int seg_index(const SegSpec &g, uint64_t i) {
-  int s = 0;
-#pragma unroll
-  for (int q = 1; q < WIN_MAX_DST; ++q) s += (q < g.nseg && i >= g.prefix[q]) ? 1 : 0;
-  return s;
-}
-__device__ __forceinline__ uint64_t seg_phys(const SegSpec &g, uint64_t i) {
-  if (g.nseg <= 1) return i;
-  const int s = seg_index(g, i);
-  return g.base[s] + (i - g.prefix[s]);
-}
 // sorted tile | per position: region (u16) + tag (u16), or one u32 (SLAB) | cur | goff (u32: positions stay < 2^32) |
 // SLAB: 4096 HLL register bytes
 template <int W> constexpr size_t rs_smem_bytes(bool slab = false) {
@@ -293,7 +282,6 @@ __global__ void __launch_bounds__(RS_BLOCK, 2) region_scatter_kernel(const uint6
     uint64_t base;                                    // first key of the tile in `keys`
     int tile_n;
     locate(tile, base, tile_n);
-    auto phys = [&](uint64_t i) -> uint64_t { return i; };
     const uint64_t next = tile + gridDim.x;
     if (next < n_tiles) {                             // pull the next tile into L2 while this one is sorted
       uint64_t nb; int nn;
@@ -311,7 +299,7 @@ __global__ void __launch_bounds__(RS_BLOCK, 2) region_scatter_kernel(const uint6
 #pragma unroll
       for (int j = 0; j < B; ++j) {
         const int e = (j0 + j) * RS_BLOCK + threadIdx.x;
-        if (e < tile_n) load_key<W>(keys, phys(base + e), k[j]);
+        if (e < tile_n) load_key<W>(keys, base + e, k[j]);
       }
 #pragma unroll
       for (int j = 0; j < B; ++j) {
@@ -368,7 +356,7 @@ __global__ void __launch_bounds__(RS_BLOCK, 2) region_scatter_kernel(const uint6
 #pragma unroll
       for (int j = 0; j < B; ++j) {
         const int e = (j0 + j) * RS_BLOCK + threadIdx.x;
-        if (e < tile_n) load_key<W>(keys, phys(base + e), k[j]);
+        if (e < tile_n) load_key<W>(keys, base + e, k[j]);
       }
 #pragma unroll
       for (int j = 0; j < B; ++j) {

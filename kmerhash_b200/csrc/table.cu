@@ -665,7 +665,6 @@ uint64_t insert_windowed(kh_table *t, const uint64_t *d_keys, const uint32_t *d_
   }
   KH_LAUNCH(window_cursor_kernel, 1, REGION_FINE, 0, s, d_fine, lp, cursors.p);
   DevBuf<uint64_t> sorted(n * t->W);
-  const int grid = t->sms * 4;
   { Trace tr("window.scatter", s);
     const BinSpec spec{0, lp, 0u, t->hash_kind, t->hp};
     const TagSpec ts{nullptr, 32, 0u, 1};
