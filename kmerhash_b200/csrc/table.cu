@@ -550,7 +550,9 @@ bool fused_candidate(const kh_table *t, const uint32_t *d_vals, uint64_t n) {
   static const bool on = !(getenv("KH_FUSED") && atoi(getenv("KH_FUSED")) == 0);
   static const bool tile_on = !(getenv("KH_TILE") && atoi(getenv("KH_TILE")) == 0);
   if (!on || !tile_on || !window_candidate(t, d_vals, n)) return false;
-  if (t->W != 1 || t->LB * t->G != 64 || t->has_sticky || n >= (1ULL << 31) || n < (1ULL << 20)) return false;
+  // n < 2^30: output positions are 32-bit in the kernel; even a batch that falls into ONE region keeps its cursor
+  // (1023 * slab + n < 2.2 n) below 2^32
+  if (t->W != 1 || t->LB * t->G != 64 || t->has_sticky || n >= (1ULL << 30) || n < (1ULL << 20)) return false;
   return t->capacity <= (1ULL << 26);          // a larger table has more than 8 tiles per region: no tile insert anyway
 }
 
