@@ -19,6 +19,7 @@
 #include "kh_table_host.h"
 #include "kh_hll.cuh"
 #include "kh_window.cuh"
+#include "kh_bulk.cuh"
 
 namespace kh {
 
@@ -538,7 +539,7 @@ int64_t khx_insert_recv_slabs_dev(kh_table *t, khx_peer *x, uint64_t slab_cap, i
     if (x->W != t->W || parity < 0 || parity > 1 || 2ULL * x->p * slab_cap > x->capacity) { set_error("khx_insert_recv_slabs_dev: bad arguments"); return KH_ERR_INVALID; }
     DeviceGuard g(t->device);
     const uint32_t p = x->p;
-    SegSpec segs{};
+    BkSegs segs{};
     segs.nseg = (int)p;
     uint64_t n = 0;
     for (uint32_t q = 0; q < p; ++q) {
@@ -549,14 +550,11 @@ int64_t khx_insert_recv_slabs_dev(kh_table *t, khx_peer *x, uint64_t slab_cap, i
     }
     segs.prefix[p] = n;
     if (n == 0) return 0;
-    cudaStream_t s = t->stream[0];
-    DevBuf<unsigned long long> fine(REGION_FINE), total(1);
-    DevBuf<uint32_t> regs(HLL_M);
-    KH_LAUNCH(merge_meta_kernel, (HLL_M + 255) / 256, 256, 0, s, reinterpret_cast<const unsigned long long *>(d_recv_meta), p,
-              fine.p, regs.p, total.p);
-    const double est = hll_finish(t->hash_kind, regs.p, nullptr, s);   // synchronises s
-    PreEstimate pre{est, fine.p, p > 1 ? &segs : nullptr};
-    return insert_dev_impl(t, x->local + (p > 1 ? 0 : segs.base[0] * t->W), nullptr, n, default_val, 1, &pre);
+    // the receiver reads its p slabs ONCE: the bulk insert's level-1 pass computes the HyperLogLog registers of the received
+    // keys itself (= the merged sender registers, bit for bit), so the metadata is not needed
+    (void)d_recv_meta;
+    PreEstimate pre{nullptr, &segs};
+    return insert_dev_impl(t, x->local, nullptr, n, default_val, 1, &pre);
   });
 }
 
@@ -739,9 +737,10 @@ int64_t khx_insert_recv_dev(kh_table *t, const uint64_t *d_keys, uint64_t n, con
               fine.p, regs.p, total.p);
     unsigned long long h_total = 0;
     KH_CUDA(cudaMemcpyAsync(&h_total, total.p, sizeof(h_total), cudaMemcpyDeviceToHost, s));
-    const double est = hll_finish(t->hash_kind, regs.p, nullptr, s);   // synchronises s
+    uint8_t batch_regs[HLL_M];
+    hll_finish(t->hash_kind, regs.p, batch_regs, s);   // synchronises s
     if (h_total != n) { set_error("received %llu keys but the metadata announces %llu", (unsigned long long)n, h_total); return KH_ERR_INVALID; }
-    PreEstimate pre{est, fine.p};
+    PreEstimate pre{batch_regs, nullptr};
     return insert_dev_impl(t, d_keys, nullptr, n, default_val, 1, &pre);
   });
 }

@@ -5,6 +5,7 @@
 #include <vector>
 #include "kh_common.h"
 #include "kh_table.cuh"
+#include "kh_hll.cuh"
 
 using namespace kh;   // internal header: only table.cu and exchange.cu include it
 
@@ -16,7 +17,9 @@ struct kh_table {
   bool window_on = true;              // L2-windowed bulk insert (KH_WINDOW=0 switches it off for A/B runs)
   uint64_t window_bytes = 32ULL << 20, window_min_keys = 1ULL << 22;
   bool uninit = false;                // slots allocated but not yet initialised (insert_dev_impl -> tile insert writes every tile)
-  bool has_sticky = false;            // an erase may have left sticky bits since the last rebuild / clear (kh_tile.cuh needs none)
+  bool has_sticky = false;            // an erase may have left sticky bits since the last rebuild / clear (the tile insert needs none)
+  uint8_t hll[HLL_M] = {0};           // HyperLogLog registers over every batch inserted with an estimate (the reference's
+                                      // cumulative this->hll, KH/robinhood_offset_hashmap_ptr.hpp:291,2520-2535)
   uint64_t capacity = 0, size = 0;
   HashParams hp;
   DevBuf<unsigned char> slots;
@@ -52,11 +55,10 @@ struct kh_table {
 
 
 namespace kh {
-// estimate + fine region histogram (REGION_FINE bins, device) of a batch, when the caller's pipeline already
-// produced them (host pipeline: accumulated behind the PCIe copy; exchange: computed by the senders)
-// segs (may be null): the batch lies in several pieces of d_keys (kh_window.cuh: SegSpec)
-struct SegSpec;
-struct PreEstimate { double est; const unsigned long long *fine; const SegSpec *segs = nullptr; };
+// what a caller's pipeline already knows about a batch: its HyperLogLog registers (HLL_M bytes on the HOST, may be null:
+// accumulated behind the PCIe copy) and/or the pieces it lies in (kh_bulk.cuh: BkSegs; the slabs of a peer receive buffer)
+struct BkSegs;
+struct PreEstimate { const uint8_t *regs; const BkSegs *segs; };
 // batch insert of device-resident keys (see table.cu); returns #new keys or a negative status
 int64_t insert_dev_impl(kh_table *t, const uint64_t *d_keys, const uint32_t *d_vals, uint64_t n, uint32_t dflt,
                         int estimate, const PreEstimate *pre = nullptr);

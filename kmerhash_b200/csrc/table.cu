@@ -20,8 +20,7 @@
 #include "kh_table.cuh"
 #include "kh_hll.cuh"
 #include "kh_partition.h"
-#include "kh_window.cuh"
-#include "kh_tile.cuh"
+#include "kh_bulk.cuh"
 #include "kh_table_host.h"
 
 namespace kh {
@@ -340,52 +339,108 @@ void seal(kh_table *t, cudaStream_t s) {
   else KH_LAUNCH((seal_kernel<2>), grid, 256, 0, s, v);
 }
 
-// bulk rebuild into `new_cap` slots: dump -> fresh table -> insert (keys are unique, fresh vals are 0,
-// so the COUNT-mode add is a plain copy for every reducer).  The side slot is not touched.
+// Streaming rebuild (kh_bulk.cuh: tile_rebuild_kernel): new tile x is fed from the contiguous range of old slots that hash
+// into it, the old table is read once and the new one written once.  Entries that sit outside "their" range (a chain that
+// crossed a tile boundary) or whose chain leaves the new tile come back as a short (key, value) list for the global kernel.
+// Returns false -- the old table untouched -- when the geometry does not fit or that list overflowed.
+bool rebuild_streamed(kh_table *t, uint64_t new_cap, cudaStream_t s) {
+  static const bool on = !(getenv("KH_BULK") && atoi(getenv("KH_BULK")) == 0);
+  const uint64_t tile_slots = (uint64_t)BK_TILE_BYTES / t->slot_bytes();
+  if (!on || t->LB * t->G != 64 || new_cap < tile_slots || t->capacity < tile_slots) return false;
+  const int W = t->W;
+  DevBuf<unsigned char> fresh(new_cap * t->slot_bytes());          // every tile is written by the kernel
+  const uint64_t dcap = t->size / 8 + 4096;
+  DevBuf<uint64_t> dk(dcap * W);
+  DevBuf<uint32_t> dv(dcap);
+  uint64_t placed, n_def;
+  uint32_t side_present = 0;             // the all-ones key lives in the side slot, not in the slots
+  { Trace tr("rebuild.stream", s);
+    zero_counter(t, s);
+    RebuildArgs a;
+    a.src = t->view(); a.dst = TableView{fresh.p, new_cap, t->side.p};
+    a.hash_kind = t->hash_kind; a.hp = t->hp; a.lbk = log2_u64(new_cap / t->bucket_slots());
+    a.n_placed = t->counters.p; a.defer_keys = dk.p; a.defer_vals = dv.p; a.defer_cap = dcap;
+    const int grid = (int)std::min<uint64_t>(new_cap / tile_slots, (uint64_t)t->sms * 2);
+    kev_begin(t, 0, s);
+    if (W == 1) {
+      KH_CUDA(cudaFuncSetAttribute(tile_rebuild_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tile_smem_bytes<1>()));
+      KH_LAUNCH(tile_rebuild_kernel<1>, grid, TI_THREADS, tile_smem_bytes<1>(), s, a);
+    } else {
+      KH_CUDA(cudaFuncSetAttribute(tile_rebuild_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tile_smem_bytes<2>()));
+      KH_LAUNCH(tile_rebuild_kernel<2>, grid, TI_THREADS, tile_smem_bytes<2>(), s, a);
+    }
+    kev_end(t, s);
+    KH_CUDA(cudaMemcpyAsync(&side_present, t->side.p, sizeof(uint32_t), cudaMemcpyDeviceToHost, s));
+    placed = read_counter(t, s);
+    n_def = t->h_counters[1]; }
+  if (n_def > dcap) return false;
+  t->slots = std::move(fresh);
+  t->capacity = new_cap;
+  if (n_def) {
+    Trace tr("rebuild.deferred", s);
+    zero_counter(t, s);
+    launch_insert(t, dk.p, dv.p, n_def, 0, INS_COUNT, s);
+    placed += read_counter(t, s);
+  }
+  if (placed + (side_present == 1u ? 1u : 0u) != t->size) {
+    set_error("rebuild lost entries: %llu of %llu", (unsigned long long)placed, (unsigned long long)t->size);
+    throw CudaError{KH_ERR_CUDA};
+  }
+  return true;
+}
+
+// bulk rebuild into `new_cap` slots.  Large tables: one streaming pass (rebuild_streamed).  Small ones: dump -> fresh table ->
+// insert (keys are unique, fresh vals are 0, so the COUNT-mode add is a plain copy for every reducer).  The side slot is not touched.
 // lazy: an EMPTY table's new slots are left uninitialised (t->uninit); the caller guarantees that the tile insert, which
 // writes every tile of a fresh table anyway, or materialize() follows before anything reads the table.
 void rebuild(kh_table *t, uint64_t new_cap, bool lazy = false) {
   cudaStream_t s = t->stream[0];
   Trace tr_all("rebuild", s);
   new_cap = std::max<uint64_t>(next_pow2(new_cap), 128);
-  t->has_sticky = false;               // every path below ends with freshly initialised slots
   if (t->capacity == 0 || t->size == 0) {
     t->slots.release();
     t->uninit = false;
     if (lazy) { t->slots.alloc(new_cap * t->slot_bytes()); t->uninit = true; }
     else alloc_slots(t, new_cap, t->slots, s);
     t->capacity = new_cap;
+    t->has_sticky = false;
     KH_CUDA(cudaStreamSynchronize(s));
     return;
   }
   materialize(t, s);
-  DevBuf<uint64_t> keys(t->size * t->W);
-  DevBuf<uint32_t> vals(t->size);
-  uint64_t n;
-  { Trace tr("rebuild.dump", s); n = dump_entries(t, keys.p, vals.p, t->size, s, 0); }
-  { Trace tr("rebuild.alloc+init", s);
-    t->slots.release();
-    alloc_slots(t, new_cap, t->slots, s);
-    t->capacity = new_cap; }
-  uint64_t placed;
-  { Trace tr("rebuild.insert", s);
-    zero_counter(t, s);
-    launch_insert(t, keys.p, vals.p, n, 0, INS_COUNT, s, nullptr, true);   // dump order = region order
-    placed = read_counter(t, s); }
-  if (placed != n) {
-    set_error("rebuild lost entries: %llu of %llu", (unsigned long long)placed, (unsigned long long)n);
-    throw CudaError{KH_ERR_CUDA};
+  if (!rebuild_streamed(t, new_cap, s)) {
+    DevBuf<uint64_t> keys(t->size * t->W);
+    DevBuf<uint32_t> vals(t->size);
+    uint64_t n;
+    { Trace tr("rebuild.dump", s); n = dump_entries(t, keys.p, vals.p, t->size, s, 0); }
+    { Trace tr("rebuild.alloc+init", s);
+      t->slots.release();
+      alloc_slots(t, new_cap, t->slots, s);
+      t->capacity = new_cap; }
+    uint64_t placed;
+    { Trace tr("rebuild.insert", s);
+      zero_counter(t, s);
+      launch_insert(t, keys.p, vals.p, n, 0, INS_COUNT, s, nullptr, true);   // dump order = region order
+      placed = read_counter(t, s); }
+    if (placed != n) {
+      set_error("rebuild lost entries: %llu of %llu", (unsigned long long)placed, (unsigned long long)n);
+      throw CudaError{KH_ERR_CUDA};
+    }
   }
+  t->has_sticky = false;               // freshly written slots carry no sticky bit
   if (t->reducer == KH_REDUCE_FIRST) { seal(t, s); KH_CUDA(cudaStreamSynchronize(s)); }
 }
 
-void ensure_room(kh_table *t, uint64_t n_more, bool lazy = false) {
-  const uint64_t want = capacity_for(t, t->size + n_more);
-  if (want > t->capacity) rebuild(t, want, lazy);
+// ---- presizing: the reference keeps ONE HyperLogLog over everything ever inserted with an estimate and reserves for ITS
+// estimate (KH/robinhood_offset_hashmap_ptr.hpp:291,2512-2535); reserve -> rehash resizes -- up or down -- whenever the target
+// differs and the entries fit (:896-901, :907-935).
+double merge_batch_registers(kh_table *t, const uint8_t *batch_regs) {
+  for (int i = 0; i < HLL_M; ++i) t->hll[i] = std::max(t->hll[i], batch_regs[i]);
+  return hll_estimate_from_regs(t->hll, hash_bits(t->hash_kind));
 }
-
-bool window_candidate(const kh_table *t, const uint32_t *d_vals, uint64_t n) {
-  return t->window_on && t->reducer == KH_REDUCE_COUNT && !d_vals && n >= t->window_min_keys && n < (1ULL << 32);
+void reserve_for_estimate(kh_table *t, double est, bool lazy) {
+  const uint64_t want = capacity_for(t, (uint64_t)(est * (1.0 + hll_error_rate())));
+  if (want != t->capacity && (double)t->size < std::ceil(t->max_load * (double)want)) rebuild(t, want, lazy);
 }
 
 // gather the deferred keys (and their addends) of a COUNT launch into fresh arrays
@@ -449,30 +504,89 @@ uint64_t insert_resident(kh_table *t, const uint64_t *d_keys, const uint32_t *d_
   return added;
 }
 
-// L2-windowed bulk insert.  Random probes into a table much larger than the 126 MB L2 run at the DRAM
-// random-access rate (~13 G read+atomic/s measured, profiles/r01_probes_l2_resident.jsonl); into a region
-// that stays resident in L2 they run at ~55 G/s.  So a large COUNT batch is first sorted by table region
-// (kh_window.cuh: top bits of the spread store hash = a contiguous 1/P of the table, window_bytes each),
-// and the probe kernel then walks the sorted batch: at any moment all resident warps work on one or two
-// regions.  Costs one extra streaming pass (16 B/key), saves the DRAM-latency-bound random traffic.
-// `d_fine`: the fine region histogram of this batch if the HLL pass already produced it, else nullptr.
-// Shared-memory tile insert (kh_tile.cuh): eligible for COUNT batches with a uniform addend into an 8-byte-key
-// table of 64-byte buckets without sticky bits, when the batch is large against the table (the whole table is
-// streamed through shared memory once) and a coarse region spans at most 8 tiles.
-bool tile_candidate(const kh_table *t, const uint32_t *d_vals, uint64_t n, int &lp, int &subs_log2) {
-  static const bool on = !(getenv("KH_TILE") && atoi(getenv("KH_TILE")) == 0);
-  if (!on || !window_candidate(t, d_vals, n)) return false;
-  if (t->W != 1 || t->LB * t->G != 64 || t->has_sticky || t->capacity < (uint64_t)TI_SLOTS) return false;
-  if (n * 4 < t->capacity) return false;
-  const int lbk = log2_u64(t->capacity / 4);               // bits of a bucket index
-  lp = std::min(REGION_FINE_BITS, lbk - TI_BUCKET_BITS);
-  subs_log2 = lbk - TI_BUCKET_BITS - lp;
-  return subs_log2 <= 3;
+// =========================================================================================================================
+// the streaming bulk insert (kh_bulk.cuh)
+// =========================================================================================================================
+bool bulk_on() { static const bool on = !(getenv("KH_BULK") && atoi(getenv("KH_BULK")) == 0); return on; }
+constexpr uint64_t BULK_MAX_KEYS = 1ULL << 30;      // record positions are 32-bit: (1.125 + 1) * n + pads stays below 2^32
+
+// COUNT batch with one addend for all keys, 64-byte buckets, large enough to pay for streaming the table once
+bool bulk_candidate(const kh_table *t, const uint32_t *d_vals, uint64_t n) {
+  return bulk_on() && t->window_on && t->reducer == KH_REDUCE_COUNT && !d_vals && t->LB * t->G == 64 &&
+         n >= t->window_min_keys && n >= 1024 && n <= BULK_MAX_KEYS;
 }
 
-// a batch handed over in pieces (SegSpec) -> one contiguous array, for the paths whose kernels want one
-const uint64_t *flatten_segments(kh_table *t, const uint64_t *d_keys, uint64_t n, const SegSpec *segs, DevBuf<uint64_t> &buf, cudaStream_t s) {
-  if (!segs || segs->nseg <= 1) return d_keys;
+// state of one batch: begin -> feed (once, or chunk by chunk as the keys arrive over PCIe or NVLink) -> finish
+struct BulkBatch {
+  uint64_t n = 0, fed = 0, slab = 0, ovf_cap = 0;
+  int lp = 0;
+  DevBuf<unsigned long long> cursors, ovf_count;
+  DevBuf<uint4> recs;
+  DevBuf<uint64_t> ovf;
+  DevBuf<uint32_t> regs;
+};
+
+// level-1 regions: as many as the LARGEST table this batch can lead to has tiles (then region == tile or finer and no
+// level 2 is needed), at most 4096, at least 64
+int bulk_region_bits(const kh_table *t, uint64_t n) {
+  const uint64_t tile_slots = (uint64_t)BK_TILE_BYTES / t->slot_bytes();
+  const uint64_t worst = std::max(t->capacity, capacity_for(t, t->size + n));
+  int lp = log2_u64(std::max<uint64_t>(worst / tile_slots, 1));
+  if (const char *e = getenv("KH_BULK_LP")) lp = atoi(e);          // experiments / tests: force level 2
+  return std::max(6, std::min(lp, BK_MAX_LP));
+}
+
+void bulk_begin(BulkBatch &b, kh_table *t, uint64_t n, cudaStream_t s) {
+  b.n = n; b.fed = 0;
+  b.lp = bulk_region_bits(t, n);
+  const uint64_t R = 1ULL << b.lp;
+  // a region's share of a uniformly hashed batch plus 12.5 % and a pad of 8 standard deviations of small shares
+  b.slab = ((uint64_t)((double)n / (double)R * 1.125) + 1024 + 127) & ~127ULL;
+  b.ovf_cap = n / 16 + 4096;
+  b.cursors.alloc((size_t)BK_CSTRIDE * R); b.ovf_count.alloc(1);
+  b.recs.alloc(b.slab * R * t->W); b.ovf.alloc(b.ovf_cap * t->W); b.regs.alloc(HLL_M);
+  KH_CUDA(cudaMemsetAsync(b.regs.p, 0, HLL_M * sizeof(uint32_t), s));
+  KH_CUDA(cudaMemsetAsync(b.ovf_count.p, 0, sizeof(unsigned long long), s));
+  KH_LAUNCH(l1_cursor_kernel, (int)((R + 255) / 256), 256, 0, s, b.cursors.p, (int)R, (unsigned long long)b.slab);
+}
+
+// m keys at d_keys (or in the pieces of `segs`) -> level 1.  Asynchronous on s.
+void bulk_feed(BulkBatch &b, kh_table *t, const uint64_t *d_keys, uint64_t m, cudaStream_t s, const BkSegs *segs = nullptr) {
+  if (!m) return;
+  L1Args a;
+  a.keys = d_keys; a.n = m; a.lp = b.lp; a.hash_kind = t->hash_kind; a.h32 = hash_bits(t->hash_kind) == 32 ? 1 : 0; a.hp = t->hp;
+  a.cursors = b.cursors.p; a.recs = b.recs.p; a.slab = b.slab;
+  a.ovf_keys = b.ovf.p; a.ovf_count = b.ovf_count.p; a.ovf_cap = b.ovf_cap; a.g_regs = b.regs.p;
+  const uint64_t tile = t->W == 1 ? L1Cfg<1>::TILE : L1Cfg<2>::TILE;
+  BkSegs sg{};
+  sg.nseg = 1;
+  uint64_t n_tiles = (m + tile - 1) / tile;
+  if (segs && segs->nseg > 1) {
+    sg = *segs;
+    sg.tprefix[0] = 0;
+    for (int q = 0; q < sg.nseg; ++q) sg.tprefix[q + 1] = sg.tprefix[q] + (sg.prefix[q + 1] - sg.prefix[q] + tile - 1) / tile;
+    n_tiles = sg.tprefix[sg.nseg];
+  } else if (segs && segs->nseg == 1) {
+    a.keys = d_keys + segs->base[0] * t->W;
+  }
+  if (!n_tiles) return;
+  const int grid = (int)std::min<uint64_t>(n_tiles, (uint64_t)t->sms);
+  kev_begin(t, 2, s);
+  if (t->W == 1) {
+    KH_CUDA(cudaFuncSetAttribute(l1_scatter_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)L1Cfg<1>::SMEM));   // per device
+    KH_LAUNCH(l1_scatter_kernel<1>, grid, L1_THREADS, L1Cfg<1>::SMEM, s, a, sg);
+  } else {
+    KH_CUDA(cudaFuncSetAttribute(l1_scatter_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)L1Cfg<2>::SMEM));
+    KH_LAUNCH(l1_scatter_kernel<2>, grid, L1_THREADS, L1Cfg<2>::SMEM, s, a, sg);
+  }
+  kev_end(t, s);
+  b.fed += m;
+}
+
+// a batch handed over in pieces -> one contiguous array, for the paths whose kernels want one
+const uint64_t *flatten_segments(kh_table *t, const uint64_t *d_keys, uint64_t n, const BkSegs *segs, DevBuf<uint64_t> &buf, cudaStream_t s) {
+  if (!segs || segs->nseg < 1) return d_keys;
+  if (segs->nseg == 1) return d_keys + segs->base[0] * t->W;
   buf.alloc(n * t->W);
   for (int q = 0; q < segs->nseg; ++q) {
     const uint64_t c = segs->prefix[q + 1] - segs->prefix[q];
@@ -481,199 +595,140 @@ const uint64_t *flatten_segments(kh_table *t, const uint64_t *d_keys, uint64_t n
   return buf.p;
 }
 
-uint64_t insert_tiled(kh_table *t, const uint64_t *d_keys, uint64_t n, uint32_t dflt, const unsigned long long *d_fine,
-                      int lp, int subs_log2, cudaStream_t s, const SegSpec *segs = nullptr) {
-  KH_CUDA(cudaFuncSetAttribute(tile_insert_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TI_SMEM));   // per device
-  static const bool old_scatter = getenv("KH_SCATTER") && !strcmp(getenv("KH_SCATTER"), "old");
-  constexpr int CSTRIDE = 16;          // one 128-byte line per cursor
-  DevBuf<unsigned long long> fine_own, cursors((size_t)CSTRIDE << lp);
-  DevBuf<uint64_t> flat;
-  if (!d_fine || old_scatter) { d_keys = flatten_segments(t, d_keys, n, segs, flat, s); segs = nullptr; }
-  if (!d_fine) {
-    fine_own.alloc(REGION_FINE);
-    kev_begin(t, 3, s);
-    hll_estimate_dev(t->hash_kind, t->hp, t->W, d_keys, n, nullptr, s, t->sms, fine_own.p);
-    kev_end(t, s);
-    d_fine = fine_own.p;
+// the general route for a resident batch: fill up to max_load, double, continue (the reference's insert_no_estimate,
+// KH/robinhood_offset_hashmap_ptr.hpp:2802-2885); `single`: the caller knows the batch fits
+void insert_general(kh_table *t, const uint64_t *d_keys, const uint32_t *d_vals, uint64_t n, uint32_t dflt, bool single, cudaStream_t s) {
+  materialize(t, s);
+  if (!single && (double)(t->size + n) <= t->max_load * (double)t->capacity) single = true;
+  if (single) { insert_resident(t, d_keys, d_vals, n, dflt, s); return; }
+  // A piece may overshoot max_load (duplicates usually keep it far below); it never fills the table: the hard limit is
+  // halfway between max_load and 1.
+  const double hard = 0.5 * (t->max_load + 1.0);
+  uint64_t off = 0;
+  while (off < n) {
+    uint64_t room = (uint64_t)std::floor(hard * (double)t->capacity);
+    room = room > t->size ? room - t->size : 0;
+    if (room == 0 || (double)t->size >= t->max_load * (double)t->capacity) { rebuild(t, t->capacity * 2); continue; }
+    const uint64_t m = std::min(n - off, room);
+    insert_resident(t, d_keys + off * t->W, d_vals ? d_vals + off : nullptr, m, dflt, s);
+    off += m;
   }
-  KH_LAUNCH(window_cursor_kernel, 1, REGION_FINE, 0, s, d_fine, lp, cursors.p, CSTRIDE);
-  DevBuf<uint64_t> sorted(n);
-  DevBuf<uint16_t> tags(((n + TI_CHUNK - 1) / TI_CHUNK + 1) * TI_CHUNK);
-  const int lbk = log2_u64(t->capacity / 4);
-  { Trace tr("tile.scatter", s);
-    const BinSpec spec{0, lp, 0u, t->hash_kind, t->hp};
-    const TagSpec ts{tags.p, 64 - lbk, (1u << (lbk - lp)) - 1u, CSTRIDE};
-    kev_begin(t, 2, s);
-    if (old_scatter) KH_LAUNCH((window_scatter_kernel<1, false, false, true>), t->sms * 4, WIN_BLOCK, 0, s, d_keys, n, spec, cursors.p,
-                               sorted.p, nullptr, BinDst{}, ts);
-    else region_scatter_launch<1, true>(t->sms, s, d_keys, n, spec, cursors.p, sorted.p, ts, segs);
-    kev_end(t, s); }
-  DevBuf<uint32_t> defer(n);
-  uint64_t added = 0, n_def = 0;
-  { Trace tr("tile.insert", s);
-    zero_counter(t, s);
-    TileArgs a;
-    a.t = t->view(); a.keys = sorted.p; a.tags = tags.p; a.bin_end = cursors.p; a.bin_stride = CSTRIDE; a.subs_log2 = subs_log2;
-    a.fresh = t->uninit ? 2 : (t->size == 0 ? 1 : 0); a.dflt = dflt;   // 2: the slots hold garbage, every tile is written
-    a.tags32 = nullptr; a.slab = 0; a.lbk = lbk;
-    t->uninit = false; a.n_new = t->counters.p; a.defer_idx = defer.p;
-    const uint64_t n_tiles = t->capacity / TI_SLOTS;
-    const int grid = (int)std::min<uint64_t>(n_tiles, (uint64_t)t->sms * 2);
-    kev_begin(t, 0, s);
-    KH_LAUNCH(tile_insert_kernel<false>, grid, TI_THREADS, TI_SMEM, s, a);
-    kev_end(t, s);
-    added = read_counter(t, s);
-    n_def = t->h_counters[1];
-    t->size += added; }
-  if (n_def) {       // chains that leave their tile, the all-ones key: a handful of keys through the global kernel
-    Trace tr("tile.deferred", s);
-    DevBuf<uint64_t> nk(n_def);
-    KH_LAUNCH((gather_deferred_kernel<1>), t->grid_for(n_def, 256), 256, 0, s, sorted.p, (const uint32_t *)nullptr, defer.p, n_def,
-              nk.p, (uint32_t *)nullptr);
-    added += insert_resident(t, nk.p, nullptr, n_def, dflt, s);
-  }
-  return added;
 }
 
-uint64_t insert_windowed(kh_table *t, const uint64_t *d_keys, const uint32_t *d_vals, uint64_t n, uint32_t dflt,
-                         const unsigned long long *d_fine, cudaStream_t s, const SegSpec *segs = nullptr);
-
-// One-read bulk insert of a batch whose distinct count is not known yet (the reference's insert(): estimate -> reserve ->
-// insert, KH/robinhood_offset_hashmap_ptr.hpp:2512-2535).  The region scatter runs FIRST, in SLAB mode: it needs no
-// histogram (every one of the 1024 regions owns a fixed range sized for a uniform hash, the rare overflow goes to a side
-// list), so the same pass that sorts the batch also computes the HyperLogLog registers.  Then: estimate -> reserve (slots
-// left uninitialised) -> tile insert cutting its keys out of the 32-bit hash tags -> deferred and overflow keys through the
-// global kernel.  Returns false without touching the table when the batch does not qualify (the caller takes the
-// two-pass route); when only the table turns out unsuitable after the estimate, the region counts serve as the histogram
-// of the two-pass route, so nothing is computed twice but the sort.
-bool fused_candidate(const kh_table *t, const uint32_t *d_vals, uint64_t n) {
-  static const bool on = !(getenv("KH_FUSED") && atoi(getenv("KH_FUSED")) == 0);
-  static const bool tile_on = !(getenv("KH_TILE") && atoi(getenv("KH_TILE")) == 0);
-  if (!on || !tile_on || !window_candidate(t, d_vals, n)) return false;
-  // n < 2^30: output positions are 32-bit in the kernel; even a batch that falls into ONE region keeps its cursor
-  // (1023 * slab + n < 2.2 n) below 2^32
-  if (t->W != 1 || t->LB * t->G != 64 || t->has_sticky || n >= (1ULL << 30) || n < (1ULL << 20)) return false;
-  return t->capacity <= (1ULL << 26);          // a larger table has more than 8 tiles per region: no tile insert anyway
-}
-
-// state of one fused batch: begin -> feed (once, or chunk by chunk as the keys arrive over PCIe) -> finish
-struct FusedBatch {
-  static constexpr int CSTRIDE = 16;
-  uint64_t n = 0, slab = 0, ovf_cap = 0;
-  DevBuf<unsigned long long> cursors, ovf_count;
-  DevBuf<uint64_t> sorted, ovf;
-  DevBuf<uint32_t> tags32, regs;
-};
-void fused_begin(FusedBatch &f, kh_table *t, uint64_t n, cudaStream_t s) {
-  f.n = n;
-  f.slab = ((uint64_t)((double)n / REGION_FINE * 1.125) + 2048 + 127) & ~127ULL;
-  f.ovf_cap = n / 16 + 4096;
-  f.cursors.alloc((size_t)FusedBatch::CSTRIDE * REGION_FINE); f.ovf_count.alloc(1);
-  f.sorted.alloc(f.slab * REGION_FINE); f.ovf.alloc(f.ovf_cap);
-  f.tags32.alloc(f.slab * REGION_FINE + 2 * TI_CHUNK); f.regs.alloc(HLL_M);
-  KH_CUDA(cudaMemsetAsync(f.regs.p, 0, HLL_M * sizeof(uint32_t), s));
-  KH_CUDA(cudaMemsetAsync(f.ovf_count.p, 0, sizeof(unsigned long long), s));
-  KH_LAUNCH(slab_cursor_kernel, (WIN_MAX_P + 255) / 256, 256, 0, s, f.cursors.p, FusedBatch::CSTRIDE, (unsigned long long)f.slab);
-}
-void fused_feed(FusedBatch &f, kh_table *t, const uint64_t *d_keys, uint64_t m, cudaStream_t s) {
-  if (!m) return;
-  const BinSpec spec{0, REGION_FINE_BITS, 0u, t->hash_kind, t->hp};
-  SlabSpec sl{};
-  sl.slab = f.slab; sl.ovf_keys = f.ovf.p; sl.ovf_count = f.ovf_count.p; sl.ovf_cap = f.ovf_cap; sl.g_regs = f.regs.p; sl.tags32 = f.tags32.p;
-  sl.h32 = hash_bits(t->hash_kind) == 32 ? 1 : 0;
-  kev_begin(t, 2, s);
-  region_scatter_slab_launch(t->sms, s, d_keys, m, spec, f.cursors.p, FusedBatch::CSTRIDE, f.sorted.p, sl);
-  kev_end(t, s);
-}
-
-// d_keys: the whole batch (only read again when the two-pass route has to take over)
-int64_t fused_finish(FusedBatch &f, kh_table *t, const uint64_t *d_keys, uint32_t dflt, cudaStream_t s) {
-  constexpr int CSTRIDE = FusedBatch::CSTRIDE;
-  const double err = 1.0 + hll_error_rate();
-  const uint64_t size0 = t->size, n = f.n, slab = f.slab, ovf_cap = f.ovf_cap;
-  DevBuf<unsigned long long> &cursors = f.cursors, &ovf_count = f.ovf_count;
-  DevBuf<uint64_t> &sorted = f.sorted, &ovf = f.ovf;
-  DevBuf<uint32_t> &tags32 = f.tags32, &regs = f.regs;
+// estimate -> reserve -> [level 2] -> tile insert -> deferred and overflow keys.  d_keys / segs: the whole batch again, read
+// only when the general route has to take over (skewed batch, table that does not suit the tiles).
+// estimate != 0: insert(): the batch registers join the table's HyperLogLog and the table is reserved for its estimate.
+// estimate == 0: insert_no_estimate(): the table keeps its capacity when the batch fits, else the general route grows it.
+int64_t bulk_finish(BulkBatch &b, kh_table *t, const uint64_t *d_keys, const BkSegs *segs, uint32_t dflt, int estimate, cudaStream_t s) {
+  const uint64_t size0 = t->size, n = b.n;
+  const int W = t->W;
   unsigned long long n_ovf = 0;
-  KH_CUDA(cudaMemcpyAsync(&n_ovf, ovf_count.p, sizeof(n_ovf), cudaMemcpyDeviceToHost, s));
-  const double est = hll_finish(t->hash_kind, regs.p, nullptr, s);       // synchronises s
-  const bool lazy = t->size == 0;
-  ensure_room(t, (uint64_t)std::ceil(std::min((double)n, est * err)), lazy);
-  int lp = 0, subs = 0;
-  if (n_ovf > ovf_cap || !tile_candidate(t, nullptr, n, lp, subs)) {
-    // the table does not suit the tile insert (or the batch is heavily skewed): two-pass route, histogram = region counts
-    std::vector<unsigned long long> h((size_t)CSTRIDE * REGION_FINE), fine_h(REGION_FINE);
-    KH_CUDA(cudaMemcpyAsync(h.data(), cursors.p, h.size() * sizeof(unsigned long long), cudaMemcpyDeviceToHost, s));
+  KH_CUDA(cudaMemcpyAsync(&n_ovf, b.ovf_count.p, sizeof(n_ovf), cudaMemcpyDeviceToHost, s));
+  uint8_t batch_regs[HLL_M];
+  const double batch_est = hll_finish(t->hash_kind, b.regs.p, batch_regs, s);        // synchronises s
+  bool fits = true;
+  if (estimate) {
+    const double est = merge_batch_registers(t, batch_regs);
+    reserve_for_estimate(t, est, t->size == 0);
+    if (t->has_sticky) rebuild(t, t->capacity);                                       // the tiles carry no sticky bits
+  } else {
+    fits = (double)t->size + std::min((double)n, batch_est * (1.0 + hll_error_rate())) <= t->max_load * (double)t->capacity;
+    if (fits && t->has_sticky) rebuild(t, t->capacity);
+  }
+  const uint64_t tile_slots = (uint64_t)BK_TILE_BYTES / t->slot_bytes();
+  const int lbk = log2_u64(std::max<uint64_t>(t->capacity / t->bucket_slots(), 1));
+  const int tile_bits = lbk - BK_BUCKET_BITS;                        // log2(number of tiles)
+  const bool suits = fits && t->capacity >= tile_slots && n * 4 >= t->capacity && lbk <= 32 && tile_bits - b.lp <= BK_MAX_LP &&
+                     n_ovf <= b.ovf_cap;
+  if (!suits) {
+    b.recs.release(); b.ovf.release();
+    DevBuf<uint64_t> flat;
+    const uint64_t *keys = flatten_segments(t, d_keys, n, segs, flat, s);
+    insert_general(t, keys, nullptr, n, dflt, estimate != 0, s);
     KH_CUDA(cudaStreamSynchronize(s));
-    for (int r = 0; r < REGION_FINE; ++r) fine_h[r] = h[(size_t)r * CSTRIDE] - (unsigned long long)r * slab;
-    DevBuf<unsigned long long> fine(REGION_FINE);
-    KH_CUDA(cudaMemcpyAsync(fine.p, fine_h.data(), REGION_FINE * sizeof(unsigned long long), cudaMemcpyHostToDevice, s));
-    sorted.release(); tags32.release(); ovf.release();
-    insert_windowed(t, d_keys, nullptr, n, dflt, fine.p, s);
     return (int64_t)(t->size - size0);
   }
-  KH_CUDA(cudaFuncSetAttribute(tile_insert_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TI_SMEM));   // per device
+  const uint4 *recs = b.recs.p;
+  const unsigned long long *ends = b.cursors.p;
+  unsigned long long slab = b.slab;
+  int rpt_log2 = b.lp - tile_bits;
+  DevBuf<uint4> recs2;
+  DevBuf<unsigned long long> l2buf;
+  if (tile_bits > b.lp) {
+    // more tiles than regions: split every region by the next tag bits (exact: histogram of the tags -> scan -> scatter)
+    Trace tr("bulk.level2", s);
+    const int tbits = tile_bits - b.lp;
+    const uint64_t R = 1ULL << b.lp, NT = 1ULL << tile_bits;
+    l2buf.alloc(R + 1 + 2 * NT);
+    recs2.alloc(std::max<uint64_t>(b.fed, 1) * W);
+    L2Args a;
+    a.recs = b.recs.p; a.cursors = b.cursors.p; a.slab = b.slab; a.lp = b.lp; a.tbits = tbits;
+    a.chunk_prefix = l2buf.p; a.tile_cnt = l2buf.p + R + 1; a.tile_cur = a.tile_cnt + NT; a.recs2 = recs2.p;
+    KH_CUDA(cudaMemsetAsync(a.tile_cnt, 0, NT * sizeof(unsigned long long), s));
+    KH_LAUNCH(l2_plan_kernel, 1, 1024, 0, s, a);
+    const int grid = t->sms * 2;
+    kev_begin(t, 2, s);
+    if (W == 1) KH_LAUNCH(l2_hist_kernel<1>, grid, L2_THREADS, 0, s, a); else KH_LAUNCH(l2_hist_kernel<2>, grid, L2_THREADS, 0, s, a);
+    size_t tmp_bytes = 0;
+    KH_CUDA(cub::DeviceScan::ExclusiveSum(nullptr, tmp_bytes, a.tile_cnt, a.tile_cur, NT, s));
+    DevBuf<unsigned char> tmp(tmp_bytes);
+    KH_CUDA(cub::DeviceScan::ExclusiveSum(tmp.p, tmp_bytes, a.tile_cnt, a.tile_cur, NT, s));
+    g_launches.fetch_add(1, std::memory_order_relaxed);
+    if (W == 1) {
+      KH_CUDA(cudaFuncSetAttribute(l2_scatter_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)l2_smem_bytes(1)));
+      KH_LAUNCH(l2_scatter_kernel<1>, grid, L2_THREADS, l2_smem_bytes(1), s, a);
+    } else {
+      KH_CUDA(cudaFuncSetAttribute(l2_scatter_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)l2_smem_bytes(2)));
+      KH_LAUNCH(l2_scatter_kernel<2>, grid, L2_THREADS, l2_smem_bytes(2), s, a);
+    }
+    kev_end(t, s);
+    KH_CUDA(cudaStreamSynchronize(s));                               // tmp goes out of scope
+    recs = recs2.p; ends = a.tile_cur; slab = 0; rpt_log2 = 0;
+  }
   DevBuf<uint32_t> defer(n);
   uint64_t n_def = 0;
-  { Trace tr("tile.insert", s);
+  { Trace tr("bulk.tiles", s);
     zero_counter(t, s);
     TileArgs a;
-    a.t = t->view(); a.keys = sorted.p; a.tags = nullptr; a.bin_end = cursors.p; a.bin_stride = CSTRIDE; a.subs_log2 = 0;
+    a.t = t->view(); a.recs = recs; a.ends = ends; a.slab = slab; a.rpt_log2 = rpt_log2; a.lbk = lbk;
     a.fresh = t->uninit ? 2 : (t->size == 0 ? 1 : 0); a.dflt = dflt; a.n_new = t->counters.p; a.defer_idx = defer.p;
-    a.tags32 = tags32.p; a.slab = slab; a.lbk = log2_u64(t->capacity / 4);
-    t->uninit = false;
-    const uint64_t n_tiles = t->capacity / TI_SLOTS;
-    const int grid = (int)std::min<uint64_t>(n_tiles, (uint64_t)t->sms * 2);
+    const int grid = (int)std::min<uint64_t>(t->capacity / tile_slots, (uint64_t)t->sms * 2);
     kev_begin(t, 0, s);
-    KH_LAUNCH(tile_insert_kernel<true>, grid, TI_THREADS, TI_SMEM, s, a);
+    if (W == 1) {
+      KH_CUDA(cudaFuncSetAttribute(tile_insert_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tile_smem_bytes<1>()));
+      KH_LAUNCH(tile_insert_kernel<1>, grid, TI_THREADS, tile_smem_bytes<1>(), s, a);
+    } else {
+      KH_CUDA(cudaFuncSetAttribute(tile_insert_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tile_smem_bytes<2>()));
+      KH_LAUNCH(tile_insert_kernel<2>, grid, TI_THREADS, tile_smem_bytes<2>(), s, a);
+    }
     kev_end(t, s);
+    t->uninit = false;                                               // enqueued: every tile gets written
     t->size += read_counter(t, s);
     n_def = t->h_counters[1]; }
-  if (n_def) {
-    Trace tr("tile.deferred", s);
-    DevBuf<uint64_t> nk(n_def);
-    KH_LAUNCH((gather_deferred_kernel<1>), t->grid_for(n_def, 256), 256, 0, s, sorted.p, (const uint32_t *)nullptr, defer.p, n_def,
-              nk.p, (uint32_t *)nullptr);
+  if (n_def) {       // chains that leave their tile, the all-ones key: a handful of keys through the global kernel
+    Trace tr("bulk.deferred", s);
+    DevBuf<uint64_t> nk(n_def * W);
+    if (W == 1) KH_LAUNCH((gather_rec_keys_kernel<1>), t->grid_for(n_def, 256), 256, 0, s, recs, defer.p, n_def, nk.p);
+    else KH_LAUNCH((gather_rec_keys_kernel<2>), t->grid_for(n_def, 256), 256, 0, s, recs, defer.p, n_def, nk.p);
     insert_resident(t, nk.p, nullptr, n_def, dflt, s);
   }
-  if (n_ovf) insert_resident(t, ovf.p, nullptr, n_ovf, dflt, s);
+  if (n_ovf) insert_resident(t, b.ovf.p, nullptr, n_ovf, dflt, s);
   KH_CUDA(cudaStreamSynchronize(s));
   return (int64_t)(t->size - size0);
 }
 
-int64_t insert_fused(kh_table *t, const uint64_t *d_keys, uint64_t n, uint32_t dflt, cudaStream_t s) {
-  FusedBatch f;
-  fused_begin(f, t, n, s);
-  { Trace tr("fused.hll+scatter", s); fused_feed(f, t, d_keys, n, s); }
-  return fused_finish(f, t, d_keys, dflt, s);
-}
-
-uint64_t insert_windowed(kh_table *t, const uint64_t *d_keys, const uint32_t *d_vals, uint64_t n, uint32_t dflt,
-                         const unsigned long long *d_fine, cudaStream_t s, const SegSpec *segs) {
-  int tile_lp = 0, tile_subs = 0;
-  if (tile_candidate(t, d_vals, n, tile_lp, tile_subs)) return insert_tiled(t, d_keys, n, dflt, d_fine, tile_lp, tile_subs, s, segs);
-  materialize(t, s);
-  const uint64_t table_bytes = t->capacity * (uint64_t)t->slot_bytes();
-  const bool windowed = window_candidate(t, d_vals, n) && table_bytes >= 4 * t->window_bytes;
-  DevBuf<uint64_t> flat;
-  if (!windowed || !d_fine) { d_keys = flatten_segments(t, d_keys, n, segs, flat, s); segs = nullptr; }
-  if (!windowed) return insert_resident(t, d_keys, d_vals, n, dflt, s);
-  const int lp = std::min(log2_u64(next_pow2(table_bytes / t->window_bytes)), REGION_FINE_BITS);
-  DevBuf<unsigned long long> fine_own, cursors(1u << lp);
-  if (!d_fine) {
-    fine_own.alloc(REGION_FINE);
-    hll_estimate_dev(t->hash_kind, t->hp, t->W, d_keys, n, nullptr, s, t->sms, fine_own.p);
-    d_fine = fine_own.p;
-  }
-  KH_LAUNCH(window_cursor_kernel, 1, REGION_FINE, 0, s, d_fine, lp, cursors.p);
-  DevBuf<uint64_t> sorted(n * t->W);
-  { Trace tr("window.scatter", s);
-    const BinSpec spec{0, lp, 0u, t->hash_kind, t->hp};
-    const TagSpec ts{nullptr, 32, 0u, 1};
-    if (t->W == 1) region_scatter_launch<1, false>(t->sms, s, d_keys, n, spec, cursors.p, sorted.p, ts, segs);
-    else region_scatter_launch<2, false>(t->sms, s, d_keys, n, spec, cursors.p, sorted.p, ts, segs); }
-  Trace tr("window.insert", s);
-  return insert_resident(t, sorted.p, nullptr, n, dflt, s, true);   // synchronises s before the scratch is released
+int64_t insert_bulk(kh_table *t, const uint64_t *d_keys, uint64_t n, uint32_t dflt, int estimate, const BkSegs *segs, cudaStream_t s) {
+  Trace tr_ins("insert.total(bulk)", s);
+  struct Materialize {                  // whatever happens: never leave uninitialised slots behind
+    kh_table *t; cudaStream_t s;
+    ~Materialize() { if (t->uninit) { try { materialize(t, s); cudaStreamSynchronize(s); } catch (...) {} } }
+  } guard{t, s};
+  BulkBatch b;
+  bulk_begin(b, t, n, s);
+  { Trace tr("bulk.level1", s); bulk_feed(b, t, d_keys, n, s, segs); }
+  const int64_t got = bulk_finish(b, t, d_keys, segs, dflt, estimate, s);
+  while ((double)t->size > t->max_load * (double)t->capacity) rebuild(t, t->capacity * 2);
+  return got;
 }
 
 }  // namespace
@@ -846,81 +901,46 @@ double kh_estimate_distinct_host(kh_table *t, const uint64_t *keys, uint64_t n, 
 }  // extern "C"
 
 // ---- insert ------------------------------------------------------------------------------
-// Growth policy without an estimate = the reference's insert_no_estimate: fill up to max_load,
-// double, continue (KH/robinhood_offset_hashmap_ptr.hpp:2802-2885).
+// estimate != 0 = the reference's insert(): HyperLogLog over the batch joins the table's registers, reserve for the estimate,
+// then one pass (KH/robinhood_offset_hashmap_ptr.hpp:2512-2535).  estimate == 0 = insert_no_estimate(): fill up to max_load,
+// double, continue (:2802-2885).  pre: batch registers the caller's pipeline already computed, and/or the pieces of the batch.
 int64_t kh::insert_dev_impl(kh_table *t, const uint64_t *d_keys, const uint32_t *d_vals, uint64_t n,
                             uint32_t dflt, int estimate, const PreEstimate *pre) {
   cudaStream_t s = t->stream[0];
   if (n == 0) return 0;
-  const double err = 1.0 + hll_error_rate();
   const uint64_t size0 = t->size;
-  // the HLL pass also histograms the batch by table region when the windowed insert may follow
-  DevBuf<unsigned long long> fine;
-  bool have_fine = false;
-  auto estimate_batch = [&]() -> double {
-    if (pre) return pre->est;
-    Trace tr("hll+hist", s);
-    if (window_candidate(t, d_vals, n)) { fine.alloc(REGION_FINE); have_fine = true; }
-    kev_begin(t, 3, s);
-    const double e = hll_estimate_dev(t->hash_kind, t->hp, t->W, d_keys, n, nullptr, s, t->sms, have_fine ? fine.p : nullptr);
-    kev_end(t, s);
-    return e;
-  };
-  // Can the whole batch go in as ONE piece?  Yes when even its distinct keys (an HLL bound) keep the load legal.
-  // (COUNT tolerates a wrong bound: keys that find no slot are deferred and re-inserted after growing.)
-  bool single = false;
-  const bool count_mode = t->reducer == KH_REDUCE_COUNT;
-  if (estimate && !pre && fused_candidate(t, d_vals, n)) {
-    Trace tr_ins("insert.total(fused)", s);
-    struct Materialize {
-      kh_table *t; cudaStream_t s;
-      ~Materialize() { if (t->uninit) { try { materialize(t, s); cudaStreamSynchronize(s); } catch (...) {} } }
-    } guard{t, s};
-    insert_fused(t, d_keys, n, dflt, s);
-    while ((double)t->size > t->max_load * (double)t->capacity) rebuild(t, t->capacity * 2);
-    return (int64_t)(t->size - size0);
-  }
-  if (estimate) {
-    // insert_impl: reserve(size + estimate * (1 + error)) then one pass (:2512-2535)
-    const double est = estimate_batch();
-    // an empty COUNT table about to take a large uniform batch: the tile insert writes every tile, skip the init pass
-    const bool lazy = t->size == 0 && window_candidate(t, d_vals, n);
-    ensure_room(t, (uint64_t)std::ceil(std::min((double)n, est * err)), lazy);
-    single = count_mode;
-  }
+  const BkSegs *segs = pre ? pre->segs : nullptr;
+  if (bulk_candidate(t, d_vals, n)) return insert_bulk(t, d_keys, n, dflt, estimate, segs, s);
+  DevBuf<uint64_t> flat;
+  d_keys = flatten_segments(t, d_keys, n, segs, flat, s);
   struct Materialize {                  // whatever path follows (or throws): never leave uninitialised slots behind
     kh_table *t; cudaStream_t s;
     ~Materialize() { if (t->uninit) { try { materialize(t, s); cudaStreamSynchronize(s); } catch (...) {} } }
   } mat_guard{t, s};
-  if (!single) materialize(t, s);
-  if (!single && (double)(t->size + n) <= t->max_load * (double)t->capacity) single = true;
-  if (!single && !estimate && count_mode && n >= (1ULL << 16)) {
-    // insert_no_estimate on a table the caller reserved (the drivers: estimate -> reserve -> insert_no_estimate):
-    // the HLL pass costs one streaming read and saves the piecewise schedule below
-    const double est = estimate_batch();
-    single = (double)t->size + std::min((double)n, est * err) <= t->max_load * (double)t->capacity;
-  }
-  Trace tr_ins("insert.total", s);
-  const SegSpec *segs = pre ? pre->segs : nullptr;
-  DevBuf<uint64_t> flat;
-  if (single) {
-    insert_windowed(t, d_keys, d_vals, n, dflt, pre ? pre->fine : (have_fine ? fine.p : nullptr), s, segs);
-  } else {
-    d_keys = flatten_segments(t, d_keys, n, segs, flat, s);
-    // Growth without an estimate = the reference's insert_no_estimate: fill up to max_load, double, continue.
-    // A piece may overshoot max_load (duplicates usually keep it far below); it never fills the table:
-    // the hard limit is halfway between max_load and 1.
-    const double hard = 0.5 * (t->max_load + 1.0);
-    uint64_t off = 0;
-    while (off < n) {
-      uint64_t room = (uint64_t)std::floor(hard * (double)t->capacity);
-      room = room > t->size ? room - t->size : 0;
-      if (room == 0 || (double)t->size >= t->max_load * (double)t->capacity) { rebuild(t, t->capacity * 2); continue; }
-      const uint64_t m = std::min(n - off, room);
-      insert_resident(t, d_keys + off * t->W, d_vals ? d_vals + off : nullptr, m, dflt, s);
-      off += m;
+  const bool count_mode = t->reducer == KH_REDUCE_COUNT;
+  bool single = false;
+  if (estimate || (count_mode && n >= (1ULL << 16) && (double)(t->size + n) > t->max_load * (double)t->capacity)) {
+    // insert_no_estimate on a table the caller reserved (the drivers: estimate -> reserve -> insert_no_estimate): the
+    // HLL pass costs one streaming read and saves the piecewise schedule
+    uint8_t regs[HLL_M];
+    const uint8_t *batch_regs = pre ? pre->regs : nullptr;
+    if (!batch_regs) {
+      Trace tr("hll", s);
+      kev_begin(t, 3, s);
+      hll_estimate_dev(t->hash_kind, t->hp, t->W, d_keys, n, regs, s, t->sms);
+      kev_end(t, s);
+      batch_regs = regs;
+    }
+    if (estimate) {
+      reserve_for_estimate(t, merge_batch_registers(t, batch_regs), false);
+      single = count_mode;              // COUNT tolerates a wrong bound: keys that find no slot are deferred and re-inserted after growing
+    } else {
+      const double est = hll_estimate_from_regs(batch_regs, hash_bits(t->hash_kind));
+      single = (double)t->size + std::min((double)n, est * (1.0 + hll_error_rate())) <= t->max_load * (double)t->capacity;
     }
   }
+  Trace tr_ins("insert.total", s);
+  insert_general(t, d_keys, d_vals, n, dflt, single, s);
   while ((double)t->size > t->max_load * (double)t->capacity) rebuild(t, t->capacity * 2);
   return (int64_t)(t->size - size0);
 }
@@ -932,7 +952,14 @@ int64_t kh_insert_dev(kh_table *t, const uint64_t *d_keys, const uint32_t *d_val
   return guarded([&]() -> int64_t {
     if (!t || (!d_keys && n)) { set_error("null table or keys"); return KH_ERR_INVALID; }
     DeviceGuard g(t->device);
-    return insert_dev_impl(t, d_keys, d_vals, n, default_val, estimate);
+    int64_t added = 0;
+    for (uint64_t off = 0; off < n; off += BULK_MAX_KEYS) {          // record positions of the bulk route are 32-bit
+      const uint64_t m = std::min(BULK_MAX_KEYS, n - off);
+      const int64_t got = insert_dev_impl(t, d_keys + off * t->W, d_vals ? d_vals + off : nullptr, m, default_val, estimate);
+      if (got < 0) return got;
+      added += got;
+    }
+    return added;
   });
 }
 
@@ -949,40 +976,38 @@ int64_t kh_insert_host(kh_table *t, const uint64_t *keys, const uint32_t *vals, 
     DeviceGuard g(t->device);
     if (n == 0) return 0;
     const int W = t->W;
-    if (estimate && !vals && fused_candidate(t, nullptr, n)) {
-      // One-read route, fed chunk by chunk BEHIND the PCIe copy: when the last chunk lands, the batch is already sorted by
+    if (estimate && !vals && bulk_candidate(t, nullptr, n)) {
+      // Bulk route, fed chunk by chunk BEHIND the PCIe copy: when the last chunk lands, the batch is already partitioned by
       // table region and its HLL registers are complete; only the estimate, the reserve and the tile insert remain.
       DevBuf<uint64_t> dk(n * W);
-      FusedBatch f;
-      fused_begin(f, t, n, t->stream[0]);
-      int b = 0;
-      for (uint64_t off = 0; off < n; off += HOST_CHUNK, b ^= 1) {
+      BulkBatch b;
+      bulk_begin(b, t, n, t->stream[0]);
+      int q = 0;
+      for (uint64_t off = 0; off < n; off += HOST_CHUNK, q ^= 1) {
         const uint64_t m = std::min(HOST_CHUNK, n - off);
         KH_CUDA(cudaMemcpyAsync(dk.p + off * W, keys + off * W, m * W * 8, cudaMemcpyHostToDevice, t->stream[1]));
-        KH_CUDA(cudaEventRecord(t->ev[b], t->stream[1]));
-        KH_CUDA(cudaStreamWaitEvent(t->stream[0], t->ev[b], 0));
-        fused_feed(f, t, dk.p + off * W, m, t->stream[0]);
+        KH_CUDA(cudaEventRecord(t->ev[q], t->stream[1]));
+        KH_CUDA(cudaStreamWaitEvent(t->stream[0], t->ev[q], 0));
+        bulk_feed(b, t, dk.p + off * W, m, t->stream[0]);
       }
       KH_CUDA(cudaStreamSynchronize(t->stream[1]));
-      const uint64_t size0 = t->size;
       struct Materialize {
         kh_table *t; cudaStream_t s;
         ~Materialize() { if (t->uninit) { try { materialize(t, s); cudaStreamSynchronize(s); } catch (...) {} } }
       } guard{t, t->stream[0]};
-      fused_finish(f, t, dk.p, default_val, t->stream[0]);
+      const int64_t got = bulk_finish(b, t, dk.p, nullptr, default_val, estimate, t->stream[0]);
       while ((double)t->size > t->max_load * (double)t->capacity) rebuild(t, t->capacity * 2);
-      return (int64_t)(t->size - size0);
+      return got;
     }
     if (estimate || t->reducer != KH_REDUCE_COUNT) {
       // Whole batch resident (the ordered reducers need stable batch positions, and presizing needs the
-      // estimate before the first insert).  The HLL registers and the region histogram are accumulated
-      // chunk by chunk BEHIND the PCIe copy, so the estimate is ready when the last chunk lands.
+      // estimate before the first insert).  The HLL registers are accumulated chunk by chunk BEHIND the
+      // PCIe copy, so the estimate is ready when the last chunk lands.
       DevBuf<uint64_t> dk(n * W);
       DevBuf<uint32_t> dv(vals ? n : 0);
       const bool pipe_hll = estimate != 0;
       DevBuf<uint32_t> regs(pipe_hll ? HLL_M : 0);
-      DevBuf<unsigned long long> fine(pipe_hll && window_candidate(t, vals ? dv.p : nullptr, n) ? REGION_FINE : 0);
-      if (pipe_hll) hll_reset(regs.p, fine.p, t->stream[0]);
+      if (pipe_hll) hll_reset(regs.p, nullptr, t->stream[0]);
       int b = 0;
       for (uint64_t off = 0; off < n; off += HOST_CHUNK, b ^= 1) {
         const uint64_t m = std::min(HOST_CHUNK, n - off);
@@ -991,12 +1016,14 @@ int64_t kh_insert_host(kh_table *t, const uint64_t *keys, const uint32_t *vals, 
         if (pipe_hll) {
           KH_CUDA(cudaEventRecord(t->ev[b], t->stream[1]));
           KH_CUDA(cudaStreamWaitEvent(t->stream[0], t->ev[b], 0));
-          hll_accumulate(t->hash_kind, t->hp, W, dk.p + off * W, m, regs.p, fine.p, t->stream[0], t->sms);
+          hll_accumulate(t->hash_kind, t->hp, W, dk.p + off * W, m, regs.p, nullptr, t->stream[0], t->sms);
         }
       }
       KH_CUDA(cudaStreamSynchronize(t->stream[1]));
       if (!pipe_hll) return insert_dev_impl(t, dk.p, vals ? dv.p : nullptr, n, default_val, 0);
-      PreEstimate pre{hll_finish(t->hash_kind, regs.p, nullptr, t->stream[0]), fine.p};
+      uint8_t batch_regs[HLL_M];
+      hll_finish(t->hash_kind, regs.p, batch_regs, t->stream[0]);
+      PreEstimate pre{batch_regs, nullptr};
       return insert_dev_impl(t, dk.p, vals ? dv.p : nullptr, n, default_val, estimate, &pre);
     }
     // COUNT without estimate: stream chunks; chunk i+1 is copied while chunk i is inserted
