@@ -20,6 +20,7 @@
 #include <vector>
 
 #include "kmerhash_b200.hpp"
+#include "generate_input.hpp"
 
 namespace {
 
@@ -87,30 +88,7 @@ struct PhaseTimer {
   }
 };
 
-// generate_input (benchmark/BenchmarkHashTables.cpp:181-227)
-template <typename KmerT, typename Value>
-void generate_input(std::vector<std::pair<KmerT, Value>> &out, size_t count, size_t repeats) {
-  out.reserve(count);
-  std::srand(23);
-  for (size_t i = 0; i < count; ++i) {
-    KmerT k;
-    for (unsigned j = 0; j < KmerT::nWords; ++j)
-      k.data[j] = static_cast<uint64_t>(static_cast<long>(std::rand()) << 32) ^ static_cast<long>(std::rand());
-    k.sanitize();
-    out.emplace_back(k, static_cast<Value>(i));
-    const size_t freq = std::rand() % repeats;
-    for (size_t j = 0; j < freq; ++j)
-      if (i + 1 < count) { ++i; out.emplace_back(k, static_cast<Value>(i)); }
-  }
-#if defined(__GNUC__)
-#pragma GCC diagnostic push
-#pragma GCC diagnostic ignored "-Wdeprecated-declarations"
-#endif
-  std::random_shuffle(out.begin(), out.end());   // libstdc++: rand()-driven, as in the reference
-#if defined(__GNUC__)
-#pragma GCC diagnostic pop
-#endif
-}
+using khdrv::generate_input;   // generate_input.hpp (benchmark/BenchmarkHashTables.cpp:181-227)
 
 // the -F format (include/kmerhash/io_utils.hpp:53-70): [u64 record bytes][u64 n][n records]
 template <typename KmerT, typename Value>

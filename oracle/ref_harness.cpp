@@ -486,24 +486,35 @@ int ref_baseline_run(int map_kind, int key_words, int hash_kind, double min_load
     sq[0].assign(queries, queries + nq * W);
     t0 = clk::now();
   } else {
-    std::vector<uint32_t> rk(n), rq(nq);
-    // parallel rank computation + serial scatter per shard (each shard scans ranks)
-    auto rank_part = [&](const uint64_t * src, size_t cnt, std::vector<uint32_t> & r) {
-      std::vector<std::thread> th;
-      for (int t = 0; t < threads; ++t) th.emplace_back([&, t]() {
-        size_t b = cnt * t / threads, e = cnt * (t + 1) / threads;
+    // one counting pass + one scatter, both parallel over input ranges: thread t ranks its range, counts it per shard, and
+    // (after a prefix over threads) copies its keys to their place inside every shard -- O(n) in total
+    auto partition = [&](const uint64_t * src, size_t cnt, std::vector<std::vector<uint64_t>> & dst) {
+      std::vector<uint32_t> r(cnt);
+      std::vector<size_t> c((size_t)threads * threads, 0);          // c[t * threads + s]: keys of range t for shard s
+      auto par = [&](std::function<void(int, size_t, size_t)> f) {
+        std::vector<std::thread> th;
+        for (int t = 0; t < threads; ++t) th.emplace_back([&, t]() { f(t, cnt * t / threads, cnt * (t + 1) / threads); });
+        for (auto & x : th) x.join();
+      };
+      par([&](int t, size_t b, size_t e) {
         ref_rank(hash_kind, key_words, src + b * W, e - b, threads, r.data() + b);
+        for (size_t i = b; i < e; ++i) ++c[(size_t)t * threads + r[i]];
       });
-      for (auto & x : th) x.join();
+      for (int s = 0; s < threads; ++s) {
+        size_t acc = 0;
+        for (int t = 0; t < threads; ++t) { const size_t v = c[(size_t)t * threads + s]; c[(size_t)t * threads + s] = acc; acc += v; }
+        dst[s].resize(acc * W);
+      }
+      par([&](int t, size_t b, size_t e) {
+        size_t * at = &c[(size_t)t * threads];
+        for (size_t i = b; i < e; ++i) {
+          uint64_t * o = dst[r[i]].data() + at[r[i]]++ * W;
+          for (size_t w = 0; w < W; ++w) o[w] = src[i * W + w];
+        }
+      });
     };
-    rank_part(keys, n, rk);
-    rank_part(queries, nq, rq);
-    std::vector<std::thread> th;
-    for (int t = 0; t < threads; ++t) th.emplace_back([&, t]() {
-      for (size_t i = 0; i < n; ++i) if (rk[i] == (uint32_t)t) for (size_t w = 0; w < W; ++w) sk[t].push_back(keys[i * W + w]);
-      for (size_t i = 0; i < nq; ++i) if (rq[i] == (uint32_t)t) for (size_t w = 0; w < W; ++w) sq[t].push_back(queries[i * W + w]);
-    });
-    for (auto & x : th) x.join();
+    partition(keys, n, sk);
+    partition(queries, nq, sq);
   }
   auto t1 = clk::now();
   out_secs[0] = (threads == 1) ? 0.0 : secs(t0, t1);
