@@ -117,7 +117,9 @@ int kh_key_words(const kh_table *t);
 /* the CUDA stream the *_dev entry points of this table launch on (a cudaStream_t), for event timing */
 void *kh_stream(kh_table *t);
 /* CUDA-event timing of the probe kernels on their launching stream: enable, run operations, then read
- * the accumulated milliseconds and launch count of which = 0 (insert kernels) / 1 (lookup kernels) */
+ * the accumulated milliseconds and launch count of which = 0 (table insert kernels: tile insert + global insert kernel) /
+ * 1 (lookup kernels) / 2 (level-1 scatter of the bulk insert) / 3 (stand-alone HyperLogLog pass) / 4 (every kernel of a
+ * rebuild: reserve, rehash, shrink after erase) / 5 (level-2 split of the bulk insert) */
 int kh_kernel_timing(kh_table *t, int enable);
 int kh_kernel_time(kh_table *t, int which, double *sum_ms, uint64_t *launches);
 /* probe geometry (experiments; empty table only): lane_bytes 16|32|64, lanes_per_bucket 1|2|4|8 (64: 1 only) -- see DESIGN.md */
@@ -297,6 +299,17 @@ int khx_peer_sync_dev(kh_table *t, khx_peer *x, uint64_t epoch, const uint64_t *
  * (d_meta[r][0]).  khx_peer_meta_ptr = this rank's area of that half: p blocks of khx_meta_words() words, block g from
  * sender g -- the d_recv_meta of khx_insert_recv_slabs_dev. */
 int khx_push_meta_sync_dev(kh_table *t, khx_peer *x, int parity, const uint64_t *d_meta, uint64_t epoch, uint64_t *counts_matrix);
+/* The insert sender without metadata: dist hash -> owner -> store into slab `rank` of half `parity` of the owner's buffer.
+ * d_counts (DEVICE, p words) = this rank's row of the count matrix, to be handed to khx_peer_sync_dev; reset_counts = 0
+ * continues a batch that arrives in chunks (e.g. behind a PCIe copy): the counts accumulate.  Asynchronous on the table's stream.  khx_insert_recv_slabs_dev accepts d_recv_meta == NULL (the receiver's level-1 pass over the slabs
+ * computes the HyperLogLog registers the reference ships with the counts, KH/distributed_batched_robinhood_map.hpp:1024-1060). */
+int khx_scatter_slabs_dev(kh_table *t, int dist_hash, uint32_t dist_seed, const uint64_t *d_keys, uint64_t n, khx_peer *x,
+                          uint64_t slab_cap, int parity, uint64_t *d_counts, int reset_counts);
+/* Teardown of IPC-mapped buffers is collective: every rank khx_peer_close_imports -> a barrier of the caller's -> every
+ * rank khx_peer_destroy (which frees the exported allocation).  khx_peer_poisoned: a barrier on these buffers timed out
+ * (on this rank or, seen through the poison flag, on a peer); every later khx_peer_sync_dev fails until they are recreated. */
+void khx_peer_close_imports(khx_peer *x);
+int khx_peer_poisoned(const khx_peer *x);
 uint64_t *khx_peer_meta_ptr(khx_peer *x, int parity);
 int khx_query_scatter_slabs_dev(kh_table *t, int dist_hash, uint32_t dist_seed, const uint64_t *d_keys, uint64_t n, khx_peer *x,
                                 uint64_t slab_cap, uint32_t *d_perm, uint64_t *d_counts);

@@ -111,6 +111,9 @@ SIGNATURES = {
     "khx_insert_recv_slabs_dev": (_i64, [_vp, _vp, _u64, _int, _vp, _vp, _u32]),
     "khx_push_meta_sync_dev": (_int, [_vp, _vp, _int, _vp, _u64, _vp]),
     "khx_peer_meta_ptr": (_vp, [_vp, _int]),
+    "khx_scatter_slabs_dev": (_int, [_vp, _int, _u32, _vp, _u64, _vp, _u64, _int, _vp, _int]),
+    "khx_peer_close_imports": (None, [_vp]),
+    "khx_peer_poisoned": (_int, [_vp]),
     "khx_peer_sync_dev": (_int, [_vp, _vp, _u64, _vp, _vp]),
     "khx_peer_create_q": (_vp, [_int, _u32, _u32, _u64, _int]),
     "khx_query_scatter_slabs_dev": (_int, [_vp, _int, _u32, _vp, _u64, _vp, _u64, _vp, _vp]),

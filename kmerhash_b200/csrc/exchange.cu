@@ -253,12 +253,14 @@ __global__ void __launch_bounds__(PS_BLOCK, 3) scatter_slabs_kernel(const uint64
 // flag in the LOCAL header has reached the epoch.  When the kernel ends, every peer's stores that preceded its flag (the
 // keys / answers of the kernels before it on its stream) are visible here -- a barrier without NCCL's launch latency, and
 // the p x p counts arrive with it.  A peer that never shows up trips the time-out instead of hanging the GPU.
+constexpr unsigned long long PEER_POISON = ~0ULL;
 struct PeerHeader { unsigned long long flags[WIN_MAX_DST]; unsigned long long counts[2][WIN_MAX_DST][WIN_MAX_DST]; };
 struct PeerHeaders { PeerHeader *h[WIN_MAX_DST]; };
 // slot: which of the two count matrices this call writes (they alternate, so a rank that is one call ahead never
 // overwrites a matrix a slower rank has not copied out yet).  cstride: distance between two entries of counts_row.
 __global__ void peer_sync_kernel(const __grid_constant__ PeerHeaders hd, uint32_t rank, uint32_t p, unsigned long long epoch,
-                                 const unsigned long long *counts_row, int cstride, int slot, int *timed_out) {
+                                 const unsigned long long *counts_row, int cstride, int slot, int *timed_out,
+                                 unsigned long long timeout_ns) {
   const uint32_t r = threadIdx.x;
   if (r >= p) return;
   if (counts_row)
@@ -269,13 +271,24 @@ __global__ void peer_sync_kernel(const __grid_constant__ PeerHeaders hd, uint32_
   unsigned long long t0;
   asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
   const volatile unsigned long long *mine = &hd.h[rank]->flags[r];
-  while (*mine < epoch) {
+  bool gave_up = false;
+  for (;;) {
+    const unsigned long long v = *mine;
+    if (v == PEER_POISON) { *timed_out = 2; break; }              // a peer gave up: fail the same barrier everywhere
+    if (v >= epoch) break;
     unsigned long long t1;
     asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1));
-    if (t1 - t0 > 10000000000ULL) { *timed_out = 1; break; }      // 10 s
+    if (t1 - t0 > timeout_ns) { *timed_out = 1; gave_up = true; break; }
     __nanosleep(200);
   }
   __threadfence_system();
+  // one thread saw a time-out: every peer's copy of this rank's flag becomes the poison value, so that a peer that arrives
+  // late (or waits in a later barrier) fails too instead of pairing this epoch with the wrong call
+  const unsigned any = __ballot_sync((1u << p) - 1u, gave_up);     // p <= 8 threads are here
+  if (any) {
+    *reinterpret_cast<volatile unsigned long long *>(&hd.h[r]->flags[rank]) = PEER_POISON;
+    __threadfence_system();
+  }
 }
 
 // insert sender: metadata block r -> owner r's metadata area (slot of this rank), by peer stores
@@ -350,6 +363,8 @@ struct khx_peer {
   uint64_t *local = nullptr;             // this rank's receive buffer (cudaMalloc: IPC cannot export pool memory)
   uint64_t count_syncs = 0;              // barriers that carried a count matrix (selects the matrix slot; same on every rank)
   uint32_t reply_bytes = 0;              // bytes per key of the answer region that follows the keys (query exchange), 0 = none
+  bool poisoned = false;                 // a barrier timed out: the epochs of the ranks no longer agree, every later call fails
+  bool imports_closed = false;           // khx_peer_close_imports ran (teardown step 1)
   uint64_t *remote[WIN_MAX_DST] = {nullptr};
   bool opened[WIN_MAX_DST] = {false};    // mapped with cudaIpcOpenMemHandle (must be closed)
 };
@@ -383,10 +398,22 @@ static khx_peer *peer_create(int device, uint32_t rank, uint32_t p, uint64_t cap
   return x;
 }
 
+// Teardown is a three-step collective (CUDA: freeing exported memory while another process still has it open is undefined):
+// every rank khx_peer_close_imports -> barrier (the caller's: torch.distributed) -> every rank khx_peer_destroy.
+void khx_peer_close_imports(khx_peer *x) {
+  if (!x || x->imports_closed) return;
+  int prev = -1; cudaGetDevice(&prev); cudaSetDevice(x->device);
+  cudaDeviceSynchronize();
+  for (uint32_t r = 0; r < x->p; ++r) if (x->opened[r]) { cudaIpcCloseMemHandle(x->remote[r]); x->opened[r] = false; x->remote[r] = nullptr; }
+  x->imports_closed = true;
+  if (prev >= 0) cudaSetDevice(prev);
+}
+int khx_peer_poisoned(const khx_peer *x) { return (x && x->poisoned) ? 1 : 0; }
+
 void khx_peer_destroy(khx_peer *x) {
   if (!x) return;
+  khx_peer_close_imports(x);
   int prev = -1; cudaGetDevice(&prev); cudaSetDevice(x->device);
-  for (uint32_t r = 0; r < x->p; ++r) if (x->opened[r]) cudaIpcCloseMemHandle(x->remote[r]);
   if (x->local) cudaFree(x->local);
   if (prev >= 0) cudaSetDevice(prev);
   delete x;
@@ -531,11 +558,49 @@ int khx_plan_scatter_slabs_dev(kh_table *t, int dist_hash, uint32_t dist_seed, c
   });
 }
 
+// The same sender without metadata (the receiver's level-1 pass computes the HyperLogLog registers of what it received
+// itself, bit-identical to the merged sender registers): ONE dist hash per key, 16 B/key of traffic.  d_counts (DEVICE, p
+// words) ends as the number of keys this rank has for every owner (also beyond slab_cap) = this rank's row of the count
+// matrix for khx_peer_sync_dev.  Asynchronous on the table's stream; the barrier kernel that follows orders it.
+int khx_scatter_slabs_dev(kh_table *t, int dist_hash, uint32_t dist_seed, const uint64_t *d_keys, uint64_t n, khx_peer *x,
+                          uint64_t slab_cap, int parity, uint64_t *d_counts, int reset_counts) {
+  return (int)guarded([&]() -> int64_t {
+    if (!t || !x || !d_counts || (n && !d_keys)) { set_error("null argument"); return KH_ERR_INVALID; }
+    if (!hash_kind_supported(dist_hash) || n >= (1ULL << 32) || x->W != t->W || x->p > (uint32_t)WIN_MAX_DST || parity < 0 || parity > 1) {
+      set_error("khx_scatter_slabs_dev: bad arguments"); return KH_ERR_INVALID;
+    }
+    if (2ULL * x->p * slab_cap > x->capacity) { set_error("receive buffers hold %llu keys, 2 x %u slabs of %llu do not fit",
+                                                          (unsigned long long)x->capacity, x->p, (unsigned long long)slab_cap); return KH_ERR_NOMEM; }
+    DeviceGuard g(t->device);
+    cudaStream_t s = t->stream[0];
+    const uint32_t p = x->p;
+    const int dk = fold_kind(dist_hash);
+    const BinSpec dist{1, 0, p, dk, make_hash_params(dk, dist_seed, t->W)};
+    unsigned long long *cursors = reinterpret_cast<unsigned long long *>(d_counts);
+    if (reset_counts) KH_CUDA(cudaMemsetAsync(cursors, 0, p * sizeof(unsigned long long), s));
+    if (n) {
+      BinDst dst{};
+      for (uint32_t r = 0; r < p; ++r) {
+        if (!x->remote[r]) { set_error("peer %u not mapped", r); return KH_ERR_INVALID; }
+        dst.base[r] = x->remote[r] + ((uint64_t)parity * p + x->rank) * slab_cap * t->W;
+      }
+      const uint64_t tile = PS_TILE_BYTES / (8 * t->W);
+      const int grid = (int)std::max<uint64_t>(1, std::min<uint64_t>((n + tile - 1) / tile, (uint64_t)t->sms * 3));
+      const size_t smem = t->W == 1 ? ps_smem_bytes<1>(p, false, false) : ps_smem_bytes<2>(p, false, false);
+      if (t->W == 1) KH_LAUNCH((scatter_slabs_kernel<1, false, false>), grid, PS_BLOCK, smem, s, d_keys, n, dist, t->hash_kind, t->hp, dst,
+                               (unsigned long long)slab_cap, cursors, (unsigned long long *)nullptr, (uint32_t *)nullptr);
+      else KH_LAUNCH((scatter_slabs_kernel<2, false, false>), grid, PS_BLOCK, smem, s, d_keys, n, dist, t->hash_kind, t->hp, dst,
+                     (unsigned long long)slab_cap, cursors, (unsigned long long *)nullptr, (uint32_t *)nullptr);
+    }
+    return KH_OK;
+  });
+}
+
 // Receiver of the slab exchange: counts[g] (HOST) keys lie in slab g of half `parity` of this rank's receive buffer.
 int64_t khx_insert_recv_slabs_dev(kh_table *t, khx_peer *x, uint64_t slab_cap, int parity, const uint64_t *counts,
                                   const uint64_t *d_recv_meta, uint32_t default_val) {
   return guarded([&]() -> int64_t {
-    if (!t || !x || !counts || !d_recv_meta) { set_error("null argument"); return KH_ERR_INVALID; }
+    if (!t || !x || !counts) { set_error("null argument"); return KH_ERR_INVALID; }
     if (x->W != t->W || parity < 0 || parity > 1 || 2ULL * x->p * slab_cap > x->capacity) { set_error("khx_insert_recv_slabs_dev: bad arguments"); return KH_ERR_INVALID; }
     DeviceGuard g(t->device);
     const uint32_t p = x->p;
@@ -646,6 +711,7 @@ int64_t khx_query_slabs_dev(kh_table *t, khx_peer *x, int op, uint64_t slab_cap,
 static int peer_sync(kh_table *t, khx_peer *x, uint64_t epoch, const uint64_t *d_counts_row, int counts_stride, uint64_t *counts_matrix) {
   return (int)guarded([&]() -> int64_t {
     if (!t || !x || epoch == 0) { set_error("bad argument"); return KH_ERR_INVALID; }
+    if (x->poisoned) { set_error("khx_peer_sync_dev: an earlier barrier on these buffers timed out; recreate them"); return KH_ERR_CUDA; }
     DeviceGuard g(t->device);
     cudaStream_t s = t->stream[0];
     const size_t body = x->capacity * (size_t)(8 * x->W + x->reply_bytes);
@@ -658,14 +724,23 @@ static int peer_sync(kh_table *t, khx_peer *x, uint64_t epoch, const uint64_t *d
     KH_CUDA(cudaMemsetAsync(flag.p, 0, sizeof(int), s));
     const int slot = (int)(x->count_syncs & 1);
     if (d_counts_row) ++x->count_syncs;
+    static const unsigned long long timeout_ns = [] {                 // KH_PEER_TIMEOUT_MS: tests shorten the 10 s
+      const char *e = getenv("KH_PEER_TIMEOUT_MS");
+      return (e && atoll(e) > 0) ? (unsigned long long)atoll(e) * 1000000ULL : 10000000000ULL;
+    }();
     KH_LAUNCH(peer_sync_kernel, 1, 32, 0, s, hd, x->rank, x->p, (unsigned long long)epoch,
-              reinterpret_cast<const unsigned long long *>(d_counts_row), counts_stride, slot, flag.p);
+              reinterpret_cast<const unsigned long long *>(d_counts_row), counts_stride, slot, flag.p, timeout_ns);
     int h_flag = 0;
     PeerHeader h_hdr;
     KH_CUDA(cudaMemcpyAsync(&h_flag, flag.p, sizeof(int), cudaMemcpyDeviceToHost, s));
     if (counts_matrix) KH_CUDA(cudaMemcpyAsync(&h_hdr, hd.h[x->rank], sizeof(PeerHeader), cudaMemcpyDeviceToHost, s));
     KH_CUDA(cudaStreamSynchronize(s));
-    if (h_flag) { set_error("khx_peer_sync_dev: a peer did not reach epoch %llu within 10 s", (unsigned long long)epoch); return KH_ERR_CUDA; }
+    if (h_flag) {
+      x->poisoned = true;
+      set_error(h_flag == 2 ? "khx_peer_sync_dev: a peer timed out in a barrier (epoch %llu); buffers are unusable"
+                            : "khx_peer_sync_dev: a peer did not reach epoch %llu in time; buffers are unusable", (unsigned long long)epoch);
+      return KH_ERR_CUDA;
+    }
     if (counts_matrix)
       for (uint32_t a = 0; a < x->p; ++a)
         for (uint32_t b = 0; b < x->p; ++b) counts_matrix[a * x->p + b] = h_hdr.counts[slot][a][b];

@@ -38,8 +38,11 @@ struct kh_table {
   // CUDA-event pairs around every probe-kernel launch (bench.py's roofline: measured on the launching stream)
   std::vector<std::pair<cudaEvent_t, cudaEvent_t>> kev;
   size_t kev_used = 0;
-  double kev_ms[4] = {0.0, 0.0, 0.0, 0.0};   // accumulated [insert kernels, lookup kernels, region scatter, HLL + histogram]
-  uint64_t kev_n[4] = {0, 0, 0, 0};
+  // accumulated per kind: 0 table insert (tile insert, global insert kernel), 1 lookup kernels, 2 level-1 scatter, 3 stand-alone HLL,
+  // 4 rebuild (every kernel launched inside rebuild(): streaming rebuild, dump, re-insert), 5 level-2 split (histogram, scan, scatter)
+  double kev_ms[6] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0};
+  uint64_t kev_n[6] = {0, 0, 0, 0, 0, 0};
+  bool kev_in_rebuild = false;
   std::vector<int> kev_kind;
   bool kev_on = false;
 

@@ -241,7 +241,7 @@ void kev_begin(kh_table *t, int kind, cudaStream_t s) {
     KH_CUDA(cudaEventCreate(&a)); KH_CUDA(cudaEventCreate(&b));
     t->kev.emplace_back(a, b); t->kev_kind.push_back(kind);
   }
-  t->kev_kind[t->kev_used] = kind;
+  t->kev_kind[t->kev_used] = t->kev_in_rebuild ? 4 : kind;
   KH_CUDA(cudaEventRecord(t->kev[t->kev_used].first, s));
 }
 void kev_end(kh_table *t, cudaStream_t s) {
@@ -396,6 +396,7 @@ bool rebuild_streamed(kh_table *t, uint64_t new_cap, cudaStream_t s) {
 void rebuild(kh_table *t, uint64_t new_cap, bool lazy = false) {
   cudaStream_t s = t->stream[0];
   Trace tr_all("rebuild", s);
+  struct InRebuild { kh_table *t; bool prev; InRebuild(kh_table *t_) : t(t_), prev(t_->kev_in_rebuild) { t->kev_in_rebuild = true; } ~InRebuild() { t->kev_in_rebuild = prev; } } in_rebuild(t);
   new_cap = std::max<uint64_t>(next_pow2(new_cap), 128);
   if (t->capacity == 0 || t->size == 0) {
     t->slots.release();
@@ -667,7 +668,7 @@ int64_t bulk_finish(BulkBatch &b, kh_table *t, const uint64_t *d_keys, const BkS
     KH_CUDA(cudaMemsetAsync(a.tile_cnt, 0, NT * sizeof(unsigned long long), s));
     KH_LAUNCH(l2_plan_kernel, 1, 1024, 0, s, a);
     const int grid = t->sms * 2;
-    kev_begin(t, 2, s);
+    kev_begin(t, 5, s);
     if (W == 1) KH_LAUNCH(l2_hist_kernel<1>, grid, L2_THREADS, 0, s, a); else KH_LAUNCH(l2_hist_kernel<2>, grid, L2_THREADS, 0, s, a);
     size_t tmp_bytes = 0;
     KH_CUDA(cub::DeviceScan::ExclusiveSum(nullptr, tmp_bytes, a.tile_cnt, a.tile_cur, NT, s));
@@ -802,11 +803,11 @@ void *kh_stream(kh_table *t) { return t ? (void *)t->stream[0] : nullptr; }
 int kh_kernel_timing(kh_table *t, int enable) {
   if (!t) return KH_ERR_INVALID;
   t->kev_on = enable != 0; t->kev_used = 0;
-  for (int i = 0; i < 4; ++i) { t->kev_ms[i] = 0.0; t->kev_n[i] = 0; }
+  for (int i = 0; i < 6; ++i) { t->kev_ms[i] = 0.0; t->kev_n[i] = 0; }
   return KH_OK;
 }
 int kh_kernel_time(kh_table *t, int which, double *sum_ms, uint64_t *launches) {
-  if (!t || which < 0 || which > 3) return KH_ERR_INVALID;
+  if (!t || which < 0 || which > 5) return KH_ERR_INVALID;
   int prev = -1; cudaGetDevice(&prev); cudaSetDevice(t->device);
   kev_resolve(t);
   if (prev >= 0) cudaSetDevice(prev);

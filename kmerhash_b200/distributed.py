@@ -50,7 +50,7 @@ class PeerBuffers:
     def __init__(self, device, rank, p, capacity, key_words, group, query=False):
         import ctypes as C
         from ._lib import lib, check
-        self.lib, self.p, self.rank = lib, p, rank
+        self.lib, self.p, self.rank, self.group = lib, p, rank, group
         self.epoch = 0                    # barriers passed on this buffer set (khx_peer_sync_dev)
         self.h = (lib.khx_peer_create_q if query else lib.khx_peer_create)(device, rank, p, int(capacity), key_words)
         ok = 1 if self.h else 0
@@ -78,11 +78,24 @@ class PeerBuffers:
         return self.lib.khx_peer_recv_ptr(self.h)
 
     def close(self):
+        """COLLECTIVE teardown: every rank unmaps its imports, a barrier, then every rank frees its own buffer (freeing an
+        exported allocation that a peer still has open is undefined in CUDA)."""
         h, self.h = getattr(self, "h", None), None
         if h:
+            self.lib.khx_peer_close_imports(h)
+            dist.barrier(group=self.group)
             self.lib.khx_peer_destroy(h)
 
-    __del__ = close
+    def __del__(self):
+        # not collective (interpreter exit, error paths): unmap the imports first, then free; a map that was closed
+        # explicitly has nothing left to do here
+        h, self.h = getattr(self, "h", None), None
+        if h:
+            try:
+                self.lib.khx_peer_close_imports(h)
+                self.lib.khx_peer_destroy(h)
+            except Exception:
+                pass
 
 
 class CudaEngine:
@@ -146,8 +159,14 @@ class CudaEngine:
     def plan_scatter_slabs(self, keys, peers, slab_cap, parity):
         return self.table.plan_scatter_slabs(keys, peers.h, peers.p, slab_cap, parity, self.dist_hash)
 
-    def insert_recv_slabs(self, peers, slab_cap, parity, counts, recv_meta, default):
-        return self.table.insert_recv_slabs(peers.h, slab_cap, parity, counts, recv_meta, default) if int(counts.sum()) else 0
+    def insert_recv_slabs(self, peers, slab_cap, parity, counts, recv_meta, default, no_meta=False):
+        return self.table.insert_recv_slabs(peers.h, slab_cap, parity, counts, recv_meta, default, no_meta=no_meta) if int(counts.sum()) else 0
+
+    def scatter_slabs(self, keys, peers, slab_cap, parity, counts, reset=True, synced=False):
+        self.table.scatter_slabs(keys, peers.h, slab_cap, parity, counts, reset, self.dist_hash, synced=synced)
+
+    def insert_ptr(self, ptr, n, default):
+        return self.table.insert_ptr(ptr, n, default) if n else 0
 
     def push_meta_sync(self, peers, parity, meta):
         peers.epoch += 1
@@ -204,6 +223,8 @@ class DistributedMap:
         self.slab_cap = 0                 # keys per (owner, sender) slab; the buffers hold 2 halves x p slabs
         self.parity = 0
         self.slab_misses = 0              # consecutive batches that overflowed a slab (skewed owners)
+        self._copy_stream = self._lib_stream = None   # host -> device pipeline of the sender (_send_slabs)
+        self._dev_keys = self._C = None
         self._exact_dirty = False         # the last batch went through the exact path: its buffer use overlaps both halves
         # queries over peer slabs with direct answer stores (csrc/exchange.cu: khx_query_*)
         self.qslabs = self.slabs
@@ -245,14 +266,34 @@ class DistributedMap:
         return self.e.unpermute(back, perm)
 
     # ---- batch operations (collective) -------------------------------------------------------------
+    MAX_BATCH = 1 << 29        # keys per exchange round: receive slabs, 32-bit slab positions and the bulk insert's record positions
+
     def insert(self, keys, default=1):
-        """returns the number of new keys on THIS rank; chunks > 1 overlaps the all-to-all of chunk i+1
-        with the local insert of chunk i (the reference's ialltoallv_and_modify schedule)."""
-        keys = self.e.as_keys(keys)
+        """returns the number of new keys on THIS rank.  Collective.  Batches above MAX_BATCH keys go in slices (every rank
+        must then bring the same number of slices, i.e. about the same number of keys, as the benchmark drivers do).
+        chunks > 1 (NCCL path only) overlaps the all-to-all of chunk i+1 with the local insert of chunk i (the reference's
+        ialltoallv_and_modify schedule)."""
+        n = int(keys.shape[0])
+        if self.p > 1 and n > self.MAX_BATCH:
+            slices = (n + self.MAX_BATCH - 1) // self.MAX_BATCH
+            added, xb = 0, 0
+            for i in range(slices):
+                added += self.insert(keys[n * i // slices:n * (i + 1) // slices], default)
+                xb += self.last_exchange_bytes
+            self.last_exchange_bytes = xb
+            return added
         self.last_exchange_bytes = 0
-        n = keys.shape[0]
         if self.p > 1 and self.chunks == 1 and getattr(self.e, "can_plan", lambda p: False)(self.p):
+            if self.peer_stores and self.slabs and hasattr(self.e, "scatter_slabs"):
+                r = self._insert_slabs(keys, default)                  # takes host keys too: the sender runs behind the PCIe copy
+                if r is not None:
+                    return r
+                return self._insert_exact(self._dev_keys, default, ordered=True)
+            keys = self.e.canonicalize(self.e.as_keys(keys))
+            if self.peer_stores and hasattr(self.e, "scatter_peers"):
+                return self._insert_exact(keys, default, ordered=False)
             return self._insert_planned(keys, default)
+        keys = self.e.as_keys(keys)
         n_chunks = self.chunks if self.p > 1 else 1
         bounds = [n * i // n_chunks for i in range(n_chunks + 1)]
         added, pending = 0, None
@@ -268,12 +309,8 @@ class DistributedMap:
         return added
 
     def _insert_planned(self, keys, default):
-        """assign_count_estimate_permute shape: the sender's metadata pass yields, per destination, the key count,
-        the HLL registers and the table-region histogram; they travel with the keys, so the receiver presizes and
-        region-sorts without a pass of its own over the received keys."""
-        keys = self.e.canonicalize(keys)
-        if self.peer_stores and hasattr(self.e, "scatter_peers"):
-            return self._insert_peer_stores(keys, default)
+        """NCCL path (no peer access): assign_count_estimate_permute shape: the sender's metadata pass yields, per
+        destination, the key count and the HLL registers; they travel with the keys."""
         with _Stage("plan+scatter"):
             permuted, meta, send_counts = self.e.plan_scatter(keys, self.p)
         with _Stage("meta a2a"):
@@ -287,17 +324,6 @@ class DistributedMap:
         with _Stage("local insert"):
             return self.e.insert_recv(recv, recv_meta, default)
 
-    def _insert_peer_stores(self, keys, default):
-        """partition and exchange as ONE kernel: the rank scatter stores every key straight into the receive buffer
-        of its owner GPU through CUDA-IPC mapped peer memory (NVLink); NCCL only carries the p x p metadata."""
-        p, rank, dev = self.p, self.rank, self.e.device
-        if self.slabs and hasattr(self.e, "plan_scatter_slabs"):
-            r = self._insert_slabs(keys, default)
-            if r is not None:
-                return r
-            return self._insert_exact(keys, default, ordered=True)
-        return self._insert_exact(keys, default, ordered=False)
-
     def _ensure_peers(self, capacity):
         """(re)allocate the receive buffers; collective.  False when IPC / peer access is unavailable."""
         if self.peers is not None:
@@ -309,10 +335,42 @@ class DistributedMap:
             return False
         return True
 
+    HOST_CHUNK = 1 << 23       # keys per piece of the host -> device pipeline
+
+    def _send_slabs(self, keys, parity, counts):
+        """keys -> the owners' slabs (khx_scatter_slabs_dev).  Host keys (pinned CPU tensor / numpy array) are copied in pieces
+        on a copy stream and the sender kernel of piece i runs behind the copy of piece i+1.  Returns the device keys."""
+        dev = self.e.device
+        if torch.is_tensor(keys) and keys.is_cuda:
+            keys = self.e.canonicalize(keys)
+            self.e.scatter_slabs(keys, self.peers, self.slab_cap, parity, counts, reset=True)
+            return keys
+        if isinstance(keys, np.ndarray):
+            keys = torch.from_numpy(np.ascontiguousarray(keys, dtype=np.uint64).view(np.int64))
+        n = int(keys.shape[0])
+        if self.e.canonical_k or n == 0:
+            d = self.e.canonicalize(keys.to(dev))
+            self.e.scatter_slabs(d, self.peers, self.slab_cap, parity, counts, reset=True)
+            return d
+        if self._copy_stream is None:
+            self._copy_stream = torch.cuda.Stream(device=dev)
+            self._lib_stream = torch.cuda.ExternalStream(self.e.table.stream_ptr(), device=dev)
+        d = torch.empty(keys.shape, dtype=torch.int64, device=dev)
+        torch.cuda.current_stream(dev).synchronize()
+        for off in range(0, n, self.HOST_CHUNK):
+            m = min(self.HOST_CHUNK, n - off)
+            with torch.cuda.stream(self._copy_stream):
+                d[off:off + m].copy_(keys[off:off + m], non_blocking=True)
+                ev = torch.cuda.Event(); ev.record(self._copy_stream)
+            self._lib_stream.wait_event(ev)
+            self.e.scatter_slabs(d[off:off + m], self.peers, self.slab_cap, parity, counts, reset=(off == 0), synced=True)
+        return d
+
     def _insert_slabs(self, keys, default):
-        """ONE pass over the keys on the sender: metadata + stores into this rank's slab of every owner's buffer; the
-        metadata all-gather that follows is also the barrier behind the stores.  Returns None when a slab overflowed
-        (every rank sees the same count matrix, so every rank takes the exact path for this batch)."""
+        """ONE pass over the keys on the sender: dist hash -> owner -> store into this rank's slab of the owner's buffer
+        (NVLink); the flag barrier that follows delivers the p x p count matrix; the receiver's bulk insert reads its p slabs
+        in place, its level-1 pass computing the HyperLogLog registers the reference ships with the counts.  Returns None
+        when a slab overflowed (every rank sees the same matrix, so every rank takes the exact path for this batch)."""
         p, rank, dev = self.p, self.rank, self.e.device
         n = int(keys.shape[0])
         if self.peers is None or self.slab_cap == 0:
@@ -320,36 +378,37 @@ class DistributedMap:
             dist.all_reduce(nmax, op=dist.ReduceOp.MAX, group=self.group)
             self.slab_cap = int(int(nmax.item()) / p * 1.25) + 4096
             if not self._ensure_peers(2 * p * self.slab_cap):
+                keys = self.e.canonicalize(self.e.as_keys(keys))
                 return self._insert_planned(keys, default)
             self.parity, self._exact_dirty = 0, False
         if self._exact_dirty:                                              # a rank may still read the exact-path buffer
             dist.barrier(group=self.group)
             self._exact_dirty = False
         parity = self.parity
-        with _Stage("plan+scatter"):
-            meta = self.e.plan_scatter_slabs(keys, self.peers, self.slab_cap, parity)
-        with _Stage("meta push+sync"):
-            # metadata block r -> owner r by peer stores, then the flag barrier: every rank's stores have landed and
-            # every rank holds the count matrix C[g][r] = keys g sends to r
-            C = self.e.push_meta_sync(self.peers, parity, meta)
+        counts = torch.zeros(p, dtype=torch.int64, device=dev)
+        with _Stage("scatter->slabs"):
+            self._dev_keys = self._send_slabs(keys, parity, counts)
+        with _Stage("sync+counts"):
+            # the flag barrier: every rank's stores have landed and every rank holds the count matrix C[g][r] = keys g sends to r
+            C = self.e.peer_sync(self.peers, counts)
         if int(C.max()) > self.slab_cap:                                   # same decision on every rank
             self.slab_misses += 1
-            allmeta = torch.empty((p,) + tuple(meta.shape), dtype=meta.dtype, device=dev)
-            dist.all_gather_into_tensor(allmeta, meta, group=self.group)   # the exact path wants every block
-            self._allmeta, self._C = allmeta, C
+            self._C = C
             return None
+        self._dev_keys = None
         self.slab_misses = 0
         self.parity ^= 1
         self.last_exchange_bytes += 8 * self.W * int(C[rank].sum() - C[rank, rank])
         with _Stage("local insert"):
-            return self.e.insert_recv_slabs(self.peers, self.slab_cap, parity, C[:, rank], None, default)
+            return self.e.insert_recv_slabs(self.peers, self.slab_cap, parity, C[:, rank], None, default, no_meta=True)
 
     def _insert_exact(self, keys, default, ordered):
-        """two-pass sender: metadata pass -> all-gather -> exact offsets -> rank scatter into the owners' buffers.
-        ordered=True: called after a slab overflow, the metadata of this batch is already gathered."""
+        """exact offsets: count matrix -> every key to its final place in the owner's buffer (khx_scatter_peers_dev) -> barrier ->
+        insert.  ordered=True: called after a slab overflow, the count matrix of this batch is already known."""
         p, rank, dev = self.p, self.rank, self.e.device
         if ordered:
-            allmeta, C = self._allmeta, self._C
+            C = self._C
+            self._dev_keys = None
             need = int(C.sum(axis=0).max())
             grow = need > self.peers.capacity
             if self.slab_misses >= 2:                        # owners stay skewed: keep to the exact path from now on
@@ -359,41 +418,37 @@ class DistributedMap:
                 grow = grow or 2 * p * self.slab_cap > self.peers.capacity
             if grow and not self._ensure_peers(max(int(need * 1.25) + 1024, 2 * p * self.slab_cap)):
                 return self._insert_planned(keys, default)
-            self._exact_dirty = True
-            self.parity = 0
-            dst_off = C[:rank, :].sum(axis=0)
-            dst_cnt = C[rank, :]
-            self.last_exchange_bytes += 8 * self.W * int(dst_cnt.sum() - dst_cnt[rank])
-            with _Stage("scatter->peers"):
-                self.e.scatter_peers(keys, self.peers, dst_off, dst_cnt)
-                dist.barrier(group=self.group)
-            recv_meta = allmeta[:, rank, :].contiguous()
-            with _Stage("local insert"):
-                return self.e.insert_recv_ptr(self.peers.recv_ptr(), int(C[:, rank].sum()), recv_meta, default)
-        with _Stage("plan"):
-            meta = self.e.plan(keys, p)
-        with _Stage("meta gather"):
-            allmeta = torch.empty((p,) + tuple(meta.shape), dtype=meta.dtype, device=dev)
-            dist.all_gather_into_tensor(allmeta, meta, group=self.group)   # also orders ranks: previous reads are done
-            C = allmeta[:, :, 0].cpu().numpy().astype(np.uint64)           # C[g][r] = keys g sends to r
-        need = int(C.sum(axis=0).max())
-        if self.peers is None or self.peers.capacity < need:               # same decision on every rank
-            if self.peers is not None:
-                self.peers.close()
-            self.peers = PeerBuffers(dev.index, rank, p, int(need * 1.25) + 1024, self.W, self.group)
-            if not self.peers.ok:                                          # no IPC / no peer access: NCCL path
-                self.peer_stores = False
-                self.peers.close(); self.peers = None
-                return self._insert_planned(keys, default)
+            if not grow:
+                dist.barrier(group=self.group)               # every rank is past its reads of the previous batch's slabs
+        else:
+            with _Stage("plan"):
+                meta = self.e.plan(keys, p)
+            with _Stage("meta gather"):
+                allmeta = torch.empty((p,) + tuple(meta.shape), dtype=meta.dtype, device=dev)
+                dist.all_gather_into_tensor(allmeta, meta, group=self.group)   # also orders ranks: previous reads are done
+                C = allmeta[:, :, 0].cpu().numpy().astype(np.uint64)           # C[g][r] = keys g sends to r
+            need = int(C.sum(axis=0).max())
+            if self.peers is None or self.peers.capacity < need:               # same decision on every rank
+                if not self._ensure_peers(int(need * 1.25) + 1024):            # no IPC / no peer access: NCCL path
+                    return self._insert_planned(keys, default)
+        self._exact_dirty = True
+        self.parity = 0
         dst_off = C[:rank, :].sum(axis=0)
         dst_cnt = C[rank, :]
         self.last_exchange_bytes += 8 * self.W * int(dst_cnt.sum() - dst_cnt[rank])
         with _Stage("scatter->peers"):
             self.e.scatter_peers(keys, self.peers, dst_off, dst_cnt)
-            dist.barrier(group=self.group)                                 # every rank's stores have landed
-        recv_meta = allmeta[:, rank, :].contiguous()
+            dist.barrier(group=self.group)                                     # every rank's stores have landed
         with _Stage("local insert"):
-            return self.e.insert_recv_ptr(self.peers.recv_ptr(), int(C[:, rank].sum()), recv_meta, default)
+            return self.e.insert_ptr(self.peers.recv_ptr(), int(C[:, rank].sum()), default)
+
+    def close(self):
+        """COLLECTIVE: releases the IPC-mapped exchange buffers (unmap imports -> barrier -> free)"""
+        for name in ("peers", "qpeers"):
+            pb = getattr(self, name, None)
+            setattr(self, name, None)
+            if pb is not None:
+                pb.close()
 
     def _query_slabs(self, op, keys, nonexistent=0):
         """find / count / erase without NCCL on the data path: keys go to the owners by peer stores (one kernel), every

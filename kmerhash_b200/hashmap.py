@@ -101,7 +101,7 @@ class HashMap:
     def kernel_time(self, which="insert"):
         """(sum of ms, launches) of the insert / lookup probe kernels since kernel_timing(True)"""
         ms, n = C.c_double(0), C.c_uint64(0)
-        check(lib.kh_kernel_time(self._h, {"insert": 0, "lookup": 1, "scatter": 2, "hll": 3}[which], C.byref(ms), C.byref(n)), "kernel_time")
+        check(lib.kh_kernel_time(self._h, {"insert": 0, "lookup": 1, "scatter": 2, "hll": 3, "rebuild": 4, "level2": 5}[which], C.byref(ms), C.byref(n)), "kernel_time")
         return ms.value, n.value
 
     def reserve(self, n):
@@ -192,11 +192,30 @@ class HashMap:
                                              int(slab_cap), int(parity), meta.data_ptr()), "plan_scatter_slabs")
         return meta
 
-    def insert_recv_slabs(self, peer_handle, slab_cap, parity, counts, recv_meta=None, default=1):
+    def scatter_slabs(self, keys, peer_handle, slab_cap, parity, counts, reset=True, dist_hash="MURMUR64avx", dist_seed=9876543, synced=False):
+        """insert sender without metadata (khx_scatter_slabs_dev): keys -> this rank's slab of every owner's receive buffer;
+        `counts` (int64 CUDA tensor, p entries) accumulates this rank's row of the count matrix.  Asynchronous on the
+        table's stream; synced=True: the caller already ordered the keys before that stream."""
+        if synced:
+            k, n = keys, keys.shape[0]
+        else:
+            k, n = _dev_keys(keys, self.W, self.device)
+        assert counts.is_cuda and counts.dtype == torch.int64
+        check(lib.khx_scatter_slabs_dev(self._h, HASH_KINDS[dist_hash], dist_seed, k.data_ptr(), n, peer_handle, int(slab_cap),
+                                        int(parity), counts.data_ptr(), int(reset)), "scatter_slabs")
+
+    def insert_ptr(self, ptr, n, default=1, estimate=True):
+        """insert n keys lying at a raw device pointer (a peer receive buffer)"""
+        torch.cuda.current_stream(self.device).synchronize()
+        return check(lib.kh_insert_dev(self._h, ptr, None, int(n), default, int(estimate)), "insert")
+
+    def insert_recv_slabs(self, peer_handle, slab_cap, parity, counts, recv_meta=None, default=1, no_meta=False):
         """receiver half reading the p slabs of this rank's receive buffer in place; counts[g] = keys sender g stored.
         recv_meta: [p, khx_meta_words] int64 CUDA tensor, or None = the buffer's own metadata area (khx_push_meta_sync_dev)"""
         cnt = np.ascontiguousarray(counts, dtype=np.uint64)
-        if recv_meta is None:
+        if no_meta:
+            mp = None
+        elif recv_meta is None:
             mp = lib.khx_peer_meta_ptr(peer_handle, int(parity))
         else:
             assert recv_meta.is_cuda and recv_meta.dtype == torch.int64 and recv_meta.is_contiguous()

@@ -120,3 +120,24 @@ def test_kmercounter_driver_is_built():
     assert os.path.exists(COUNTER)
     r = subprocess.run([COUNTER, "--help"], capture_output=True, text=True, timeout=60)
     assert r.returncode == 0 and "BenchmarkKmerCounter" in r.stdout
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("world", [2])
+def test_distributed_map_on_real_gpus_under_torchrun(world):
+    """one process per GPU (torchrun, NCCL + CUDA-IPC mapped peer buffers): tools/dist_parity.py checks every rank's table
+    contents against the oracle's per-rank rule through the slab exchange, its overflow fallback, slab growth, empty
+    batches, queries in input order and erase.  Needs >= 2 visible GPUs (the emulated-p tests cover the kernels on one)."""
+    import subprocess
+    import socket
+    import sys
+    import torch
+    if torch.cuda.device_count() < world:
+        pytest.skip("needs %d GPUs" % world)
+    s = socket.socket(); s.bind(("127.0.0.1", 0)); port = s.getsockname()[1]; s.close()
+    env = dict(os.environ, KH_PARITY_SHORT="1", KH_PARITY_N0="3000000,150000")
+    r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", str(world),
+                        "--master-addr", "127.0.0.1", "--master-port", str(port), os.path.join(ROOT, "tools", "dist_parity.py")],
+                       capture_output=True, text=True, timeout=600, env=env)
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
+    assert r.stdout.count(" OK") >= world

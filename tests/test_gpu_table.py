@@ -510,6 +510,98 @@ def test_single_pass_slab_exchange(kh, oracle_mod, p, W, n_per, tiled):
                 lib.khx_peer_destroy(h)
 
 
+
+@pytest.mark.parametrize("p,W,n_per,pieces", [(2, 1, 90000, 1), (8, 1, 70000, 3), (3, 2, 60000, 2), (8, 1, 1500000, 4)])
+def test_slab_exchange_without_metadata(kh, oracle_mod, p, W, n_per, pieces):
+    """khx_scatter_slabs_dev (sender without metadata; the batch handed over in `pieces` chunks with accumulating counts, as
+    behind a PCIe copy) + khx_insert_recv_slabs_dev(d_recv_meta = NULL): slab (owner r, sender g) must hold exactly the keys
+    the reference's rule sends from g to r, the counts must be the true ones also when a slab overflows, and every
+    receiver -- whose level-1 pass estimates from the received keys themselves -- must build the reference's per-rank table
+    with the reference's capacity."""
+    import ctypes
+    import torch
+    from kmerhash_b200._lib import lib
+    o = oracle_mod.port
+    cudart = ctypes.CDLL("libcudart.so")
+    rng = np.random.default_rng(910 + p + W)
+    n_base = max(20000, n_per // 4)
+    base = rng.integers(0, 2**62, size=(n_base, W), dtype=np.uint64)
+    tables = [kh.HashMap(W, "MURMUR64avx", "COUNT") for _ in range(p)]
+    slab_cap = int(n_per / p * 1.5) + 1024
+    cap = 2 * p * slab_cap + 64
+    peers = [lib.khx_peer_create(0, r, p, cap, W) for r in range(p)]
+
+    def read_buf(r):
+        buf = torch.empty((cap, W), dtype=torch.int64, device="cuda")
+        torch.cuda.synchronize()
+        assert cudart.cudaMemcpy(ctypes.c_void_p(buf.data_ptr()), ctypes.c_void_p(lib.khx_peer_recv_ptr(peers[r])),
+                                 ctypes.c_size_t(cap * 8 * W), 3) == 0
+        return buf.cpu().numpy().view(np.uint64)
+
+    def srt(a):
+        return np.sort(a[:, 0]) if W == 1 else a[np.lexsort(a.T[::-1])]
+
+    try:
+        assert all(peers)
+        for r in range(p):
+            for q in range(p):
+                if q != r:
+                    assert lib.khx_peer_set(peers[r], q, lib.khx_peer_recv_ptr(peers[q])) == 0
+        gm = o.Map(W, "COUNT")
+        ref = getattr(oracle_mod, "ref", None)              # the compiled reference (capacity rule incl. its cumulative HLL)
+        refs = [ref.Map("OFFSETS_COUNT", W, "MURMUR64avx", 0.2, 0.8) for _ in range(p)] if ref is not None else None
+        for parity in (0, 1):
+            batches = [np.ascontiguousarray(base[rng.integers(0, n_base, size=n_per + 777 * g)]) for g in range(p)]
+            flat = [b if W == 2 else np.ascontiguousarray(b[:, 0]) for b in batches]
+            dkeys = [torch.from_numpy(b.view(np.int64)).cuda() for b in flat]
+            counts = [torch.zeros(p, dtype=torch.int64, device="cuda") for _ in range(p)]
+            for g in range(p):
+                n = dkeys[g].shape[0]
+                for i in range(pieces):
+                    tables[g].scatter_slabs(dkeys[g][n * i // pieces:n * (i + 1) // pieces].contiguous(), peers[g], slab_cap, parity,
+                                            counts[g], reset=(i == 0))
+            for g in range(p):
+                assert lib.kh_count_dev(tables[g]._h, None, 0, None) == 0          # synchronises table g's stream (the sender is asynchronous)
+            Cm = torch.stack(counts).cpu().numpy().astype(np.uint64)
+            assert int(Cm.max()) <= slab_cap
+            for r in range(p):
+                got = read_buf(r)
+                for g in range(p):
+                    lo = (parity * p + g) * slab_cap
+                    src = batches[g][o.rank("MURMUR64avx", flat[g], p) == r]
+                    assert int(Cm[g, r]) == len(src)
+                    assert np.array_equal(srt(got[lo:lo + len(src)]), srt(src))
+            gm.insert(np.concatenate(flat), default=1)
+            gk, gv = gm.to_vector()
+            owner = o.rank("MURMUR64avx", gk, p)
+            allk = np.concatenate(flat)
+            allowner = o.rank("MURMUR64avx", allk, p)
+            for r in range(p):
+                tables[r].insert_recv_slabs(peers[r], slab_cap, parity, Cm[:, r], None, 1, no_meta=True)
+                ek, ev = sort_pairs(gk[owner == r], gv[owner == r])
+                tk, tv = sort_pairs(*tables[r].to_vector())
+                assert np.array_equal(tk, ek) and np.array_equal(tv, ev)
+                if refs is not None:
+                    refs[r].insert(np.ascontiguousarray(allk[allowner == r]), default=1)
+                    assert tables[r].capacity() == refs[r].capacity()
+        # overflow: the slabs far too small.  Nothing is written past a slab; the counts stay the true ones.
+        small = 1000
+        before = [read_buf(r) for r in range(p)]
+        cnt = torch.zeros(p, dtype=torch.int64, device="cuda")
+        tables[0].scatter_slabs(dkeys[0], peers[0], small, 0, cnt)
+        assert lib.kh_count_dev(tables[0]._h, None, 0, None) == 0
+        exp = np.bincount(o.rank("MURMUR64avx", flat[0], p), minlength=p)
+        assert np.array_equal(cnt.cpu().numpy(), exp) and int(exp.max()) > small
+        for r in range(p):
+            after = read_buf(r)
+            changed = np.nonzero((after != before[r]).any(axis=1))[0]
+            assert changed.size == 0 or (changed.min() >= 0 and changed.max() < small)
+    finally:
+        for h in peers:
+            if h:
+                lib.khx_peer_destroy(h)
+
+
 @pytest.mark.parametrize("n,distinct,skew", [(3_000_000, 40_000, 0.0), (3_000_000, 1_500_000, 0.0), (6_000_000, 5_000_000, 0.0),
                                              (3_000_000, 1_000_000, 0.5), (2_000_000, 1_900_000, 0.97)])
 def test_fused_one_read_bulk_insert(kh, oracle_mod, n, distinct, skew):
@@ -696,3 +788,27 @@ def test_tile_insert_deferred_chains_and_side_key(kh, oracle_mod, max_load):
     assert m.insert_no_estimate(more, default=1) == om.insert(more, default=1)     # sticky bits: global path
     check_against(m, om)
     assert np.array_equal(m.find(q, 0), om.find(q, 0))
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("n,distinct,bulk", [(3_000_000, 700_000, True), (3_000_000, 2_500_000, True), (200_000, 90_000, False)])
+def test_capacity_follows_compiled_reference_over_overlapping_batches(kh, oracle_mod, n, distinct, bulk):
+    """insert() reserves from ONE cumulative HyperLogLog over everything inserted with an estimate, as the reference does
+    (KH/robinhood_offset_hashmap_ptr.hpp:291,2520-2535): re-inserting overlapping batches (the k-mer counting case) must
+    leave the capacity where the compiled reference leaves it, batch after batch -- bulk route and general route."""
+    ref = getattr(oracle_mod, "ref", None)
+    if ref is None:
+        pytest.skip("oracle/_ref not built")
+    import torch
+    rng = np.random.default_rng(n + distinct)
+    base = rng.integers(0, 2**62, size=distinct, dtype=np.uint64)
+    m = kh.HashMap(1, "MURMUR64avx", "COUNT", min_load=0.2, max_load=0.8)
+    m.set_insert_window(bulk, 32 << 20, 1 << 20)
+    rm = ref.Map("OFFSETS_COUNT", 1, "MURMUR64avx", 0.2, 0.8)
+    for batch in range(4):
+        lo = 0 if batch != 2 else distinct // 2                        # batch 2 draws from the upper half only
+        keys = np.ascontiguousarray(base[rng.integers(lo, distinct, size=n)])
+        m.insert(torch.from_numpy(keys.view(np.int64)).cuda(), default=1)
+        rm.insert(keys, default=1)
+        assert m.size() == rm.size()
+        assert m.capacity() == rm.capacity(), (batch, m.capacity(), rm.capacity())

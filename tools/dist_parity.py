@@ -110,6 +110,7 @@ for n0 in SIZES:
     ok = ok and np.array_equal(m.count(torch.from_numpy(q.view(np.int64)).cuda()).cpu().numpy(), ref.count(q).astype(np.uint8))
     print("rank %d n0 %d paths %s queries %s size %d %s" % (rank, n0, ",".join(path), ",".join(qpath), m.local_size(),
                                                            "OK" if ok else "FAIL"), flush=True)
+    m.close()                                   # collective: unmap imports -> barrier -> free
 
 flag = torch.tensor([1 if ok else 0], device="cuda")
 dist.all_reduce(flag, op=dist.ReduceOp.MIN)
