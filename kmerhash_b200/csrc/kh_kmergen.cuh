@@ -1,0 +1,307 @@
+// kh_kmergen.cuh -- block-level streaming k-mer generation (2-bit DNA, k <= 64), one pass over the base buffer.
+//
+// Replaces the hot loop of KmerParser::operator() (KI/io/kmer_parser.hpp:232-293) over the N-splitting, EOL-skipping
+// sequence iterator (KI/io/filtered_sequence_iterator.hpp:225-247,429-440; KI/utils/file_utils.hpp:43-47) with
+// Kmer::nextFromChar (KI/common/kmer.hpp:716-726) and, fused, reverse_complement + lex_less (KI/common/kmer.hpp:1078-1087,
+// KI/common/kmer_transform.hpp:109-125).  The reference pushes one base at a time through a serial shift per read; the
+// first GPU version gave one warp per read.  Here the unit of work is a TILE of the byte buffer, independent of the reads:
+//
+//   1. a CTA loads GEN_TILE_BYTES consecutive bytes (16 per thread, one coalesced 16-byte load): GEN_LOOKBACK bytes of
+//      context + GEN_SPAN bytes whose k-mers (by END position) this tile emits;
+//   2. every thread classifies its bytes (EOL / N / 2-bit code) and packs its clean bases; a block scan of the clean counts
+//      gives every thread its place in the tile's COMPACT base sequence (EOL characters squeezed out), where it ORs its
+//      packed codes and N flags into shared-memory bit arrays; the read starts that fall into the tile (binary search in
+//      `offsets`, then one thread per start) become bits of a third array;
+//   3. every thread takes 16 consecutive compact positions: validity of the 16 windows from the bit arrays, a block scan of
+//      the valid counts, then a rolling update  fwd = (fwd << 2 | c) & mask,  rc = rc >> 2 | (3 - c) << (2k - 2)  from a
+//      start window cut out of the packed codes with funnel shifts -- no per-k-mer gather, no warp reduction per step;
+//   4. the tile's k-mers go to a shared-memory tile in output order and leave with coalesced 16-byte stores.  Where the tile's
+//      output begins is settled without a second pass by a decoupled look-back over per-tile aggregates (tiles are handed
+//      out by an atomic ticket, so a tile only ever waits for tiles that already run).
+//
+// Output order = the reference's: reads in order, windows in order.  A window that would reach behind the tile's context
+// (more than GEN_LOOKBACK - k EOL characters inside k bases) cannot be decided here: the kernel raises `fallback` and the
+// host repeats the call with the warp-per-read kernel (kmer_api.cu), which has no such bound.
+#pragma once
+#include <cstdint>
+#include <cub/block/block_scan.cuh>
+#include "kh_kmer.cuh"
+#include "kh_table.cuh"
+
+namespace kh {
+
+constexpr int GEN_THREADS = 512;
+constexpr int GEN_TILE_BYTES = GEN_THREADS * 16;          // 8192
+constexpr int GEN_LOOKBACK = 256;
+constexpr int GEN_SPAN = GEN_TILE_BYTES - GEN_LOOKBACK;   // 7936 output positions per tile
+constexpr int GEN_PAD = 64;                               // compact positions of zero history in front of the tile
+constexpr int GEN_RUN = 16;                               // compact positions per thread in the rolling stage
+constexpr int GEN_BITS = GEN_TILE_BYTES + GEN_PAD + 64;   // compact positions the bit arrays hold (incl. slack for 64-bit reads)
+
+constexpr unsigned long long GEN_ST_AGG = 1ULL << 62, GEN_ST_INC = 2ULL << 62, GEN_ST_MASK = 3ULL << 62;
+
+struct GenArgs {
+  const unsigned char *bases;      // 16-byte aligned origin (the caller's pointer rounded down; `delta` = the difference)
+  const uint64_t *offsets;         // [n_reads + 1], relative to the caller's pointer
+  uint64_t n_reads, delta;
+  uint64_t first, end;             // offsets[0] + delta, offsets[n_reads] + delta
+  int k, canonical;
+  uint64_t n_tiles;
+  unsigned long long *ticket;      // tile dispenser
+  unsigned long long *state;       // [n_tiles] look-back words
+  uint64_t *out_keys;              // may be null: count only
+  uint64_t out_cap;
+  int *fallback;
+};
+
+template <int W> constexpr size_t gen_smem_bytes() {
+  // out tile | packed codes (u32) | N bits | start bits | per-thread clean mask + compact base
+  return (size_t)GEN_SPAN * 8 * W + (size_t)(GEN_BITS / 16) * 4 + 2 * (size_t)(GEN_BITS / 32) * 4 + (size_t)GEN_THREADS * 8 + 64;
+}
+
+// 64 bits starting at bit position `bit` of a little-endian u32 array
+__device__ __forceinline__ uint64_t bits64(const uint32_t *a, uint32_t bit) {
+  const uint32_t w = bit >> 5, s = bit & 31u;
+  const uint32_t x0 = a[w], x1 = a[w + 1], x2 = a[w + 2];
+  const uint32_t lo = __funnelshift_r(x0, x1, s), hi = __funnelshift_r(x1, x2, s);
+  return ((uint64_t)hi << 32) | lo;
+}
+
+// Consumer: what happens to a tile's k-mers.  store(): coalesced copy of the shared-memory tile to out_keys (the stand-alone API).
+template <int W>
+__global__ void __launch_bounds__(GEN_THREADS, 2) kmer_tiles_kernel(const GenArgs a) {
+  using Scan = cub::BlockScan<uint32_t, GEN_THREADS>;
+  __shared__ typename Scan::TempStorage scan_tmp;
+  __shared__ unsigned long long s_tile, s_base;
+  __shared__ uint32_t s_rfirst, s_firstbreak;
+  extern __shared__ __align__(16) unsigned char gen_smem[];
+  uint64_t *otile = reinterpret_cast<uint64_t *>(gen_smem);
+  uint32_t *pc = reinterpret_cast<uint32_t *>(otile + (size_t)GEN_SPAN * W);   // 2 bits per compact position
+  uint32_t *nb = pc + GEN_BITS / 16;                                            // 1 bit: N
+  uint32_t *sb = nb + GEN_BITS / 32;                                            // 1 bit: a read starts here
+  uint32_t *cbase = sb + GEN_BITS / 32;                                         // [GEN_THREADS] compact index of the thread's first byte
+  uint32_t *cmask = cbase + GEN_THREADS;                                        // [GEN_THREADS] clean mask of the thread's 16 bytes
+  const int tid = threadIdx.x, lane = tid & 31;
+  const int k = a.k;
+  const int topbits = 2 * k - 64 * (W - 1);
+  const uint64_t topmask = topbits >= 64 ? ~0ULL : ((1ULL << topbits) - 1ULL);
+
+  for (;;) {
+    if (tid == 0) s_tile = atomicAdd(a.ticket, 1ULL);
+    // bit arrays zero (the previous tile's readers are behind the barrier at the end of the loop body)
+    for (int i = tid; i < GEN_BITS / 16 + 2 * (GEN_BITS / 32); i += GEN_THREADS) pc[i] = 0;
+    if (tid == 0) s_firstbreak = 0xffffffffu;
+    __syncthreads();
+    const uint64_t tile = s_tile;
+    if (tile >= a.n_tiles) break;
+    // byte positions (relative to the aligned origin) [lo, hi): lo may be "negative" for tile 0 -> clamp by a flag
+    const int64_t lo = (int64_t)(tile * GEN_SPAN) - GEN_LOOKBACK;
+    const int64_t g0 = lo + 16 * tid;                       // this thread's first byte
+
+    // ---- 1. load + classify ---------------------------------------------------------------------------------------------
+    uint32_t clean = 0, nmask = 0, codes = 0;
+    {
+      unsigned char c[16];
+      if (g0 >= 0 && (uint64_t)g0 + 16 <= a.end) {
+        const uint4 v = __ldg(reinterpret_cast<const uint4 *>(a.bases + g0));
+        memcpy(c, &v, 16);
+      } else {
+#pragma unroll
+        for (int i = 0; i < 16; ++i) {
+          const int64_t g = g0 + i;
+          c[i] = (g >= 0 && (uint64_t)g < a.end) ? __ldg(a.bases + g) : (unsigned char)'\n';
+        }
+      }
+      int m = 0;
+#pragma unroll
+      for (int i = 0; i < 16; ++i) {
+        const int64_t g = g0 + i;
+        const bool inside = g >= (int64_t)a.first && (uint64_t)g < a.end;       // bytes in front of the first read are not data
+        const bool skip = !inside || c[i] == '\n' || c[i] == '\r';
+        if (!skip) {
+          clean |= 1u << i;
+          codes |= dna_code(c[i]) << (2 * m);
+          nmask |= ((c[i] == 'N' || c[i] == 'n') ? 1u : 0u) << m;
+          ++m;
+        }
+      }
+    }
+    const uint32_t nclean = __popc(clean);
+    uint32_t cb, ctotal;
+    Scan(scan_tmp).ExclusiveSum(nclean, cb, ctotal);
+    cbase[tid] = cb; cmask[tid] = clean;
+    if (nclean) {
+      const uint32_t bit = 2u * (cb + GEN_PAD);
+      const uint64_t v = (uint64_t)codes << (bit & 31u);
+      atomicOr(&pc[bit >> 5], (uint32_t)v);
+      if (v >> 32) atomicOr(&pc[(bit >> 5) + 1], (uint32_t)(v >> 32));
+      if (nmask) {
+        const uint32_t nbit = cb + GEN_PAD;
+        const uint64_t nv = (uint64_t)nmask << (nbit & 31u);
+        atomicOr(&nb[nbit >> 5], (uint32_t)nv);
+        if (nv >> 32) atomicOr(&nb[(nbit >> 5) + 1], (uint32_t)(nv >> 32));
+        atomicMin(&s_firstbreak, cb + (uint32_t)(__ffs(nmask) - 1));
+      }
+    }
+    // first read whose start lies at or behind the tile's first byte (lower bound over offsets + delta)
+    if (tid == 0) {
+      uint64_t l = 0, h = a.n_reads + 1;                      // invariant: offsets[l-1] + delta < max(lo,0) <= offsets[h] + delta
+      const uint64_t want = lo > 0 ? (uint64_t)lo : 0ULL;
+      while (l < h) {
+        const uint64_t mid = (l + h) >> 1;
+        if (a.offsets[mid] + a.delta < want) l = mid + 1; else h = mid;
+      }
+      s_rfirst = (uint32_t)0; s_base = l;                     // s_base reused: index of that read
+    }
+    __syncthreads();
+
+    // ---- 2. read starts inside the tile -> start bits in compact space -------------------------------------------------------
+    {
+      const uint64_t hi = (uint64_t)(lo + GEN_TILE_BYTES);
+      for (uint64_t r = s_base + tid; r <= a.n_reads; r += GEN_THREADS) {
+        const uint64_t b = a.offsets[r] + a.delta;
+        if (b >= hi) break;                                   // offsets ascend
+        const uint32_t local = (uint32_t)((int64_t)b - lo);   // 0 <= local < GEN_TILE_BYTES
+        const uint32_t th = local >> 4, within = local & 15u;
+        const uint32_t ci = cbase[th] + __popc(cmask[th] & ((1u << within) - 1u));   // clean bases in front of byte `local`
+        atomicOr(&sb[(ci + GEN_PAD) >> 5], 1u << ((ci + GEN_PAD) & 31u));
+        if (r < a.n_reads) atomicMin(&s_firstbreak, ci);
+      }
+    }
+    __syncthreads();
+    // compact index of the first output position (byte lo + GEN_LOOKBACK); tile 0 emits from its first byte
+    const uint32_t c_lo = cbase[GEN_LOOKBACK / 16];
+    // context check: a window of an output position may reach behind compact position 0 only if data lies there
+    if (tid == 0 && lo > (int64_t)a.first && c_lo < (uint32_t)(k - 1) && s_firstbreak > c_lo && ctotal > c_lo) *a.fallback = 1;
+
+    // ---- 3. validity of this thread's GEN_RUN windows ---------------------------------------------------------------------------
+    const uint32_t j0 = c_lo + (uint32_t)tid * GEN_RUN;       // first compact position of the run
+    uint32_t vmask = 0;
+    uint32_t len0 = 0;                                        // good run length at j0 - 1
+    const bool active = j0 < ctotal;
+    uint32_t nrun = 0, srun = 0;
+    if (active) {
+      // previous 64 positions: the run of good bases ending at j0 - 1 starts behind the last N / at the last read start;
+      // position 0 of the tile counts as a start (nothing in front of it is known)
+      const uint64_t pn = bits64(nb, j0 + GEN_PAD - 64), ps = bits64(sb, j0 + GEN_PAD - 64);
+      const uint32_t back_n = pn ? (uint32_t)__clzll((long long)pn) : 64u;                 // good positions behind the last N
+      const uint32_t back_s = ps ? (uint32_t)__clzll((long long)ps) + 1u : 65u;            // positions from the last start on
+      len0 = min(min(back_n, back_s), j0);                                                 // never longer than what the tile holds
+      nrun = (uint32_t)bits64(nb, j0 + GEN_PAD) & 0xffffu;
+      srun = (uint32_t)bits64(sb, j0 + GEN_PAD) & 0xffffu;
+      uint32_t len = len0;
+#pragma unroll
+      for (int i = 0; i < GEN_RUN; ++i) {
+        const bool isn = (nrun >> i) & 1u, st = (srun >> i) & 1u;
+        len = isn ? 0u : (st ? 1u : len + 1u);
+        if (len >= (uint32_t)k && j0 + i < ctotal) vmask |= 1u << i;
+      }
+    }
+    uint32_t obase, ototal;
+    Scan(scan_tmp).ExclusiveSum((uint32_t)__popc(vmask), obase, ototal);
+
+    // ---- look-back: where this tile's output starts -------------------------------------------------------------------------------
+    if (tid < 32) {
+      unsigned long long sum = 0;
+      if (tile == 0) {
+        if (lane == 0) atomicExch(&a.state[0], GEN_ST_INC | (unsigned long long)ototal);
+      } else {
+        if (lane == 0) atomicExch(&a.state[tile], GEN_ST_AGG | (unsigned long long)ototal);
+        int64_t i = (int64_t)tile - 1;
+        for (;;) {
+          const int64_t idx = i - lane;
+          unsigned long long v = GEN_ST_INC;                  // in front of tile 0: inclusive prefix 0
+          if (idx >= 0) {
+            const volatile unsigned long long *p = a.state + idx;
+            do { v = *p; } while ((v & GEN_ST_MASK) == 0);
+          }
+          const uint32_t inc = __ballot_sync(FULL_MASK, (v & GEN_ST_MASK) == GEN_ST_INC);
+          const int firstinc = inc ? __ffs(inc) - 1 : 32;
+          unsigned long long part = lane <= firstinc ? (v & ~GEN_ST_MASK) : 0ULL;
+#pragma unroll
+          for (int o = 16; o > 0; o >>= 1) part += __shfl_xor_sync(FULL_MASK, part, o);
+          sum += part;
+          if (inc) break;
+          i -= 32;
+        }
+        if (lane == 0) atomicExch(&a.state[tile], GEN_ST_INC | (sum + (unsigned long long)ototal));
+      }
+      if (lane == 0) s_base = sum;
+    }
+
+    // ---- 4. rolling generation into the shared-memory out tile ------------------------------------------------------------------
+    if (a.out_keys && vmask) {
+      // window ending at j0 - 1, little-endian (oldest base lowest): the top k of the 32 W positions in front of j0
+      uint64_t x[W], fwd[W], rc[W];
+      const uint32_t hb = 2u * (j0 + GEN_PAD - 32u * W);
+      if (W == 1) {
+        x[0] = bits64(pc, hb) >> (64 - 2 * k);                // k >= 1
+      } else {
+        const uint64_t h0 = bits64(pc, hb), h1 = bits64(pc, hb + 64);
+        const int s = 128 - 2 * k;                            // 0 <= s < 64 for 33 <= k <= 64
+        x[0] = s ? ((h0 >> s) | (h1 << (64 - s))) : h0;
+        x[W - 1] = h1 >> s;
+      }
+      // forward k-mer = 2-bit groups of x reversed (newest base lowest); reverse complement = ~x
+      const int sh = 64 * W - 2 * k;
+      if (W == 1) fwd[0] = rev2bit64(x[0] << sh);
+      else {
+        // reverse the 128-bit value (x << sh): words swap and reverse
+        const uint64_t y0 = sh ? (x[0] << sh) : x[0];
+        const uint64_t y1 = sh ? ((x[W - 1] << sh) | (x[0] >> (64 - sh))) : x[W - 1];
+        fwd[0] = rev2bit64(y1); fwd[W - 1] = rev2bit64(y0);
+      }
+#pragma unroll
+      for (int q = 0; q < W; ++q) rc[q] = ~x[q];
+      rc[W - 1] &= topmask;
+      const uint32_t nxt = (uint32_t)bits64(pc, 2u * (j0 + GEN_PAD));
+      uint32_t o = obase;
+#pragma unroll
+      for (int i = 0; i < GEN_RUN; ++i) {
+        const uint64_t c = (nxt >> (2 * i)) & 3u;
+        if (W == 1) {
+          fwd[0] = ((fwd[0] << 2) | c) & topmask;
+          rc[0] = (rc[0] >> 2) | ((3ULL - c) << (2 * k - 2));
+        } else {
+          fwd[W - 1] = ((fwd[W - 1] << 2) | (fwd[0] >> 62)) & topmask;
+          fwd[0] = (fwd[0] << 2) | c;
+          rc[0] = (rc[0] >> 2) | (rc[W - 1] << 62);
+          rc[W - 1] = (rc[W - 1] >> 2) | ((3ULL - c) << (topbits - 2));
+        }
+        if ((vmask >> i) & 1u) {
+          const bool use_rc = a.canonical && !kmer_less<W>(fwd, rc);
+#pragma unroll
+          for (int q = 0; q < W; ++q) otile[(size_t)o * W + q] = use_rc ? rc[q] : fwd[q];
+          ++o;
+        }
+      }
+    }
+    __syncthreads();
+
+    // ---- the tile leaves: coalesced stores ------------------------------------------------------------------------------------------
+    if (a.out_keys) {
+      const uint64_t gbase = s_base;
+      uint64_t room = a.out_cap > gbase ? a.out_cap - gbase : 0;
+      const uint32_t cnt = (uint32_t)min((uint64_t)ototal, room);
+      uint64_t *dst = a.out_keys + gbase * W;
+      const uint32_t words = cnt * W;
+      // head up to a 16-byte boundary, body as uint4, tail
+      const uint32_t head = min(words, (uint32_t)((reinterpret_cast<uintptr_t>(dst) >> 3) & 1u));
+      if (tid < (int)head) dst[tid] = otile[tid];
+      const uint32_t body = (words - head) >> 1;
+      const uint4 *s4 = reinterpret_cast<const uint4 *>(otile);   // only aligned when head == 0; otherwise go through u64 pairs
+      if (head == 0) {
+        uint4 *d4 = reinterpret_cast<uint4 *>(dst);
+        for (uint32_t i = tid; i < body; i += GEN_THREADS) d4[i] = s4[i];
+      } else {
+        ulonglong2 *d2 = reinterpret_cast<ulonglong2 *>(dst + head);
+        for (uint32_t i = tid; i < body; i += GEN_THREADS) d2[i] = make_ulonglong2(otile[head + 2 * i], otile[head + 2 * i + 1]);
+      }
+      const uint32_t done = head + 2 * body;
+      if (tid == 0 && done < words) dst[done] = otile[done];
+    }
+    __syncthreads();
+  }
+}
+
+}  // namespace kh
