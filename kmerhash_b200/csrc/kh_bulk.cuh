@@ -103,9 +103,21 @@ template <int W> struct L1Cfg {
   static constexpr size_t SMEM = (size_t)2 * RAW_BYTES + (size_t)TILE * 4 + BK_MAX_BINS * 2 + BK_MAX_BINS * 4 + HLL_M + 16;
 };
 
+// dsegs: the pieces as a DEVICE-resident table (may be null: the launch argument `segs_arg` holds them).  The pipelined
+// multi-GPU receiver (exchange.cu) launches this kernel before the host knows how many keys every sender stored: a small
+// kernel behind the flag barrier writes the table, the grid is fixed and every CTA reads its tile count from it.
 template <int W>
-__global__ void __launch_bounds__(L1_THREADS, 1) l1_scatter_kernel(const L1Args a, const __grid_constant__ BkSegs segs) {
+__global__ void __launch_bounds__(L1_THREADS, 1) l1_scatter_kernel(const L1Args a, const __grid_constant__ BkSegs segs_arg,
+                                                                   const BkSegs *dsegs) {
   using Cfg = L1Cfg<W>;
+  __shared__ BkSegs segs;
+  {
+    static_assert(sizeof(BkSegs) % 8 == 0, "BkSegs is copied word by word");
+    const unsigned long long *src = reinterpret_cast<const unsigned long long *>(dsegs ? dsegs : &segs_arg);
+    unsigned long long *dst = reinterpret_cast<unsigned long long *>(&segs);
+    for (int i = threadIdx.x; i < (int)(sizeof(BkSegs) / 8); i += L1_THREADS) dst[i] = src[i];
+    __syncthreads();
+  }
   constexpr int TILE = Cfg::TILE, KPT = Cfg::KPT;
   using Scan = cub::BlockScan<uint32_t, L1_THREADS>;
   __shared__ typename Scan::TempStorage scan_tmp;
@@ -125,7 +137,7 @@ __global__ void __launch_bounds__(L1_THREADS, 1) l1_scatter_kernel(const L1Args 
   if (tid == 0) { mbar_init(mbar, 1); fence_proxy_async(); }
 
   const int rshift = 32 - a.lp;
-  const bool pieces = segs.nseg > 1;
+  const bool pieces = segs.nseg > 1 || dsegs != nullptr;
   const uint64_t n_tiles = pieces ? segs.tprefix[segs.nseg] : (a.n + TILE - 1) / TILE;
   // where tile t starts in `keys` and how many keys it holds (tile-uniform; a handful of compares per tile)
   auto locate = [&](uint64_t t, uint64_t &start, int &cnt) {

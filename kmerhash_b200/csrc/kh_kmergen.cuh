@@ -16,8 +16,10 @@
 //      the valid counts, then a rolling update  fwd = (fwd << 2 | c) & mask,  rc = rc >> 2 | (3 - c) << (2k - 2)  from a
 //      start window cut out of the packed codes with funnel shifts -- no per-k-mer gather, no warp reduction per step;
 //   4. the tile's k-mers go to a shared-memory tile in output order and leave with coalesced 16-byte stores.  Where the tile's
-//      output begins is settled without a second pass by a decoupled look-back over per-tile aggregates (tiles are handed
-//      out by an atomic ticket, so a tile only ever waits for tiles that already run).
+//      output begins is settled without a second pass by a decoupled look-back over per-tile aggregates (the grid is
+//      persistent and takes the tiles round-robin, so a tile only ever waits for tiles of CTAs that are resident and run).
+// The first read of every tile comes from a tiny pre-kernel (one binary search per tile, all in parallel); the next tile's
+// bytes are fetched into registers while the current tile is processed.
 //
 // Output order = the reference's: reads in order, windows in order.  A window that would reach behind the tile's context
 // (more than GEN_LOOKBACK - k EOL characters inside k bases) cannot be decided here: the kernel raises `fallback` and the
@@ -47,7 +49,7 @@ struct GenArgs {
   uint64_t first, end;             // offsets[0] + delta, offsets[n_reads] + delta
   int k, canonical;
   uint64_t n_tiles;
-  unsigned long long *ticket;      // tile dispenser
+  const uint64_t *tile_read;       // [n_tiles] first read whose start lies at or behind the tile's first byte (gen_tile_reads_kernel)
   unsigned long long *state;       // [n_tiles] look-back words
   uint64_t *out_keys;              // may be null: count only
   uint64_t out_cap;
@@ -67,13 +69,33 @@ __device__ __forceinline__ uint64_t bits64(const uint32_t *a, uint32_t bit) {
   return ((uint64_t)hi << 32) | lo;
 }
 
+// first read whose start lies at or behind byte max(lo, 0) of every tile: lower bound over offsets + delta
+static __global__ void gen_tile_reads_kernel(const uint64_t *offsets, uint64_t n_reads, uint64_t delta, uint64_t n_tiles, uint64_t *tile_read) {
+  const uint64_t t = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= n_tiles) return;
+  const int64_t lo = (int64_t)(t * GEN_SPAN) - GEN_LOOKBACK;
+  const uint64_t want = lo > 0 ? (uint64_t)lo : 0ULL;
+  uint64_t l = 0, h = n_reads + 1;
+  while (l < h) {
+    const uint64_t mid = (l + h) >> 1;
+    if (offsets[mid] + delta < want) l = mid + 1; else h = mid;
+  }
+  tile_read[t] = l;
+}
+
+// four bytes at a time: 0xff per byte where the byte equals the constant
+__device__ __forceinline__ uint32_t eq4(uint32_t w, uint32_t c4) { return __vcmpeq4(w, c4); }
+// one flag bit per byte (bit 0 of every byte of m) -> bits 0,1,2,3 / bits 0,2,4,6 of the result
+__device__ __forceinline__ uint32_t mask4(uint32_t m) { return ((m & 0x01010101u) * 0x01020408u) >> 24; }
+__device__ __forceinline__ uint32_t spread4(uint32_t m) { return ((m & 0x01010101u) * 0x01041040u) >> 24; }
+
 // Consumer: what happens to a tile's k-mers.  store(): coalesced copy of the shared-memory tile to out_keys (the stand-alone API).
 template <int W>
 __global__ void __launch_bounds__(GEN_THREADS, 2) kmer_tiles_kernel(const GenArgs a) {
   using Scan = cub::BlockScan<uint32_t, GEN_THREADS>;
   __shared__ typename Scan::TempStorage scan_tmp;
-  __shared__ unsigned long long s_tile, s_base;
-  __shared__ uint32_t s_rfirst, s_firstbreak;
+  __shared__ unsigned long long s_base;
+  __shared__ uint32_t s_firstbreak;
   extern __shared__ __align__(16) unsigned char gen_smem[];
   uint64_t *otile = reinterpret_cast<uint64_t *>(gen_smem);
   uint32_t *pc = reinterpret_cast<uint32_t *>(otile + (size_t)GEN_SPAN * W);   // 2 bits per compact position
@@ -86,44 +108,59 @@ __global__ void __launch_bounds__(GEN_THREADS, 2) kmer_tiles_kernel(const GenArg
   const int topbits = 2 * k - 64 * (W - 1);
   const uint64_t topmask = topbits >= 64 ? ~0ULL : ((1ULL << topbits) - 1ULL);
 
-  for (;;) {
-    if (tid == 0) s_tile = atomicAdd(a.ticket, 1ULL);
+  // the 16 bytes of this thread in tile t; bytes outside [first, end) read as EOL
+  auto fetch = [&](uint64_t t) -> uint4 {
+    const int64_t g0 = (int64_t)(t * GEN_SPAN) - GEN_LOOKBACK + 16 * tid;
+    if (g0 >= (int64_t)a.first && (uint64_t)g0 + 16 <= a.end) return __ldg(reinterpret_cast<const uint4 *>(a.bases + g0));
+    unsigned char c[16];
+#pragma unroll
+    for (int i = 0; i < 16; ++i) {
+      const int64_t g = g0 + i;
+      c[i] = (g >= (int64_t)a.first && (uint64_t)g < a.end) ? __ldg(a.bases + g) : (unsigned char)'\n';
+    }
+    uint4 v;
+    memcpy(&v, c, 16);
+    return v;
+  };
+  uint4 vnext = make_uint4(0, 0, 0, 0);
+  if (blockIdx.x < a.n_tiles) vnext = fetch(blockIdx.x);
+
+  for (uint64_t tile = blockIdx.x; tile < a.n_tiles; tile += gridDim.x) {
     // bit arrays zero (the previous tile's readers are behind the barrier at the end of the loop body)
     for (int i = tid; i < GEN_BITS / 16 + 2 * (GEN_BITS / 32); i += GEN_THREADS) pc[i] = 0;
-    if (tid == 0) s_firstbreak = 0xffffffffu;
-    __syncthreads();
-    const uint64_t tile = s_tile;
-    if (tile >= a.n_tiles) break;
-    // byte positions (relative to the aligned origin) [lo, hi): lo may be "negative" for tile 0 -> clamp by a flag
+    if (tid == 0) { s_firstbreak = 0xffffffffu; s_base = a.tile_read[tile]; }
+    // byte positions (relative to the aligned origin) [lo, hi): lo is negative for tile 0
     const int64_t lo = (int64_t)(tile * GEN_SPAN) - GEN_LOOKBACK;
-    const int64_t g0 = lo + 16 * tid;                       // this thread's first byte
+    const uint4 v = vnext;
+    if (tile + gridDim.x < a.n_tiles) vnext = fetch(tile + gridDim.x);          // in flight while this tile is processed
 
-    // ---- 1. load + classify ---------------------------------------------------------------------------------------------
+    // ---- 1. classify: four bytes at a time --------------------------------------------------------------------------------
     uint32_t clean = 0, nmask = 0, codes = 0;
     {
-      unsigned char c[16];
-      if (g0 >= 0 && (uint64_t)g0 + 16 <= a.end) {
-        const uint4 v = __ldg(reinterpret_cast<const uint4 *>(a.bases + g0));
-        memcpy(c, &v, 16);
-      } else {
+      const uint32_t w[4] = {v.x, v.y, v.z, v.w};
+      uint32_t skip16 = 0;
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        const uint32_t u = w[q] & 0xDFDFDFDFu;                                  // case folded (only compared with letters)
+        const uint32_t eC = eq4(u, 0x43434343u), eG = eq4(u, 0x47474747u), eT = eq4(u, 0x54545454u), eN = eq4(u, 0x4E4E4E4Eu);
+        const uint32_t eol = eq4(w[q], 0x0A0A0A0Au) | eq4(w[q], 0x0D0D0D0Du);
+        skip16 |= mask4(eol) << (4 * q);
+        codes |= (spread4(eC | eT) | (spread4(eG | eT) << 1)) << (8 * q);       // DNA::FROM_ASCII: A 0, C 1, G 2, T 3, all else 0
+        nmask |= mask4(eN) << (4 * q);
+      }
+      clean = ~skip16 & 0xffffu;
+      if (skip16) {                                                             // squeeze the EOL positions out
+        uint32_t cc = 0, nn = 0;
+        int m = 0;
 #pragma unroll
         for (int i = 0; i < 16; ++i) {
-          const int64_t g = g0 + i;
-          c[i] = (g >= 0 && (uint64_t)g < a.end) ? __ldg(a.bases + g) : (unsigned char)'\n';
+          if ((clean >> i) & 1u) {
+            cc |= ((codes >> (2 * i)) & 3u) << (2 * m);
+            nn |= ((nmask >> i) & 1u) << m;
+            ++m;
+          }
         }
-      }
-      int m = 0;
-#pragma unroll
-      for (int i = 0; i < 16; ++i) {
-        const int64_t g = g0 + i;
-        const bool inside = g >= (int64_t)a.first && (uint64_t)g < a.end;       // bytes in front of the first read are not data
-        const bool skip = !inside || c[i] == '\n' || c[i] == '\r';
-        if (!skip) {
-          clean |= 1u << i;
-          codes |= dna_code(c[i]) << (2 * m);
-          nmask |= ((c[i] == 'N' || c[i] == 'n') ? 1u : 0u) << m;
-          ++m;
-        }
+        codes = cc; nmask = nn;
       }
     }
     const uint32_t nclean = __popc(clean);
@@ -142,16 +179,6 @@ __global__ void __launch_bounds__(GEN_THREADS, 2) kmer_tiles_kernel(const GenArg
         if (nv >> 32) atomicOr(&nb[(nbit >> 5) + 1], (uint32_t)(nv >> 32));
         atomicMin(&s_firstbreak, cb + (uint32_t)(__ffs(nmask) - 1));
       }
-    }
-    // first read whose start lies at or behind the tile's first byte (lower bound over offsets + delta)
-    if (tid == 0) {
-      uint64_t l = 0, h = a.n_reads + 1;                      // invariant: offsets[l-1] + delta < max(lo,0) <= offsets[h] + delta
-      const uint64_t want = lo > 0 ? (uint64_t)lo : 0ULL;
-      while (l < h) {
-        const uint64_t mid = (l + h) >> 1;
-        if (a.offsets[mid] + a.delta < want) l = mid + 1; else h = mid;
-      }
-      s_rfirst = (uint32_t)0; s_base = l;                     // s_base reused: index of that read
     }
     __syncthreads();
 
@@ -189,12 +216,17 @@ __global__ void __launch_bounds__(GEN_THREADS, 2) kmer_tiles_kernel(const GenArg
       len0 = min(min(back_n, back_s), j0);                                                 // never longer than what the tile holds
       nrun = (uint32_t)bits64(nb, j0 + GEN_PAD) & 0xffffu;
       srun = (uint32_t)bits64(sb, j0 + GEN_PAD) & 0xffffu;
-      uint32_t len = len0;
+      const uint32_t left = min((uint32_t)GEN_RUN, ctotal - j0);
+      if ((nrun | srun) == 0 && len0 + 1u >= (uint32_t)k) {
+        vmask = 0xffffu >> (GEN_RUN - left);                  // the common case: nothing breaks the run
+      } else {
+        uint32_t len = len0;
 #pragma unroll
-      for (int i = 0; i < GEN_RUN; ++i) {
-        const bool isn = (nrun >> i) & 1u, st = (srun >> i) & 1u;
-        len = isn ? 0u : (st ? 1u : len + 1u);
-        if (len >= (uint32_t)k && j0 + i < ctotal) vmask |= 1u << i;
+        for (int i = 0; i < GEN_RUN; ++i) {
+          const bool isn = (nrun >> i) & 1u, st = (srun >> i) & 1u;
+          len = isn ? 0u : (st ? 1u : len + 1u);
+          if (len >= (uint32_t)k && i < (int)left) vmask |= 1u << i;
+        }
       }
     }
     uint32_t obase, ototal;

@@ -1,6 +1,7 @@
 // kh_table_host.h -- the table object and the internal entry points shared by table.cu and exchange.cu
 #pragma once
 #include <algorithm>
+#include <functional>
 #include <utility>
 #include <vector>
 #include "kh_common.h"
@@ -58,9 +59,26 @@ struct kh_table {
 
 
 namespace kh {
+// state of one bulk-insert batch (table.cu): begin -> feed (once, or chunk by chunk as the keys arrive over PCIe or NVLink) -> finish
+struct BulkBatch {
+  uint64_t n = 0, fed = 0, slab = 0, ovf_cap = 0;
+  int lp = 0;
+  DevBuf<unsigned long long> cursors, ovf_count;
+  DevBuf<uint4> recs;
+  DevBuf<uint64_t> ovf;
+  DevBuf<uint32_t> regs;
+  // the whole batch again as ONE array, for the rare case that the general route has to take over (table that does not suit the
+  // tiles, skewed batch); unset: the caller's key pointer / pieces are used
+  std::function<const uint64_t *(DevBuf<uint64_t> &, cudaStream_t)> refetch;
+};
+struct BkSegs;
+// the bulk insert in pieces (pipelined multi-GPU receiver): n_upper / m_upper bound the keys, dsegs = DEVICE-resident pieces
+void bulk_pipe_begin(BulkBatch &b, kh_table *t, uint64_t n_upper, cudaStream_t s);
+void bulk_pipe_feed(BulkBatch &b, kh_table *t, const uint64_t *d_base, uint64_t m_upper, const BkSegs *dsegs, cudaStream_t s);
+int64_t bulk_pipe_finish(BulkBatch &b, kh_table *t, uint64_t n_recv, uint32_t dflt, cudaStream_t s);
+bool bulk_pipe_candidate(const kh_table *t, uint64_t n);
 // what a caller's pipeline already knows about a batch: its HyperLogLog registers (HLL_M bytes on the HOST, may be null:
 // accumulated behind the PCIe copy) and/or the pieces it lies in (kh_bulk.cuh: BkSegs; the slabs of a peer receive buffer)
-struct BkSegs;
 struct PreEstimate { const uint8_t *regs; const BkSegs *segs; };
 // batch insert of device-resident keys (see table.cu); returns #new keys or a negative status
 int64_t insert_dev_impl(kh_table *t, const uint64_t *d_keys, const uint32_t *d_vals, uint64_t n, uint32_t dflt,

@@ -19,6 +19,7 @@
 #include "kh_common.h"
 #include "kh_kmer.cuh"
 #include "kh_table.cuh"
+#include "kh_kmergen.cuh"
 
 namespace kh {
 
@@ -138,10 +139,10 @@ __global__ void canonicalize_kernel(const uint64_t *in, uint64_t n, int k, int m
   }
 }
 
-int64_t kmers_from_reads_dev(int device, const char *d_bases, const uint64_t *d_offsets, uint64_t n_reads, int k,
-                             int canonical, uint64_t *d_out_keys, uint64_t out_cap) {
-  if (k < 1 || k > 64) { set_error("k must be in [1,64]"); return KH_ERR_INVALID; }
-  if (n_reads == 0) return 0;
+// the warp-per-read kernel: count per read -> exclusive scan -> emit.  No bound on EOL characters inside a window; the
+// fallback of the tile kernel and the reference point of its tests (KH_KMERGEN=0).
+int64_t kmers_from_reads_warp(int device, const char *d_bases, const uint64_t *d_offsets, uint64_t n_reads, int k,
+                              int canonical, uint64_t *d_out_keys, uint64_t out_cap) {
   const int W = kmer_words(k);
   const int sms = sm_count(device);
   const int grid = (int)std::max<uint64_t>(1, std::min<uint64_t>((n_reads + 7) / 8, (uint64_t)sms * 8));
@@ -163,6 +164,53 @@ int64_t kmers_from_reads_dev(int device, const char *d_bases, const uint64_t *d_
     KH_CUDA(cudaStreamSynchronize(0));
   }
   return (int64_t)total;
+}
+
+// the streaming tile kernel (kh_kmergen.cuh): one pass, output order kept by a decoupled look-back
+int64_t kmers_from_reads_dev(int device, const char *d_bases, const uint64_t *d_offsets, uint64_t n_reads, int k,
+                             int canonical, uint64_t *d_out_keys, uint64_t out_cap) {
+  if (k < 1 || k > 64) { set_error("k must be in [1,64]"); return KH_ERR_INVALID; }
+  if (n_reads == 0) return 0;
+  static const bool tiles_on = !(getenv("KH_KMERGEN") && atoi(getenv("KH_KMERGEN")) == 0);
+  if (!tiles_on) return kmers_from_reads_warp(device, d_bases, d_offsets, n_reads, k, canonical, d_out_keys, out_cap);
+  const int W = kmer_words(k);
+  uint64_t h_off[2] = {0, 0};
+  KH_CUDA(cudaMemcpy(&h_off[0], d_offsets, sizeof(uint64_t), cudaMemcpyDeviceToHost));
+  KH_CUDA(cudaMemcpy(&h_off[1], d_offsets + n_reads, sizeof(uint64_t), cudaMemcpyDeviceToHost));
+  if (h_off[1] <= h_off[0]) return 0;
+  GenArgs a;
+  a.delta = (uint64_t)(reinterpret_cast<uintptr_t>(d_bases) & 15u);
+  a.bases = reinterpret_cast<const unsigned char *>(d_bases) - a.delta;
+  a.offsets = d_offsets; a.n_reads = n_reads;
+  a.first = h_off[0] + a.delta; a.end = h_off[1] + a.delta;
+  a.k = k; a.canonical = canonical;
+  a.n_tiles = (a.end + GEN_SPAN - 1) / GEN_SPAN;
+  a.out_keys = (d_out_keys && out_cap) ? d_out_keys : nullptr; a.out_cap = out_cap;
+  DevBuf<unsigned long long> state(a.n_tiles);
+  DevBuf<uint64_t> tile_read(a.n_tiles);
+  DevBuf<int> flag(1);
+  KH_CUDA(cudaMemsetAsync(state.p, 0, a.n_tiles * sizeof(unsigned long long), 0));
+  KH_CUDA(cudaMemsetAsync(flag.p, 0, sizeof(int), 0));
+  KH_LAUNCH(gen_tile_reads_kernel, (int)((a.n_tiles + 255) / 256), 256, 0, 0, d_offsets, n_reads, a.delta, a.n_tiles, tile_read.p);
+  a.state = state.p; a.tile_read = tile_read.p; a.fallback = flag.p;
+  const int sms = sm_count(device);
+  const size_t smem = W == 1 ? gen_smem_bytes<1>() : gen_smem_bytes<2>();
+  const int per_sm = std::max<int>(1, std::min<int>(2, (int)((227 * 1024) / (smem + 1024))));
+  const int grid = (int)std::min<uint64_t>(a.n_tiles, (uint64_t)sms * per_sm);
+  if (W == 1) {
+    KH_CUDA(cudaFuncSetAttribute(kmer_tiles_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    KH_LAUNCH(kmer_tiles_kernel<1>, grid, GEN_THREADS, smem, 0, a);
+  } else {
+    KH_CUDA(cudaFuncSetAttribute(kmer_tiles_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    KH_LAUNCH(kmer_tiles_kernel<2>, grid, GEN_THREADS, smem, 0, a);
+  }
+  unsigned long long last = 0;
+  int h_flag = 0;
+  KH_CUDA(cudaMemcpyAsync(&last, state.p + a.n_tiles - 1, sizeof(last), cudaMemcpyDeviceToHost, 0));
+  KH_CUDA(cudaMemcpyAsync(&h_flag, flag.p, sizeof(int), cudaMemcpyDeviceToHost, 0));
+  KH_CUDA(cudaStreamSynchronize(0));
+  if (h_flag) return kmers_from_reads_warp(device, d_bases, d_offsets, n_reads, k, canonical, d_out_keys, out_cap);   // EOL-dense input
+  return (int64_t)(last & ~GEN_ST_MASK);
 }
 
 }  // namespace kh

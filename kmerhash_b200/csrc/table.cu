@@ -517,16 +517,6 @@ bool bulk_candidate(const kh_table *t, const uint32_t *d_vals, uint64_t n) {
          n >= t->window_min_keys && n >= 1024 && n <= BULK_MAX_KEYS;
 }
 
-// state of one batch: begin -> feed (once, or chunk by chunk as the keys arrive over PCIe or NVLink) -> finish
-struct BulkBatch {
-  uint64_t n = 0, fed = 0, slab = 0, ovf_cap = 0;
-  int lp = 0;
-  DevBuf<unsigned long long> cursors, ovf_count;
-  DevBuf<uint4> recs;
-  DevBuf<uint64_t> ovf;
-  DevBuf<uint32_t> regs;
-};
-
 // level-1 regions: as many as the LARGEST table this batch can lead to has tiles (then region == tile or finer and no
 // level 2 is needed), at most 4096, at least 64
 int bulk_region_bits(const kh_table *t, uint64_t n) {
@@ -552,7 +542,10 @@ void bulk_begin(BulkBatch &b, kh_table *t, uint64_t n, cudaStream_t s) {
 }
 
 // m keys at d_keys (or in the pieces of `segs`) -> level 1.  Asynchronous on s.
-void bulk_feed(BulkBatch &b, kh_table *t, const uint64_t *d_keys, uint64_t m, cudaStream_t s, const BkSegs *segs = nullptr) {
+// dsegs != nullptr: the pieces lie in a DEVICE-resident table (written by a kernel earlier on s); m is then only an upper
+// bound, the grid is fixed and b.fed is set by the caller once the counts are known
+void bulk_feed(BulkBatch &b, kh_table *t, const uint64_t *d_keys, uint64_t m, cudaStream_t s, const BkSegs *segs = nullptr,
+               const BkSegs *dsegs = nullptr) {
   if (!m) return;
   L1Args a;
   a.keys = d_keys; a.n = m; a.lp = b.lp; a.hash_kind = t->hash_kind; a.h32 = hash_bits(t->hash_kind) == 32 ? 1 : 0; a.hp = t->hp;
@@ -571,17 +564,17 @@ void bulk_feed(BulkBatch &b, kh_table *t, const uint64_t *d_keys, uint64_t m, cu
     a.keys = d_keys + segs->base[0] * t->W;
   }
   if (!n_tiles) return;
-  const int grid = (int)std::min<uint64_t>(n_tiles, (uint64_t)t->sms);
+  const int grid = dsegs ? t->sms : (int)std::min<uint64_t>(n_tiles, (uint64_t)t->sms);
   kev_begin(t, 2, s);
   if (t->W == 1) {
     KH_CUDA(cudaFuncSetAttribute(l1_scatter_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)L1Cfg<1>::SMEM));   // per device
-    KH_LAUNCH(l1_scatter_kernel<1>, grid, L1_THREADS, L1Cfg<1>::SMEM, s, a, sg);
+    KH_LAUNCH(l1_scatter_kernel<1>, grid, L1_THREADS, L1Cfg<1>::SMEM, s, a, sg, dsegs);
   } else {
     KH_CUDA(cudaFuncSetAttribute(l1_scatter_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)L1Cfg<2>::SMEM));
-    KH_LAUNCH(l1_scatter_kernel<2>, grid, L1_THREADS, L1Cfg<2>::SMEM, s, a, sg);
+    KH_LAUNCH(l1_scatter_kernel<2>, grid, L1_THREADS, L1Cfg<2>::SMEM, s, a, sg, dsegs);
   }
   kev_end(t, s);
-  b.fed += m;
+  if (!dsegs) b.fed += m;
 }
 
 // a batch handed over in pieces -> one contiguous array, for the paths whose kernels want one
@@ -644,7 +637,7 @@ int64_t bulk_finish(BulkBatch &b, kh_table *t, const uint64_t *d_keys, const BkS
   if (!suits) {
     b.recs.release(); b.ovf.release();
     DevBuf<uint64_t> flat;
-    const uint64_t *keys = flatten_segments(t, d_keys, n, segs, flat, s);
+    const uint64_t *keys = b.refetch ? b.refetch(flat, s) : flatten_segments(t, d_keys, n, segs, flat, s);
     insert_general(t, keys, nullptr, n, dflt, estimate != 0, s);
     KH_CUDA(cudaStreamSynchronize(s));
     return (int64_t)(t->size - size0);
@@ -733,6 +726,23 @@ int64_t insert_bulk(kh_table *t, const uint64_t *d_keys, uint64_t n, uint32_t df
 }
 
 }  // namespace
+
+// ---- the bulk insert in pieces, for the pipelined multi-GPU receiver (exchange.cu) -------------------------------------------
+void kh::bulk_pipe_begin(BulkBatch &b, kh_table *t, uint64_t n_upper, cudaStream_t s) { bulk_begin(b, t, n_upper, s); }
+void kh::bulk_pipe_feed(BulkBatch &b, kh_table *t, const uint64_t *d_base, uint64_t m_upper, const BkSegs *dsegs, cudaStream_t s) {
+  bulk_feed(b, t, d_base, m_upper, s, nullptr, dsegs);
+}
+int64_t kh::bulk_pipe_finish(BulkBatch &b, kh_table *t, uint64_t n_recv, uint32_t dflt, cudaStream_t s) {
+  struct Materialize {                  // whatever happens: never leave uninitialised slots behind
+    kh_table *t; cudaStream_t s;
+    ~Materialize() { if (t->uninit) { try { materialize(t, s); cudaStreamSynchronize(s); } catch (...) {} } }
+  } guard{t, s};
+  b.n = b.fed = n_recv;
+  const int64_t got = bulk_finish(b, t, nullptr, nullptr, dflt, 1, s);
+  while ((double)t->size > t->max_load * (double)t->capacity) rebuild(t, t->capacity * 2);
+  return got;
+}
+bool kh::bulk_pipe_candidate(const kh_table *t, uint64_t n) { return bulk_candidate(t, nullptr, n); }
 
 // ---------------------------------------------------------------------------------------
 // C ABI

@@ -50,13 +50,14 @@ def kmers_from_reads_dev(bases, offsets, k, canonical=False):
     n_reads = offsets.shape[0] - 1
     W = kmer_words(k)
     torch.cuda.current_stream(dev).synchronize()
-    total = check(lib.kh_kmers_from_reads_dev(dev, bases.data_ptr(), offsets.data_ptr(), n_reads, k, int(canonical), None, 0),
-                  "kmers_from_reads(count)")
-    out = torch.empty((total, W) if W > 1 else (total,), dtype=torch.int64, device=bases.device)
-    if total:
-        check(lib.kh_kmers_from_reads_dev(dev, bases.data_ptr(), offsets.data_ptr(), n_reads, k, int(canonical),
-                                          out.data_ptr(), total), "kmers_from_reads")
-    return out
+    # one pass: every k-mer ends at its own byte, so the byte count bounds the output; the tile kernel keeps the order
+    cap = int(bases.shape[0])
+    out = torch.empty((cap, W) if W > 1 else (cap,), dtype=torch.int64, device=bases.device)
+    total = 0
+    if cap and n_reads:
+        total = check(lib.kh_kmers_from_reads_dev(dev, bases.data_ptr(), offsets.data_ptr(), n_reads, k, int(canonical),
+                                                  out.data_ptr(), cap), "kmers_from_reads")
+    return out[:total]
 
 
 def canonicalize(kmers, k, device=0):

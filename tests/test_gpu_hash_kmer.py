@@ -74,6 +74,46 @@ def test_kmers_from_reads_other_bytes_map_to_A(kh, oracle_mod):
         assert np.array_equal(kh.kmers_from_reads(read, offs, k), oracle_mod.port.kmers_from_reads(read, offs, k, False))
 
 
+@pytest.mark.parametrize("k,canonical", [(31, True), (21, False), (32, True), (33, True), (63, True), (64, False), (1, False)])
+def test_kmers_tile_kernel_large_inputs(kh, oracle_mod, k, canonical):
+    """the streaming tile kernel (kh_kmergen.cuh) over inputs of many tiles: reads straddling tile borders, N runs, EOL
+    characters, empty reads, a base pointer that is not 16-byte aligned and offsets that do not start at 0; device and
+    host entry points; output identical to the oracle's, in the reference's order"""
+    import torch
+    rng = np.random.default_rng(1000 + k)
+    cases = [make_reads(rng, 3000, 100, 151),                               # Illumina-like, 450 KB
+             make_reads(rng, 400, 0, 2500, n_rate=0.003, eol=True, lower=True),
+             make_reads(rng, 2, 150000, 200000, n_rate=0.0005, eol=True),   # chromosomes: one read over many tiles
+             make_reads(rng, 20000, 0, 40)]                                 # many reads per tile, lots of them shorter than k
+    for bases, offs in cases:
+        exp = oracle_mod.port.kmers_from_reads(bases, offs, k, canonical)
+        got = kh.kmers_from_reads(bases, offs, k, canonical)
+        assert got.shape == exp.shape and np.array_equal(got, exp), k
+        # device entry: junk in front (misaligned start), offsets[0] = shift
+        for shift in (3, 16, 37):
+            pad = rng.integers(65, 85, size=shift).astype(np.uint8)
+            db = torch.from_numpy(np.concatenate([pad, bases])).cuda()
+            do = torch.from_numpy((offs + np.uint64(shift)).astype(np.int64)).cuda()
+            out = kh.kmers_from_reads_dev(db, do, k, canonical).cpu().numpy().view(np.uint64)
+            assert out.shape == exp.shape and np.array_equal(out, exp), (k, shift)
+            out2 = kh.kmers_from_reads_dev(db[shift:], torch.from_numpy(offs.astype(np.int64)).cuda(), k, canonical).cpu().numpy().view(np.uint64)
+            assert np.array_equal(out2, exp), (k, shift)
+
+
+def test_kmers_tile_kernel_eol_dense_falls_back(kh, oracle_mod):
+    """more EOL characters inside a window than the tile kernel's context holds: the call must still be exact (it repeats
+    through the warp-per-read kernel)"""
+    rng = np.random.default_rng(5)
+    seq = np.frombuffer(b"ACGT", dtype=np.uint8)[rng.integers(0, 4, size=30000)]
+    dense = np.empty(4 * len(seq), dtype=np.uint8)
+    dense[0::4] = seq; dense[1::4] = 10; dense[2::4] = 13; dense[3::4] = 10   # every base followed by "\n\r\n"
+    offs = np.array([0, len(dense) // 2, len(dense)], dtype=np.uint64)
+    for k in (31, 63):
+        exp = oracle_mod.port.kmers_from_reads(dense, offs, k, True)
+        assert len(exp) > 0
+        assert np.array_equal(kh.kmers_from_reads(dense, offs, k, True), exp)
+
+
 def test_kmers_no_reads(kh):
     out = kh.kmers_from_reads(b"", np.array([0], dtype=np.uint64), 31)
     assert out.shape == (0,)
