@@ -549,15 +549,19 @@ def ours_single(args):
     print(json.dumps(line), flush=True)
 
 
-def multi_parity_check(dm, rank, world, dev):
-    """before anything is timed: a 2 M-key batch per rank through insert / find / count / erase of the distributed map;
+def multi_parity_check(args, rank, world, dev):
+    """before anything is timed: a 6 M-key batch per rank (large enough for the pipelined exchange and the bulk insert) through
+    insert / find / count / erase of a distributed map of its own;
     every rank's table contents must equal {(k, c) of the global count map : owner(k) == rank}, answers must come back in
     input order.  Expected values from numpy (exact counts) and the owner rule restated above.  Raises on mismatch."""
     import torch
     import torch.distributed as dist
-    nb = 2_000_000
+    from kmerhash_b200.distributed import DistributedMap
+    dm = DistributedMap(1, args.hash, args.hash, "COUNT", canonical_k=0, device=dev.index)
+    dm.e.table.set_load_factors(0.35, 0.8)
+    nb = 6_000_000
     rng = np.random.default_rng(777)                      # the SAME global pool on every rank
-    pool = rng.integers(0, 1 << 62, size=1_500_000, dtype=np.uint64)
+    pool = rng.integers(0, 1 << 62, size=4_000_000, dtype=np.uint64)
     mine = pool[np.random.default_rng(1000 + rank).integers(0, len(pool), size=nb)]
     batches = [pool[np.random.default_rng(1000 + r).integers(0, len(pool), size=nb)] for r in range(world)]
     allk = np.concatenate(batches)
@@ -565,7 +569,6 @@ def multi_parity_check(dm, rank, world, dev):
     owner = (np_murmur3_x86_128_lo64(uk, DIST_SEED) & np.uint64(world - 1)).astype(np.int64) if (world & (world - 1)) == 0 else \
         (np_murmur3_x86_128_lo64(uk, DIST_SEED) % np.uint64(world)).astype(np.int64)
     d = torch.from_numpy(mine.view(np.int64)).to(dev)
-    dm.e.table.clear(); dm.e.table.rehash(128)
     dm.insert(d)
     dist.barrier()
     gk, gv = dm.to_vector()
@@ -591,7 +594,7 @@ def multi_parity_check(dm, rank, world, dev):
     dist.all_reduce(flag, op=dist.ReduceOp.MIN)
     if int(flag.item()) != 1:
         raise SystemExit("bench.py: distributed parity check FAILED on rank %d (ok=%s)" % (rank, ok))
-    dm.e.table.clear(); dm.e.table.rehash(128)
+    dm.close()
     return {"keys_per_rank": nb, "distinct_global": int(len(uk)), "checked": "per-rank sorted (key,count) == numpy count map restricted "
             "to owner(k) == rank (murmur3 x86_128 seed 9876543 restated in numpy); find/count in input order; erase; count after erase"}
 
@@ -619,7 +622,7 @@ def ours_multi(args):
     d_q = d_keys[:nq].contiguous()
     dm = DistributedMap(1, args.hash, args.hash, "COUNT", canonical_k=0, device=local)
     dm.e.table.set_load_factors(0.35, 0.8)
-    parity = None if args.no_parity else multi_parity_check(dm, rank, world, dev)
+    parity = None if args.no_parity else multi_parity_check(args, rank, world, dev)
 
     f_host = torch.empty(nq, dtype=torch.int32).pin_memory()
 
@@ -629,14 +632,21 @@ def ours_multi(args):
     def reset():
         dm.e.table.clear(); dm.e.table.rehash(128)
 
+    import kmerhash_b200.distributed as kd
+    stage_log = []                                                    # host-side stage times of every find step on rank 0
+
     def step(k_in, q_in, to_host):
         reset(); barrier()
         e0 = torch.cuda.Event(enable_timing=True); e1 = torch.cuda.Event(enable_timing=True); e2 = torch.cuda.Event(enable_timing=True)
         e0.record(); dm.insert(k_in); xb = dm.last_exchange_bytes
-        barrier(); e1.record(); f = dm.find(q_in, 0)
+        barrier(); e1.record()
+        kd.STAGE_LOG = []
+        t0 = time.perf_counter(); f = dm.find(q_in, 0); t1 = time.perf_counter()
         if to_host:
             f_host.copy_(f); f = f_host                               # D2H into pinned memory (a fresh pageable tensor costs ~10 ms of page faults)
-        barrier(); e2.record(); torch.cuda.synchronize()
+        barrier(); t2 = time.perf_counter(); e2.record(); torch.cuda.synchronize()
+        stage_log.append(dict(kd.STAGE_LOG, find_call=round(1e3 * (t1 - t0), 3), barrier_after=round(1e3 * (t2 - t1), 3)))
+        kd.STAGE_LOG = None
         return e0.elapsed_time(e1), e1.elapsed_time(e2), f, xb
 
     step_log = []                                                     # rank 0's per-step times (device and e2e runs)
@@ -654,7 +664,8 @@ def ours_multi(args):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)                      # max over ranks
         assert int((f != 0).sum()) == nq                              # every query key is present
         gc.enable()
-        step_log.append({"insert_ms": [round(x, 3) for x in ti], "find_ms": [round(x, 3) for x in tf]})
+        step_log.append({"insert_ms": [round(x, 3) for x in ti], "find_ms": [round(x, 3) for x in tf],
+                         "find_stages_host_ms": stage_log[-args.steps:]})
         return t.tolist(), xb
 
     sampler = ClockSampler(local)
@@ -686,6 +697,7 @@ def ours_multi(args):
                                    "hash-partitioned (murmur3 x86_128, seed 9876543) over %d GPUs, exchange by peer stores over NVLink (NCCL as fallback), "
                                    "count map insert, then %d finds per GPU with reply" % (n, world, nq),
                        "n_keys_per_gpu": n, "n_query_per_gpu": nq, "hash": args.hash, "config": args.config,
+                       "exchange_pieces": dm.pipe_chunks,
                        "input": ("generate_input of the reference with srand(23 + rank)" if args.config == "1" else "torch generator on the device, seed 1000 + rank, every distinct key 1..8 times"),
                        "l2": "inputs larger than L2; tables rebuilt from capacity 128 every step"},
             "finds_per_s": world * nq / (tf * 1e-3), "finds_per_s_median": world * nq / (tf_med * 1e-3),

@@ -305,6 +305,16 @@ int khx_push_meta_sync_dev(kh_table *t, khx_peer *x, int parity, const uint64_t 
  * computes the HyperLogLog registers the reference ships with the counts, KH/distributed_batched_robinhood_map.hpp:1024-1060). */
 int khx_scatter_slabs_dev(kh_table *t, int dist_hash, uint32_t dist_seed, const uint64_t *d_keys, uint64_t n, khx_peer *x,
                           uint64_t slab_cap, int parity, uint64_t *d_counts, int reset_counts);
+/* The exchange overlapped with the local insertion (the reference's ialltoallv_and_modify, KH/incremental_mxx.hpp:3437-3645):
+ * the batch goes in `chunks` pieces; per piece a sender kernel, a flag barrier and -- on a second stream, launched before
+ * the host knows any count -- the level-1 pass of the bulk insert over the p sub-slabs that piece filled, so that the
+ * receiver works on piece c while the senders store piece c + 1.  slab_cap must be a multiple of 2 * chunks.  Consumes the
+ * epochs epoch0 .. epoch0 + chunks - 1.  counts_matrix (HOST, p x p) = keys sender g had for owner r.  *overflowed = 1: a
+ * sub-slab was too small (the same verdict on every rank); the table is untouched, repeat the batch on the exact path.
+ * COUNT tables on the bulk route only (khx_insert_recv_slabs_dev serves the rest).  Returns the number of new keys. */
+int64_t khx_insert_pipelined_dev(kh_table *t, khx_peer *x, int dist_hash, uint32_t dist_seed, const uint64_t *d_keys, uint64_t n,
+                                 uint64_t slab_cap, int parity, int chunks, uint64_t epoch0, uint32_t default_val,
+                                 uint64_t *counts_matrix, int *overflowed);
 /* Teardown of IPC-mapped buffers is collective: every rank khx_peer_close_imports -> a barrier of the caller's -> every
  * rank khx_peer_destroy (which frees the exported allocation).  khx_peer_poisoned: a barrier on these buffers timed out
  * (on this rank or, seen through the poison flag, on a peer); every later khx_peer_sync_dev fails until they are recreated. */

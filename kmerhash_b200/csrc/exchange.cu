@@ -311,6 +311,36 @@ __global__ void unpermute_slabs_kernel(const T *reply, const uint32_t *perm, con
   }
 }
 
+// Behind the flag barrier of chunk c: the counts of that chunk, as they stand in the LOCAL header, become (a) the pieces
+// of the receiver's level-1 launch -- piece g = sender g's sub-slab of this chunk, clamped to its capacity -- and (b) a
+// private copy of the whole p x p matrix (the header slot is overwritten two barriers later).  One thread.
+__global__ void make_segs_kernel(const PeerHeader *hdr, int slot, uint32_t p, uint32_t rank, unsigned long long sub_cap,
+                                 unsigned long long first_key, unsigned long long slab_cap, unsigned long long tile,
+                                 BkSegs *out, unsigned long long *matrix, int *overflow) {
+  if (threadIdx.x != 0 || blockIdx.x != 0) return;
+  unsigned long long acc = 0, tiles = 0;
+  out->nseg = (int)p;
+  for (uint32_t g = 0; g < p; ++g) {
+    unsigned long long c = hdr->counts[slot][g][rank];
+    if (c > sub_cap) c = sub_cap;
+    out->prefix[g] = acc;
+    out->base[g] = first_key + (unsigned long long)g * slab_cap;
+    out->tprefix[g] = tiles;
+    acc += c;
+    tiles += (c + tile - 1) / tile;
+  }
+  out->prefix[p] = acc;
+  out->tprefix[p] = tiles;
+  bool over = false;
+  for (uint32_t g = 0; g < p; ++g)
+    for (uint32_t r = 0; r < p; ++r) {
+      const unsigned long long c = hdr->counts[slot][g][r];
+      matrix[g * p + r] = c;
+      over = over || c > sub_cap;
+    }
+  if (over) *overflow = 1;
+}
+
 }  // namespace kh
 
 using namespace kh;
@@ -817,6 +847,123 @@ int64_t khx_insert_recv_dev(kh_table *t, const uint64_t *d_keys, uint64_t n, con
     if (h_total != n) { set_error("received %llu keys but the metadata announces %llu", (unsigned long long)n, h_total); return KH_ERR_INVALID; }
     PreEstimate pre{batch_regs, nullptr};
     return insert_dev_impl(t, d_keys, nullptr, n, default_val, 1, &pre);
+  });
+}
+
+// ---- pipelined distributed insert: the exchange overlapped with the local insertion -----------------------------------------
+// The reference's ialltoallv_and_modify (KH/incremental_mxx.hpp:3437-3645) posts the transfers of all pieces and runs the
+// local insert on every piece as it lands.  Here the batch is cut into `chunks` pieces; for piece c, on the send stream:
+//   sender kernel (dist hash -> owner -> peer stores into sub-slab c of this rank's slab)  ->  flag barrier kernel, which
+//   also delivers the p x p counts of the piece  ->  make_segs_kernel (pieces of the receive side, device resident);
+// and on the receive stream, behind an event: the level-1 kernel of the bulk insert over the p sub-slabs of piece c --
+// launched with a fixed grid before the host knows any count.  Nothing synchronises with the host until the last piece,
+// so the level-1 pass of piece c runs WHILE the senders of piece c+1 store (the sender takes one CTA per SM, the
+// level-1 kernel the other).  Then: estimate -> reserve -> tile insert as for any bulk batch.
+// counts_matrix (HOST, p x p): keys sender g had for owner r, summed over the pieces.  *overflowed = 1: a sub-slab was too
+// small -- the same verdict on every rank, the table is untouched and the caller repeats the batch on the exact path.
+// Epochs epoch0 .. epoch0 + chunks - 1 are consumed.  Returns the number of new keys.
+int64_t khx_insert_pipelined_dev(kh_table *t, khx_peer *x, int dist_hash, uint32_t dist_seed, const uint64_t *d_keys, uint64_t n,
+                                 uint64_t slab_cap, int parity, int chunks, uint64_t epoch0, uint32_t default_val,
+                                 uint64_t *counts_matrix, int *overflowed) {
+  return guarded([&]() -> int64_t {
+    if (!t || !x || !counts_matrix || !overflowed || (n && !d_keys) || epoch0 == 0) { set_error("null argument"); return KH_ERR_INVALID; }
+    const uint32_t p = x->p;
+    const int W = t->W;
+    if (!hash_kind_supported(dist_hash) || n >= (1ULL << 32) || x->W != W || parity < 0 || parity > 1 || chunks < 1 || chunks > 16 ||
+        slab_cap % (2ULL * chunks) != 0 || 2ULL * p * slab_cap > x->capacity || p > (uint32_t)BK_MAX_SEG) {
+      set_error("khx_insert_pipelined_dev: bad arguments (slab_cap must be a multiple of 2 * chunks, 2 * p * slab_cap keys must fit)");
+      return KH_ERR_INVALID;
+    }
+    if (x->poisoned) { set_error("khx_insert_pipelined_dev: an earlier barrier on these buffers timed out; recreate them"); return KH_ERR_CUDA; }
+    if (!bulk_pipe_candidate(t, (uint64_t)p * slab_cap)) { set_error("khx_insert_pipelined_dev: the table does not take the bulk route"); return KH_ERR_INVALID; }
+    DeviceGuard g(t->device);
+    cudaStream_t S = t->stream[0], R = t->stream[1];
+    const uint64_t sub_cap = slab_cap / chunks;
+    const int dk = fold_kind(dist_hash);
+    const BinSpec dist{1, 0, p, dk, make_hash_params(dk, dist_seed, W)};
+    const size_t body = x->capacity * (size_t)(8 * x->W + x->reply_bytes);
+    PeerHeaders hd{};
+    for (uint32_t r = 0; r < p; ++r) {
+      if (!x->remote[r]) { set_error("peer %u not mapped", r); return KH_ERR_INVALID; }
+      hd.h[r] = reinterpret_cast<PeerHeader *>(reinterpret_cast<unsigned char *>(x->remote[r]) + body);
+    }
+    static const unsigned long long timeout_ns = [] {
+      const char *e = getenv("KH_PEER_TIMEOUT_MS");
+      return (e && atoll(e) > 0) ? (unsigned long long)atoll(e) * 1000000ULL : 10000000000ULL;
+    }();
+    DevBuf<unsigned long long> d_counts((size_t)chunks * p), d_matrix((size_t)chunks * p * p);
+    DevBuf<BkSegs> d_segs(chunks);
+    DevBuf<int> d_flags(2);                                   // [0] barrier time-out, [1] sub-slab overflow
+    KH_CUDA(cudaMemsetAsync(d_counts.p, 0, (size_t)chunks * p * sizeof(unsigned long long), S));
+    KH_CUDA(cudaMemsetAsync(d_flags.p, 0, 2 * sizeof(int), S));
+    std::vector<cudaEvent_t> ev(chunks, nullptr);
+    struct EvGuard { std::vector<cudaEvent_t> &e; ~EvGuard() { for (auto v : e) if (v) cudaEventDestroy(v); } } evg{ev};
+    for (auto &e : ev) KH_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+
+    BulkBatch b;
+    bulk_pipe_begin(b, t, (uint64_t)p * slab_cap, R);
+    const uint64_t tile_send = PS_TILE_BYTES / (8 * W);
+    const uint64_t tile_l1 = W == 1 ? L1Cfg<1>::TILE : L1Cfg<2>::TILE;
+    const size_t smem = W == 1 ? ps_smem_bytes<1>(p, false, false) : ps_smem_bytes<2>(p, false, false);
+    for (int c = 0; c < chunks; ++c) {
+      const uint64_t k0 = n * (uint64_t)c / chunks, k1 = n * (uint64_t)(c + 1) / chunks, m = k1 - k0;
+      unsigned long long *cursors = d_counts.p + (size_t)c * p;
+      if (m) {
+        BinDst dst{};
+        for (uint32_t r = 0; r < p; ++r) dst.base[r] = x->remote[r] + (((uint64_t)parity * p + x->rank) * slab_cap + (uint64_t)c * sub_cap) * W;
+        // one CTA per SM: the level-1 kernel of the previous piece holds the rest of the SM
+        const int grid = (int)std::max<uint64_t>(1, std::min<uint64_t>((m + tile_send - 1) / tile_send, (uint64_t)t->sms * (c == 0 ? 3 : 1)));
+        if (W == 1) KH_LAUNCH((scatter_slabs_kernel<1, false, false>), grid, PS_BLOCK, smem, S, d_keys + k0 * W, m, dist, t->hash_kind, t->hp, dst,
+                              (unsigned long long)sub_cap, cursors, (unsigned long long *)nullptr, (uint32_t *)nullptr);
+        else KH_LAUNCH((scatter_slabs_kernel<2, false, false>), grid, PS_BLOCK, smem, S, d_keys + k0 * W, m, dist, t->hash_kind, t->hp, dst,
+                       (unsigned long long)sub_cap, cursors, (unsigned long long *)nullptr, (uint32_t *)nullptr);
+      }
+      const int slot = (int)(x->count_syncs & 1);
+      ++x->count_syncs;
+      KH_LAUNCH(peer_sync_kernel, 1, 32, 0, S, hd, x->rank, p, (unsigned long long)(epoch0 + c), cursors, 1, slot, d_flags.p, timeout_ns);
+      KH_LAUNCH(make_segs_kernel, 1, 32, 0, S, hd.h[x->rank], slot, p, x->rank, (unsigned long long)sub_cap,
+                (unsigned long long)((uint64_t)parity * p * slab_cap + (uint64_t)c * sub_cap), (unsigned long long)slab_cap,
+                (unsigned long long)tile_l1, d_segs.p + c, d_matrix.p + (size_t)c * p * p, d_flags.p + 1);
+      KH_CUDA(cudaEventRecord(ev[c], S));
+      KH_CUDA(cudaStreamWaitEvent(R, ev[c], 0));
+      bulk_pipe_feed(b, t, x->local, (uint64_t)p * sub_cap, d_segs.p + c, R);
+    }
+    std::vector<unsigned long long> h_matrix((size_t)chunks * p * p);
+    int h_flags[2] = {0, 0};
+    KH_CUDA(cudaMemcpyAsync(h_matrix.data(), d_matrix.p, h_matrix.size() * sizeof(unsigned long long), cudaMemcpyDeviceToHost, S));
+    KH_CUDA(cudaMemcpyAsync(h_flags, d_flags.p, sizeof(h_flags), cudaMemcpyDeviceToHost, S));
+    KH_CUDA(cudaStreamSynchronize(S));
+    KH_CUDA(cudaStreamSynchronize(R));
+    if (h_flags[0]) {
+      x->poisoned = true;
+      set_error("khx_insert_pipelined_dev: a peer did not reach the barrier in time; buffers are unusable");
+      return KH_ERR_CUDA;
+    }
+    uint64_t n_recv = 0;
+    for (uint32_t a = 0; a < p * p; ++a) counts_matrix[a] = 0;
+    for (int c = 0; c < chunks; ++c)
+      for (uint32_t a = 0; a < p; ++a)
+        for (uint32_t r = 0; r < p; ++r) {
+          const unsigned long long v = h_matrix[((size_t)c * p + a) * p + r];
+          counts_matrix[a * p + r] += v;
+          if (r == x->rank) n_recv += v;
+        }
+    *overflowed = h_flags[1] ? 1 : 0;
+    if (h_flags[1] || n_recv == 0) return 0;                  // table untouched
+    // the received keys as one array, should the general route have to take over
+    b.refetch = [&](DevBuf<uint64_t> &flat, cudaStream_t s) -> const uint64_t * {
+      flat.alloc(n_recv * W);
+      uint64_t off = 0;
+      for (int c = 0; c < chunks; ++c)
+        for (uint32_t a = 0; a < p; ++a) {
+          const uint64_t cnt = h_matrix[((size_t)c * p + a) * p + x->rank];
+          if (cnt) cudaMemcpyAsync(flat.p + off * W, x->local + (((uint64_t)parity * p + a) * slab_cap + (uint64_t)c * sub_cap) * W, cnt * 8 * W,
+                                   cudaMemcpyDeviceToDevice, s);
+          off += cnt;
+        }
+      return flat.p;
+    };
+    return bulk_pipe_finish(b, t, n_recv, default_val, S);
   });
 }
 

@@ -34,8 +34,9 @@ namespace kh {
 
 constexpr int GEN_THREADS = 512;
 constexpr int GEN_TILE_BYTES = GEN_THREADS * 16;          // 8192
-constexpr int GEN_LOOKBACK = 256;
-constexpr int GEN_SPAN = GEN_TILE_BYTES - GEN_LOOKBACK;   // 7936 output positions per tile
+constexpr int GEN_LOOKBACK = 512;
+constexpr int GEN_SPAN = GEN_TILE_BYTES - GEN_LOOKBACK;   // 7680 output positions per tile = 15 warps x 32 lanes x 16: the last warp
+                                                          // is free for the look-back while the others generate
 constexpr int GEN_PAD = 64;                               // compact positions of zero history in front of the tile
 constexpr int GEN_RUN = 16;                               // compact positions per thread in the rolling stage
 constexpr int GEN_BITS = GEN_TILE_BYTES + GEN_PAD + 64;   // compact positions the bit arrays hold (incl. slack for 64-bit reads)
@@ -83,11 +84,14 @@ static __global__ void gen_tile_reads_kernel(const uint64_t *offsets, uint64_t n
   tile_read[t] = l;
 }
 
-// four bytes at a time: 0xff per byte where the byte equals the constant
-__device__ __forceinline__ uint32_t eq4(uint32_t w, uint32_t c4) { return __vcmpeq4(w, c4); }
-// one flag bit per byte (bit 0 of every byte of m) -> bits 0,1,2,3 / bits 0,2,4,6 of the result
-__device__ __forceinline__ uint32_t mask4(uint32_t m) { return ((m & 0x01010101u) * 0x01020408u) >> 24; }
-__device__ __forceinline__ uint32_t spread4(uint32_t m) { return ((m & 0x01010101u) * 0x01041040u) >> 24; }
+// four bytes at a time: bit 7 of every byte that equals the constant (exact: the add cannot carry across bytes)
+__device__ __forceinline__ uint32_t eq4(uint32_t w, uint32_t c4) {
+  const uint32_t z = w ^ c4;
+  return ~(((z & 0x7F7F7F7Fu) + 0x7F7F7F7Fu) | z | 0x7F7F7F7Fu);
+}
+// one flag bit per byte (bit 7 of every byte of m) -> bits 0,1,2,3 / bits 0,2,4,6 of the result
+__device__ __forceinline__ uint32_t mask4(uint32_t m) { return ((m >> 7) * 0x01020408u) >> 24; }
+__device__ __forceinline__ uint32_t spread4(uint32_t m) { return ((m >> 7) * 0x01041040u) >> 24; }
 
 // Consumer: what happens to a tile's k-mers.  store(): coalesced copy of the shared-memory tile to out_keys (the stand-alone API).
 template <int W>
@@ -217,23 +221,26 @@ __global__ void __launch_bounds__(GEN_THREADS, 2) kmer_tiles_kernel(const GenArg
       nrun = (uint32_t)bits64(nb, j0 + GEN_PAD) & 0xffffu;
       srun = (uint32_t)bits64(sb, j0 + GEN_PAD) & 0xffffu;
       const uint32_t left = min((uint32_t)GEN_RUN, ctotal - j0);
-      if ((nrun | srun) == 0 && len0 + 1u >= (uint32_t)k) {
-        vmask = 0xffffu >> (GEN_RUN - left);                  // the common case: nothing breaks the run
-      } else {
-        uint32_t len = len0;
-#pragma unroll
-        for (int i = 0; i < GEN_RUN; ++i) {
-          const bool isn = (nrun >> i) & 1u, st = (srun >> i) & 1u;
-          len = isn ? 0u : (st ? 1u : len + 1u);
-          if (len >= (uint32_t)k && i < (int)left) vmask |= 1u << i;
-        }
+      // segment by segment between the breaks of the run: inside a segment that starts at position s0 with L good bases in
+      // front of it, window i is valid from i >= s0 + k - 1 - L on
+      uint32_t breaks = nrun | srun, s0 = 0, L = len0;
+      for (;;) {
+        const uint32_t b = breaks ? (uint32_t)__ffs(breaks) - 1u : (uint32_t)GEN_RUN;
+        const uint32_t need = (uint32_t)k - 1u > L ? (uint32_t)k - 1u - L : 0u;
+        const uint32_t fv = s0 + need;
+        if (fv < b) vmask |= (0xffffu >> (GEN_RUN - b)) & ~((1u << fv) - 1u);
+        if (b >= (uint32_t)GEN_RUN) break;
+        L = 0;
+        s0 = ((nrun >> b) & 1u) ? b + 1u : b;                 // N: the run restarts behind it; read start: at it
+        breaks &= breaks - 1u;
       }
+      vmask &= 0xffffu >> (GEN_RUN - left);
     }
     uint32_t obase, ototal;
     Scan(scan_tmp).ExclusiveSum((uint32_t)__popc(vmask), obase, ototal);
 
     // ---- look-back: where this tile's output starts -------------------------------------------------------------------------------
-    if (tid < 32) {
+    if (tid >= GEN_THREADS - 32) {                            // the last warp generates nothing (GEN_SPAN / GEN_RUN = 480 runs)
       unsigned long long sum = 0;
       if (tile == 0) {
         if (lane == 0) atomicExch(&a.state[0], GEN_ST_INC | (unsigned long long)ototal);

@@ -509,7 +509,7 @@ uint64_t insert_resident(kh_table *t, const uint64_t *d_keys, const uint32_t *d_
 // the streaming bulk insert (kh_bulk.cuh)
 // =========================================================================================================================
 bool bulk_on() { static const bool on = !(getenv("KH_BULK") && atoi(getenv("KH_BULK")) == 0); return on; }
-constexpr uint64_t BULK_MAX_KEYS = 1ULL << 30;      // record positions are 32-bit: (1.125 + 1) * n + pads stays below 2^32
+constexpr uint64_t BULK_MAX_KEYS = 3ULL << 29;      // record positions are 32-bit: (1.125 + 1) * n + pads stays below 2^32
 
 // COUNT batch with one addend for all keys, 64-byte buckets, large enough to pay for streaming the table once
 bool bulk_candidate(const kh_table *t, const uint32_t *d_vals, uint64_t n) {

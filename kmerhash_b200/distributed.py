@@ -26,21 +26,29 @@ import torch.distributed as dist
 _TRACE = os.environ.get("KH_TRACE", "0") not in ("", "0")
 
 
+STAGE_LOG = None      # a list: host wall time (name, ms) of every stage, WITHOUT extra synchronisation (bench.py's per-step breakdown)
+
+
 class _Stage:
-    """KH_TRACE=1: wall time of one stage of a distributed call on rank 0 (device synchronised at both ends)"""
+    """KH_TRACE=1: wall time of one stage of a distributed call on rank 0 (device synchronised at both ends).
+    STAGE_LOG set: host time of the stage as it runs (every stage ends in a call that synchronises its own stream)."""
 
     def __init__(self, name):
         self.name = name
 
     def __enter__(self):
         if _TRACE:
-            torch.cuda.synchronize(); self.t0 = time.perf_counter()
+            torch.cuda.synchronize()
+        if _TRACE or STAGE_LOG is not None:
+            self.t0 = time.perf_counter()
 
     def __exit__(self, *a):
         if _TRACE:
             torch.cuda.synchronize()
             if dist.get_rank() == 0:
                 sys.stderr.write("[kh-trace] dist.%-14s %8.3f ms\n" % (self.name, 1e3 * (time.perf_counter() - self.t0)))
+        if STAGE_LOG is not None:
+            STAGE_LOG.append((self.name, round(1e3 * (time.perf_counter() - self.t0), 3)))
 
 
 class PeerBuffers:
@@ -116,12 +124,24 @@ class CudaEngine:
         from . import ops
         return ops.canonicalize(keys, self.canonical_k) if (self.canonical_k and keys.shape[0]) else keys
 
-    def partition(self, keys, p, want_perm):
+    def partition(self, keys, p, want_perm, stable=False):
         from . import ops
         if keys.shape[0] == 0:
             return keys, torch.empty(0, dtype=torch.int32, device=self.device), [0] * p
-        # order inside a destination is irrelevant here (COUNT commutes; queries carry their permutation)
-        return ops.partition_dev(keys, p, self.dist_hash, want_perm=want_perm, stable=False)
+        # order inside a destination is irrelevant for COUNT (it commutes) and for queries (they carry their permutation);
+        # the order-dependent reducers ask for the stable scatter (permute_by_bucketid, KH/distributed_batched_robinhood_map.hpp:291-380)
+        return ops.partition_dev(keys, p, self.dist_hash, want_perm=want_perm, stable=stable)
+
+    def as_vals(self, vals):
+        if isinstance(vals, np.ndarray):
+            vals = torch.from_numpy(np.ascontiguousarray(vals, dtype=np.uint32).view(np.int32))
+        return vals.to(self.device)
+
+    def insert_pairs(self, keys, vals, default):
+        return self.table.insert(keys, vals=vals, default=default) if keys.shape[0] else 0
+
+    def ordered(self):
+        return self.table.reducer != "COUNT"
 
     def unpermute(self, vals, perm):
         from . import ops
@@ -161,6 +181,11 @@ class CudaEngine:
 
     def insert_recv_slabs(self, peers, slab_cap, parity, counts, recv_meta, default, no_meta=False):
         return self.table.insert_recv_slabs(peers.h, slab_cap, parity, counts, recv_meta, default, no_meta=no_meta) if int(counts.sum()) else 0
+
+    def insert_pipelined(self, keys, peers, slab_cap, parity, chunks, default):
+        got, C, over = self.table.insert_pipelined(keys, peers.h, peers.p, slab_cap, parity, chunks, peers.epoch + 1, default, self.dist_hash)
+        peers.epoch += chunks
+        return got, C, over
 
     def scatter_slabs(self, keys, peers, slab_cap, parity, counts, reset=True, synced=False):
         self.table.scatter_slabs(keys, peers.h, slab_cap, parity, counts, reset, self.dist_hash, synced=synced)
@@ -223,6 +248,9 @@ class DistributedMap:
         self.slab_cap = 0                 # keys per (owner, sender) slab; the buffers hold 2 halves x p slabs
         self.parity = 0
         self.slab_misses = 0              # consecutive batches that overflowed a slab (skewed owners)
+        # exchange overlapped with the local insert (csrc/exchange.cu: khx_insert_pipelined_dev): pieces per batch, 1 = off
+        self.pipe_chunks = int(os.environ.get("KH_PIPE_CHUNKS", "1"))
+        self.pipe_min_keys = 1 << 22
         self._copy_stream = self._lib_stream = None   # host -> device pipeline of the sender (_send_slabs)
         self._dev_keys = self._C = None
         self._exact_dirty = False         # the last batch went through the exact path: its buffer use overlaps both halves
@@ -268,8 +296,32 @@ class DistributedMap:
     # ---- batch operations (collective) -------------------------------------------------------------
     MAX_BATCH = 1 << 29        # keys per exchange round: receive slabs, 32-bit slab positions and the bulk insert's record positions
 
-    def insert(self, keys, default=1):
-        """returns the number of new keys on THIS rank.  Collective.  Batches above MAX_BATCH keys go in slices (every rank
+    def _insert_ordered(self, keys, vals, default):
+        """(key, value) pairs under FIRST / LAST (DiscardReducer / ReplaceReducer, benchmark/BenchmarkDistHashTables.cpp:976-1020):
+        which value a key keeps depends on the order in which the owner sees the pairs.  The reference's owner sees them
+        sender by sender in rank order, every sender's pairs in its input order (stable permute_by_bucketid + alltoallv,
+        KH/distributed_batched_robinhood_map.hpp:291-380,910-1179); the same order is produced here: stable partition,
+        all-to-all of keys and of values (NCCL), one local insert over the received sequence."""
+        keys = self.e.canonicalize(self.e.as_keys(keys))
+        if vals is not None:
+            vals = self.e.as_vals(vals)
+        if self.p == 1:
+            return self.e.insert_pairs(keys, vals, default)
+        permuted, perm, send_counts = self.e.partition(keys, self.p, True, stable=True)
+        recv_counts = self._counts_a2a(send_counts)
+        recv = self.e.empty_keys(sum(recv_counts))
+        dist.all_to_all_single(recv, permuted, output_split_sizes=recv_counts, input_split_sizes=send_counts, group=self.group)
+        self.last_exchange_bytes += 8 * self.W * (sum(send_counts) - send_counts[self.rank])
+        rv = None
+        if vals is not None:
+            pv = vals[perm.long()] if vals.shape[0] else vals
+            rv = torch.empty(sum(recv_counts), dtype=pv.dtype, device=pv.device)
+            dist.all_to_all_single(rv, pv, output_split_sizes=recv_counts, input_split_sizes=send_counts, group=self.group)
+            self.last_exchange_bytes += 4 * (sum(send_counts) - send_counts[self.rank])
+        return self.e.insert_pairs(recv, rv, default)
+
+    def insert(self, keys, default=1, vals=None):
+        """returns the number of new keys on THIS rank.  Collective.  vals: one 32-bit value per key (FIRST / LAST tables).  Batches above MAX_BATCH keys go in slices (every rank
         must then bring the same number of slices, i.e. about the same number of keys, as the benchmark drivers do).
         chunks > 1 (NCCL path only) overlaps the all-to-all of chunk i+1 with the local insert of chunk i (the reference's
         ialltoallv_and_modify schedule)."""
@@ -278,11 +330,14 @@ class DistributedMap:
             slices = (n + self.MAX_BATCH - 1) // self.MAX_BATCH
             added, xb = 0, 0
             for i in range(slices):
-                added += self.insert(keys[n * i // slices:n * (i + 1) // slices], default)
+                lo, hi = n * i // slices, n * (i + 1) // slices
+                added += self.insert(keys[lo:hi], default, None if vals is None else vals[lo:hi])
                 xb += self.last_exchange_bytes
             self.last_exchange_bytes = xb
             return added
         self.last_exchange_bytes = 0
+        if vals is not None or getattr(self.e, "ordered", lambda: False)():
+            return self._insert_ordered(keys, vals, default)
         if self.p > 1 and self.chunks == 1 and getattr(self.e, "can_plan", lambda p: False)(self.p):
             if self.peer_stores and self.slabs and hasattr(self.e, "scatter_slabs"):
                 r = self._insert_slabs(keys, default)                  # takes host keys too: the sender runs behind the PCIe copy
@@ -376,7 +431,7 @@ class DistributedMap:
         if self.peers is None or self.slab_cap == 0:
             nmax = torch.tensor([n], dtype=torch.int64, device=dev)
             dist.all_reduce(nmax, op=dist.ReduceOp.MAX, group=self.group)
-            self.slab_cap = int(int(nmax.item()) / p * 1.25) + 4096
+            self.slab_cap = (int(int(nmax.item()) / p * 1.25) + 4096 + 63) // 64 * 64     # divisible by 2 * chunks (pipelined pieces)
             if not self._ensure_peers(2 * p * self.slab_cap):
                 keys = self.e.canonicalize(self.e.as_keys(keys))
                 return self._insert_planned(keys, default)
@@ -385,6 +440,21 @@ class DistributedMap:
             dist.barrier(group=self.group)
             self._exact_dirty = False
         parity = self.parity
+        if (self.pipe_chunks > 1 and torch.is_tensor(keys) and keys.is_cuda and p <= 8 and hasattr(self.e, "insert_pipelined")
+                and self.slab_cap % (2 * self.pipe_chunks) == 0 and self.pipe_min_keys <= p * self.slab_cap <= 3 << 29):
+            # every rank takes this branch or none: the decision rests on the slab size, which all ranks share, and on where the
+            # keys live, which a collective caller keeps uniform (device tensors on every rank, or host arrays on every rank)
+            keys = self.e.canonicalize(keys)
+            with _Stage("pipelined insert"):
+                got, C, over = self.e.insert_pipelined(keys, self.peers, self.slab_cap, parity, self.pipe_chunks, default)
+            self.parity ^= 1
+            if over:                                                       # same verdict on every rank
+                self.slab_misses += 1
+                self._C, self._dev_keys = C, keys
+                return None
+            self.slab_misses = 0
+            self.last_exchange_bytes += 8 * self.W * int(C[rank].sum() - C[rank, rank])
+            return got
         counts = torch.zeros(p, dtype=torch.int64, device=dev)
         with _Stage("scatter->slabs"):
             self._dev_keys = self._send_slabs(keys, parity, counts)
@@ -414,7 +484,7 @@ class DistributedMap:
             if self.slab_misses >= 2:                        # owners stay skewed: keep to the exact path from now on
                 self.slabs = False
             elif int(C.max()) * p <= 2 * int(C.sum(axis=1).max()):   # balanced owners, larger batches: larger slabs
-                self.slab_cap = int(int(C.max()) * 1.25) + 4096
+                self.slab_cap = (int(int(C.max()) * 1.25) + 4096 + 63) // 64 * 64
                 grow = grow or 2 * p * self.slab_cap > self.peers.capacity
             if grow and not self._ensure_peers(max(int(need * 1.25) + 1024, 2 * p * self.slab_cap)):
                 return self._insert_planned(keys, default)
@@ -471,8 +541,9 @@ class DistributedMap:
                 self.qpeers.close(); self.qpeers = None
                 return None
         cap = self.q_slab_cap
-        perm = torch.empty(p * cap, dtype=torch.int32, device=dev)
-        counts = torch.zeros(p, dtype=torch.int64, device=dev)
+        with _Stage("q.alloc"):
+            perm = torch.empty(p * cap, dtype=torch.int32, device=dev)
+            counts = torch.zeros(p, dtype=torch.int64, device=dev)
         with _Stage("q.scatter"):
             self.e.query_scatter_slabs(keys, self.qpeers, cap, perm, counts)
         with _Stage("q.sync+counts"):

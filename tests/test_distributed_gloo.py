@@ -28,7 +28,7 @@ class OracleEngine:
         import oracle
         self.o = oracle.port
         self.device = torch.device("cpu")
-        self.W, self.dist_hash, self.canonical_k = key_words, dist_hash, canonical_k
+        self.W, self.dist_hash, self.canonical_k, self.reducer = key_words, dist_hash, canonical_k, reducer
         self.table = self.o.Map(key_words, reducer)
 
     def _np(self, t):
@@ -47,7 +47,18 @@ class OracleEngine:
             return keys
         return self._t(self.o.canonical(self.canonical_k, self._np(keys)))
 
-    def partition(self, keys, p, want_perm):
+    def ordered(self):
+        return self.reducer != "COUNT"
+
+    def as_vals(self, vals):
+        return torch.from_numpy(np.ascontiguousarray(vals, dtype=np.uint32).view(np.int32)) if isinstance(vals, np.ndarray) else vals
+
+    def insert_pairs(self, keys, vals, default):
+        if not keys.shape[0]:
+            return 0
+        return self.table.insert(self._np(keys), None if vals is None else vals.numpy().view(np.uint32), default=default)
+
+    def partition(self, keys, p, want_perm, stable=False):
         n = keys.shape[0]
         if n == 0:
             return keys, torch.empty(0, dtype=torch.int32), [0] * p
@@ -172,6 +183,59 @@ def test_distributed_map_gloo(world, W, canonical_k, chunks, empty_rank):
     q = ctx.Queue()
     port = _free_port()
     procs = [ctx.Process(target=_worker, args=(r, world, port, W, canonical_k, chunks, empty_rank, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    res = [q.get(timeout=180) for _ in procs]
+    for p in procs:
+        p.join(timeout=60)
+    for rank, msg in res:
+        assert msg == "ok", "rank %d: %s" % (rank, msg)
+
+
+def _ordered_worker(rank, world, port, reducer, q):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        import oracle
+        from kmerhash_b200.distributed import DistributedMap
+        o = oracle.port
+        batches = []
+        for r in range(world):                       # heavy overlap between the ranks: the winner depends on the global order
+            rng = np.random.default_rng(40 + r)
+            pool = np.random.default_rng(9).integers(0, 2**62, size=300, dtype=np.uint64)
+            k = np.ascontiguousarray(pool[rng.integers(0, 300, size=900)])
+            v = (np.arange(900, dtype=np.uint32) + np.uint32(100000 * (r + 1)))
+            batches.append((k, v))
+        eng = OracleEngine(1, "MURMUR64avx", reducer, 0)
+        dm = DistributedMap(1, "MURMUR64avx", "MURMUR64avx", reducer, 0, engine=eng)
+        for rep in range(2):                         # a second batch: FIRST keeps the old values, LAST takes the new ones
+            k, v = batches[rank]
+            dm.insert(k.copy(), vals=v + np.uint32(rep))
+        # the reference's order at an owner: sender by sender in rank order, input order inside a sender; batch by batch
+        g = o.Map(1, reducer)
+        for rep in range(2):
+            g.insert(np.concatenate([b[0] for b in batches]), np.concatenate([b[1] + np.uint32(rep) for b in batches]))
+        gk, gv = g.to_vector()
+        mine = o.rank("MURMUR64avx", gk, world) == rank
+        lk, lv = dm.to_vector()
+        a, b = np.argsort(gk[mine]), np.argsort(np.asarray(lk))
+        assert np.array_equal(gk[mine][a], np.asarray(lk)[b]) and np.array_equal(np.asarray(gv)[mine][a], np.asarray(lv)[b])
+        q.put((rank, "ok"))
+    except Exception as e:  # pragma: no cover
+        import traceback
+        q.put((rank, "FAIL: %s\n%s" % (e, traceback.format_exc())))
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("world,reducer", [(2, "FIRST"), (2, "LAST"), (3, "FIRST")])
+def test_distributed_first_last_gloo(world, reducer):
+    """(key, value) pairs through the exchange under DiscardReducer / ReplaceReducer: the value a key keeps follows the
+    reference's global order (sender rank, then input position), benchmark/BenchmarkDistHashTables.cpp:976-1020"""
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_ordered_worker, args=(r, world, port, reducer, q)) for r in range(world)]
     for p in procs:
         p.start()
     res = [q.get(timeout=180) for _ in procs]

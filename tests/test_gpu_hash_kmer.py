@@ -105,8 +105,8 @@ def test_kmers_tile_kernel_eol_dense_falls_back(kh, oracle_mod):
     through the warp-per-read kernel)"""
     rng = np.random.default_rng(5)
     seq = np.frombuffer(b"ACGT", dtype=np.uint8)[rng.integers(0, 4, size=30000)]
-    dense = np.empty(4 * len(seq), dtype=np.uint8)
-    dense[0::4] = seq; dense[1::4] = 10; dense[2::4] = 13; dense[3::4] = 10   # every base followed by "\n\r\n"
+    dense = np.full(12 * len(seq), 10, dtype=np.uint8)
+    dense[0::12] = seq; dense[5::12] = 13                                     # every base followed by eleven EOL characters
     offs = np.array([0, len(dense) // 2, len(dense)], dtype=np.uint64)
     for k in (31, 63):
         exp = oracle_mod.port.kmers_from_reads(dense, offs, k, True)

@@ -33,6 +33,44 @@ def ev():
     e = torch.cuda.Event(enable_timing=True); e.record(); return e
 
 
+def ref_keys(n, k, canonical):
+    """the reference's generate_input bytes (drivers/libkh_geninput.so, as bench.py)"""
+    from bench import generate_workload
+    return generate_workload(n, 1, seed=23, k=k, canonical=canonical)[0]
+
+
+def peak_gbs():
+    try:
+        return float(json.load(open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "..", "MEASURED_PEAKS.json")))["hbm_gbs"])
+    except Exception:
+        return 6650.0
+
+
+def cpu_arm(keys, map_kind, hash_kind, min_load, max_load, n_sample=10_000_000):
+    """the compiled reference (oracle/_ref) on the first n_sample keys, one thread, same map / hash / load factors"""
+    import oracle
+    if oracle.ref is None:
+        return None
+    ns = min(n_sample, len(keys))
+    nq = max(1, ns // 10)
+    try:
+        secs, cnts = oracle.ref.baseline_run(np.ascontiguousarray(keys[:ns]), np.ascontiguousarray(keys[:nq]), map_kind, hash_kind,
+                                             threads=1, min_load=min_load, max_load=max_load)
+    except Exception as e:          # combination not instantiated in the harness
+        return {"unavailable": str(e)}
+    return {"kind": "reference", "cores": 1, "sample_keys": ns, "inserts_per_s": ns / (secs["estimate"] + secs["insert"]),
+            "finds_per_s": nq / secs["find"], "counts_per_s": nq / secs["count"], "erases_per_s": nq / secs["erase"]}
+
+
+def roofline(n, nq, ph, W):
+    """phase-level, SURVEY.md 8d bytes: insert 72 / 80 B per key, find 44 / 52 B"""
+    pk = peak_gbs()
+    bi, bf = (72, 44) if W == 1 else (80, 52)
+    gi, gf = bi * n / ph[0] / 1e6, bf * nq / ph[1] / 1e6
+    return {"bound": "hbm", "peak": pk, "unit": "GB/s", "insert": {"achieved": gi, "frac": gi / pk, "bytes_per_key": bi},
+            "find": {"achieved": gf, "frac": gf / pk, "bytes_per_key": bf}}
+
+
 def gen_keys(n, words, repeats=10, seed=23):
     """generate_input's shape (benchmark/BenchmarkHashTables.cpp:181-227): 62 significant bits per word"""
     rng = np.random.default_rng(seed)
@@ -68,7 +106,7 @@ def timed_phases(m, d_keys, d_q, estimate, steps=3, start_cap=128):
 
 def run_lp(args):
     n, nq = args.n, args.n // 10
-    keys = gen_keys(n, 1)
+    keys = ref_keys(n, 31, False)
     distinct = int(np.unique(keys).shape[0])
     d = torch.from_numpy(keys.view(np.int64)).cuda()
     q = d[:nq].contiguous()
@@ -80,7 +118,9 @@ def run_lp(args):
                 m = ctor(1, "MURMUR64", min_load=0.35, max_load=max_load)
                 ph, chk = timed_phases(m, d, q, estimate=(mode == "presized"))
                 assert chk[0] == distinct and chk[1] == nq and chk[2] == nq and chk[3] == q_distinct and chk[4] == 0, chk
+                cpu = cpu_arm(keys, "LINEARPROBE" if "linear" in kind else "ROBINHOOD", "MURMUR64", 0.35, max_load) if mode == "doubling" else None
                 print(json.dumps({"config": 2, "map": kind, "max_load": max_load, "mode": mode, "n": n, "nq": nq,
+                                  "roofline": roofline(n, nq, ph, 1), "cpu_baseline": cpu,
                                   "distinct": distinct, "capacity_after_insert": None, "final_capacity": chk[5],
                                   "inserts_per_s": n / ph[0] * 1e3, "finds_per_s": nq / ph[1] * 1e3,
                                   "counts_per_s": nq / ph[2] * 1e3, "erases_per_s": nq / ph[3] * 1e3,
@@ -90,10 +130,12 @@ def run_lp(args):
 
 def run_k63(args):
     n, nq = args.n, args.n // 10
-    keys = gen_keys(n, 2)
-    d = torch.from_numpy(keys.view(np.int64)).cuda()
+    raw = ref_keys(n, 63, False)
+    keys = ref_keys(n, 63, True)                    # generate_input(canonical = true), the reference's -c
+    d = torch.from_numpy(raw.view(np.int64)).cuda()
     t0 = ev(); d = ops.canonicalize(d, 63); t1 = ev(); torch.cuda.synchronize()
     canon_ms = t0.elapsed_time(t1)
+    assert np.array_equal(d.cpu().numpy().view(np.uint64), keys), "device canonicalisation differs from the reference generator's"
     # exact distinct count of the canonical keys on the device (sort of (hi, lo) pairs)
     u = torch.unique(d, dim=0).shape[0] if n <= 20_000_000 else None
     q = d[:nq].contiguous()
@@ -103,6 +145,7 @@ def run_k63(args):
         assert chk[1] == nq and chk[2] == nq and chk[4] == 0 and (u is None or chk[0] == u), (chk, u)
         u = chk[0]                      # every hash variant must find the same number of distinct keys
         print(json.dumps({"config": 3, "k": 63, "hash": h, "n": n, "nq": nq, "distinct": chk[0],
+                          "roofline": roofline(n, nq, ph, 2), "cpu_baseline": cpu_arm(keys, "OFFSETS_COUNT", h, 0.35, 0.8),
                           "canonicalize_keys_per_s": n / canon_ms * 1e3,
                           "inserts_per_s": n / ph[0] * 1e3, "finds_per_s": nq / ph[1] * 1e3,
                           "counts_per_s": nq / ph[2] * 1e3, "erases_per_s": nq / ph[3] * 1e3,
