@@ -339,6 +339,10 @@ int khd_n_gpus(const khd_map *m);
 /* 1 when partition+exchange run as one kernel storing into peer GPUs' buffers (peer access available) */
 int khd_uses_peer_stores(const khd_map *m);
 int64_t khd_insert_host(khd_map *m, const uint64_t *keys, uint64_t n, uint32_t default_val);
+/* (key, value) pairs for FIRST / LAST maps (benchmark/BenchmarkDistHashTables.cpp:976-1020): the owner sees the pairs sender by
+ * sender in rank order, input order inside a sender, as the reference's owner rank does after its alltoallv */
+int64_t khd_insert_pairs_host(khd_map *m, const uint64_t *keys, const uint32_t *vals, uint64_t n);
+int khd_set_load_factors(khd_map *m, double min_load, double max_load);
 int64_t khd_count_host(khd_map *m, const uint64_t *keys, uint64_t n, uint8_t *out);
 int64_t khd_find_host(khd_map *m, const uint64_t *keys, uint64_t n, uint32_t *out, uint32_t nonexistent);
 int64_t khd_erase_host(khd_map *m, const uint64_t *keys, uint64_t n);

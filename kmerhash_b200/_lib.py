@@ -130,6 +130,8 @@ SIGNATURES = {
     "khd_n_gpus": (_int, [_vp]),
     "khd_uses_peer_stores": (_int, [_vp]),
     "khd_insert_host": (_i64, [_vp, _vp, _u64, _u32]),
+    "khd_insert_pairs_host": (_i64, [_vp, _vp, _vp, _u64]),
+    "khd_set_load_factors": (_int, [_vp, _dbl, _dbl]),
     "khd_count_host": (_i64, [_vp, _vp, _u64, _vp]),
     "khd_find_host": (_i64, [_vp, _vp, _u64, _vp, _u32]),
     "khd_erase_host": (_i64, [_vp, _vp, _u64]),

@@ -151,6 +151,12 @@ void return_results(khd_map *m, Exchange &x, std::vector<DevBuf<T>> &d_res, T *o
   });
 }
 
+// values follow their keys: pv[i] = v[perm[i]] (perm = original index of every permuted position)
+__global__ void gather_vals_kernel(const uint32_t *v, const uint32_t *perm, uint64_t n, uint32_t *pv) {
+  const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+  for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) pv[i] = v[perm[i]];
+}
+
 }  // namespace
 
 extern "C" {
@@ -239,6 +245,54 @@ int64_t khd_insert_host(khd_map *m, const uint64_t *keys, uint64_t n, uint32_t d
     int64_t tot = 0; for (auto a : added) tot += a;
     return tot;
   });
+}
+
+// (key, value) pairs (batched_robinhood_map under DiscardReducer / ReplaceReducer, benchmark/BenchmarkDistHashTables.cpp:976-1020;
+// insert_p with pair payloads, KH/distributed_batched_robinhood_map.hpp:910-1179).  The value a key keeps depends on the
+// order in which its owner sees the pairs: sender by sender in rank order, input order inside a sender -- which is the order
+// of the receive buffers here (exact offsets per sender, STABLE scatter), so one ordered insert per GPU reproduces it.
+int64_t khd_insert_pairs_host(khd_map *m, const uint64_t *keys, const uint32_t *vals, uint64_t n) {
+  return guarded([&]() -> int64_t {
+    if (!m || (n && (!keys || !vals))) { set_error("null argument"); return KH_ERR_INVALID; }
+    const int p = m->p;
+    Exchange x;
+    run_exchange(m, keys, n, true, x);
+    std::vector<DevBuf<uint32_t>> d_rv(p);
+    parallel_for(p, [&](int r) {
+      DeviceGuard dg(m->dev[r]);
+      d_rv[r].alloc(std::max<uint64_t>(x.recv_n[r], 1));
+    });
+    parallel_for(p, [&](int g) {
+      DeviceGuard dg(m->dev[g]);
+      cudaStream_t s = m->stream[g];
+      const uint64_t ng = x.slice_beg[g + 1] - x.slice_beg[g];
+      if (ng == 0) return;
+      DevBuf<uint32_t> v(ng), pv(ng);
+      KH_CUDA(cudaMemcpyAsync(v.p, vals + x.slice_beg[g], ng * sizeof(uint32_t), cudaMemcpyHostToDevice, s));
+      if (p == 1) {
+        KH_CUDA(cudaMemcpyAsync(d_rv[0].p, v.p, ng * sizeof(uint32_t), cudaMemcpyDeviceToDevice, s));
+      } else {
+        KH_LAUNCH(gather_vals_kernel, (int)std::min<uint64_t>((ng + 255) / 256, 1184), 256, 0, s, v.p, x.d_perm[g].p, ng, pv.p);
+        for (int r = 0; r < p; ++r) if (x.C[g][r])
+          KH_CUDA(cudaMemcpyPeerAsync(d_rv[r].p + x.recv_off[r][g], m->dev[r], pv.p + x.plan[g].seg_h[r], m->dev[g],
+                                      x.C[g][r] * sizeof(uint32_t), s));
+      }
+      KH_CUDA(cudaStreamSynchronize(s));
+    });
+    std::vector<int64_t> added(p, 0);
+    parallel_for(p, [&](int r) {
+      added[r] = kh_insert_dev(m->table[r], x.d_recv[r].p, d_rv[r].p, x.recv_n[r], 0, 1);
+      if (added[r] < 0) throw CudaError{(int)added[r]};
+    });
+    int64_t tot = 0; for (auto a : added) tot += a;
+    return tot;
+  });
+}
+
+int khd_set_load_factors(khd_map *m, double min_load, double max_load) {
+  if (!m) return KH_ERR_INVALID;
+  for (auto *t : m->table) { const int rc = kh_set_load_factors(t, min_load, max_load); if (rc != KH_OK) return rc; }
+  return KH_OK;
 }
 
 int64_t khd_count_host(khd_map *m, const uint64_t *keys, uint64_t n, uint8_t *out) {

@@ -145,9 +145,16 @@ class MultiGpuMap:
     def uses_peer_stores(self):
         return bool(lib.khd_uses_peer_stores(self._h))
 
-    def insert(self, keys, default=1):
+    def insert(self, keys, default=1, vals=None):
         a, n = _host_keys(keys, self.W)
+        if vals is not None:              # (key, value) pairs: FIRST / LAST maps
+            v = np.ascontiguousarray(vals, dtype=np.uint32)
+            assert v.shape[0] == n
+            return check(lib.khd_insert_pairs_host(self._h, a.ctypes.data, v.ctypes.data, n), "khd_insert_pairs")
         return check(lib.khd_insert_host(self._h, a.ctypes.data, n, default), "khd_insert")
+
+    def set_load_factors(self, min_load, max_load):
+        check(lib.khd_set_load_factors(self._h, min_load, max_load), "khd_set_load_factors")
 
     def count(self, keys):
         a, n = _host_keys(keys, self.W)
