@@ -38,8 +38,12 @@ namespace kh {
 constexpr int BK_TILE_BYTES = 131072;          // bytes of table per tile
 constexpr int BK_BUCKET_BITS = 11;             // 64-byte buckets per tile = 2048
 constexpr int BK_BUCKETS = 1 << BK_BUCKET_BITS;
-constexpr int BK_MAX_LP = 12;                  // level-1 regions <= 4096
+constexpr int BK_MAX_LP = 12;                  // level-2 tiles per region <= 4096; level-1 regions <= 4096 (8-byte keys)
 constexpr int BK_MAX_BINS = 1 << BK_MAX_LP;
+// level-1 regions: 4096 for 8-byte keys, 8192 for 16-byte keys -- their tiles hold half the slots, so a table of the same
+// bytes has twice the tiles, and a run of ONE 32-byte record is still a full sector (16-byte records want two per run)
+template <int W> struct BkL1 { static constexpr int MAX_LP = 11 + W; static constexpr int BINS = 1 << MAX_LP; };
+inline int bk_l1_max_lp(int W) { return W == 1 ? BkL1<1>::MAX_LP : BkL1<2>::MAX_LP; }
 constexpr int BK_CSTRIDE = 16;                 // one 128-byte line per region cursor (atomics of different regions never share a line)
 template <int W> struct BkGeom {
   static constexpr int SLOTS = BK_TILE_BYTES / (16 * W);       // 8192 / 4096 slots per tile
@@ -100,7 +104,9 @@ template <int W> struct L1Cfg {
   static constexpr int TILE = L1_THREADS * KPT;                // 8192 / 4096 keys = 64 KB
   static constexpr int RAW_BYTES = TILE * 8 * W;
   // raw tile | sorted keys | sorted tags | packed 16-bit counters | run offsets | HLL register bytes | mbarrier
-  static constexpr size_t SMEM = (size_t)2 * RAW_BYTES + (size_t)TILE * 4 + BK_MAX_BINS * 2 + BK_MAX_BINS * 4 + HLL_M + 16;
+  static constexpr int BINS = BkL1<W>::BINS;
+  static constexpr int BPT = BINS / L1_THREADS;                // bins per thread in the run-start step: 4 / 8
+  static constexpr size_t SMEM = (size_t)2 * RAW_BYTES + (size_t)TILE * 4 + BINS * 2 + BINS * 4 + HLL_M + 16;
 };
 
 // dsegs: the pieces as a DEVICE-resident table (may be null: the launch argument `segs_arg` holds them).  The pipelined
@@ -126,14 +132,16 @@ __global__ void __launch_bounds__(L1_THREADS, 1) l1_scatter_kernel(const L1Args 
   uint64_t *skeys = reinterpret_cast<uint64_t *>(l1_smem + Cfg::RAW_BYTES);
   uint32_t *stags = reinterpret_cast<uint32_t *>(l1_smem + 2 * Cfg::RAW_BYTES);
   uint32_t *cnt32 = stags + TILE;                              // two 16-bit counters per word: count, then run start
-  uint32_t *goff = cnt32 + BK_MAX_BINS / 2;                    // run start in recs - run start in tile (mod 2^32)
-  uint32_t *regs = goff + BK_MAX_BINS;                         // HLL register bytes, four to a word
+  constexpr int BINS = Cfg::BINS, BPT = Cfg::BPT;
+  uint32_t *goff = cnt32 + BINS / 2;                           // run start in recs - run start in tile (mod 2^32)
+  uint32_t *regs = goff + BINS;                                // HLL register bytes, four to a word
   const uint32_t mbar = (uint32_t)__cvta_generic_to_shared(regs + HLL_M / 4);
   const uint32_t raw_s = (uint32_t)__cvta_generic_to_shared(raw);
   const int tid = threadIdx.x;
 
   for (int i = tid; i < HLL_M / 4; i += L1_THREADS) regs[i] = 0;
-  cnt32[2 * tid] = 0; cnt32[2 * tid + 1] = 0;
+#pragma unroll
+  for (int q = 0; q < BPT / 2; ++q) cnt32[(BPT / 2) * tid + q] = 0;
   if (tid == 0) { mbar_init(mbar, 1); fence_proxy_async(); }
 
   const int rshift = 32 - a.lp;
@@ -220,19 +228,24 @@ __global__ void __launch_bounds__(L1_THREADS, 1) l1_scatter_kernel(const L1Args 
     __syncthreads();
 
     // ---- run starts inside the tile; ONE global atomicAdd per (tile, region) reserves the output run ---------------
-    uint32_t c[4], lo[4];
-    unsigned long long gb[4];
+    uint32_t c[BPT], lo[BPT];
+    uint32_t gb[BPT];                                  // record positions fit 32 bits (the host bounds the batch)
     {
-      const uint2 w2 = *reinterpret_cast<const uint2 *>(cnt32 + 2 * tid);
-      c[0] = w2.x & 0xffffu; c[1] = w2.x >> 16; c[2] = w2.y & 0xffffu; c[3] = w2.y >> 16;
-      uint32_t st;
-      Scan(scan_tmp).ExclusiveSum(c[0] + c[1] + c[2] + c[3], st);
-      lo[0] = st; lo[1] = lo[0] + c[0]; lo[2] = lo[1] + c[1]; lo[3] = lo[2] + c[2];
-      *reinterpret_cast<uint2 *>(cnt32 + 2 * tid) = make_uint2(lo[0] | (lo[1] << 16), lo[2] | (lo[3] << 16));
+      uint32_t w[BPT / 2];
 #pragma unroll
-      for (int q = 0; q < 4; ++q) {
+      for (int q = 0; q < BPT / 2; ++q) w[q] = cnt32[(BPT / 2) * tid + q];
+      uint32_t tot = 0, st;
+#pragma unroll
+      for (int q = 0; q < BPT; ++q) { c[q] = (w[q >> 1] >> ((q & 1) << 4)) & 0xffffu; tot += c[q]; }
+      Scan(scan_tmp).ExclusiveSum(tot, st);
+#pragma unroll
+      for (int q = 0; q < BPT; ++q) { lo[q] = st; st += c[q]; }
+#pragma unroll
+      for (int q = 0; q < BPT / 2; ++q) cnt32[(BPT / 2) * tid + q] = lo[2 * q] | (lo[2 * q + 1] << 16);
+#pragma unroll
+      for (int q = 0; q < BPT; ++q) {
         gb[q] = 0;
-        if (c[q]) gb[q] = atomicAdd(&a.cursors[(size_t)(4 * tid + q) * BK_CSTRIDE], (unsigned long long)c[q]);
+        if (c[q]) gb[q] = (uint32_t)atomicAdd(&a.cursors[(size_t)(BPT * tid + q) * BK_CSTRIDE], (unsigned long long)c[q]);
       }
     }
     __syncthreads();
@@ -250,13 +263,14 @@ __global__ void __launch_bounds__(L1_THREADS, 1) l1_scatter_kernel(const L1Args 
       }
     }
 #pragma unroll
-    for (int q = 0; q < 4; ++q) goff[4 * tid + q] = (uint32_t)gb[q] - lo[q];
+    for (int q = 0; q < BPT; ++q) goff[BPT * tid + q] = gb[q] - lo[q];
     __syncthreads();
 
     // ---- the raw buffer is free: fetch the next tile while this one goes out ----------------------------------------
     const uint64_t next = tile + gridDim.x;
     if (next < n_tiles) cur_bulk = stage(next);
-    cnt32[2 * tid] = 0; cnt32[2 * tid + 1] = 0;
+#pragma unroll
+    for (int q = 0; q < BPT / 2; ++q) cnt32[(BPT / 2) * tid + q] = 0;
 
     // ---- sorted tile out: consecutive threads = consecutive records inside a run ------------------------------------
 #pragma unroll 2
@@ -308,9 +322,15 @@ struct L2Args {
   unsigned long long slab;
   int lp, tbits;                       // regions = 2^lp, tiles per region = 2^tbits (tbits <= 12)
   unsigned long long *chunk_prefix;    // [2^lp + 1] chunks of L2_TILE records in front of region r
-  unsigned long long *tile_cnt;        // [2^(lp+tbits)] histogram, then (after the scan) unused
-  unsigned long long *tile_cur;        // [2^(lp+tbits)] starts at tile_begin, ends as tile_end
-  uint4 *recs2;                        // exact-packed output
+  unsigned long long *tile_cnt;        // [2^(lp+tbits)] histogram, then (after the scan) unused (exact mode only)
+  unsigned long long *tile_cur;        // [2^(lp+tbits)] x cstride: starts at tile_begin, ends as tile_end
+  uint4 *recs2;                        // output: exact-packed, or one slab of slab2 positions per tile
+  // slab mode (slab2 != 0): no histogram pass -- tile x owns [x * slab2, (x+1) * slab2), sized for a uniform hash like the
+  // level-1 slabs; the rare record that does not fit gives its key to the overflow list.  cstride: words between two cursors.
+  unsigned long long slab2;
+  int cstride;
+  uint64_t *ovf_keys;
+  unsigned long long *ovf_count, ovf_cap;
 };
 
 __device__ __forceinline__ unsigned long long l2_region_len(const L2Args &a, uint32_t r) {
@@ -426,7 +446,7 @@ __global__ void __launch_bounds__(L2_THREADS, 2) l2_scatter_kernel(L2Args a) {
 #pragma unroll
       for (int q = 0; q < BPT; ++q) {
         gb[q] = 0;
-        if (c[q]) gb[q] = atomicAdd(&a.tile_cur[((size_t)r << a.tbits) + BPT * tid + q], (unsigned long long)c[q]);
+        if (c[q]) gb[q] = atomicAdd(&a.tile_cur[(((size_t)r << a.tbits) + BPT * tid + q) * a.cstride], (unsigned long long)c[q]);
       }
     }
     __syncthreads();
@@ -440,14 +460,23 @@ __global__ void __launch_bounds__(L2_THREADS, 2) l2_scatter_kernel(L2Args a) {
       }
     }
 #pragma unroll
-    for (int q = 0; q < BPT; ++q) goff[BPT * tid + q] = (uint32_t)gb[q] - lo[q];
+    for (int q = 0; q < BPT; ++q) goff[BPT * tid + q] = gb[q] - lo[q];
     __syncthreads();
     for (int e = tid; e < cnt; e += L2_THREADS) {
       const uint4 r0 = srec[e * W];
       const uint32_t t32 = W == 1 ? r0.z : srec[e * W + W - 1].x;
-      const uint32_t gpos = goff[(t32 >> tshift) & (T - 1)] + (uint32_t)e;
-      a.recs2[(size_t)gpos * W] = r0;
-      if (W == 2) a.recs2[(size_t)gpos * W + W - 1] = srec[e * W + W - 1];
+      const uint32_t sub = (t32 >> tshift) & (T - 1);
+      const uint32_t gpos = goff[sub] + (uint32_t)e;
+      if (a.slab2 == 0 || (unsigned long long)gpos < ((((unsigned long long)r << a.tbits) + sub + 1ULL) * a.slab2)) {
+        a.recs2[(size_t)gpos * W] = r0;
+        if (W == 2) a.recs2[(size_t)gpos * W + W - 1] = srec[e * W + W - 1];
+      } else {                                          // the tile's slab is full
+        const unsigned long long at = atomicAdd(a.ovf_count, 1ULL);
+        if (at < a.ovf_cap) {
+          a.ovf_keys[at * W] = (uint64_t)r0.x | ((uint64_t)r0.y << 32);
+          if (W == 2) a.ovf_keys[at * W + W - 1] = (uint64_t)r0.z | ((uint64_t)r0.w << 32);
+        }
+      }
     }
     __syncthreads();
   }

@@ -524,7 +524,7 @@ int bulk_region_bits(const kh_table *t, uint64_t n) {
   const uint64_t worst = std::max(t->capacity, capacity_for(t, t->size + n));
   int lp = log2_u64(std::max<uint64_t>(worst / tile_slots, 1));
   if (const char *e = getenv("KH_BULK_LP")) lp = atoi(e);          // experiments / tests: force level 2
-  return std::max(6, std::min(lp, BK_MAX_LP));
+  return std::max(6, std::min(lp, bk_l1_max_lp(t->W)));
 }
 
 void bulk_begin(BulkBatch &b, kh_table *t, uint64_t n, cudaStream_t s) {
@@ -649,25 +649,41 @@ int64_t bulk_finish(BulkBatch &b, kh_table *t, const uint64_t *d_keys, const BkS
   DevBuf<uint4> recs2;
   DevBuf<unsigned long long> l2buf;
   if (tile_bits > b.lp) {
-    // more tiles than regions: split every region by the next tag bits (exact: histogram of the tags -> scan -> scatter)
+    // more tiles than regions: split every region by the next tag bits.  Default: into one SLAB per tile, sized for a
+    // uniform hash like the level-1 slabs (no histogram pass; a record that does not fit hands its key to the overflow
+    // list).  KH_L2_EXACT=1: histogram of the tags -> scan -> scatter into exactly packed runs.
     Trace tr("bulk.level2", s);
+    const bool exact = getenv("KH_L2_EXACT") && atoi(getenv("KH_L2_EXACT")) != 0;      // read per call: tests switch it
     const int tbits = tile_bits - b.lp;
     const uint64_t R = 1ULL << b.lp, NT = 1ULL << tile_bits;
-    l2buf.alloc(R + 1 + 2 * NT);
-    recs2.alloc(std::max<uint64_t>(b.fed, 1) * W);
+    const uint64_t slab2 = exact ? 0 : (((uint64_t)((double)std::max<uint64_t>(b.fed, 1) / (double)NT * 1.125) + 512 + 127) & ~127ULL);
+    const bool fits32 = exact || NT * slab2 < (1ULL << 32);
+    const bool use_slab = !exact && fits32;
+    const int cstride = use_slab ? BK_CSTRIDE : 1;
+    l2buf.alloc(R + 1 + (use_slab ? NT * cstride : 2 * NT));
+    recs2.alloc((use_slab ? NT * slab2 : std::max<uint64_t>(b.fed, 1)) * W);
     L2Args a;
     a.recs = b.recs.p; a.cursors = b.cursors.p; a.slab = b.slab; a.lp = b.lp; a.tbits = tbits;
-    a.chunk_prefix = l2buf.p; a.tile_cnt = l2buf.p + R + 1; a.tile_cur = a.tile_cnt + NT; a.recs2 = recs2.p;
-    KH_CUDA(cudaMemsetAsync(a.tile_cnt, 0, NT * sizeof(unsigned long long), s));
+    a.chunk_prefix = l2buf.p; a.recs2 = recs2.p;
+    a.slab2 = use_slab ? slab2 : 0; a.cstride = cstride;
+    a.ovf_keys = b.ovf.p; a.ovf_count = b.ovf_count.p; a.ovf_cap = b.ovf_cap;
     KH_LAUNCH(l2_plan_kernel, 1, 1024, 0, s, a);
     const int grid = t->sms * 2;
     kev_begin(t, 5, s);
-    if (W == 1) KH_LAUNCH(l2_hist_kernel<1>, grid, L2_THREADS, 0, s, a); else KH_LAUNCH(l2_hist_kernel<2>, grid, L2_THREADS, 0, s, a);
-    size_t tmp_bytes = 0;
-    KH_CUDA(cub::DeviceScan::ExclusiveSum(nullptr, tmp_bytes, a.tile_cnt, a.tile_cur, NT, s));
-    DevBuf<unsigned char> tmp(tmp_bytes);
-    KH_CUDA(cub::DeviceScan::ExclusiveSum(tmp.p, tmp_bytes, a.tile_cnt, a.tile_cur, NT, s));
-    g_launches.fetch_add(1, std::memory_order_relaxed);
+    DevBuf<unsigned char> tmp;
+    if (use_slab) {
+      a.tile_cnt = nullptr; a.tile_cur = l2buf.p + R + 1;
+      KH_LAUNCH(l1_cursor_kernel, (int)((NT + 255) / 256), 256, 0, s, a.tile_cur, (int)NT, (unsigned long long)slab2);
+    } else {
+      a.tile_cnt = l2buf.p + R + 1; a.tile_cur = a.tile_cnt + NT;
+      KH_CUDA(cudaMemsetAsync(a.tile_cnt, 0, NT * sizeof(unsigned long long), s));
+      if (W == 1) KH_LAUNCH(l2_hist_kernel<1>, grid, L2_THREADS, 0, s, a); else KH_LAUNCH(l2_hist_kernel<2>, grid, L2_THREADS, 0, s, a);
+      size_t tmp_bytes = 0;
+      KH_CUDA(cub::DeviceScan::ExclusiveSum(nullptr, tmp_bytes, a.tile_cnt, a.tile_cur, NT, s));
+      tmp.alloc(tmp_bytes);
+      KH_CUDA(cub::DeviceScan::ExclusiveSum(tmp.p, tmp_bytes, a.tile_cnt, a.tile_cur, NT, s));
+      g_launches.fetch_add(1, std::memory_order_relaxed);
+    }
     if (W == 1) {
       KH_CUDA(cudaFuncSetAttribute(l2_scatter_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)l2_smem_bytes(1)));
       KH_LAUNCH(l2_scatter_kernel<1>, grid, L2_THREADS, l2_smem_bytes(1), s, a);
@@ -676,8 +692,17 @@ int64_t bulk_finish(BulkBatch &b, kh_table *t, const uint64_t *d_keys, const BkS
       KH_LAUNCH(l2_scatter_kernel<2>, grid, L2_THREADS, l2_smem_bytes(2), s, a);
     }
     kev_end(t, s);
-    KH_CUDA(cudaStreamSynchronize(s));                               // tmp goes out of scope
-    recs = recs2.p; ends = a.tile_cur; slab = 0; rpt_log2 = 0;
+    if (use_slab) KH_CUDA(cudaMemcpyAsync(&n_ovf, b.ovf_count.p, sizeof(n_ovf), cudaMemcpyDeviceToHost, s));
+    KH_CUDA(cudaStreamSynchronize(s));                               // tmp goes out of scope; the overflow count is final
+    recs = recs2.p; ends = a.tile_cur; slab = use_slab ? slab2 : 0; rpt_log2 = 0;
+    if (n_ovf > b.ovf_cap) {                                         // a heavily skewed batch: the general route takes over
+      b.recs.release(); recs2.release();
+      DevBuf<uint64_t> flat;
+      const uint64_t *keys = b.refetch ? b.refetch(flat, s) : flatten_segments(t, d_keys, n, segs, flat, s);
+      insert_general(t, keys, nullptr, n, dflt, estimate != 0, s);
+      KH_CUDA(cudaStreamSynchronize(s));
+      return (int64_t)(t->size - size0);
+    }
   }
   DevBuf<uint32_t> defer(n);
   uint64_t n_def = 0;

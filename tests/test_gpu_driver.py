@@ -142,3 +142,24 @@ def test_distributed_map_on_real_gpus_under_torchrun(world, pipe):
                        capture_output=True, text=True, timeout=600, env=env)
     assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
     assert r.stdout.count(" OK") >= world
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("gpus", [1, 2])
+@pytest.mark.parametrize("index", ["count", "first", "last"])
+def test_dist_hash_tables_driver(kh, gpus, index):
+    """drivers/BenchmarkDistHashTables (the reference's driver shape over khd_*): --check compares every count / find answer
+    with a host gold map that applies the reducer in input order -- for FIRST / LAST on several GPUs that is the exchange
+    order (sender slice, then position) the reference's owner ranks see; after erasing every key the map must be empty"""
+    if kh.device_count() < gpus:
+        pytest.skip("needs %d GPUs" % gpus)
+    exe = os.path.join(ROOT, "drivers", "BenchmarkDistHashTables")
+    r = subprocess.run([exe, "-C", "400000", "-R", "4", "-G", str(gpus), "-I", index, "--check", "--missing-frac", "0"],
+                       capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stdout + r.stderr
+    assert "0 mismatches" in r.stdout
+    for phase in ("init", "copy_insert", "insert", "count", "find", "erase"):
+        assert phase in r.stdout
+    r = subprocess.run([exe, "-C", "200000", "-R", "8", "-G", str(gpus), "-I", index, "--check", "--missing-frac", "0.25"],
+                       capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0 and "0 mismatches" in r.stdout, r.stdout + r.stderr

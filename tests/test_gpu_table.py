@@ -812,3 +812,34 @@ def test_capacity_follows_compiled_reference_over_overlapping_batches(kh, oracle
         rm.insert(keys, default=1)
         assert m.size() == rm.size()
         assert m.capacity() == rm.capacity(), (batch, m.capacity(), rm.capacity())
+
+
+@pytest.mark.parametrize("W,exact,skew", [(1, "0", 0.0), (1, "1", 0.0), (2, "0", 0.0), (2, "1", 0.0), (1, "0", 0.3), (1, "0", 0.9)])
+def test_bulk_insert_level2_split(kh, oracle_mod, monkeypatch, W, exact, skew):
+    """tables with more tiles than level-1 regions (forced here with 64 regions; reached without forcing above 2^25 slots):
+    the level-2 split of every region into its tiles, in slab mode (default: no histogram pass, overflow list) and in exact
+    mode (histogram -> scan -> scatter), 8- and 16-byte keys, a second batch into the filled table, and skewed batches whose
+    hot key overflows its tile's slab (30 %) or the overflow list itself (90 %: the general route takes over)."""
+    import torch
+    monkeypatch.setenv("KH_BULK_LP", "6")
+    monkeypatch.setenv("KH_L2_EXACT", exact)
+    o = oracle_mod.port
+    rng = np.random.default_rng(77 + W)
+    distinct, n = 1_200_000, 2_500_000
+    base = rng.integers(0, 2**62, size=(distinct, W), dtype=np.uint64)
+    m = kh.HashMap(W, "MURMUR64avx", "COUNT")
+    m.set_insert_window(True, 32 << 20, 1 << 20)
+    gm = o.Map(W, "COUNT")
+    for batch in range(2):
+        keys = base[rng.integers(0, distinct, size=n)]
+        if skew:
+            keys[rng.random(n) < skew] = base[7]
+        keys = np.ascontiguousarray(keys if W == 2 else keys[:, 0])
+        new = m.insert(torch.from_numpy(keys.view(np.int64)).cuda(), default=1)
+        before = gm.size()
+        gm.insert(keys, default=1)
+        assert new == gm.size() - before and m.size() == gm.size()
+        assert skew >= 0.5 or m.capacity() >= 128 * 8192 // W        # more than 64 tiles: level 2 ran
+        ek, ev = sort_pairs(*gm.to_vector())
+        tk, tv = sort_pairs(*m.to_vector())
+        assert np.array_equal(tk, ek) and np.array_equal(tv, ev)
