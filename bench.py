@@ -652,8 +652,13 @@ def ours_multi(args):
     step_log = []                                                     # rank 0's per-step times (device and e2e runs)
 
     def run(k_in, q_in, to_host):
+        f = None
         for _ in range(args.warmup):
-            step(k_in, q_in, to_host)
+            # the SAME object lifetimes as the timed loop: the previous step's result stays referenced while the next step
+            # allocates its own, so the caching allocator reaches its steady state (two result blocks) during the warm-up.
+            # (Round 1's "one slow find step per run" was exactly that: the first cudaMalloc of a second 40 MB block, inside
+            # the second timed step -- 2-50 ms with IPC-mapped peer buffers present.)
+            _, _, f, _ = step(k_in, q_in, to_host)
         gc.collect(); gc.disable()                                    # no collector pause inside a sub-millisecond phase
         ti, tf, xb = [], [], 0
         for _ in range(args.steps):

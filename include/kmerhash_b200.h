@@ -315,6 +315,13 @@ int khx_scatter_slabs_dev(kh_table *t, int dist_hash, uint32_t dist_seed, const 
 int64_t khx_insert_pipelined_dev(kh_table *t, khx_peer *x, int dist_hash, uint32_t dist_seed, const uint64_t *d_keys, uint64_t n,
                                  uint64_t slab_cap, int parity, int chunks, uint64_t epoch0, uint32_t default_val,
                                  uint64_t *counts_matrix, int *overflowed);
+/* k-mer generation fused with the sender (SURVEY.md 2.4 "fused with k-mer gen on the way in"; KmerParser -> transform_input ->
+ * assign_count_permute of the reference, KI/io/kmer_parser.hpp:232-293, KH/distributed_batched_robinhood_map.hpp:632-741): reads ->
+ * canonical k-mers -> owner -> peer stores, one kernel, the k-mers never written to this GPU's memory.  d_counts as for
+ * khx_scatter_slabs_dev.  KH_ERR_FULL: EOL-dense input the tile kernel cannot decide -- generate with kh_kmers_from_reads_dev and
+ * send with khx_scatter_slabs_dev instead (what was stored meanwhile is to be ignored). */
+int khx_kmers_scatter_slabs_dev(kh_table *t, const char *d_bases, const uint64_t *d_offsets, uint64_t n_reads, int k, int canonical,
+                                int dist_hash, uint32_t dist_seed, khx_peer *x, uint64_t slab_cap, int parity, uint64_t *d_counts);
 /* Teardown of IPC-mapped buffers is collective: every rank khx_peer_close_imports -> a barrier of the caller's -> every
  * rank khx_peer_destroy (which frees the exported allocation).  khx_peer_poisoned: a barrier on these buffers timed out
  * (on this rank or, seen through the poison flag, on a peer); every later khx_peer_sync_dev fails until they are recreated. */

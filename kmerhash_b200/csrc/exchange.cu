@@ -20,6 +20,7 @@
 #include "kh_hll.cuh"
 #include "kh_window.cuh"
 #include "kh_bulk.cuh"
+#include "kh_kmergen.cuh"
 
 namespace kh {
 
@@ -622,6 +623,70 @@ int khx_scatter_slabs_dev(kh_table *t, int dist_hash, uint32_t dist_seed, const 
       else KH_LAUNCH((scatter_slabs_kernel<2, false, false>), grid, PS_BLOCK, smem, s, d_keys, n, dist, t->hash_kind, t->hp, dst,
                      (unsigned long long)slab_cap, cursors, (unsigned long long *)nullptr, (uint32_t *)nullptr);
     }
+    return KH_OK;
+  });
+}
+
+// k-mer generation FUSED with the sender ("fused with k-mer gen on the way in"): the tile kernel of
+// kh_kmergen.cuh in SCATTER mode -- reads -> canonical k-mers in a shared-memory tile -> dist hash -> owner -> peer stores
+// into this rank's slab of the owner's buffer.  The k-mers never exist as an array in this GPU's HBM (8 B written + 8 B read
+// per k-mer saved).  d_counts (DEVICE, p words) as for khx_scatter_slabs_dev.  Returns KH_OK, or KH_ERR_FULL when the input
+// holds more EOL characters inside a window than a tile's context (nothing usable was stored: the caller generates the
+// k-mers with kh_kmers_from_reads_dev and sends them with khx_scatter_slabs_dev).  Synchronises the table's stream.
+int khx_kmers_scatter_slabs_dev(kh_table *t, const char *d_bases, const uint64_t *d_offsets, uint64_t n_reads, int k, int canonical,
+                                int dist_hash, uint32_t dist_seed, khx_peer *x, uint64_t slab_cap, int parity, uint64_t *d_counts) {
+  return (int)guarded([&]() -> int64_t {
+    if (!t || !x || !d_counts || (n_reads && (!d_bases || !d_offsets))) { set_error("null argument"); return KH_ERR_INVALID; }
+    if (k < 1 || k > 32 * t->W || kmer_words(k) != t->W || !hash_kind_supported(dist_hash) || x->W != t->W || x->p > (uint32_t)WIN_MAX_DST ||
+        parity < 0 || parity > 1 || 2ULL * x->p * slab_cap > x->capacity) {
+      set_error("khx_kmers_scatter_slabs_dev: bad arguments (k must match the table's key width)"); return KH_ERR_INVALID;
+    }
+    DeviceGuard g(t->device);
+    cudaStream_t s = t->stream[0];
+    const uint32_t p = x->p;
+    const int W = t->W;
+    KH_CUDA(cudaMemsetAsync(d_counts, 0, p * sizeof(unsigned long long), s));
+    if (n_reads == 0) { KH_CUDA(cudaStreamSynchronize(s)); return KH_OK; }
+    uint64_t h_off[2] = {0, 0};
+    KH_CUDA(cudaMemcpyAsync(&h_off[0], d_offsets, sizeof(uint64_t), cudaMemcpyDeviceToHost, s));
+    KH_CUDA(cudaMemcpyAsync(&h_off[1], d_offsets + n_reads, sizeof(uint64_t), cudaMemcpyDeviceToHost, s));
+    KH_CUDA(cudaStreamSynchronize(s));
+    if (h_off[1] <= h_off[0]) return KH_OK;
+    GenArgs a{};
+    a.delta = (uint64_t)(reinterpret_cast<uintptr_t>(d_bases) & 15u);
+    a.bases = reinterpret_cast<const unsigned char *>(d_bases) - a.delta;
+    a.offsets = d_offsets; a.n_reads = n_reads;
+    a.first = h_off[0] + a.delta; a.end = h_off[1] + a.delta;
+    a.k = k; a.canonical = canonical;
+    a.n_tiles = (a.end + GEN_SPAN - 1) / GEN_SPAN;
+    a.out_keys = nullptr; a.out_cap = 0; a.state = nullptr;
+    const int dk = fold_kind(dist_hash);
+    a.dist = BinSpec{1, 0, p, dk, make_hash_params(dk, dist_seed, W)};
+    for (uint32_t r = 0; r < p; ++r) {
+      if (!x->remote[r]) { set_error("peer %u not mapped", r); return KH_ERR_INVALID; }
+      a.dst.base[r] = x->remote[r] + ((uint64_t)parity * p + x->rank) * slab_cap * W;
+    }
+    a.slab_cap = slab_cap;
+    a.cursors = reinterpret_cast<unsigned long long *>(d_counts);
+    DevBuf<uint64_t> tile_read(a.n_tiles);
+    DevBuf<int> flag(1);
+    KH_CUDA(cudaMemsetAsync(flag.p, 0, sizeof(int), s));
+    KH_LAUNCH(gen_tile_reads_kernel, (int)((a.n_tiles + 255) / 256), 256, 0, s, d_offsets, n_reads, a.delta, a.n_tiles, tile_read.p);
+    a.tile_read = tile_read.p; a.fallback = flag.p;
+    const size_t smem = W == 1 ? gen_smem_bytes<1>(true) : gen_smem_bytes<2>(true);
+    const int per_sm = std::max<int>(1, std::min<int>(2, (int)((227 * 1024) / (smem + 3 * 1024))));
+    const int grid = (int)std::min<uint64_t>(a.n_tiles, (uint64_t)t->sms * per_sm);
+    if (W == 1) {
+      KH_CUDA(cudaFuncSetAttribute((kmer_tiles_kernel<1, true>), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+      KH_LAUNCH((kmer_tiles_kernel<1, true>), grid, GEN_THREADS, smem, s, a);
+    } else {
+      KH_CUDA(cudaFuncSetAttribute((kmer_tiles_kernel<2, true>), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+      KH_LAUNCH((kmer_tiles_kernel<2, true>), grid, GEN_THREADS, smem, s, a);
+    }
+    int h_flag = 0;
+    KH_CUDA(cudaMemcpyAsync(&h_flag, flag.p, sizeof(int), cudaMemcpyDeviceToHost, s));
+    KH_CUDA(cudaStreamSynchronize(s));
+    if (h_flag) { set_error("khx_kmers_scatter_slabs_dev: EOL-dense input, use the two-step path"); return KH_ERR_FULL; }
     return KH_OK;
   });
 }

@@ -29,6 +29,7 @@
 #include <cub/block/block_scan.cuh>
 #include "kh_kmer.cuh"
 #include "kh_table.cuh"
+#include "kh_window.cuh"
 
 namespace kh {
 
@@ -55,11 +56,19 @@ struct GenArgs {
   uint64_t *out_keys;              // may be null: count only
   uint64_t out_cap;
   int *fallback;
+  // SCATTER mode (fused with the multi-GPU sender, exchange.cu): the tile's k-mers do not go to out_keys but straight to their
+  // OWNER's slab: dist hash -> owner, tile sorted by owner in shared memory, runs stored through peer pointers (NVLink).
+  // Output order is free there (COUNT commutes), so no look-back: one global atomicAdd per (tile, owner) on `cursors`.
+  BinSpec dist;
+  BinDst dst;
+  unsigned long long slab_cap;
+  unsigned long long *cursors;     // [p]: ends as the number of k-mers this rank has for every owner
 };
 
-template <int W> constexpr size_t gen_smem_bytes() {
-  // out tile | packed codes (u32) | N bits | start bits | per-thread clean mask + compact base
-  return (size_t)GEN_SPAN * 8 * W + (size_t)(GEN_BITS / 16) * 4 + 2 * (size_t)(GEN_BITS / 32) * 4 + (size_t)GEN_THREADS * 8 + 64;
+template <int W> constexpr size_t gen_smem_bytes(bool scatter = false) {
+  // out tile | packed codes (u32) | N bits | start bits | per-thread clean mask + compact base | SCATTER: sorted index of the tile
+  return (size_t)GEN_SPAN * 8 * W + (size_t)(GEN_BITS / 16) * 4 + 2 * (size_t)(GEN_BITS / 32) * 4 + (size_t)GEN_THREADS * 8 + 64 +
+         (scatter ? (size_t)GEN_SPAN * 2 : 0);
 }
 
 // 64 bits starting at bit position `bit` of a little-endian u32 array
@@ -94,12 +103,14 @@ __device__ __forceinline__ uint32_t mask4(uint32_t m) { return ((m >> 7) * 0x010
 __device__ __forceinline__ uint32_t spread4(uint32_t m) { return ((m >> 7) * 0x01041040u) >> 24; }
 
 // Consumer: what happens to a tile's k-mers.  store(): coalesced copy of the shared-memory tile to out_keys (the stand-alone API).
-template <int W>
-__global__ void __launch_bounds__(GEN_THREADS, 2) kmer_tiles_kernel(const GenArgs a) {
+template <int W, bool SCATTER>
+__global__ void __launch_bounds__(GEN_THREADS, 2) kmer_tiles_kernel(const __grid_constant__ GenArgs a) {
   using Scan = cub::BlockScan<uint32_t, GEN_THREADS>;
   __shared__ typename Scan::TempStorage scan_tmp;
   __shared__ unsigned long long s_base;
   __shared__ uint32_t s_firstbreak;
+  __shared__ uint32_t s_cnt[WIN_MAX_DST], s_lo[WIN_MAX_DST + 1];
+  __shared__ unsigned long long s_gbase[WIN_MAX_DST];
   extern __shared__ __align__(16) unsigned char gen_smem[];
   uint64_t *otile = reinterpret_cast<uint64_t *>(gen_smem);
   uint32_t *pc = reinterpret_cast<uint32_t *>(otile + (size_t)GEN_SPAN * W);   // 2 bits per compact position
@@ -107,6 +118,7 @@ __global__ void __launch_bounds__(GEN_THREADS, 2) kmer_tiles_kernel(const GenArg
   uint32_t *sb = nb + GEN_BITS / 32;                                            // 1 bit: a read starts here
   uint32_t *cbase = sb + GEN_BITS / 32;                                         // [GEN_THREADS] compact index of the thread's first byte
   uint32_t *cmask = cbase + GEN_THREADS;                                        // [GEN_THREADS] clean mask of the thread's 16 bytes
+  uint16_t *sidx = reinterpret_cast<uint16_t *>(cmask + GEN_THREADS + 16);      // SCATTER: [GEN_SPAN] tile position of every sorted k-mer
   const int tid = threadIdx.x, lane = tid & 31;
   const int k = a.k;
   const int topbits = 2 * k - 64 * (W - 1);
@@ -240,7 +252,7 @@ __global__ void __launch_bounds__(GEN_THREADS, 2) kmer_tiles_kernel(const GenArg
     Scan(scan_tmp).ExclusiveSum((uint32_t)__popc(vmask), obase, ototal);
 
     // ---- look-back: where this tile's output starts -------------------------------------------------------------------------------
-    if (tid >= GEN_THREADS - 32) {                            // the last warp generates nothing (GEN_SPAN / GEN_RUN = 480 runs)
+    if (!SCATTER && tid >= GEN_THREADS - 32) {                // the last warp generates nothing (GEN_SPAN / GEN_RUN = 480 runs)
       unsigned long long sum = 0;
       if (tile == 0) {
         if (lane == 0) atomicExch(&a.state[0], GEN_ST_INC | (unsigned long long)ototal);
@@ -269,7 +281,8 @@ __global__ void __launch_bounds__(GEN_THREADS, 2) kmer_tiles_kernel(const GenArg
     }
 
     // ---- 4. rolling generation into the shared-memory out tile ------------------------------------------------------------------
-    if (a.out_keys && vmask) {
+    if (SCATTER && tid < WIN_MAX_DST) s_cnt[tid] = 0;
+    if ((SCATTER || a.out_keys) && vmask) {
       // window ending at j0 - 1, little-endian (oldest base lowest): the top k of the 32 W positions in front of j0
       uint64_t x[W], fwd[W], rc[W];
       const uint32_t hb = 2u * (j0 + GEN_PAD - 32u * W);
@@ -317,8 +330,61 @@ __global__ void __launch_bounds__(GEN_THREADS, 2) kmer_tiles_kernel(const GenArg
     }
     __syncthreads();
 
+    // ---- SCATTER: the tile leaves for its owners -----------------------------------------------------------------------------------------
+    if constexpr (SCATTER) {
+      constexpr int PER = (GEN_SPAN + GEN_THREADS - 1) / GEN_THREADS;            // k-mers per thread, strided
+      const uint32_t p = a.dist.p;
+      const uint32_t lt_mask = (1u << lane) - 1u;
+      uint32_t own_loc[PER];                                                     // owner (4 bits) | rank inside the owner's run of this tile
+#pragma unroll
+      for (int j = 0; j < PER; ++j) {
+        const uint32_t i = (uint32_t)j * GEN_THREADS + tid;
+        uint32_t own = 0xffu;
+        if (i < ototal) {
+          uint64_t key[W];
+#pragma unroll
+          for (int q = 0; q < W; ++q) key[q] = otile[(size_t)i * W + q];
+          own = bin_of<W>(a.dist, key);
+        }
+        // one shared-memory atomic per (warp, owner)
+        const uint32_t peers = __match_any_sync(FULL_MASK, own);
+        uint32_t start = 0;
+        if (own != 0xffu && (peers & lt_mask) == 0) start = atomicAdd(&s_cnt[own], (uint32_t)__popc(peers));
+        start = __shfl_sync(FULL_MASK, start, __ffs(peers) - 1);
+        own_loc[j] = (own << 16) | (start + __popc(peers & lt_mask));
+      }
+      __syncthreads();
+      if (tid < (int)p) {
+        uint32_t st = 0;
+        for (uint32_t r = 0; r < (uint32_t)tid; ++r) st += s_cnt[r];
+        const uint32_t c = s_cnt[tid];
+        s_lo[tid] = st;
+        if (tid == (int)p - 1) s_lo[p] = st + c;
+        s_gbase[tid] = c ? atomicAdd(&a.cursors[tid], (unsigned long long)c) : 0ULL;
+      }
+      __syncthreads();
+#pragma unroll
+      for (int j = 0; j < PER; ++j) {
+        const uint32_t i = (uint32_t)j * GEN_THREADS + tid;
+        if (i < ototal) sidx[s_lo[own_loc[j] >> 16] + (own_loc[j] & 0xffffu)] = (uint16_t)i;
+      }
+      __syncthreads();
+      // sorted tile out: consecutive threads = consecutive positions inside an owner's run
+      for (uint32_t e = tid; e < ototal; e += GEN_THREADS) {
+        uint32_t r = 0;
+#pragma unroll
+        for (int q = 1; q < WIN_MAX_DST; ++q) r += (q < (int)p && e >= s_lo[q]) ? 1u : 0u;
+        const unsigned long long gpos = s_gbase[r] + (e - s_lo[r]);
+        if (gpos < a.slab_cap) {
+          const uint32_t src = sidx[e];
+          uint64_t *o = a.dst.base[r] + gpos * W;
+#pragma unroll
+          for (int q = 0; q < W; ++q) o[q] = otile[(size_t)src * W + q];
+        }
+      }
+    }
     // ---- the tile leaves: coalesced stores ------------------------------------------------------------------------------------------
-    if (a.out_keys) {
+    if (!SCATTER && a.out_keys) {
       const uint64_t gbase = s_base;
       uint64_t room = a.out_cap > gbase ? a.out_cap - gbase : 0;
       const uint32_t cnt = (uint32_t)min((uint64_t)ototal, room);

@@ -198,11 +198,11 @@ int64_t kmers_from_reads_dev(int device, const char *d_bases, const uint64_t *d_
   const int per_sm = std::max<int>(1, std::min<int>(2, (int)((227 * 1024) / (smem + 1024))));
   const int grid = (int)std::min<uint64_t>(a.n_tiles, (uint64_t)sms * per_sm);
   if (W == 1) {
-    KH_CUDA(cudaFuncSetAttribute(kmer_tiles_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    KH_LAUNCH(kmer_tiles_kernel<1>, grid, GEN_THREADS, smem, 0, a);
+    KH_CUDA(cudaFuncSetAttribute((kmer_tiles_kernel<1, false>), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    KH_LAUNCH((kmer_tiles_kernel<1, false>), grid, GEN_THREADS, smem, 0, a);
   } else {
-    KH_CUDA(cudaFuncSetAttribute(kmer_tiles_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    KH_LAUNCH(kmer_tiles_kernel<2>, grid, GEN_THREADS, smem, 0, a);
+    KH_CUDA(cudaFuncSetAttribute((kmer_tiles_kernel<2, false>), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    KH_LAUNCH((kmer_tiles_kernel<2, false>), grid, GEN_THREADS, smem, 0, a);
   }
   unsigned long long last = 0;
   int h_flag = 0;

@@ -187,6 +187,9 @@ class CudaEngine:
         peers.epoch += chunks
         return got, C, over
 
+    def kmers_scatter_slabs(self, bases, offsets, k, canonical, peers, slab_cap, parity, counts):
+        return self.table.kmers_scatter_slabs(bases, offsets, k, canonical, peers.h, slab_cap, parity, counts, self.dist_hash)
+
     def scatter_slabs(self, keys, peers, slab_cap, parity, counts, reset=True, synced=False):
         self.table.scatter_slabs(keys, peers.h, slab_cap, parity, counts, reset, self.dist_hash, synced=synced)
 
@@ -421,13 +424,32 @@ class DistributedMap:
             self.e.scatter_slabs(d[off:off + m], self.peers, self.slab_cap, parity, counts, reset=(off == 0), synced=True)
         return d
 
-    def _insert_slabs(self, keys, default):
+    def insert_reads(self, bases, offsets, k, canonical=True, default=1):
+        """BenchmarkKmerCounter's hot path (KmerParser -> transform_input -> insert, KI/index/kmer_index.hpp:99-225) on device
+        buffers: `bases` uint8 CUDA tensor (reads back to back), `offsets` int64 CUDA tensor [n_reads + 1].  With peer
+        access the k-mers are generated INSIDE the sender kernel and go straight to their owners' slabs
+        (khx_kmers_scatter_slabs_dev); otherwise they are generated first and inserted like any batch.  Collective."""
+        from . import ops
+        self.last_exchange_bytes = 0
+        fused = (self.p > 1 and self.peer_stores and self.slabs and hasattr(self.e, "kmers_scatter_slabs")
+                 and getattr(self.e, "can_plan", lambda p: False)(self.p) and not self.e.ordered())
+        if not fused:
+            return self.insert(ops.kmers_from_reads_dev(bases, offsets, k, canonical), default)
+        reads = (bases, offsets, int(k), bool(canonical))
+        r = self._insert_slabs(None, default, reads=reads)
+        if r is not None:
+            return r
+        if self._dev_keys is None:                                          # overflow: the exact path wants the k-mers as an array
+            self._dev_keys = ops.kmers_from_reads_dev(bases, offsets, k, canonical)
+        return self._insert_exact(self._dev_keys, default, ordered=True)
+
+    def _insert_slabs(self, keys, default, reads=None):
         """ONE pass over the keys on the sender: dist hash -> owner -> store into this rank's slab of the owner's buffer
         (NVLink); the flag barrier that follows delivers the p x p count matrix; the receiver's bulk insert reads its p slabs
         in place, its level-1 pass computing the HyperLogLog registers the reference ships with the counts.  Returns None
         when a slab overflowed (every rank sees the same matrix, so every rank takes the exact path for this batch)."""
         p, rank, dev = self.p, self.rank, self.e.device
-        n = int(keys.shape[0])
+        n = int(keys.shape[0]) if reads is None else int(reads[0].shape[0])  # reads: every k-mer ends at its own byte
         if self.peers is None or self.slab_cap == 0:
             nmax = torch.tensor([n], dtype=torch.int64, device=dev)
             dist.all_reduce(nmax, op=dist.ReduceOp.MAX, group=self.group)
@@ -440,7 +462,7 @@ class DistributedMap:
             dist.barrier(group=self.group)
             self._exact_dirty = False
         parity = self.parity
-        if (self.pipe_chunks > 1 and torch.is_tensor(keys) and keys.is_cuda and p <= 8 and hasattr(self.e, "insert_pipelined")
+        if (reads is None and self.pipe_chunks > 1 and torch.is_tensor(keys) and keys.is_cuda and p <= 8 and hasattr(self.e, "insert_pipelined")
                 and self.slab_cap % (2 * self.pipe_chunks) == 0 and self.pipe_min_keys <= p * self.slab_cap <= 3 << 29):
             # every rank takes this branch or none: the decision rests on the slab size, which all ranks share, and on where the
             # keys live, which a collective caller keeps uniform (device tensors on every rank, or host arrays on every rank)
@@ -457,7 +479,14 @@ class DistributedMap:
             return got
         counts = torch.zeros(p, dtype=torch.int64, device=dev)
         with _Stage("scatter->slabs"):
-            self._dev_keys = self._send_slabs(keys, parity, counts)
+            if reads is None:
+                self._dev_keys = self._send_slabs(keys, parity, counts)
+            else:
+                self._dev_keys = None
+                if not self.e.kmers_scatter_slabs(reads[0], reads[1], reads[2], reads[3], self.peers, self.slab_cap, parity, counts):
+                    from . import ops                                      # EOL-dense input: generate, then send
+                    self._dev_keys = ops.kmers_from_reads_dev(*reads)
+                    self.e.scatter_slabs(self._dev_keys, self.peers, self.slab_cap, parity, counts, reset=True)
         with _Stage("sync+counts"):
             # the flag barrier: every rank's stores have landed and every rank holds the count matrix C[g][r] = keys g sends to r
             C = self.e.peer_sync(self.peers, counts)
@@ -466,6 +495,7 @@ class DistributedMap:
             self._C = C
             return None
         self._dev_keys = None
+        self.last_batch_keys = int(C[rank].sum())                          # keys (k-mers) this rank contributed
         self.slab_misses = 0
         self.parity ^= 1
         self.last_exchange_bytes += 8 * self.W * int(C[rank].sum() - C[rank, rank])

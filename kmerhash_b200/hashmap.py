@@ -215,6 +215,18 @@ class HashMap:
                     "insert_pipelined")
         return got, mat, bool(over.value)
 
+    def kmers_scatter_slabs(self, bases, offsets, k, canonical, peer_handle, slab_cap, parity, counts, dist_hash="MURMUR64avx", dist_seed=9876543):
+        """k-mer generation fused with the sender (khx_kmers_scatter_slabs_dev).  bases: uint8 CUDA tensor, offsets: int64 CUDA
+        tensor.  Returns False when the input is EOL-dense and the caller has to take the two-step path."""
+        assert bases.is_cuda and bases.dtype == torch.uint8 and offsets.is_cuda and offsets.dtype == torch.int64
+        torch.cuda.current_stream(self.device).synchronize()
+        rc = lib.khx_kmers_scatter_slabs_dev(self._h, bases.data_ptr(), offsets.data_ptr(), offsets.shape[0] - 1, int(k), int(canonical),
+                                             HASH_KINDS[dist_hash], dist_seed, peer_handle, int(slab_cap), int(parity), counts.data_ptr())
+        if rc == -4:
+            return False
+        check(rc, "kmers_scatter_slabs")
+        return True
+
     def insert_ptr(self, ptr, n, default=1, estimate=True):
         """insert n keys lying at a raw device pointer (a peer receive buffer)"""
         torch.cuda.current_stream(self.device).synchronize()

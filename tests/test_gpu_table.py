@@ -843,3 +843,64 @@ def test_bulk_insert_level2_split(kh, oracle_mod, monkeypatch, W, exact, skew):
         ek, ev = sort_pairs(*gm.to_vector())
         tk, tv = sort_pairs(*m.to_vector())
         assert np.array_equal(tk, ek) and np.array_equal(tv, ev)
+
+
+@pytest.mark.parametrize("p,k,canonical", [(2, 31, True), (8, 31, True), (4, 21, False), (2, 63, True), (8, 64, False)])
+def test_kmer_generation_fused_with_sender(kh, oracle_mod, p, k, canonical):
+    """khx_kmers_scatter_slabs_dev (k-mer tile kernel in SCATTER mode; p ranks emulated on one GPU): slab (owner r, sender g)
+    must hold exactly the k-mers of g's reads that the reference's rule sends to r -- as a multiset, order is free -- and the
+    counts must be the true ones; reads with N, EOL characters and lower case, a misaligned base pointer"""
+    import ctypes
+    import torch
+    from conftest import make_reads
+    from kmerhash_b200._lib import lib
+    o = oracle_mod.port
+    W = 1 if k <= 32 else 2
+    cudart = ctypes.CDLL("libcudart.so")
+    rng = np.random.default_rng(600 + p + k)
+    inputs = [make_reads(rng, 900, 60, 260, n_rate=0.002, eol=(g % 2 == 1), lower=True) for g in range(p)]
+    n_max = max(len(b) for b, _ in inputs)
+    tables = [kh.HashMap(W, "MURMUR64avx", "COUNT") for _ in range(p)]
+    slab_cap = (int(n_max / p * 1.6) + 4096 + 63) // 64 * 64
+    cap = 2 * p * slab_cap + 64
+    peers = [lib.khx_peer_create(0, r, p, cap, W) for r in range(p)]
+
+    def read_buf(r):
+        buf = torch.empty((cap, W), dtype=torch.int64, device="cuda")
+        torch.cuda.synchronize()
+        assert cudart.cudaMemcpy(ctypes.c_void_p(buf.data_ptr()), ctypes.c_void_p(lib.khx_peer_recv_ptr(peers[r])),
+                                 ctypes.c_size_t(cap * 8 * W), 3) == 0
+        return buf.cpu().numpy().view(np.uint64)
+
+    def srt(a):
+        a = a.reshape(-1, W)
+        return np.sort(a[:, 0]) if W == 1 else a[np.lexsort(a.T[::-1])]
+
+    try:
+        assert all(peers)
+        for r in range(p):
+            for q in range(p):
+                if q != r:
+                    assert lib.khx_peer_set(peers[r], q, lib.khx_peer_recv_ptr(peers[q])) == 0
+        parity = 1
+        counts = []
+        for g, (bases, offs) in enumerate(inputs):
+            shift = 5 * g + 1                                              # misaligned base pointer, offsets not starting at 0
+            db = torch.from_numpy(np.concatenate([np.full(shift, 65, dtype=np.uint8), bases])).cuda()
+            do = torch.from_numpy((offs + np.uint64(shift)).astype(np.int64)).cuda()
+            c = torch.zeros(p, dtype=torch.int64, device="cuda")
+            assert tables[g].kmers_scatter_slabs(db, do, k, canonical, peers[g], slab_cap, parity, c)
+            counts.append(c.cpu().numpy())
+        for r in range(p):
+            got = read_buf(r)
+            for g, (bases, offs) in enumerate(inputs):
+                km = o.kmers_from_reads(bases, offs, k, canonical)
+                own = o.rank("MURMUR64avx", km, p)
+                exp = km[own == r]
+                assert int(counts[g][r]) == len(exp)
+                lo = (parity * p + g) * slab_cap
+                assert np.array_equal(srt(got[lo:lo + len(exp)]), srt(exp)), (g, r)
+    finally:
+        for h in peers:
+            if h:
+                lib.khx_peer_destroy(h)

@@ -112,6 +112,34 @@ for n0 in SIZES:
                                                            "OK" if ok else "FAIL"), flush=True)
     m.close()                                   # collective: unmap imports -> barrier -> free
 
+# reads -> canonical 31-mers generated inside the sender kernel (DistributedMap.insert_reads): per-rank table contents against
+# the oracle's k-mers of ALL ranks' reads restricted to this rank's owner rule
+if os.environ.get("KH_PARITY_READS", "1") not in ("", "0"):
+    def reads_of(g):
+        rng = np.random.default_rng(31000 + g)
+        genome = np.frombuffer(b"ACGT", dtype=np.uint8)[rng.integers(0, 4, size=200000)]
+        L, nr = 150, 40000 + 1000 * g
+        st = rng.integers(0, len(genome) - L, size=nr)
+        b = genome[st[:, None] + np.arange(L)[None, :]].copy()
+        b[rng.random(b.shape) < 0.0005] = ord("N")
+        return b.reshape(-1), (np.arange(nr + 1, dtype=np.uint64) * np.uint64(L))
+    m = DistributedMap(1, "MURMUR64avx", "MURMUR64avx", "COUNT", device=local)
+    ref = o.Map(1, "COUNT")
+    for rep in range(2):
+        for g in range(p):
+            b, off = reads_of(g)
+            ref.insert(o.kmers_from_reads(b, off, 31, True), default=1)
+        b, off = reads_of(rank)
+        m.insert_reads(torch.from_numpy(b).cuda(), torch.from_numpy(off.astype(np.int64)).cuda(), 31, canonical=True)
+    gk, gv = ref.to_vector()
+    own = o.rank("MURMUR64avx", gk, p) == rank
+    ek, ev = sort_pairs(gk[own], gv[own])
+    tk, tv = sort_pairs(*m.to_vector())
+    good = np.array_equal(tk, ek) and np.array_equal(tv.astype(np.uint32), ev.astype(np.uint32))
+    ok = ok and good
+    print("rank %d reads->k-mers fused with the sender: %d distinct %s" % (rank, len(tk), "OK" if good else "FAIL"), flush=True)
+    m.close()
+
 flag = torch.tensor([1 if ok else 0], device="cuda")
 dist.all_reduce(flag, op=dist.ReduceOp.MIN)
 dist.barrier()
