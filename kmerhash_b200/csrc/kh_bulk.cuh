@@ -96,8 +96,6 @@ struct L1Args {
   uint64_t *ovf_keys;                  // keys whose region was full
   unsigned long long *ovf_count, ovf_cap;
   uint32_t *g_regs;                    // HLL_M registers of the table (cumulative over batches), merged with atomicMax
-  uint32_t stagger_ns;                 // CTA b starts b * stagger_ns / gridDim later: all CTAs do the same work per tile, and
-                                       // without it they reach the 2^lp region cursors (one atomic each per tile) in lockstep
 };
 
 constexpr int L1_THREADS = 1024;
@@ -185,12 +183,6 @@ __global__ void __launch_bounds__(L1_THREADS, 1) l1_scatter_kernel(const L1Args 
   uint32_t parity = 0;
   bool cur_bulk = false;
   if (blockIdx.x < n_tiles) cur_bulk = stage(blockIdx.x);
-  if (a.stagger_ns && tid == 0) {
-    unsigned long long t0, t1;
-    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
-    const unsigned long long wait = (unsigned long long)a.stagger_ns * blockIdx.x / gridDim.x;
-    do { __nanosleep(64); asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1)); } while (t1 - t0 < wait);
-  }
   __syncthreads();
 
   for (uint64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
