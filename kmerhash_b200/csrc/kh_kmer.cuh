@@ -67,4 +67,61 @@ KH_HD uint32_t dna_code(uint8_t c) {
   return (u == 'C') ? 1u : (u == 'G') ? 2u : (u == 'T') ? 3u : 0u;
 }
 
+// ---- other alphabets: DNA5 = the reference's 3-bit DNA6 table, DNA16 = 4-bit IUPAC codes -------------------
+// KI/common/alphabets.hpp:197-292 (gap 0, A 1, C 3, T 4, G 6, N/X 7, all else 2), :648-739 (. A C M G R S V T W Y H K D B N = 0..15,
+// U = T, all else 15).  A k-mer holds bits * k bits, newest base lowest; up to two words here: k <= 42 (DNA5), k <= 32 (DNA16).
+// Reverse complement of both = reversal of ALL bits of the value (KI/common/kmer.hpp:1476-1497): reversing a code's bits complements it.
+constexpr int KH_ALPHA_DNA = 4, KH_ALPHA_DNA5 = 5, KH_ALPHA_DNA16 = 16;
+KH_HD int alpha_bits(int alpha) { return alpha == KH_ALPHA_DNA ? 2 : alpha == KH_ALPHA_DNA5 ? 3 : alpha == KH_ALPHA_DNA16 ? 4 : 0; }
+KH_HD int kmer_words_alpha(int alpha, int k) { const int b = alpha_bits(alpha); return b ? (b * k + 63) / 64 : 0; }
+KH_HD uint32_t dna5_code(uint8_t c) {
+  const uint8_t u = c & 0xDF;
+  return (c == '-' || c == '.') ? 0u : (u == 'A') ? 1u : (u == 'C') ? 3u : (u == 'T') ? 4u : (u == 'G') ? 6u : (u == 'N' || u == 'X') ? 7u : 2u;
+}
+KH_HD uint32_t dna16_code(uint8_t c) {
+  if (c == '-' || c == '.') return 0u;
+  switch (c & 0xDF) {
+    case 'A': return 1u;  case 'C': return 2u;  case 'M': return 3u;  case 'G': return 4u;  case 'R': return 5u;
+    case 'S': return 6u;  case 'V': return 7u;  case 'T': case 'U': return 8u;  case 'W': return 9u;  case 'Y': return 10u;
+    case 'H': return 11u; case 'K': return 12u; case 'D': return 13u; case 'B': return 14u;
+    default: return 15u;
+  }
+}
+template <int B> KH_HD uint32_t alpha_code(uint8_t c) { return B == 2 ? dna_code(c) : B == 3 ? dna5_code(c) : dna16_code(c); }
+// complement of one code: DNA 3 - c; DNA5 / DNA16: the code's bits reversed
+template <int B> KH_HD uint32_t alpha_comp(uint32_t c) {
+  if (B == 2) return 3u - c;
+  if (B == 3) return ((c & 1u) << 2) | (c & 2u) | (c >> 2);
+  return ((c & 1u) << 3) | ((c & 2u) << 1) | ((c & 4u) >> 1) | (c >> 3);
+}
+KH_HD uint64_t brev64(uint64_t x) {
+#ifdef __CUDA_ARCH__
+  return ((uint64_t)__brev((uint32_t)x) << 32) | __brev((uint32_t)(x >> 32));
+#else
+  x = ((x >> 1) & 0x5555555555555555ULL) | ((x & 0x5555555555555555ULL) << 1);
+  x = ((x >> 2) & 0x3333333333333333ULL) | ((x & 0x3333333333333333ULL) << 2);
+  x = ((x >> 4) & 0x0F0F0F0F0F0F0F0FULL) | ((x & 0x0F0F0F0F0F0F0F0FULL) << 4);
+  x = ((x >> 8) & 0x00FF00FF00FF00FFULL) | ((x & 0x00FF00FF00FF00FFULL) << 8);
+  x = ((x >> 16) & 0x0000FFFF0000FFFFULL) | ((x & 0x0000FFFF0000FFFFULL) << 16);
+  return (x >> 32) | (x << 32);
+#endif
+}
+template <int W>
+KH_HD void kmer_revcomp_alpha(const uint64_t (&in)[W], int alpha, int k, uint64_t (&out)[W]) {
+  if (alpha == KH_ALPHA_DNA) { kmer_revcomp<W>(in, k, out); return; }
+  const int sh = 64 * W - alpha_bits(alpha) * k;   // 0 <= sh < 64
+  if (W == 1) { out[0] = brev64(in[0]) >> sh; return; }
+  const uint64_t t0 = brev64(in[W - 1]), t1 = brev64(in[0]);
+  out[0] = sh ? ((t0 >> sh) | (t1 << (64 - sh))) : t0;
+  out[W - 1] = t1 >> sh;
+}
+template <int W>
+KH_HD void kmer_canonical_alpha(const uint64_t (&in)[W], int alpha, int k, uint64_t (&out)[W]) {
+  uint64_t rc[W];
+  kmer_revcomp_alpha<W>(in, alpha, k, rc);
+  const bool fwd = kmer_less<W>(in, rc);
+#pragma unroll
+  for (int i = 0; i < W; ++i) out[i] = fwd ? in[i] : rc[i];
+}
+
 }  // namespace kh

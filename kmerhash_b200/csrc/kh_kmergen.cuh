@@ -41,6 +41,7 @@ constexpr int GEN_SPAN = GEN_TILE_BYTES - GEN_LOOKBACK;   // 7680 output positio
 constexpr int GEN_PAD = 64;                               // compact positions of zero history in front of the tile
 constexpr int GEN_RUN = 16;                               // compact positions per thread in the rolling stage
 constexpr int GEN_BITS = GEN_TILE_BYTES + GEN_PAD + 64;   // compact positions the bit arrays hold (incl. slack for 64-bit reads)
+constexpr int GEN_PC_WORDS = GEN_BITS / 8;                // packed codes: up to 4 bits per position (DNA 2, DNA5 3, DNA16 4)
 
 constexpr unsigned long long GEN_ST_AGG = 1ULL << 62, GEN_ST_INC = 2ULL << 62, GEN_ST_MASK = 3ULL << 62;
 
@@ -67,7 +68,7 @@ struct GenArgs {
 
 template <int W> constexpr size_t gen_smem_bytes(bool scatter = false) {
   // out tile | packed codes (u32) | N bits | start bits | per-thread clean mask + compact base | SCATTER: sorted index of the tile
-  return (size_t)GEN_SPAN * 8 * W + (size_t)(GEN_BITS / 16) * 4 + 2 * (size_t)(GEN_BITS / 32) * 4 + (size_t)GEN_THREADS * 8 + 64 +
+  return (size_t)GEN_SPAN * 8 * W + (size_t)GEN_PC_WORDS * 4 + 2 * (size_t)(GEN_BITS / 32) * 4 + (size_t)GEN_THREADS * 8 + 64 +
          (scatter ? (size_t)GEN_SPAN * 2 : 0);
 }
 
@@ -103,7 +104,10 @@ __device__ __forceinline__ uint32_t mask4(uint32_t m) { return ((m >> 7) * 0x010
 __device__ __forceinline__ uint32_t spread4(uint32_t m) { return ((m >> 7) * 0x01041040u) >> 24; }
 
 // Consumer: what happens to a tile's k-mers.  store(): coalesced copy of the shared-memory tile to out_keys (the stand-alone API).
-template <int W, bool SCATTER>
+// B = bits per base: 2 (DNA), 3 (DNA5), 4 (DNA16).  The DNA path classifies four bytes per step and cuts its start window out of
+// the packed codes; the other alphabets go through their code function byte by byte and roll the start window up from its
+// k - 1 bases (they are the reference's side configurations, benchmark/CMakeLists.txt:175-196, not the measured path).
+template <int W, bool SCATTER, int B = 2>
 __global__ void __launch_bounds__(GEN_THREADS, 2) kmer_tiles_kernel(const __grid_constant__ GenArgs a) {
   using Scan = cub::BlockScan<uint32_t, GEN_THREADS>;
   __shared__ typename Scan::TempStorage scan_tmp;
@@ -114,14 +118,14 @@ __global__ void __launch_bounds__(GEN_THREADS, 2) kmer_tiles_kernel(const __grid
   extern __shared__ __align__(16) unsigned char gen_smem[];
   uint64_t *otile = reinterpret_cast<uint64_t *>(gen_smem);
   uint32_t *pc = reinterpret_cast<uint32_t *>(otile + (size_t)GEN_SPAN * W);   // 2 bits per compact position
-  uint32_t *nb = pc + GEN_BITS / 16;                                            // 1 bit: N
+  uint32_t *nb = pc + GEN_PC_WORDS;                                             // 1 bit: N
   uint32_t *sb = nb + GEN_BITS / 32;                                            // 1 bit: a read starts here
   uint32_t *cbase = sb + GEN_BITS / 32;                                         // [GEN_THREADS] compact index of the thread's first byte
   uint32_t *cmask = cbase + GEN_THREADS;                                        // [GEN_THREADS] clean mask of the thread's 16 bytes
   uint16_t *sidx = reinterpret_cast<uint16_t *>(cmask + GEN_THREADS + 16);      // SCATTER: [GEN_SPAN] tile position of every sorted k-mer
   const int tid = threadIdx.x, lane = tid & 31;
   const int k = a.k;
-  const int topbits = 2 * k - 64 * (W - 1);
+  const int topbits = B * k - 64 * (W - 1);
   const uint64_t topmask = topbits >= 64 ? ~0ULL : ((1ULL << topbits) - 1ULL);
 
   // the 16 bytes of this thread in tile t; bytes outside [first, end) read as EOL
@@ -143,7 +147,7 @@ __global__ void __launch_bounds__(GEN_THREADS, 2) kmer_tiles_kernel(const __grid
 
   for (uint64_t tile = blockIdx.x; tile < a.n_tiles; tile += gridDim.x) {
     // bit arrays zero (the previous tile's readers are behind the barrier at the end of the loop body)
-    for (int i = tid; i < GEN_BITS / 16 + 2 * (GEN_BITS / 32); i += GEN_THREADS) pc[i] = 0;
+    for (int i = tid; i < GEN_PC_WORDS + 2 * (GEN_BITS / 32); i += GEN_THREADS) pc[i] = 0;
     if (tid == 0) { s_firstbreak = 0xffffffffu; s_base = a.tile_read[tile]; }
     // byte positions (relative to the aligned origin) [lo, hi): lo is negative for tile 0
     const int64_t lo = (int64_t)(tile * GEN_SPAN) - GEN_LOOKBACK;
@@ -151,8 +155,22 @@ __global__ void __launch_bounds__(GEN_THREADS, 2) kmer_tiles_kernel(const __grid
     if (tile + gridDim.x < a.n_tiles) vnext = fetch(tile + gridDim.x);          // in flight while this tile is processed
 
     // ---- 1. classify: four bytes at a time --------------------------------------------------------------------------------
-    uint32_t clean = 0, nmask = 0, codes = 0;
-    {
+    uint32_t clean = 0, nmask = 0;
+    uint64_t codes = 0;                                                         // B bits per clean base, 16 bases at most
+    if constexpr (B != 2) {
+      unsigned char c[16];
+      memcpy(c, &v, 16);
+      int m = 0;
+#pragma unroll
+      for (int i = 0; i < 16; ++i) {
+        if (c[i] != '\n' && c[i] != '\r') {
+          clean |= 1u << i;
+          codes |= (uint64_t)alpha_code<B>(c[i]) << (B * m);
+          nmask |= ((c[i] == 'N' || c[i] == 'n') ? 1u : 0u) << m;
+          ++m;
+        }
+      }
+    } else {
       const uint32_t w[4] = {v.x, v.y, v.z, v.w};
       uint32_t skip16 = 0;
 #pragma unroll
@@ -161,7 +179,7 @@ __global__ void __launch_bounds__(GEN_THREADS, 2) kmer_tiles_kernel(const __grid
         const uint32_t eC = eq4(u, 0x43434343u), eG = eq4(u, 0x47474747u), eT = eq4(u, 0x54545454u), eN = eq4(u, 0x4E4E4E4Eu);
         const uint32_t eol = eq4(w[q], 0x0A0A0A0Au) | eq4(w[q], 0x0D0D0D0Du);
         skip16 |= mask4(eol) << (4 * q);
-        codes |= (spread4(eC | eT) | (spread4(eG | eT) << 1)) << (8 * q);       // DNA::FROM_ASCII: A 0, C 1, G 2, T 3, all else 0
+        codes |= (uint64_t)((spread4(eC | eT) | (spread4(eG | eT) << 1)) << (8 * q));   // DNA::FROM_ASCII: A 0, C 1, G 2, T 3, all else 0
         nmask |= mask4(eN) << (4 * q);
       }
       clean = ~skip16 & 0xffffu;
@@ -171,7 +189,7 @@ __global__ void __launch_bounds__(GEN_THREADS, 2) kmer_tiles_kernel(const __grid
 #pragma unroll
         for (int i = 0; i < 16; ++i) {
           if ((clean >> i) & 1u) {
-            cc |= ((codes >> (2 * i)) & 3u) << (2 * m);
+            cc |= ((uint32_t)(codes >> (2 * i)) & 3u) << (2 * m);
             nn |= ((nmask >> i) & 1u) << m;
             ++m;
           }
@@ -184,10 +202,13 @@ __global__ void __launch_bounds__(GEN_THREADS, 2) kmer_tiles_kernel(const __grid
     Scan(scan_tmp).ExclusiveSum(nclean, cb, ctotal);
     cbase[tid] = cb; cmask[tid] = clean;
     if (nclean) {
-      const uint32_t bit = 2u * (cb + GEN_PAD);
-      const uint64_t v = (uint64_t)codes << (bit & 31u);
-      atomicOr(&pc[bit >> 5], (uint32_t)v);
-      if (v >> 32) atomicOr(&pc[(bit >> 5) + 1], (uint32_t)(v >> 32));
+      const uint32_t bit = (uint32_t)B * (cb + GEN_PAD);
+      const uint32_t sh0 = bit & 31u;
+      const uint64_t vlo = codes << sh0;                                        // 64 code bits shifted by < 32: up to three words
+      const uint32_t vhi = sh0 ? (uint32_t)(codes >> (64 - sh0)) : 0u;
+      atomicOr(&pc[bit >> 5], (uint32_t)vlo);
+      if (vlo >> 32) atomicOr(&pc[(bit >> 5) + 1], (uint32_t)(vlo >> 32));
+      if (vhi) atomicOr(&pc[(bit >> 5) + 2], vhi);
       if (nmask) {
         const uint32_t nbit = cb + GEN_PAD;
         const uint64_t nv = (uint64_t)nmask << (nbit & 31u);
@@ -283,43 +304,62 @@ __global__ void __launch_bounds__(GEN_THREADS, 2) kmer_tiles_kernel(const __grid
     // ---- 4. rolling generation into the shared-memory out tile ------------------------------------------------------------------
     if (SCATTER && tid < WIN_MAX_DST) s_cnt[tid] = 0;
     if ((SCATTER || a.out_keys) && vmask) {
-      // window ending at j0 - 1, little-endian (oldest base lowest): the top k of the 32 W positions in front of j0
-      uint64_t x[W], fwd[W], rc[W];
-      const uint32_t hb = 2u * (j0 + GEN_PAD - 32u * W);
-      if (W == 1) {
-        x[0] = bits64(pc, hb) >> (64 - 2 * k);                // k >= 1
-      } else {
-        const uint64_t h0 = bits64(pc, hb), h1 = bits64(pc, hb + 64);
-        const int s = 128 - 2 * k;                            // 0 <= s < 64 for 33 <= k <= 64
-        x[0] = s ? ((h0 >> s) | (h1 << (64 - s))) : h0;
-        x[W - 1] = h1 >> s;
-      }
-      // forward k-mer = 2-bit groups of x reversed (newest base lowest); reverse complement = ~x
-      const int sh = 64 * W - 2 * k;
-      if (W == 1) fwd[0] = rev2bit64(x[0] << sh);
-      else {
-        // reverse the 128-bit value (x << sh): words swap and reverse
-        const uint64_t y0 = sh ? (x[0] << sh) : x[0];
-        const uint64_t y1 = sh ? ((x[W - 1] << sh) | (x[0] >> (64 - sh))) : x[W - 1];
-        fwd[0] = rev2bit64(y1); fwd[W - 1] = rev2bit64(y0);
-      }
+      uint64_t fwd[W], rc[W];
+      if constexpr (B == 2) {
+        // window ending at j0 - 1, little-endian (oldest base lowest): the top k of the 32 W positions in front of j0
+        uint64_t x[W];
+        const uint32_t hb = 2u * (j0 + GEN_PAD - 32u * W);
+        if (W == 1) {
+          x[0] = bits64(pc, hb) >> (64 - 2 * k);                // k >= 1
+        } else {
+          const uint64_t h0 = bits64(pc, hb), h1 = bits64(pc, hb + 64);
+          const int s = 128 - 2 * k;                            // 0 <= s < 64 for 33 <= k <= 64
+          x[0] = s ? ((h0 >> s) | (h1 << (64 - s))) : h0;
+          x[W - 1] = h1 >> s;
+        }
+        // forward k-mer = 2-bit groups of x reversed (newest base lowest); reverse complement = ~x
+        const int sh = 64 * W - 2 * k;
+        if (W == 1) fwd[0] = rev2bit64(x[0] << sh);
+        else {
+          // reverse the 128-bit value (x << sh): words swap and reverse
+          const uint64_t y0 = sh ? (x[0] << sh) : x[0];
+          const uint64_t y1 = sh ? ((x[W - 1] << sh) | (x[0] >> (64 - sh))) : x[W - 1];
+          fwd[0] = rev2bit64(y1); fwd[W - 1] = rev2bit64(y0);
+        }
 #pragma unroll
-      for (int q = 0; q < W; ++q) rc[q] = ~x[q];
-      rc[W - 1] &= topmask;
-      const uint32_t nxt = (uint32_t)bits64(pc, 2u * (j0 + GEN_PAD));
+        for (int q = 0; q < W; ++q) rc[q] = ~x[q];
+        rc[W - 1] &= topmask;
+      } else {
+#pragma unroll
+        for (int q = 0; q < W; ++q) { fwd[q] = 0; rc[q] = 0; }
+      }
+      // one step of both windows: the new base enters fwd at the bottom, its complement enters rc at the top
+      const int tp = B * (k - 1);                               // bit position of the oldest base of fwd = newest of rc
+      auto roll = [&](uint64_t c) {
+        const uint64_t cc = (uint64_t)alpha_comp<B>((uint32_t)c);
+        if (W == 1) {
+          fwd[0] = ((fwd[0] << B) | c) & topmask;
+          rc[0] = (rc[0] >> B) | (cc << tp);
+        } else {
+          fwd[W - 1] = ((fwd[W - 1] << B) | (fwd[0] >> (64 - B))) & topmask;
+          fwd[0] = (fwd[0] << B) | c;
+          rc[0] = (rc[0] >> B) | (rc[W - 1] << (64 - B));
+          rc[W - 1] >>= B;
+          if (tp >= 64) rc[W - 1] |= cc << (tp - 64);
+          else { rc[0] |= cc << tp; if (tp + B > 64) rc[W - 1] |= cc >> (64 - tp); }
+        }
+      };
+      if constexpr (B != 2) {                                   // start windows rolled up from the k - 1 bases in front of j0
+        for (int i = k - 1; i >= 1; --i) {
+          const uint32_t bit = (uint32_t)B * (j0 + GEN_PAD - (uint32_t)i);
+          roll((uint64_t)(__funnelshift_r(pc[bit >> 5], pc[(bit >> 5) + 1], bit & 31u) & ((1u << B) - 1u)));
+        }
+      }
+      const uint64_t nxt = bits64(pc, (uint32_t)B * (j0 + GEN_PAD));
       uint32_t o = obase;
 #pragma unroll
       for (int i = 0; i < GEN_RUN; ++i) {
-        const uint64_t c = (nxt >> (2 * i)) & 3u;
-        if (W == 1) {
-          fwd[0] = ((fwd[0] << 2) | c) & topmask;
-          rc[0] = (rc[0] >> 2) | ((3ULL - c) << (2 * k - 2));
-        } else {
-          fwd[W - 1] = ((fwd[W - 1] << 2) | (fwd[0] >> 62)) & topmask;
-          fwd[0] = (fwd[0] << 2) | c;
-          rc[0] = (rc[0] >> 2) | (rc[W - 1] << 62);
-          rc[W - 1] = (rc[W - 1] >> 2) | ((3ULL - c) << (topbits - 2));
-        }
+        roll((nxt >> (B * i)) & ((1u << B) - 1u));
         if ((vmask >> i) & 1u) {
           const bool use_rc = a.canonical && !kmer_less<W>(fwd, rc);
 #pragma unroll

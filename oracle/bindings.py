@@ -56,6 +56,13 @@ class _Port:
         L.orc_kmers_from_reads.restype = C.c_long
         L.orc_rank.argtypes = [C.c_int, C.c_int, _u64p, C.c_size_t, C.c_uint32, _u32p]
         L.orc_rank.restype = C.c_int
+        L.orc_kmer_words_alpha.argtypes = [C.c_int, C.c_int]
+        L.orc_kmer_windows_alpha.argtypes = [C.c_int, C.c_int, C.c_char_p, C.c_size_t, _u64p]
+        L.orc_kmer_windows_alpha.restype = C.c_long
+        L.orc_revcomp_alpha.argtypes = [C.c_int, C.c_int, _u64p, C.c_size_t, _u64p]
+        L.orc_canonical_alpha.argtypes = [C.c_int, C.c_int, _u64p, C.c_size_t, _u64p]
+        L.orc_kmers_from_reads_alpha.argtypes = [C.c_int, C.c_char_p, _u64p, C.c_size_t, C.c_int, C.c_int, C.c_void_p]
+        L.orc_kmers_from_reads_alpha.restype = C.c_long
         L.orc_hll_update.argtypes = [_u8p, _u64p, C.c_size_t, C.c_int]
         L.orc_hll_estimate.argtypes = [_u8p, C.c_int]
         L.orc_hll_estimate.restype = C.c_double
@@ -126,6 +133,41 @@ class _Port:
         w = self.words(k)
         out = np.zeros((max(n, 1), w), dtype=np.uint64)
         self.lib.orc_kmers_from_reads(bases, offsets, n_reads, k, int(canonical), out.ctypes.data_as(C.c_void_p))
+        return out[:n] if w > 1 else out[:n, 0].copy()
+
+    # ---- other alphabets: alpha = 5 (DNA5, 3 bits) / 16 (DNA16, 4 bits) / 4 (DNA) ----
+    def words_alpha(self, alpha, k):
+        return self.lib.orc_kmer_words_alpha(alpha, k)
+
+    def kmer_windows_alpha(self, alpha, k, s):
+        if isinstance(s, str):
+            s = s.encode()
+        w = self.words_alpha(alpha, k)
+        out = np.zeros((max(len(s), 1), w), dtype=np.uint64)
+        n = self.lib.orc_kmer_windows_alpha(alpha, k, s, len(s), out)
+        return out[:n].reshape(n, w) if w > 1 else out[:n, 0].copy()
+
+    def revcomp_alpha(self, alpha, k, kmers):
+        kmers = np.ascontiguousarray(kmers, dtype=np.uint64)
+        out = np.empty_like(kmers)
+        assert self.lib.orc_revcomp_alpha(alpha, k, kmers, kmers.shape[0], out) == 0
+        return out
+
+    def canonical_alpha(self, alpha, k, kmers):
+        kmers = np.ascontiguousarray(kmers, dtype=np.uint64)
+        out = np.empty_like(kmers)
+        assert self.lib.orc_canonical_alpha(alpha, k, kmers, kmers.shape[0], out) == 0
+        return out
+
+    def kmers_from_reads_alpha(self, alpha, bases, offsets, k, canonical):
+        if isinstance(bases, np.ndarray):
+            bases = bases.tobytes()
+        offsets = np.ascontiguousarray(offsets, dtype=np.uint64)
+        n_reads = offsets.shape[0] - 1
+        n = self.lib.orc_kmers_from_reads_alpha(alpha, bases, offsets, n_reads, k, int(canonical), None)
+        w = self.words_alpha(alpha, k)
+        out = np.zeros((max(n, 1), w), dtype=np.uint64)
+        self.lib.orc_kmers_from_reads_alpha(alpha, bases, offsets, n_reads, k, int(canonical), out.ctypes.data_as(C.c_void_p))
         return out[:n] if w > 1 else out[:n, 0].copy()
 
     def rank(self, kind, keys, p):
@@ -224,6 +266,12 @@ class _Ref:
         L.ref_canonical.argtypes = [C.c_int, _u64p, C.c_size_t, _u64p]
         L.ref_canonical.restype = C.c_int
         L.ref_kmer_words.argtypes = [C.c_int]
+        if hasattr(L, "ref_kmer_windows_alpha"):
+            L.ref_kmer_windows_alpha.argtypes = [C.c_int, C.c_int, C.c_char_p, C.c_size_t, _u64p]
+            L.ref_kmer_windows_alpha.restype = C.c_long
+            L.ref_revcomp_alpha.argtypes = [C.c_int, C.c_int, _u64p, C.c_size_t, _u64p]
+            L.ref_canonical_alpha.argtypes = [C.c_int, C.c_int, _u64p, C.c_size_t, _u64p]
+            L.ref_kmer_words_alpha.argtypes = [C.c_int, C.c_int]
         L.ref_kmer_words.restype = C.c_int
         L.ref_map_create.argtypes = [C.c_int, C.c_int, C.c_int, C.c_double, C.c_double]
         L.ref_map_create.restype = C.c_void_p
@@ -286,6 +334,29 @@ class _Ref:
         kmers = np.ascontiguousarray(kmers, dtype=np.uint64)
         out = np.empty_like(kmers)
         assert self.lib.ref_canonical(k, kmers, kmers.shape[0], out) == 0
+        return out
+
+    # ---- other alphabets (compiled reference: Kmer<k, DNA5 / DNA16, uint64_t> for the (alpha, k) pairs instantiated) ----
+    def kmer_windows_alpha(self, alpha, k, s):
+        if isinstance(s, str):
+            s = s.encode()
+        w = self.lib.ref_kmer_words_alpha(alpha, k)
+        if w < 0:
+            raise ValueError("(alphabet, k) not instantiated in oracle/_ref")
+        out = np.zeros((max(len(s), 1), w), dtype=np.uint64)
+        n = self.lib.ref_kmer_windows_alpha(alpha, k, s, len(s), out)
+        return out[:n] if w > 1 else out[:n, 0].copy()
+
+    def revcomp_alpha(self, alpha, k, kmers):
+        kmers = np.ascontiguousarray(kmers, dtype=np.uint64)
+        out = np.empty_like(kmers)
+        assert self.lib.ref_revcomp_alpha(alpha, k, kmers, kmers.shape[0], out) == 0
+        return out
+
+    def canonical_alpha(self, alpha, k, kmers):
+        kmers = np.ascontiguousarray(kmers, dtype=np.uint64)
+        out = np.empty_like(kmers)
+        assert self.lib.ref_canonical_alpha(alpha, k, kmers, kmers.shape[0], out) == 0
         return out
 
     def rank(self, kind, keys, p):

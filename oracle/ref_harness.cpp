@@ -57,6 +57,15 @@ using K15 = ::bliss::common::Kmer<15, ::bliss::common::DNA, uint64_t>;
 using K47 = ::bliss::common::Kmer<47, ::bliss::common::DNA, uint64_t>;
 using K33 = ::bliss::common::Kmer<33, ::bliss::common::DNA, uint64_t>;
 using K5  = ::bliss::common::Kmer<5,  ::bliss::common::DNA, uint64_t>;
+// other alphabets (benchmark/CMakeLists.txt:175-196: testKmerIndex 31 x {DNA, DNA5, DNA16}); DNA5 is the 3-bit DNA6 table
+using K31_5  = ::bliss::common::Kmer<31, ::bliss::common::DNA5, uint64_t>;
+using K21_5  = ::bliss::common::Kmer<21, ::bliss::common::DNA5, uint64_t>;
+using K42_5  = ::bliss::common::Kmer<42, ::bliss::common::DNA5, uint64_t>;
+using K7_5   = ::bliss::common::Kmer<7,  ::bliss::common::DNA5, uint64_t>;
+using K31_16 = ::bliss::common::Kmer<31, ::bliss::common::DNA16, uint64_t>;
+using K15_16 = ::bliss::common::Kmer<15, ::bliss::common::DNA16, uint64_t>;
+using K32_16 = ::bliss::common::Kmer<32, ::bliss::common::DNA16, uint64_t>;
+using K17_16 = ::bliss::common::Kmer<17, ::bliss::common::DNA16, uint64_t>;
 
 static_assert(sizeof(K31) == 8,  "K31 must be one 64-bit word");
 static_assert(sizeof(K63) == 16, "K63 must be two 64-bit words");
@@ -386,9 +395,42 @@ size_t generate_input_impl(size_t count, size_t repeats, int canonical, uint64_t
   return output.size();
 }
 
+#define KH_DISPATCH_AK(alpha, k, CALL)                                  \
+  switch ((alpha) * 1000 + (k)) {                                        \
+    case 5031:  { using KM = K31_5;  CALL; } break;                      \
+    case 5021:  { using KM = K21_5;  CALL; } break;                      \
+    case 5042:  { using KM = K42_5;  CALL; } break;                      \
+    case 5007:  { using KM = K7_5;   CALL; } break;                      \
+    case 16031: { using KM = K31_16; CALL; } break;                      \
+    case 16015: { using KM = K15_16; CALL; } break;                      \
+    case 16032: { using KM = K32_16; CALL; } break;                      \
+    case 16017: { using KM = K17_16; CALL; } break;                      \
+    default: return -1;                                                  \
+  }
+
 }  // namespace
 
 extern "C" {
+
+// alphabet = 5 (DNA5 = the 3-bit DNA6 table, KI/common/alphabets.hpp:197-292,746) or 16 (DNA16, :648-739)
+long ref_kmer_windows_alpha(int alpha, int k, const char * s, size_t len, uint64_t * out) {
+  size_t n = 0;
+  KH_DISPATCH_AK(alpha, k, n = windows_impl<KM>(s, len, out));
+  return static_cast<long>(n);
+}
+int ref_revcomp_alpha(int alpha, int k, const uint64_t * in, size_t n, uint64_t * out) {
+  KH_DISPATCH_AK(alpha, k, revcomp_impl<KM>(in, n, out));
+  return 0;
+}
+int ref_canonical_alpha(int alpha, int k, const uint64_t * in, size_t n, uint64_t * out) {
+  KH_DISPATCH_AK(alpha, k, canonical_impl<KM>(in, n, out));
+  return 0;
+}
+int ref_kmer_words_alpha(int alpha, int k) {
+  int w = -1;
+  KH_DISPATCH_AK(alpha, k, w = KM::nWords);
+  return w;
+}
 
 int ref_hash(int kind, uint64_t seed, int key_words, const uint64_t * keys, size_t n, uint64_t * out, int batch) {
   if (key_words == 1) return hash_dispatch(kind, seed, reinterpret_cast<K31 const *>(keys), n, out, batch);
