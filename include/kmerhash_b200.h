@@ -203,6 +203,17 @@ int64_t kh_kmers_from_reads_dev(int device, const char *d_bases, const uint64_t 
                                 int k, int canonical, uint64_t *d_out_keys, uint64_t out_cap);
 /* replaces transform_input with lex_less (KI/containers/distributed_map_base.hpp:287-301): in-place allowed */
 int kh_canonicalize_dev(int device, int k, const uint64_t *d_in, uint64_t n, uint64_t *d_out);
+/* Other alphabets (the reference instantiates testKmerIndex 31 x {DNA, DNA5, DNA16}, benchmark/CMakeLists.txt:175-196):
+ * alphabet = 4 (DNA, 2 bits), 5 (DNA5 = the 3-bit DNA6 table, KI/common/alphabets.hpp:197-292,746) or 16 (DNA16, 4-bit IUPAC codes,
+ * :648-739); keys of up to two words, i.e. k <= 64 / 42 / 32.  Reverse complement of DNA5 / DNA16 = reversal of all bits of the value
+ * (KI/common/kmer.hpp:1476-1497).  The table, hashes and exchange take these keys like any 8- or 16-byte key. */
+int kh_kmer_words_alpha(int alphabet, int k);
+int64_t kh_kmers_from_reads_alpha_dev(int device, int alphabet, const char *d_bases, const uint64_t *d_offsets, uint64_t n_reads,
+                                      int k, int canonical, uint64_t *d_out_keys, uint64_t out_cap);
+int64_t kh_kmers_from_reads_alpha_host(int device, int alphabet, const char *bases, const uint64_t *offsets, uint64_t n_reads,
+                                       int k, int canonical, uint64_t *out_keys, uint64_t out_cap);
+int kh_canonicalize_alpha_host(int device, int alphabet, int k, const uint64_t *in, uint64_t n, uint64_t *out);
+int kh_revcomp_alpha_host(int device, int alphabet, int k, const uint64_t *in, uint64_t n, uint64_t *out);
 int kh_canonicalize_host(int device, int k, const uint64_t *in, uint64_t n, uint64_t *out);
 int kh_revcomp_host(int device, int k, const uint64_t *in, uint64_t n, uint64_t *out);
 

@@ -8,7 +8,7 @@ from ._lib import (lib, LIB_PATH, HASH_KINDS, REDUCERS, MAP_KINDS, DEFAULT_SEED,
                    KmerHashError, build_library, last_error)
 from .hashmap import (HashMap, hashmap_robinhood_offsets_count, hashmap_robinhood_offsets,
                       hashmap_robinhood_offsets_reduction, hashmap_robinhood_doubling, hashmap_linearprobe_doubling)
-from .ops import (kmer_words, hash_batch, kmers_from_reads, kmers_from_reads_dev, canonicalize, revcomp, rank_of,
+from .ops import (kmer_words, hash_batch, kmers_from_reads, kmers_from_reads_dev, canonicalize, canonicalize_alpha, revcomp, rank_of,
                   partition, partition_dev, unpermute_dev, MultiGpuMap, probe_random_access, probe_stream_copy)
 
 

@@ -92,6 +92,11 @@ SIGNATURES = {
     "kh_hash_host": (_int, [_int, _int, _u32, _int, _vp, _u64, _vp]),
     "kh_hash_dev": (_int, [_int, _int, _u32, _int, _vp, _u64, _vp]),
     "kh_kmers_from_reads_host": (_i64, [_int, _vp, _vp, _u64, _int, _int, _vp, _u64]),
+    "kh_kmer_words_alpha": (_int, [_int, _int]),
+    "kh_kmers_from_reads_alpha_dev": (_i64, [_int, _int, _vp, _vp, _u64, _int, _int, _vp, _u64]),
+    "kh_kmers_from_reads_alpha_host": (_i64, [_int, _int, _vp, _vp, _u64, _int, _int, _vp, _u64]),
+    "kh_canonicalize_alpha_host": (_int, [_int, _int, _int, _vp, _u64, _vp]),
+    "kh_revcomp_alpha_host": (_int, [_int, _int, _int, _vp, _u64, _vp]),
     "kh_kmers_from_reads_dev": (_i64, [_int, _vp, _vp, _u64, _int, _int, _vp, _u64]),
     "kh_canonicalize_dev": (_int, [_int, _int, _vp, _u64, _vp]),
     "kh_canonicalize_host": (_int, [_int, _int, _vp, _u64, _vp]),

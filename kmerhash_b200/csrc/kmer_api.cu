@@ -128,14 +128,54 @@ __global__ void __launch_bounds__(256) kmers_from_reads_kernel(const unsigned ch
 }
 
 template <int W>
-__global__ void canonicalize_kernel(const uint64_t *in, uint64_t n, int k, int mode, uint64_t *out) {
+__global__ void canonicalize_kernel(const uint64_t *in, uint64_t n, int alpha, int k, int mode, uint64_t *out) {
   const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
   for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
     uint64_t key[W], res[W];
     load_key<W>(in, i, key);
-    if (mode == 0) kmer_canonical<W>(key, k, res); else kmer_revcomp<W>(key, k, res);
+    if (mode == 0) kmer_canonical_alpha<W>(key, alpha, k, res); else kmer_revcomp_alpha<W>(key, alpha, k, res);
 #pragma unroll
     for (int q = 0; q < W; ++q) out[i * W + q] = res[q];
+  }
+}
+
+// one THREAD per read, serial: the fallback of the tile kernel for the other alphabets (EOL-dense input only; the restatement of
+// KmerParser over the N-splitting, EOL-skipping iterator with Kmer::nextFromChar, nothing more)
+template <int W, int B, bool EMIT>
+__global__ void kmers_serial_kernel(const unsigned char *bases, const uint64_t *offsets, uint64_t n_reads, int k, int canonical,
+                                    uint64_t *counts, const uint64_t *out_off, uint64_t *out_keys, uint64_t out_cap) {
+  const int alpha = B == 2 ? KH_ALPHA_DNA : B == 3 ? KH_ALPHA_DNA5 : KH_ALPHA_DNA16;
+  const int topbits = B * k - 64 * (W - 1);
+  const uint64_t topmask = topbits >= 64 ? ~0ULL : ((1ULL << topbits) - 1ULL);
+  const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+  for (uint64_t r = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; r < n_reads; r += stride) {
+    uint64_t w[W];
+#pragma unroll
+    for (int q = 0; q < W; ++q) w[q] = 0;
+    uint64_t run = 0, emitted = 0;
+    const uint64_t obase = EMIT ? out_off[r] : 0;
+    for (uint64_t p = offsets[r]; p < offsets[r + 1]; ++p) {
+      const unsigned char c = bases[p];
+      if (c == 'N' || c == 'n') { run = 0; continue; }
+      if (c == '\n' || c == '\r') continue;
+      if (W == 2) w[W - 1] = ((w[W - 1] << B) | (w[0] >> (64 - B)));
+      w[0] = (w[0] << B) | alpha_code<B>(c);
+      w[W - 1] &= topmask;
+      if (++run >= (uint64_t)k) {
+        if (EMIT && obase + emitted < out_cap) {
+          uint64_t res[W];
+          if (canonical) kmer_canonical_alpha<W>(w, alpha, k, res);
+          else {
+#pragma unroll
+            for (int q = 0; q < W; ++q) res[q] = w[q];
+          }
+#pragma unroll
+          for (int q = 0; q < W; ++q) out_keys[(obase + emitted) * W + q] = res[q];
+        }
+        ++emitted;
+      }
+    }
+    if (!EMIT) counts[r] = emitted;
   }
 }
 
@@ -166,14 +206,45 @@ int64_t kmers_from_reads_warp(int device, const char *d_bases, const uint64_t *d
   return (int64_t)total;
 }
 
+template <int W, int B>
+int64_t kmers_from_reads_serial(int device, const unsigned char *b, const uint64_t *d_offsets, uint64_t n_reads, int k,
+                                int canonical, uint64_t *d_out_keys, uint64_t out_cap) {
+  const int grid = (int)std::max<uint64_t>(1, std::min<uint64_t>((n_reads + 127) / 128, (uint64_t)sm_count(device) * 16));
+  DevBuf<uint64_t> counts(n_reads + 1), offs(n_reads + 1);
+  KH_CUDA(cudaMemsetAsync(counts.p + n_reads, 0, sizeof(uint64_t), 0));
+  KH_LAUNCH((kmers_serial_kernel<W, B, false>), grid, 128, 0, 0, b, d_offsets, n_reads, k, canonical, counts.p, nullptr, nullptr, 0);
+  size_t tmp_bytes = 0;
+  KH_CUDA(cub::DeviceScan::ExclusiveSum(nullptr, tmp_bytes, counts.p, offs.p, n_reads + 1, 0));
+  DevBuf<unsigned char> tmp(tmp_bytes);
+  KH_CUDA(cub::DeviceScan::ExclusiveSum(tmp.p, tmp_bytes, counts.p, offs.p, n_reads + 1, 0));
+  g_launches.fetch_add(1, std::memory_order_relaxed);
+  uint64_t total = 0;
+  KH_CUDA(cudaMemcpy(&total, offs.p + n_reads, sizeof(uint64_t), cudaMemcpyDeviceToHost));
+  if (d_out_keys && total) {
+    KH_LAUNCH((kmers_serial_kernel<W, B, true>), grid, 128, 0, 0, b, d_offsets, n_reads, k, canonical, nullptr, offs.p, d_out_keys, out_cap);
+    KH_CUDA(cudaStreamSynchronize(0));
+  }
+  return (int64_t)total;
+}
+
 // the streaming tile kernel (kh_kmergen.cuh): one pass, output order kept by a decoupled look-back
-int64_t kmers_from_reads_dev(int device, const char *d_bases, const uint64_t *d_offsets, uint64_t n_reads, int k,
+int64_t kmers_from_reads_dev(int device, int alpha, const char *d_bases, const uint64_t *d_offsets, uint64_t n_reads, int k,
                              int canonical, uint64_t *d_out_keys, uint64_t out_cap) {
-  if (k < 1 || k > 64) { set_error("k must be in [1,64]"); return KH_ERR_INVALID; }
+  const int B = alpha_bits(alpha);
+  const int W = kmer_words_alpha(alpha, k);
+  if (!B) { set_error("alphabet must be 4 (DNA), 5 (DNA5) or 16 (DNA16)"); return KH_ERR_INVALID; }
+  if (k < 1 || W < 1 || W > 2) { set_error("k must be in [1,%d] for this alphabet", 128 / B); return KH_ERR_INVALID; }
   if (n_reads == 0) return 0;
   static const bool tiles_on = !(getenv("KH_KMERGEN") && atoi(getenv("KH_KMERGEN")) == 0);
-  if (!tiles_on) return kmers_from_reads_warp(device, d_bases, d_offsets, n_reads, k, canonical, d_out_keys, out_cap);
-  const int W = kmer_words(k);
+  const unsigned char *ub = reinterpret_cast<const unsigned char *>(d_bases);
+  auto slow = [&]() -> int64_t {
+    if (B == 2) return kmers_from_reads_warp(device, d_bases, d_offsets, n_reads, k, canonical, d_out_keys, out_cap);
+    if (B == 3) return W == 1 ? kmers_from_reads_serial<1, 3>(device, ub, d_offsets, n_reads, k, canonical, d_out_keys, out_cap)
+                              : kmers_from_reads_serial<2, 3>(device, ub, d_offsets, n_reads, k, canonical, d_out_keys, out_cap);
+    return W == 1 ? kmers_from_reads_serial<1, 4>(device, ub, d_offsets, n_reads, k, canonical, d_out_keys, out_cap)
+                  : kmers_from_reads_serial<2, 4>(device, ub, d_offsets, n_reads, k, canonical, d_out_keys, out_cap);
+  };
+  if (!tiles_on) return slow();
   uint64_t h_off[2] = {0, 0};
   KH_CUDA(cudaMemcpy(&h_off[0], d_offsets, sizeof(uint64_t), cudaMemcpyDeviceToHost));
   KH_CUDA(cudaMemcpy(&h_off[1], d_offsets + n_reads, sizeof(uint64_t), cudaMemcpyDeviceToHost));
@@ -197,19 +268,21 @@ int64_t kmers_from_reads_dev(int device, const char *d_bases, const uint64_t *d_
   const size_t smem = W == 1 ? gen_smem_bytes<1>() : gen_smem_bytes<2>();
   const int per_sm = std::max<int>(1, std::min<int>(2, (int)((227 * 1024) / (smem + 1024))));
   const int grid = (int)std::min<uint64_t>(a.n_tiles, (uint64_t)sms * per_sm);
-  if (W == 1) {
-    KH_CUDA(cudaFuncSetAttribute((kmer_tiles_kernel<1, false>), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    KH_LAUNCH((kmer_tiles_kernel<1, false>), grid, GEN_THREADS, smem, 0, a);
-  } else {
-    KH_CUDA(cudaFuncSetAttribute((kmer_tiles_kernel<2, false>), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    KH_LAUNCH((kmer_tiles_kernel<2, false>), grid, GEN_THREADS, smem, 0, a);
-  }
+#define KH_GEN_LAUNCH(Wv, Bv)                                                                                                  \
+  do {                                                                                                                         \
+    KH_CUDA(cudaFuncSetAttribute((kmer_tiles_kernel<Wv, false, Bv>), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); \
+    KH_LAUNCH((kmer_tiles_kernel<Wv, false, Bv>), grid, GEN_THREADS, smem, 0, a);                                               \
+  } while (0)
+  if (B == 2) { if (W == 1) KH_GEN_LAUNCH(1, 2); else KH_GEN_LAUNCH(2, 2); }
+  else if (B == 3) { if (W == 1) KH_GEN_LAUNCH(1, 3); else KH_GEN_LAUNCH(2, 3); }
+  else { if (W == 1) KH_GEN_LAUNCH(1, 4); else KH_GEN_LAUNCH(2, 4); }
+#undef KH_GEN_LAUNCH
   unsigned long long last = 0;
   int h_flag = 0;
   KH_CUDA(cudaMemcpyAsync(&last, state.p + a.n_tiles - 1, sizeof(last), cudaMemcpyDeviceToHost, 0));
   KH_CUDA(cudaMemcpyAsync(&h_flag, flag.p, sizeof(int), cudaMemcpyDeviceToHost, 0));
   KH_CUDA(cudaStreamSynchronize(0));
-  if (h_flag) return kmers_from_reads_warp(device, d_bases, d_offsets, n_reads, k, canonical, d_out_keys, out_cap);   // EOL-dense input
+  if (h_flag) return slow();                                         // EOL-dense input
   return (int64_t)(last & ~GEN_ST_MASK);
 }
 
@@ -219,31 +292,37 @@ using namespace kh;
 
 extern "C" {
 
-int64_t kh_kmers_from_reads_dev(int device, const char *d_bases, const uint64_t *d_offsets, uint64_t n_reads,
-                                int k, int canonical, uint64_t *d_out_keys, uint64_t out_cap) {
+int kh_kmer_words_alpha(int alphabet, int k) { return (k >= 1 && alpha_bits(alphabet)) ? kmer_words_alpha(alphabet, k) : 0; }
+
+int64_t kh_kmers_from_reads_alpha_dev(int device, int alphabet, const char *d_bases, const uint64_t *d_offsets, uint64_t n_reads,
+                                      int k, int canonical, uint64_t *d_out_keys, uint64_t out_cap) {
   return guarded([&]() -> int64_t {
     if (kh_device_count() <= 0) { set_error("no CUDA device: kmerhash_b200 has no CPU fallback"); return KH_ERR_CUDA; }
     DeviceGuard g(device);
-    return kmers_from_reads_dev(device, d_bases, d_offsets, n_reads, k, canonical, d_out_keys, out_cap);
+    return kmers_from_reads_dev(device, alphabet, d_bases, d_offsets, n_reads, k, canonical, d_out_keys, out_cap);
   });
 }
+int64_t kh_kmers_from_reads_dev(int device, const char *d_bases, const uint64_t *d_offsets, uint64_t n_reads,
+                                int k, int canonical, uint64_t *d_out_keys, uint64_t out_cap) {
+  return kh_kmers_from_reads_alpha_dev(device, KH_ALPHA_DNA, d_bases, d_offsets, n_reads, k, canonical, d_out_keys, out_cap);
+}
 
-int64_t kh_kmers_from_reads_host(int device, const char *bases, const uint64_t *offsets, uint64_t n_reads,
-                                 int k, int canonical, uint64_t *out_keys, uint64_t out_cap) {
+int64_t kh_kmers_from_reads_alpha_host(int device, int alphabet, const char *bases, const uint64_t *offsets, uint64_t n_reads,
+                                       int k, int canonical, uint64_t *out_keys, uint64_t out_cap) {
   return guarded([&]() -> int64_t {
     if (kh_device_count() <= 0) { set_error("no CUDA device: kmerhash_b200 has no CPU fallback"); return KH_ERR_CUDA; }
-    if (k < 1 || k > 64) { set_error("k must be in [1,64]"); return KH_ERR_INVALID; }
+    const int W = kh_kmer_words_alpha(alphabet, k);
+    if (W < 1 || W > 2) { set_error("alphabet 4 / 5 / 16 with k up to 64 / 42 / 32"); return KH_ERR_INVALID; }
     if (n_reads == 0) return 0;
     DeviceGuard g(device);
     const uint64_t nbytes = offsets[n_reads];
-    const int W = kmer_words(k);
     DevBuf<char> db(std::max<uint64_t>(nbytes, 1));
     DevBuf<uint64_t> doff(n_reads + 1);
     KH_CUDA(cudaMemcpy(db.p, bases, nbytes, cudaMemcpyHostToDevice));
     KH_CUDA(cudaMemcpy(doff.p, offsets, (n_reads + 1) * 8, cudaMemcpyHostToDevice));
     DevBuf<uint64_t> dout;
     if (out_keys && out_cap) dout.alloc(out_cap * W);
-    const int64_t total = kmers_from_reads_dev(device, db.p, doff.p, n_reads, k, canonical, dout.p, out_keys ? out_cap : 0);
+    const int64_t total = kmers_from_reads_dev(device, alphabet, db.p, doff.p, n_reads, k, canonical, dout.p, out_keys ? out_cap : 0);
     if (total > 0 && out_keys) {
       const uint64_t c = std::min<uint64_t>((uint64_t)total, out_cap);
       KH_CUDA(cudaMemcpy(out_keys, dout.p, c * W * 8, cudaMemcpyDeviceToHost));
@@ -251,14 +330,18 @@ int64_t kh_kmers_from_reads_host(int device, const char *bases, const uint64_t *
     return total;
   });
 }
+int64_t kh_kmers_from_reads_host(int device, const char *bases, const uint64_t *offsets, uint64_t n_reads,
+                                 int k, int canonical, uint64_t *out_keys, uint64_t out_cap) {
+  return kh_kmers_from_reads_alpha_host(device, KH_ALPHA_DNA, bases, offsets, n_reads, k, canonical, out_keys, out_cap);
+}
 
-static int canon_impl(int device, int k, const uint64_t *d_in, uint64_t n, uint64_t *d_out, int mode) {
-  if (k < 1 || k > 64) { set_error("k must be in [1,64]"); return KH_ERR_INVALID; }
+static int canon_impl(int device, int alpha, int k, const uint64_t *d_in, uint64_t n, uint64_t *d_out, int mode) {
+  const int W = kh_kmer_words_alpha(alpha, k);
+  if (W < 1 || W > 2) { set_error("alphabet 4 / 5 / 16 with k up to 64 / 42 / 32"); return KH_ERR_INVALID; }
   if (n == 0) return KH_OK;
-  const int W = kmer_words(k);
   const int grid = (int)std::max<uint64_t>(1, std::min<uint64_t>((n + 255) / 256, (uint64_t)sm_count(device) * 8));
-  if (W == 1) KH_LAUNCH((canonicalize_kernel<1>), grid, 256, 0, 0, d_in, n, k, mode, d_out);
-  else KH_LAUNCH((canonicalize_kernel<2>), grid, 256, 0, 0, d_in, n, k, mode, d_out);
+  if (W == 1) KH_LAUNCH((canonicalize_kernel<1>), grid, 256, 0, 0, d_in, n, alpha, k, mode, d_out);
+  else KH_LAUNCH((canonicalize_kernel<2>), grid, 256, 0, 0, d_in, n, alpha, k, mode, d_out);
   KH_CUDA(cudaStreamSynchronize(0));
   return KH_OK;
 }
@@ -267,26 +350,28 @@ int kh_canonicalize_dev(int device, int k, const uint64_t *d_in, uint64_t n, uin
   return (int)guarded([&]() -> int64_t {
     if (kh_device_count() <= 0) { set_error("no CUDA device: kmerhash_b200 has no CPU fallback"); return KH_ERR_CUDA; }
     DeviceGuard g(device);
-    return canon_impl(device, k, d_in, n, d_out, 0);
+    return canon_impl(device, KH_ALPHA_DNA, k, d_in, n, d_out, 0);
   });
 }
 
-static int canon_host(int device, int k, const uint64_t *in, uint64_t n, uint64_t *out, int mode) {
+static int canon_host(int device, int alpha, int k, const uint64_t *in, uint64_t n, uint64_t *out, int mode) {
   return (int)guarded([&]() -> int64_t {
     if (kh_device_count() <= 0) { set_error("no CUDA device: kmerhash_b200 has no CPU fallback"); return KH_ERR_CUDA; }
-    if (k < 1 || k > 64) { set_error("k must be in [1,64]"); return KH_ERR_INVALID; }
+    const int W = kh_kmer_words_alpha(alpha, k);
+    if (W < 1 || W > 2) { set_error("alphabet 4 / 5 / 16 with k up to 64 / 42 / 32"); return KH_ERR_INVALID; }
     if (n == 0) return KH_OK;
     DeviceGuard g(device);
-    const int W = kmer_words(k);
     DevBuf<uint64_t> d(n * W);
     KH_CUDA(cudaMemcpy(d.p, in, n * W * 8, cudaMemcpyHostToDevice));
-    const int rc = canon_impl(device, k, d.p, n, d.p, mode);
+    const int rc = canon_impl(device, alpha, k, d.p, n, d.p, mode);
     if (rc != KH_OK) return rc;
     KH_CUDA(cudaMemcpy(out, d.p, n * W * 8, cudaMemcpyDeviceToHost));
     return KH_OK;
   });
 }
-int kh_canonicalize_host(int device, int k, const uint64_t *in, uint64_t n, uint64_t *out) { return canon_host(device, k, in, n, out, 0); }
-int kh_revcomp_host(int device, int k, const uint64_t *in, uint64_t n, uint64_t *out) { return canon_host(device, k, in, n, out, 1); }
+int kh_canonicalize_host(int device, int k, const uint64_t *in, uint64_t n, uint64_t *out) { return canon_host(device, KH_ALPHA_DNA, k, in, n, out, 0); }
+int kh_revcomp_host(int device, int k, const uint64_t *in, uint64_t n, uint64_t *out) { return canon_host(device, KH_ALPHA_DNA, k, in, n, out, 1); }
+int kh_canonicalize_alpha_host(int device, int alphabet, int k, const uint64_t *in, uint64_t n, uint64_t *out) { return canon_host(device, alphabet, k, in, n, out, 0); }
+int kh_revcomp_alpha_host(int device, int alphabet, int k, const uint64_t *in, uint64_t n, uint64_t *out) { return canon_host(device, alphabet, k, in, n, out, 1); }
 
 }  // extern "C"

@@ -27,21 +27,36 @@ def hash_batch(keys, hash_kind="MURMUR64avx", seed=None, device=0):
     return out
 
 
-def kmers_from_reads(bases, offsets, k, canonical=False, device=0):
-    """KmerParser over N-split sequences (+ lex_less): all k-mers of every read, in read order."""
+ALPHABETS = {"DNA": 4, "DNA5": 5, "DNA16": 16, 4: 4, 5: 5, 16: 16}
+
+
+def kmers_from_reads(bases, offsets, k, canonical=False, device=0, alphabet="DNA"):
+    """KmerParser over N-split sequences (+ lex_less): all k-mers of every read, in read order.  alphabet: "DNA" (2 bits, k <= 64),
+    "DNA5" (3 bits, k <= 42), "DNA16" (4 bits, k <= 32) -- bliss::common::Kmer<k, Alphabet, uint64_t> of up to two words."""
     if isinstance(bases, str):
         bases = bases.encode()
     buf = np.frombuffer(bases, dtype=np.uint8) if isinstance(bases, (bytes, bytearray)) else np.ascontiguousarray(bases, dtype=np.uint8)
     offsets = np.ascontiguousarray(offsets, dtype=np.uint64)
     n_reads = offsets.shape[0] - 1
-    W = kmer_words(k)
-    total = check(lib.kh_kmers_from_reads_host(device, buf.ctypes.data, offsets.ctypes.data, n_reads, k, int(canonical), None, 0),
+    al = ALPHABETS[alphabet]
+    W = lib.kh_kmer_words_alpha(al, k)
+    total = check(lib.kh_kmers_from_reads_alpha_host(device, al, buf.ctypes.data, offsets.ctypes.data, n_reads, k, int(canonical), None, 0),
                   "kmers_from_reads(count)")
     out = np.empty((max(total, 1), W), dtype=np.uint64)
     if total:
-        check(lib.kh_kmers_from_reads_host(device, buf.ctypes.data, offsets.ctypes.data, n_reads, k, int(canonical),
-                                           out.ctypes.data, total), "kmers_from_reads")
+        check(lib.kh_kmers_from_reads_alpha_host(device, al, buf.ctypes.data, offsets.ctypes.data, n_reads, k, int(canonical),
+                                                 out.ctypes.data, total), "kmers_from_reads")
     return out[:total] if W > 1 else out[:total, 0].copy()
+
+
+def canonicalize_alpha(kmers, k, alphabet, device=0, revcomp_only=False):
+    """lex_less / reverse_complement for DNA5 / DNA16 (and DNA) k-mers on host arrays"""
+    al = ALPHABETS[alphabet]
+    a = np.ascontiguousarray(kmers, dtype=np.uint64)
+    out = np.empty_like(a)
+    fn = lib.kh_revcomp_alpha_host if revcomp_only else lib.kh_canonicalize_alpha_host
+    check(fn(device, al, k, a.ctypes.data, a.shape[0], out.ctypes.data), "canonicalize_alpha")
+    return out
 
 
 def kmers_from_reads_dev(bases, offsets, k, canonical=False):

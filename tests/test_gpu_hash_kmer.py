@@ -114,6 +114,53 @@ def test_kmers_tile_kernel_eol_dense_falls_back(kh, oracle_mod):
         assert np.array_equal(kh.kmers_from_reads(dense, offs, k, True), exp)
 
 
+@pytest.mark.parametrize("alphabet,ks", [("DNA5", (7, 21, 31, 42)), ("DNA16", (15, 17, 31, 32))])
+def test_kmers_other_alphabets(kh, oracle_mod, alphabet, ks):
+    """N3 of SURVEY.md 8f, the part that fits two key words: DNA5 (3 bits, the reference's DNA6 table) and DNA16 (4 bits, IUPAC)
+    k-mers -- generation from reads (N-split, EOL skipped, many tiles, also the EOL-dense fallback), reverse complement (= bit
+    reversal, KI/common/kmer.hpp:1476-1497) and canonical form against vectors of the COMPILED reference and against the
+    oracle; the k-mers then count in a 16-byte-key table like any key"""
+    import os
+    al = {"DNA5": 5, "DNA16": 16}[alphabet]
+    g = dict(np.load(os.path.join(os.path.dirname(__file__), "golden", "alphabet_vectors.npz")))
+    o = oracle_mod.port
+    rng = np.random.default_rng(al)
+    sym = np.frombuffer(b"ACGTACGTACGTacgtMRWSYKVHDBU.-X?", dtype=np.uint8)
+    for k in ks:
+        w = g["windows_a%d_k%d" % (al, k)]
+        assert np.array_equal(kh.canonicalize_alpha(w, k, alphabet, revcomp_only=True), g["revcomp_a%d_k%d" % (al, k)]), k
+        assert np.array_equal(kh.canonicalize_alpha(w, k, alphabet), g["canonical_a%d_k%d" % (al, k)]), k
+        cases = [make_reads(rng, 400, 0, 300, n_rate=0.004, eol=True, lower=True), make_reads(rng, 2, 30000, 50000, n_rate=0.0005, eol=True)]
+        # IUPAC / gap symbols sprinkled in
+        for bases, offs in cases:
+            hit = rng.random(len(bases)) < 0.05
+            keep = (bases != 10) & (bases != 13) & (bases != ord("N")) & (bases != ord("n"))
+            bases[hit & keep] = sym[rng.integers(0, len(sym), size=int((hit & keep).sum()))]
+            for canonical in (False, True):
+                exp = o.kmers_from_reads_alpha(al, bases, offs, k, canonical)
+                got = kh.kmers_from_reads(bases, offs, k, canonical, alphabet=alphabet)
+                assert got.shape == exp.shape and np.array_equal(got, exp), (alphabet, k, canonical)
+    # EOL-dense input -> serial fallback
+    k = ks[2]
+    seq = sym[rng.integers(0, len(sym), size=6000)]
+    dense = np.full(16 * len(seq), 10, dtype=np.uint8)
+    dense[0::16] = seq
+    offs = np.array([0, len(dense)], dtype=np.uint64)
+    exp = o.kmers_from_reads_alpha(al, dense, offs, k, True)
+    assert len(exp) > 0 and np.array_equal(kh.kmers_from_reads(dense, offs, k, True, alphabet=alphabet), exp)
+    # the table counts them like any 16-byte key
+    bases, offs = make_reads(rng, 3000, 100, 150)
+    km = kh.kmers_from_reads(bases, offs, 31, True, alphabet=alphabet)
+    assert km.ndim == 2 and km.shape[1] == 2
+    m = kh.HashMap(2, "MURMUR64avx", "COUNT")
+    gm = o.Map(2, "COUNT")
+    assert m.insert(km, default=1) == gm.insert(km, default=1)
+    ek, ev = gm.to_vector()
+    tk, tv = m.to_vector()
+    a, b = np.lexsort(ek.T[::-1]), np.lexsort(tk.T[::-1])
+    assert np.array_equal(ek[a], tk[b]) and np.array_equal(np.asarray(ev)[a], np.asarray(tv)[b])
+
+
 def test_kmers_no_reads(kh):
     out = kh.kmers_from_reads(b"", np.array([0], dtype=np.uint64), 31)
     assert out.shape == (0,)
