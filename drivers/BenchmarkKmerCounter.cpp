@@ -9,8 +9,9 @@
 // -G n runs the count map hash-partitioned over n GPUs of the box (owner = murmur3avx64_{9876543}(kmer) & (n-1)),
 // which is what `mpirun -np n` is to the reference.
 //
-// File parsing here is the host-side minimum needed to hand reads to the GPU (record splitting; the k-mer
-// generation kernel itself skips CR/LF and splits at N): one process reads whole files, no MPI-IO partitioning.
+// File reading is partitioned like the reference's (byte ranges, record-boundary search, k - 1 overlap for FASTA sequences
+// that cross a range border; host threads stand where MPI ranks stand); the k-mer generation kernel itself skips CR/LF and
+// splits at N.
 #include <algorithm>
 #include <chrono>
 #include <cstdio>
@@ -19,7 +20,12 @@
 #include <fstream>
 #include <random>
 #include <string>
+#include <thread>
 #include <vector>
+#include <fcntl.h>
+#include <sys/mman.h>
+#include <sys/stat.h>
+#include <unistd.h>
 
 #include "kmerhash_b200.hpp"
 
@@ -35,6 +41,7 @@ struct Options {
   size_t syn_reads = 0, syn_len = 150, syn_genome = 100000000;
   int gpus = 1;
   size_t sample = 1000000;
+  std::string reads_only;      // test hook: write what the reader produced ([u64 n_reads][offsets][bases]) and stop
 };
 
 struct PhaseTimer {
@@ -56,29 +63,116 @@ struct PhaseTimer {
   }
 };
 
-// FASTA ('>') and FASTQ ('@', 4-line records) into one base buffer + record offsets.  FASTA sequences keep their
-// line breaks (the kernel filters EOL like the reference's iterator, ext/kmerind/src/utils/file_utils.hpp:43-47).
-void read_sequences(const std::string &path, std::string &bases, std::vector<uint64_t> &offsets) {
-  std::ifstream in(path, std::ios::binary);
-  if (!in) { std::fprintf(stderr, "cannot open %s\n", path.c_str()); std::exit(1); }
-  std::string line;
-  if (offsets.empty()) offsets.push_back(0);
-  bool fastq = false, in_seq = false;
-  while (std::getline(in, line)) {
-    if (line.empty()) continue;
-    if (!in_seq && (line[0] == '@' || line[0] == '>')) { fastq = line[0] == '@'; in_seq = true; continue; }
-    if (fastq) {
-      bases += line; offsets.push_back(bases.size());
-      std::getline(in, line);            // '+'
-      std::getline(in, line);            // qualities
-      in_seq = false;
-    } else if (line[0] == '>') {
-      offsets.push_back(bases.size());   // next FASTA record
-    } else {
-      bases += line; bases += '\n';
+// ---- partitioned file reading -----------------------------------------------------------------------------------------------
+// The reference hands every MPI rank a byte range of the file (KI/io/kmer_file_helper.hpp:407-645 read_file_mmap / _posix /
+// _mpiio): a rank looks for the first record boundary inside its range (FASTQ: a line starting with '@' whose next-but-one
+// line starts with '+', KI/io/fastq_loader.hpp; FASTA: a line starting with '>', KI/io/fasta_loader.hpp), parses the records
+// that START in its range, and a FASTA sequence that runs across a range border is cut there with the next k - 1 bases
+// repeated, so that every k-mer is produced exactly once (KI/io/filtered_sequence_iterator.hpp:179-440).  Same scheme here with
+// host threads in the role of the ranks: the file is mapped, split into byte ranges, every thread fills its own
+// (bases, offsets) piece, the pieces are concatenated in order -- the k-mers and their order are those of a serial parse.
+// FASTA pieces keep their line breaks (the kernel filters EOL like the reference's iterator, KI/utils/file_utils.hpp:43-47).
+struct Piece { std::string bases; std::vector<uint64_t> ends; };   // ends[i] = end of read i inside `bases`
+
+inline const char *line_end(const char *p, const char *e) { const void *q = memchr(p, '\n', (size_t)(e - p)); return q ? (const char *)q : e; }
+inline const char *next_line(const char *p, const char *e) { const char *q = line_end(p, e); return q < e ? q + 1 : e; }
+
+// first FASTQ record start at or behind `from` (a line start)
+const char *fastq_record_start(const char *base, const char *from, const char *e) {
+  const char *p = from;
+  if (p != base) p = next_line(p - 1, e);                 // first line start >= from  (from - 1 may be '\n' itself)
+  while (p < e) {
+    if (*p == '@') {
+      const char *l2 = next_line(next_line(p, e), e);     // next-but-one line
+      if (l2 < e && *l2 == '+') return p;
     }
+    p = next_line(p, e);
   }
-  if (!fastq && in_seq && offsets.back() != bases.size()) offsets.push_back(bases.size());
+  return e;
+}
+
+void parse_fastq_range(const char *base, const char *b, const char *e_range, const char *e, Piece &out) {
+  const char *p = fastq_record_start(base, b, e);
+  while (p < e && p < e_range) {                          // records that START inside the range
+    const char *seq = next_line(p, e);
+    const char *seq_end = line_end(seq, e);
+    size_t len = (size_t)(seq_end - seq);
+    if (len && seq[len - 1] == '\r') --len;
+    out.bases.append(seq, len);
+    out.ends.push_back(out.bases.size());
+    p = next_line(next_line(next_line(seq, e), e), e);    // behind sequence, '+' and quality lines
+  }
+}
+
+// FASTA: [b, e_range) of the file; `k`: the last piece of a sequence that continues behind e_range gets k - 1 more bases
+void parse_fasta_range(const char *base, const char *b, const char *e_range, const char *e, unsigned k, Piece &out) {
+  const char *p = b;
+  if (p != base && p[-1] != '\n') {                       // mid-line: is it a header line?  then skip it (it belongs to its record)
+    const char *ls = p;
+    while (ls > base && ls[-1] != '\n') --ls;
+    if (*ls == '>') p = next_line(p, e);
+  }
+  bool open = false;                                      // a read is being filled
+  while (p < e_range) {
+    if (*p == '>' && (p == base || p[-1] == '\n')) {
+      if (open) { out.ends.push_back(out.bases.size()); open = false; }
+      p = next_line(p, e);
+      continue;
+    }
+    const char *le = line_end(p, e);
+    const char *stop = le < e_range ? le : e_range;       // never past the range: the next thread takes over there
+    out.bases.append(p, (size_t)(stop - p));
+    open = true;
+    if (stop == le && le < e) { out.bases += '\n'; p = le + 1; } else p = stop;
+  }
+  if (open) {
+    // the sequence may continue in the next range: repeat its next k - 1 bases (EOL characters do not count, a header ends it)
+    unsigned need = k - 1;
+    const char *q = p;
+    while (need && q < e) {
+      if (*q == '>' && (q == base || q[-1] == '\n')) break;
+      if (*q != '\n' && *q != '\r') --need;
+      out.bases += *q++;
+    }
+    out.ends.push_back(out.bases.size());
+  }
+}
+
+void read_sequences(const std::string &path, unsigned k, std::string &bases, std::vector<uint64_t> &offsets) {
+  if (offsets.empty()) offsets.push_back(0);
+  const int fd = ::open(path.c_str(), O_RDONLY);
+  if (fd < 0) { std::fprintf(stderr, "cannot open %s\n", path.c_str()); std::exit(1); }
+  struct stat st;
+  if (::fstat(fd, &st) != 0 || st.st_size == 0) { ::close(fd); return; }
+  const size_t size = (size_t)st.st_size;
+  void *map = ::mmap(nullptr, size, PROT_READ, MAP_PRIVATE, fd, 0);
+  ::close(fd);
+  if (map == MAP_FAILED) { std::fprintf(stderr, "cannot map %s\n", path.c_str()); std::exit(1); }
+  const char *base = (const char *)map, *e = base + size;
+  const char *first = base;
+  while (first < e && (*first == '\n' || *first == '\r')) ++first;
+  const bool fastq = first < e && *first == '@';
+  unsigned threads = std::max(1u, std::thread::hardware_concurrency());
+  if (const char *ev = std::getenv("KH_READ_THREADS")) threads = std::max(1, std::atoi(ev));
+  const size_t min_range = std::getenv("KH_READ_THREADS") ? 1 : (size_t)1 << 20;      // tests force tiny ranges
+  threads = (unsigned)std::max<size_t>(1, std::min<size_t>(threads, size / min_range + 1));
+  std::vector<Piece> pieces(threads);
+  std::vector<std::thread> th;
+  for (unsigned t = 0; t < threads; ++t) th.emplace_back([&, t]() {
+    const char *b = base + size * t / threads, *er = base + size * (t + 1) / threads;
+    if (fastq) parse_fastq_range(base, b, er, e, pieces[t]);
+    else parse_fasta_range(base, b, er, e, k, pieces[t]);
+  });
+  for (auto &x : th) x.join();
+  size_t total = bases.size();
+  for (auto &pc : pieces) total += pc.bases.size();
+  bases.reserve(total);
+  for (auto &pc : pieces) {
+    const uint64_t at = bases.size();
+    bases += pc.bases;
+    for (uint64_t end : pc.ends) offsets.push_back(at + end);
+  }
+  ::munmap(map, size);
 }
 
 // uniform random genome (mt19937_64 seed 1), reads from either strand (seed 2),
@@ -123,6 +217,7 @@ Options parse(int argc, char **argv) {
     else if (a == "-G" || a == "--gpus") o.gpus = std::atoi(next());
     else if (a == "-A" || a == "--algo" || a == "-B" || a == "--output_algo") next();   // reader / writer ids: one path here
     else if (a == "--sample") o.sample = std::strtoull(next(), nullptr, 10);
+    else if (a == "--reads-only") o.reads_only = next();
     else if (a == "--synthetic") {
       if (std::sscanf(next(), "%zu,%zu,%zu", &o.syn_reads, &o.syn_len, &o.syn_genome) < 1) { std::fprintf(stderr, "--synthetic reads[,len[,genome]]\n"); std::exit(2); }
     } else if (a == "-h" || a == "--help") {
@@ -146,9 +241,19 @@ int main(int argc, char **argv) {
 
     tm.start();
     if (o.syn_reads) synthetic_reads(o, bases, offsets);
-    for (auto &f : o.files) read_sequences(f, bases, offsets);
+    for (auto &f : o.files) read_sequences(f, K, bases, offsets);
     if (offsets.empty()) offsets.push_back(0);
     tm.end("read", offsets.size() - 1);
+    if (!o.reads_only.empty()) {
+      std::FILE *f = std::fopen(o.reads_only.c_str(), "wb");
+      if (!f) { std::fprintf(stderr, "cannot write %s\n", o.reads_only.c_str()); return 1; }
+      const uint64_t nr = offsets.size() - 1;
+      std::fwrite(&nr, 8, 1, f);
+      std::fwrite(offsets.data(), 8, offsets.size(), f);
+      std::fwrite(bases.data(), 1, bases.size(), f);
+      std::fclose(f);
+      return 0;
+    }
 
     // KmerParser + lex_less (canonical)
     tm.start();

@@ -113,3 +113,77 @@ def test_murmur32fin_rejected(kh):
     # murmur3finalizer_avx32 is defined for keys <= 4 bytes only (murmurhash3finalizer_32_avx.hpp:527)
     with pytest.raises((ValueError, kh.KmerHashError)):
         kh.hash_batch(np.arange(4, dtype=np.uint64), "MURMUR32FINALIZER")
+
+
+def _serial_kmers(path, k, oracle_mod):
+    """serial parse of a FASTA / FASTQ file (one read per record) -> the oracle's k-mers, in order"""
+    import numpy as np
+    reads, cur, fastq = [], None, None
+    lines = open(path, "rb").read().split(b"\n")
+    i = 0
+    while i < len(lines):
+        ln = lines[i]
+        if fastq is None and ln[:1] in (b"@", b">"):
+            fastq = ln[:1] == b"@"
+        if fastq:
+            if ln[:1] == b"@" and i + 2 < len(lines) and lines[i + 2][:1] == b"+":
+                reads.append(lines[i + 1].rstrip(b"\r")); i += 4; continue
+        elif ln[:1] == b">":
+            if cur is not None:
+                reads.append(cur)
+            cur = b""
+        elif cur is not None:
+            cur += ln + b"\n"
+        i += 1
+    if cur is not None:
+        reads.append(cur)
+    bases = np.frombuffer(b"".join(reads), dtype=np.uint8)
+    offs = np.concatenate([[0], np.cumsum([len(r) for r in reads])]).astype(np.uint64)
+    return oracle_mod.port.kmers_from_reads(bases, offs, k, True)
+
+
+@pytest.mark.parametrize("kind", ["fasta", "fastq"])
+def test_partitioned_file_reader_of_the_kmercounter_driver(tmp_path, oracle_mod, kind):
+    """drivers/BenchmarkKmerCounter reads files the reference's way (byte ranges, record-boundary search, k - 1 overlap for
+    FASTA sequences cut at a range border, KI/io/kmer_file_helper.hpp:407-645): whatever the number of ranges, the reads
+    it hands to the k-mer kernel must yield exactly the k-mers of a serial parse, in the same order (checked with the
+    oracle's generator on the host; no GPU involved)."""
+    import subprocess
+    import numpy as np
+    exe = os.path.join(ROOT, "drivers", "BenchmarkKmerCounter")
+    rng = np.random.default_rng(5)
+    path = str(tmp_path / ("in." + kind))
+    with open(path, "w") as f:
+        if kind == "fasta":
+            for r in range(7):
+                n = int(rng.integers(1, 9000)) if r != 3 else 10
+                seq = "".join("ACGTN"[c] for c in rng.choice(5, size=n, p=[0.2495, 0.2495, 0.2495, 0.2495, 0.002]))
+                f.write(">chr%d some description that is a little longer than usual %s\n" % (r, "x" * int(rng.integers(0, 90))))
+                w = int(rng.integers(40, 80))
+                for i in range(0, n, w):
+                    f.write(seq[i:i + w] + ("\r\n" if r == 5 else "\n"))
+                if r == 2:
+                    f.write("\n")
+        else:
+            for r in range(900):
+                n = int(rng.integers(1, 160))
+                seq = "".join("ACGTN"[c] for c in rng.choice(5, size=n, p=[0.2475, 0.2475, 0.2475, 0.2475, 0.01]))
+                qual = "".join(chr(c) for c in rng.integers(33, 74, size=n))
+                if r % 5 == 0:
+                    qual = "@" + qual[1:]            # a quality line that looks like a header
+                if r % 7 == 0:
+                    qual = "+" + qual[1:]
+                f.write("@read%d/1\n%s\n+\n%s\n" % (r, seq, qual))
+    exp = _serial_kmers(path, 31, oracle_mod)
+    assert len(exp) > 1000
+    for threads in (1, 2, 3, 7, 16, 61):
+        out = str(tmp_path / "reads.bin")
+        r = subprocess.run([exe, "--reads-only", out, path], capture_output=True, text=True, timeout=120,
+                           env=dict(os.environ, KH_READ_THREADS=str(threads)))
+        assert r.returncode == 0, r.stdout + r.stderr
+        raw = open(out, "rb").read()
+        nr = int(np.frombuffer(raw[:8], dtype=np.uint64)[0])
+        offs = np.frombuffer(raw[8:8 + 8 * (nr + 1)], dtype=np.uint64)
+        bases = np.frombuffer(raw[8 + 8 * (nr + 1):], dtype=np.uint8)
+        got = oracle_mod.port.kmers_from_reads(bases, offs, 31, True)
+        assert got.shape == exp.shape and np.array_equal(got, exp), (kind, threads)
