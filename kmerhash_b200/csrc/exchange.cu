@@ -257,6 +257,11 @@ __global__ void __launch_bounds__(PS_BLOCK, 3) scatter_slabs_kernel(const uint64
 constexpr unsigned long long PEER_POISON = ~0ULL;
 struct PeerHeader { unsigned long long flags[WIN_MAX_DST]; unsigned long long counts[2][WIN_MAX_DST][WIN_MAX_DST]; };
 struct PeerHeaders { PeerHeader *h[WIN_MAX_DST]; };
+// KH_PEER_TIMEOUT_MS (read per call: tests shorten the 10 s)
+static unsigned long long peer_timeout_ns() {
+  const char *e = getenv("KH_PEER_TIMEOUT_MS");
+  return (e && atoll(e) > 0) ? (unsigned long long)atoll(e) * 1000000ULL : 10000000000ULL;
+}
 // slot: which of the two count matrices this call writes (they alternate, so a rank that is one call ahead never
 // overwrites a matrix a slower rank has not copied out yet).  cstride: distance between two entries of counts_row.
 __global__ void peer_sync_kernel(const __grid_constant__ PeerHeaders hd, uint32_t rank, uint32_t p, unsigned long long epoch,
@@ -819,10 +824,7 @@ static int peer_sync(kh_table *t, khx_peer *x, uint64_t epoch, const uint64_t *d
     KH_CUDA(cudaMemsetAsync(flag.p, 0, sizeof(int), s));
     const int slot = (int)(x->count_syncs & 1);
     if (d_counts_row) ++x->count_syncs;
-    static const unsigned long long timeout_ns = [] {                 // KH_PEER_TIMEOUT_MS: tests shorten the 10 s
-      const char *e = getenv("KH_PEER_TIMEOUT_MS");
-      return (e && atoll(e) > 0) ? (unsigned long long)atoll(e) * 1000000ULL : 10000000000ULL;
-    }();
+    const unsigned long long timeout_ns = peer_timeout_ns();
     KH_LAUNCH(peer_sync_kernel, 1, 32, 0, s, hd, x->rank, x->p, (unsigned long long)epoch,
               reinterpret_cast<const unsigned long long *>(d_counts_row), counts_stride, slot, flag.p, timeout_ns);
     int h_flag = 0;
@@ -952,10 +954,7 @@ int64_t khx_insert_pipelined_dev(kh_table *t, khx_peer *x, int dist_hash, uint32
       if (!x->remote[r]) { set_error("peer %u not mapped", r); return KH_ERR_INVALID; }
       hd.h[r] = reinterpret_cast<PeerHeader *>(reinterpret_cast<unsigned char *>(x->remote[r]) + body);
     }
-    static const unsigned long long timeout_ns = [] {
-      const char *e = getenv("KH_PEER_TIMEOUT_MS");
-      return (e && atoll(e) > 0) ? (unsigned long long)atoll(e) * 1000000ULL : 10000000000ULL;
-    }();
+    const unsigned long long timeout_ns = peer_timeout_ns();
     DevBuf<unsigned long long> d_counts((size_t)chunks * p), d_matrix((size_t)chunks * p * p);
     DevBuf<BkSegs> d_segs(chunks);
     DevBuf<int> d_flags(2);                                   // [0] barrier time-out, [1] sub-slab overflow

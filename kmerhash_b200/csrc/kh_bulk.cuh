@@ -29,6 +29,7 @@
 // tile of keys lands in shared memory while the current one is sorted and written out.
 #pragma once
 #include <cstdint>
+#include <cooperative_groups.h>
 #include <cub/block/block_scan.cuh>
 #include "kh_table.cuh"
 #include "kh_hll.cuh"
@@ -674,6 +675,133 @@ __global__ void __launch_bounds__(TI_THREADS, 2) tile_insert_kernel(const TileAr
       }
     }
     __syncthreads();
+    tile_writeback<W>(sk, sv, g);
+    __syncthreads();
+  }
+  fresh = warp_sum(fresh);
+  if ((threadIdx.x & 31) == 0 && fresh) atomicAdd(a.n_new, (unsigned long long)fresh);
+}
+
+// ---------------------------------------------------------------------------------------------------------------------
+// region insert: a thread-block CLUSTER per level-1 region, for tables with more tiles than regions
+// ---------------------------------------------------------------------------------------------------------------------
+// When a region spans T = 2^tb tiles (1 <= tb <= 4), the level-2 pass -- another read and write of every record -- can
+// be saved: a cluster of T CTAs takes the region, CTA c stages tile (region << tb) + c in ITS shared memory, all CTAs
+// stream the region's records (interleaved chunks) and every record is inserted into the tile its tag names, local or
+// in a neighbour SM's shared memory (distributed shared memory: cluster.map_shared_rank + generic loads / atomics).
+// Probe rule, deferral and write-back are the tile insert's; the cluster barrier separates stage / insert / write-back.
+
+// 16 bytes in ONE load through a generic pointer (a key of two words must not be seen half written by a neighbour's 128-bit CAS)
+__device__ __forceinline__ void ldg_v2(const uint64_t *p, uint64_t &a, uint64_t &b) {
+  asm volatile("ld.volatile.v2.u64 {%0,%1}, [%2];" : "=l"(a), "=l"(b) : "l"(p) : "memory");
+}
+// tile_put on GENERIC pointers (the tile may live in another CTA's shared memory)
+template <int W>
+__device__ __forceinline__ uint32_t tile_put_cluster(uint64_t *sk, uint32_t *sv, const uint64_t (&key)[W], uint32_t lb, uint32_t v) {
+  if (key_is_empty<W>(key)) return 2u;
+  while (lb < (uint32_t)BK_BUCKETS) {
+    if constexpr (W == 1) {
+      uint64_t k0, k1, k2, k3;
+      ldg_v2(sk + lb * 4, k0, k1);
+      ldg_v2(sk + lb * 4 + 2, k2, k3);
+      int m = k3 == key[0] ? 3 : -1;
+      m = k2 == key[0] ? 2 : m; m = k1 == key[0] ? 1 : m; m = k0 == key[0] ? 0 : m;
+      uint32_t is_new = 0;
+      if (m < 0) {
+        int e = k3 == EMPTY_WORD ? 3 : -1;
+        e = k2 == EMPTY_WORD ? 2 : e; e = k1 == EMPTY_WORD ? 1 : e; e = k0 == EMPTY_WORD ? 0 : e;
+        if (e < 0) { ++lb; continue; }
+        const uint64_t old = atomicCAS(reinterpret_cast<unsigned long long *>(&sk[lb * 4 + e]), (unsigned long long)EMPTY_WORD,
+                                       (unsigned long long)key[0]);
+        if (old != EMPTY_WORD && old != key[0]) continue;
+        is_new = old == EMPTY_WORD ? 1u : 0u;
+        m = e;
+      }
+      atomicAdd(&sv[lb * 4 + m], v);
+      return is_new;
+    } else {
+      uint64_t a0, a1, b0, b1;
+      ldg_v2(sk + lb * 4, a0, a1);
+      ldg_v2(sk + lb * 4 + 2, b0, b1);
+      int m = (b0 == key[0] && b1 == key[W - 1]) ? 1 : -1;
+      m = (a0 == key[0] && a1 == key[W - 1]) ? 0 : m;
+      uint32_t is_new = 0;
+      if (m < 0) {
+        int e = (b0 == EMPTY_WORD && b1 == EMPTY_WORD) ? 1 : -1;
+        e = (a0 == EMPTY_WORD && a1 == EMPTY_WORD) ? 0 : e;
+        if (e < 0) { ++lb; continue; }
+        uint64_t o0, o1;
+        uint64_t *p = sk + lb * 4 + e * 2;
+        asm volatile("{\n\t.reg .b128 c, n, o;\n\tmov.b128 c, {%3, %4};\n\tmov.b128 n, {%5, %6};\n\t"
+                     "atom.relaxed.cluster.cas.b128 o, [%2], c, n;\n\tmov.b128 {%0, %1}, o;\n\t}"
+                     : "=l"(o0), "=l"(o1) : "l"(p), "l"(EMPTY_WORD), "l"(EMPTY_WORD), "l"(key[0]), "l"(key[W - 1]) : "memory");
+        const bool was_empty = o0 == EMPTY_WORD && o1 == EMPTY_WORD;
+        if (!was_empty && !(o0 == key[0] && o1 == key[W - 1])) continue;
+        is_new = was_empty ? 1u : 0u;
+        m = e;
+      }
+      atomicAdd(&sv[lb * 2 + m], v);
+      return is_new;
+    }
+  }
+  return 2u;
+}
+
+template <int W>
+__global__ void __launch_bounds__(TI_THREADS, 2) region_insert_kernel(const TileArgs a, const int tb) {
+  namespace cg = cooperative_groups;
+  cg::cluster_group cluster = cg::this_cluster();
+  constexpr int SLOTS = BkGeom<W>::SLOTS;
+  constexpr int TI_MLP = TiMlp<W>::value;
+  extern __shared__ __align__(16) unsigned char ti_smem[];
+  uint64_t *sk = reinterpret_cast<uint64_t *>(ti_smem);
+  uint32_t *sv = reinterpret_cast<uint32_t *>(sk + (size_t)SLOTS * W);
+  const uint32_t T = 1u << tb;                                     // == cluster.num_blocks()
+  const uint32_t crank = cluster.block_rank();
+  const uint64_t n_regions = (a.t.capacity / SLOTS) >> tb;
+  const uint64_t cid = blockIdx.x >> tb, ncl = gridDim.x >> tb;
+  const int lb_shift = 32 - a.lbk;                                 // table bucket = tag >> lb_shift
+  constexpr uint32_t CH = TI_THREADS * TI_MLP;                     // records per CTA and step
+  uint32_t fresh = 0;
+
+  for (uint64_t region = cid; region < n_regions; region += ncl) {
+    const uint32_t begin = (uint32_t)(region * a.slab);
+    const uint32_t end = (uint32_t)min(a.ends[(size_t)region * BK_CSTRIDE], (unsigned long long)(region + 1) * a.slab);
+    if (a.fresh == 1 && begin == end) continue;                    // cluster-uniform: nothing to add to empty, initialised tiles
+    const uint64_t tile = (region << tb) + crank;
+    uint4 *g = reinterpret_cast<uint4 *>(a.t.slots) + tile * (uint64_t)SLOTS * W;
+    tile_stage<W>(sk, sv, g, a.fresh == 0);
+    cluster.sync();
+    for (uint64_t i0 = (uint64_t)begin + (uint64_t)crank * CH + threadIdx.x; i0 < end; i0 += (uint64_t)T * CH) {
+      uint4 rec[TI_MLP][W];
+#pragma unroll
+      for (int j = 0; j < TI_MLP; ++j) {
+        const uint64_t i = i0 + (uint64_t)j * TI_THREADS;
+        if (i < end) {
+#pragma unroll
+          for (int w = 0; w < W; ++w) rec[j][w] = __ldg(a.recs + i * W + w);
+        }
+      }
+#pragma unroll
+      for (int j = 0; j < TI_MLP; ++j) {
+        const uint64_t i = i0 + (uint64_t)j * TI_THREADS;
+        if (i < end) {
+          uint64_t key[W];
+          uint32_t tag;
+          key[0] = (uint64_t)rec[j][0].x | ((uint64_t)rec[j][0].y << 32);
+          if (W == 1) tag = rec[j][0].z;
+          else { key[W - 1] = (uint64_t)rec[j][0].z | ((uint64_t)rec[j][0].w << 32); tag = rec[j][W - 1].x; }
+          const uint32_t gb = tag >> lb_shift;                     // bucket of the table
+          const uint32_t owner = (gb >> BK_BUCKET_BITS) & (T - 1u);
+          uint64_t *rk = cluster.map_shared_rank(sk, owner);
+          uint32_t *rv = cluster.map_shared_rank(sv, owner);
+          const uint32_t res = tile_put_cluster<W>(rk, rv, key, gb & (uint32_t)(BK_BUCKETS - 1), a.dflt);
+          if (res == 2u) a.defer_idx[atomicAdd(a.n_new + 1, 1ULL)] = (uint32_t)i;
+          else fresh += res;
+        }
+      }
+    }
+    cluster.sync();
     tile_writeback<W>(sk, sv, g);
     __syncthreads();
   }

@@ -648,7 +648,12 @@ int64_t bulk_finish(BulkBatch &b, kh_table *t, const uint64_t *d_keys, const BkS
   int rpt_log2 = b.lp - tile_bits;
   DevBuf<uint4> recs2;
   DevBuf<unsigned long long> l2buf;
-  if (tile_bits > b.lp) {
+  // more tiles than regions, at most 16 per region: a cluster of CTAs per region can insert into its tiles over distributed shared
+  // memory, which saves the level-2 pass (kh_bulk.cuh: region_insert_kernel).  OFF by default: measured at 1 B keys / 16 tiles
+  // per region the remote atomics cost 78 ms against 19.6 ms for level 2 + tile insert.  KH_CLUSTER=1 switches it on.
+  const bool cluster_on = getenv("KH_CLUSTER") && atoi(getenv("KH_CLUSTER")) != 0;         // read per call: tests switch it
+  const int cluster_tb = (cluster_on && tile_bits > b.lp && tile_bits - b.lp <= 4) ? tile_bits - b.lp : 0;
+  if (tile_bits > b.lp && !cluster_tb) {
     // more tiles than regions: split every region by the next tag bits.  Default: into one SLAB per tile, sized for a
     // uniform hash like the level-1 slabs (no histogram pass; a record that does not fit hands its key to the overflow
     // list).  KH_L2_EXACT=1: histogram of the tags -> scan -> scatter into exactly packed runs.
@@ -713,7 +718,27 @@ int64_t bulk_finish(BulkBatch &b, kh_table *t, const uint64_t *d_keys, const BkS
     a.fresh = t->uninit ? 2 : (t->size == 0 ? 1 : 0); a.dflt = dflt; a.n_new = t->counters.p; a.defer_idx = defer.p;
     const int grid = (int)std::min<uint64_t>(t->capacity / tile_slots, (uint64_t)t->sms * 2);
     kev_begin(t, 0, s);
-    if (W == 1) {
+    if (cluster_tb) {
+      const int T = 1 << cluster_tb;
+      const size_t smem = W == 1 ? tile_smem_bytes<1>() : tile_smem_bytes<2>();
+      const void *fn = W == 1 ? (const void *)region_insert_kernel<1> : (const void *)region_insert_kernel<2>;
+      KH_CUDA(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+      if (T > 8) KH_CUDA(cudaFuncSetAttribute(fn, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
+      cudaLaunchConfig_t cfg{};
+      cudaLaunchAttribute attr[1];
+      attr[0].id = cudaLaunchAttributeClusterDimension;
+      attr[0].val.clusterDim.x = (unsigned)T; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+      cfg.blockDim = dim3(TI_THREADS); cfg.dynamicSmemBytes = smem; cfg.stream = s; cfg.attrs = attr; cfg.numAttrs = 1;
+      cfg.gridDim = dim3((unsigned)T);
+      int max_clusters = 0;
+      KH_CUDA(cudaOccupancyMaxActiveClusters(&max_clusters, fn, &cfg));
+      const uint64_t n_regions = (t->capacity / tile_slots) >> cluster_tb;
+      const uint64_t ncl = std::max<uint64_t>(1, std::min<uint64_t>(n_regions, (uint64_t)std::max(max_clusters, 1)));
+      cfg.gridDim = dim3((unsigned)(ncl * T));
+      if (W == 1) KH_CUDA(cudaLaunchKernelEx(&cfg, region_insert_kernel<1>, a, cluster_tb));
+      else KH_CUDA(cudaLaunchKernelEx(&cfg, region_insert_kernel<2>, a, cluster_tb));
+      g_launches.fetch_add(1, std::memory_order_relaxed);
+    } else if (W == 1) {
       KH_CUDA(cudaFuncSetAttribute(tile_insert_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tile_smem_bytes<1>()));
       KH_LAUNCH(tile_insert_kernel<1>, grid, TI_THREADS, tile_smem_bytes<1>(), s, a);
     } else {

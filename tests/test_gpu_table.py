@@ -702,6 +702,38 @@ def test_peer_memory_barrier(kh):
                 lib.khx_peer_destroy(h)
 
 
+def test_peer_barrier_timeout_poisons_every_rank(kh, monkeypatch):
+    """a rank that gives up in the flag barrier must not leave its peers paired with the wrong epoch: it writes a poison
+    value into every peer's copy of its flag, its own buffers become unusable, and a peer that reaches the barrier later
+    (or any later barrier) fails too instead of passing with stale counts"""
+    import torch
+    from kmerhash_b200._lib import lib, KmerHashError
+    monkeypatch.setenv("KH_PEER_TIMEOUT_MS", "150")
+    p = 2
+    tables = [kh.HashMap(1, "MURMUR64avx", "COUNT") for _ in range(p)]
+    peers = [lib.khx_peer_create(0, r, p, 1024, 1) for r in range(p)]
+    try:
+        assert all(peers)
+        for r in range(p):
+            for q in range(p):
+                if q != r:
+                    assert lib.khx_peer_set(peers[r], q, lib.khx_peer_recv_ptr(peers[q])) == 0
+        row = torch.tensor([5, 6], dtype=torch.int64, device="cuda")
+        torch.cuda.synchronize()
+        with pytest.raises(KmerHashError):
+            tables[0].peer_sync(peers[0], 1, row, p)          # rank 1 never shows up
+        assert lib.khx_peer_poisoned(peers[0]) == 1
+        with pytest.raises(KmerHashError):
+            tables[0].peer_sync(peers[0], 2)                   # poisoned buffers refuse further barriers
+        with pytest.raises(KmerHashError):
+            tables[1].peer_sync(peers[1], 1, row, p)          # the late peer sees the poison, not a passed barrier
+        assert lib.khx_peer_poisoned(peers[1]) == 1
+    finally:
+        for h in peers:
+            if h:
+                lib.khx_peer_destroy(h)
+
+
 @pytest.mark.parametrize("p,W", [(2, 1), (3, 2), (8, 1), (8, 2)])
 def test_query_slab_exchange(kh, oracle_mod, p, W):
     """khx_query_scatter_slabs_dev / khx_query_slabs_dev / khx_unpermute_slabs_dev with p ranks emulated on one GPU: every
@@ -814,6 +846,36 @@ def test_capacity_follows_compiled_reference_over_overlapping_batches(kh, oracle
         assert m.capacity() == rm.capacity(), (batch, m.capacity(), rm.capacity())
 
 
+@pytest.mark.parametrize("W,lp,skew", [(1, 6, 0.0), (1, 7, 0.0), (2, 6, 0.0), (2, 8, 0.0), (1, 6, 0.3), (1, 6, 0.9), (2, 7, 0.3)])
+def test_bulk_insert_cluster_region_insert(kh, oracle_mod, monkeypatch, W, lp, skew):
+    """tables with more tiles than level-1 regions, up to 16 tiles per region (forced here with 64..256 regions; reached without
+    forcing above 2^25 slots): a thread-block cluster per region inserts into its tiles over distributed shared memory
+    (region_insert_kernel: clusters of 2, 4 and 8 CTAs here), 8- and 16-byte keys, a second batch into the filled table, skewed
+    batches (overflow list; at 90 % the general route takes over)"""
+    import torch
+    monkeypatch.setenv("KH_BULK_LP", str(lp))
+    monkeypatch.setenv("KH_CLUSTER", "1")
+    o = oracle_mod.port
+    rng = np.random.default_rng(170 + W + lp)
+    distinct, n = 1_200_000, 2_500_000
+    base = rng.integers(0, 2**62, size=(distinct, W), dtype=np.uint64)
+    m = kh.HashMap(W, "MURMUR64avx", "COUNT")
+    m.set_insert_window(True, 32 << 20, 1 << 20)
+    gm = o.Map(W, "COUNT")
+    for batch in range(2):
+        keys = base[rng.integers(0, distinct, size=n)]
+        if skew:
+            keys[rng.random(n) < skew] = base[7]
+        keys = np.ascontiguousarray(keys if W == 2 else keys[:, 0])
+        new = m.insert(torch.from_numpy(keys.view(np.int64)).cuda(), default=1)
+        before = gm.size()
+        gm.insert(keys, default=1)
+        assert new == gm.size() - before and m.size() == gm.size()
+        ek, ev = sort_pairs(*gm.to_vector())
+        tk, tv = sort_pairs(*m.to_vector())
+        assert np.array_equal(tk, ek) and np.array_equal(tv, ev)
+
+
 @pytest.mark.parametrize("W,exact,skew", [(1, "0", 0.0), (1, "1", 0.0), (2, "0", 0.0), (2, "1", 0.0), (1, "0", 0.3), (1, "0", 0.9)])
 def test_bulk_insert_level2_split(kh, oracle_mod, monkeypatch, W, exact, skew):
     """tables with more tiles than level-1 regions (forced here with 64 regions; reached without forcing above 2^25 slots):
@@ -823,6 +885,7 @@ def test_bulk_insert_level2_split(kh, oracle_mod, monkeypatch, W, exact, skew):
     import torch
     monkeypatch.setenv("KH_BULK_LP", "6")
     monkeypatch.setenv("KH_L2_EXACT", exact)
+    monkeypatch.setenv("KH_CLUSTER", "0")
     o = oracle_mod.port
     rng = np.random.default_rng(77 + W)
     distinct, n = 1_200_000, 2_500_000
