@@ -967,7 +967,7 @@ int64_t khx_insert_pipelined_dev(kh_table *t, khx_peer *x, int dist_hash, uint32
     BulkBatch b;
     bulk_pipe_begin(b, t, (uint64_t)p * slab_cap, R);
     const uint64_t tile_send = PS_TILE_BYTES / (8 * W);
-    const uint64_t tile_l1 = W == 1 ? L1Cfg<1>::TILE : L1Cfg<2>::TILE;
+    const uint64_t tile_l1 = l1_tile_keys(W);
     const size_t smem = W == 1 ? ps_smem_bytes<1>(p, false, false) : ps_smem_bytes<2>(p, false, false);
     for (int c = 0; c < chunks; ++c) {
       const uint64_t k0 = n * (uint64_t)c / chunks, k1 = n * (uint64_t)(c + 1) / chunks, m = k1 - k0;

@@ -304,6 +304,9 @@ __global__ void __launch_bounds__(L1_THREADS, 1) l1_scatter_kernel(const L1Args 
   }
 }
 
+// keys per level-1 tile (the pieces of a segmented batch are cut into tiles of this size)
+inline uint64_t l1_tile_keys(int W) { return W == 1 ? L1Cfg<1>::TILE : L1Cfg<2>::TILE; }
+
 // region r's cursor starts at r * slab
 static __global__ void l1_cursor_kernel(unsigned long long *cursors, int n_regions, unsigned long long slab) {
   const int r = blockIdx.x * blockDim.x + threadIdx.x;

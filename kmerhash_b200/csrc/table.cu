@@ -551,7 +551,7 @@ void bulk_feed(BulkBatch &b, kh_table *t, const uint64_t *d_keys, uint64_t m, cu
   a.keys = d_keys; a.n = m; a.lp = b.lp; a.hash_kind = t->hash_kind; a.h32 = hash_bits(t->hash_kind) == 32 ? 1 : 0; a.hp = t->hp;
   a.cursors = b.cursors.p; a.recs = b.recs.p; a.slab = b.slab;
   a.ovf_keys = b.ovf.p; a.ovf_count = b.ovf_count.p; a.ovf_cap = b.ovf_cap; a.g_regs = b.regs.p;
-  const uint64_t tile = t->W == 1 ? L1Cfg<1>::TILE : L1Cfg<2>::TILE;
+  const uint64_t tile = l1_tile_keys(t->W);
   BkSegs sg{};
   sg.nseg = 1;
   uint64_t n_tiles = (m + tile - 1) / tile;
