@@ -94,6 +94,12 @@ static __global__ void gen_tile_reads_kernel(const uint64_t *offsets, uint64_t n
   tile_read[t] = l;
 }
 
+// Where k-mer number i of a tile lies in the shared-memory out tile.  Every thread emits a run of up to 16 consecutive k-mers, so
+// in a plain layout the 32 lanes of a store instruction would hit addresses 128 bytes (W = 2: 256) apart: one bank, 32-way
+// conflict.  XOR of the low four index bits with the next four spreads them; the layout is a bijection inside every aligned group
+// of 16, so the copy-out can still walk the tile in order.
+__device__ __forceinline__ uint32_t gen_slot(uint32_t i) { return i ^ ((i >> 4) & 15u); }
+
 // four bytes at a time: bit 7 of every byte that equals the constant (exact: the add cannot carry across bytes)
 __device__ __forceinline__ uint32_t eq4(uint32_t w, uint32_t c4) {
   const uint32_t z = w ^ c4;
@@ -199,7 +205,8 @@ __global__ void __launch_bounds__(GEN_THREADS, 2) kmer_tiles_kernel(const __grid
     }
     const uint32_t nclean = __popc(clean);
     uint32_t cb, ctotal;
-    Scan(scan_tmp).ExclusiveSum(nclean, cb, ctotal);
+    if (__syncthreads_or(clean != 0xffffu)) Scan(scan_tmp).ExclusiveSum(nclean, cb, ctotal);
+    else { cb = 16u * (uint32_t)tid; ctotal = (uint32_t)GEN_TILE_BYTES; }          // no EOL character in the tile: positions are byte offsets
     cbase[tid] = cb; cmask[tid] = clean;
     if (nclean) {
       const uint32_t bit = (uint32_t)B * (cb + GEN_PAD);
@@ -363,7 +370,7 @@ __global__ void __launch_bounds__(GEN_THREADS, 2) kmer_tiles_kernel(const __grid
         if ((vmask >> i) & 1u) {
           const bool use_rc = a.canonical && !kmer_less<W>(fwd, rc);
 #pragma unroll
-          for (int q = 0; q < W; ++q) otile[(size_t)o * W + q] = use_rc ? rc[q] : fwd[q];
+          for (int q = 0; q < W; ++q) otile[(size_t)gen_slot(o) * W + q] = use_rc ? rc[q] : fwd[q];
           ++o;
         }
       }
@@ -383,7 +390,7 @@ __global__ void __launch_bounds__(GEN_THREADS, 2) kmer_tiles_kernel(const __grid
         if (i < ototal) {
           uint64_t key[W];
 #pragma unroll
-          for (int q = 0; q < W; ++q) key[q] = otile[(size_t)i * W + q];
+          for (int q = 0; q < W; ++q) key[q] = otile[(size_t)gen_slot(i) * W + q];
           own = bin_of<W>(a.dist, key);
         }
         // one shared-memory atomic per (warp, owner)
@@ -419,7 +426,7 @@ __global__ void __launch_bounds__(GEN_THREADS, 2) kmer_tiles_kernel(const __grid
           const uint32_t src = sidx[e];
           uint64_t *o = a.dst.base[r] + gpos * W;
 #pragma unroll
-          for (int q = 0; q < W; ++q) o[q] = otile[(size_t)src * W + q];
+          for (int q = 0; q < W; ++q) o[q] = otile[(size_t)gen_slot(src) * W + q];
         }
       }
     }
@@ -429,21 +436,19 @@ __global__ void __launch_bounds__(GEN_THREADS, 2) kmer_tiles_kernel(const __grid
       uint64_t room = a.out_cap > gbase ? a.out_cap - gbase : 0;
       const uint32_t cnt = (uint32_t)min((uint64_t)ototal, room);
       uint64_t *dst = a.out_keys + gbase * W;
-      const uint32_t words = cnt * W;
-      // head up to a 16-byte boundary, body as uint4, tail
-      const uint32_t head = min(words, (uint32_t)((reinterpret_cast<uintptr_t>(dst) >> 3) & 1u));
-      if (tid < (int)head) dst[tid] = otile[tid];
-      const uint32_t body = (words - head) >> 1;
-      const uint4 *s4 = reinterpret_cast<const uint4 *>(otile);   // only aligned when head == 0; otherwise go through u64 pairs
-      if (head == 0) {
-        uint4 *d4 = reinterpret_cast<uint4 *>(dst);
-        for (uint32_t i = tid; i < body; i += GEN_THREADS) d4[i] = s4[i];
-      } else {
+      if (W == 2) {                                             // one 16-byte store per k-mer
+        for (uint32_t i = tid; i < cnt; i += GEN_THREADS)
+          *reinterpret_cast<ulonglong2 *>(dst + 2 * (size_t)i) = *reinterpret_cast<const ulonglong2 *>(otile + 2 * (size_t)gen_slot(i));
+      } else {                                                  // 16-byte stores of two k-mers behind an 8-byte aligned head
+        const uint32_t head = min(cnt, (uint32_t)((reinterpret_cast<uintptr_t>(dst) >> 3) & 1u));
+        if (tid < (int)head) dst[tid] = otile[gen_slot(tid)];
+        const uint32_t body = (cnt - head) >> 1;
         ulonglong2 *d2 = reinterpret_cast<ulonglong2 *>(dst + head);
-        for (uint32_t i = tid; i < body; i += GEN_THREADS) d2[i] = make_ulonglong2(otile[head + 2 * i], otile[head + 2 * i + 1]);
+        for (uint32_t i = tid; i < body; i += GEN_THREADS)
+          d2[i] = make_ulonglong2(otile[gen_slot(head + 2 * i)], otile[gen_slot(head + 2 * i + 1)]);
+        const uint32_t done = head + 2 * body;
+        if (tid == 0 && done < cnt) dst[done] = otile[gen_slot(done)];
       }
-      const uint32_t done = head + 2 * body;
-      if (tid == 0 && done < words) dst[done] = otile[done];
     }
     __syncthreads();
   }
