@@ -33,7 +33,7 @@ struct HashParams {
 
 KH_HD constexpr int hash_bits(int kind) {
   return (kind == KH_HASH_MURMUR32 || kind == KH_HASH_MURMUR32AVX || kind == KH_HASH_MURMUR32SSE ||
-          kind == KH_HASH_FARM32 || kind == KH_HASH_CRC32C || kind == KH_HASH_MURMUR32FIN) ? 32 : 64;
+          kind == KH_HASH_FARM32 || kind == KH_HASH_CRC32C) ? 32 : 64;   // MURMUR32FIN is rejected by every entry point (keys <= 4 bytes only)
 }
 
 KH_HD uint32_t rotl32(uint32_t x, int r) { return (x << r) | (x >> (32 - r)); }
