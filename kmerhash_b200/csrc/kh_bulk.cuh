@@ -97,6 +97,7 @@ struct L1Args {
   uint64_t *ovf_keys;                  // keys whose region was full
   unsigned long long *ovf_count, ovf_cap;
   uint32_t *g_regs;                    // HLL_M registers of the table (cumulative over batches), merged with atomicMax
+  unsigned long long pos_base;         // ORD: batch position of keys[0] (the records carry their key's position in the batch)
 };
 
 constexpr int L1_THREADS = 1024;
@@ -108,12 +109,15 @@ template <int W> struct L1Cfg {
   static constexpr int BINS = BkL1<W>::BINS;
   static constexpr int BPT = BINS / L1_THREADS;                // bins per thread in the run-start step: 4 / 8
   static constexpr size_t SMEM = (size_t)2 * RAW_BYTES + (size_t)TILE * 4 + BINS * 2 + BINS * 4 + HLL_M + 16;
+  static constexpr size_t SMEM_ORD = SMEM + (size_t)TILE * 2;  // + where in the tile every sorted key came from
 };
 
 // dsegs: the pieces as a DEVICE-resident table (may be null: the launch argument `segs_arg` holds them).  The pipelined
 // multi-GPU receiver (exchange.cu) launches this kernel before the host knows how many keys every sender stored: a small
 // kernel behind the flag barrier writes the table, the grid is fixed and every CTA reads its tile count from it.
-template <int W>
+// ORD: the order-dependent reducers (FIRST / LAST with per-key values): every record also carries the position of its key in
+// the batch (the spare word of the record), from which the tile insert decides the winner and fetches its value.
+template <int W, bool ORD = false>
 __global__ void __launch_bounds__(L1_THREADS, 1) l1_scatter_kernel(const L1Args a, const __grid_constant__ BkSegs segs_arg,
                                                                    const BkSegs *dsegs) {
   using Cfg = L1Cfg<W>;
@@ -137,6 +141,7 @@ __global__ void __launch_bounds__(L1_THREADS, 1) l1_scatter_kernel(const L1Args 
   uint32_t *goff = cnt32 + BINS / 2;                           // run start in recs - run start in tile (mod 2^32)
   uint32_t *regs = goff + BINS;                                // HLL register bytes, four to a word
   const uint32_t mbar = (uint32_t)__cvta_generic_to_shared(regs + HLL_M / 4);
+  uint16_t *sorg = reinterpret_cast<uint16_t *>(regs + HLL_M / 4 + 4);   // ORD: [TILE] index inside the tile of every sorted key
   const uint32_t raw_s = (uint32_t)__cvta_generic_to_shared(raw);
   const int tid = threadIdx.x;
 
@@ -261,6 +266,7 @@ __global__ void __launch_bounds__(L1_THREADS, 1) l1_scatter_kernel(const L1Args 
 #pragma unroll
         for (int q = 0; q < W; ++q) skeys[pos * W + q] = raw[e * W + q];
         stags[pos] = hm[j];
+        if (ORD) sorg[pos] = (uint16_t)e;
       }
     }
 #pragma unroll
@@ -282,11 +288,11 @@ __global__ void __launch_bounds__(L1_THREADS, 1) l1_scatter_kernel(const L1Args 
         uint4 *o = a.recs + (size_t)gpos * W;
         if (W == 1) {
           const uint64_t k = skeys[e];
-          o[0] = make_uint4((uint32_t)k, (uint32_t)(k >> 32), t32, 0u);
+          o[0] = make_uint4((uint32_t)k, (uint32_t)(k >> 32), t32, ORD ? (uint32_t)(a.pos_base + base + sorg[e]) : 0u);
         } else {
           const ulonglong2 k = *reinterpret_cast<const ulonglong2 *>(skeys + 2 * e);
           o[0] = make_uint4((uint32_t)k.x, (uint32_t)(k.x >> 32), (uint32_t)k.y, (uint32_t)(k.y >> 32));
-          o[W - 1] = make_uint4(t32, 0u, 0u, 0u);
+          o[W - 1] = make_uint4(t32, ORD ? (uint32_t)(a.pos_base + base + sorg[e]) : 0u, 0u, 0u);
         }
       } else {                                        // the region's slab is full
         const unsigned long long at = atomicAdd(a.ovf_count, 1ULL);
@@ -508,6 +514,7 @@ struct TileArgs {
   uint32_t dflt;                         // addend of every key
   unsigned long long *n_new;             // [0] += new keys, [1] += deferred keys
   uint32_t *defer_idx;                   // positions (in recs) of the deferred keys
+  const uint32_t *vals;                  // ORD kernels: the batch's values by batch position (null: dflt for every key)
 };
 
 __device__ __forceinline__ void lds_v2(const uint64_t *p, uint64_t &a, uint64_t &b) {
@@ -525,9 +532,20 @@ __device__ __forceinline__ void cas128_shared(uint64_t *p, uint64_t e0, uint64_t
 // One key into the staged tile.  Probe rule = the table's own (kh_table.cuh): 64-byte buckets, linear over buckets, a key is
 // claimed in the FIRST empty slot in probe order, a lost race re-scans.  Returns 1 when the key was new, 0 when it was
 // present, 2 when its chain leaves the tile (or it is the all-ones key of the side slot): the caller defers it.
-// SET: the value is stored, not added (rebuild: keys are unique).
-template <int W, bool SET>
-__device__ __forceinline__ uint32_t tile_put(uint64_t *sk, uint32_t *sv, const uint64_t (&key)[W], uint32_t lb, uint32_t v) {
+// MODE: what happens to the value word of the key's slot: TP_ADD (COUNT), TP_SET (rebuild: keys are unique), TP_MIN / TP_MAX
+// (FIRST / LAST: v is the encoded batch position, the smallest / largest wins; under TP_MIN a key that was in the table
+// before the batch -- its bit in `oldbits` -- keeps its value word untouched).
+enum : int { TP_ADD = 0, TP_SET = 1, TP_MIN = 2, TP_MAX = 3 };
+template <int MODE>
+__device__ __forceinline__ void tile_value(uint32_t *sv, uint32_t slot, uint32_t v, uint32_t is_new, const uint32_t *oldbits) {
+  if (MODE == TP_SET) sv[slot] = v;
+  else if (MODE == TP_ADD) atomicAdd(&sv[slot], v);
+  else if (MODE == TP_MAX) atomicMax(&sv[slot], v);
+  else if (is_new || !oldbits || !((oldbits[slot >> 5] >> (slot & 31)) & 1u)) atomicMin(&sv[slot], v);
+}
+template <int W, int MODE>
+__device__ __forceinline__ uint32_t tile_put(uint64_t *sk, uint32_t *sv, const uint64_t (&key)[W], uint32_t lb, uint32_t v,
+                                             const uint32_t *oldbits = nullptr) {
   if (key_is_empty<W>(key)) return 2u;
   while (lb < (uint32_t)BK_BUCKETS) {
     if constexpr (W == 1) {
@@ -547,7 +565,7 @@ __device__ __forceinline__ uint32_t tile_put(uint64_t *sk, uint32_t *sv, const u
         is_new = old == EMPTY_WORD ? 1u : 0u;
         m = e;
       }
-      if (SET) sv[lb * 4 + m] = v; else atomicAdd(&sv[lb * 4 + m], v);
+      tile_value<MODE>(sv, lb * 4 + m, v, is_new, oldbits);
       return is_new;
     } else {
       uint64_t a0, a1, b0, b1;
@@ -567,7 +585,7 @@ __device__ __forceinline__ uint32_t tile_put(uint64_t *sk, uint32_t *sv, const u
         is_new = was_empty ? 1u : 0u;
         m = e;
       }
-      if (SET) sv[lb * 2 + m] = v; else atomicAdd(&sv[lb * 2 + m], v);
+      tile_value<MODE>(sv, lb * 2 + m, v, is_new, oldbits);
       return is_new;
     }
   }
@@ -670,7 +688,7 @@ __global__ void __launch_bounds__(TI_THREADS, 2) tile_insert_kernel(const TileAr
             if (W == 1) tag = rec[j][0].z;
             else { key[W - 1] = (uint64_t)rec[j][0].z | ((uint64_t)rec[j][0].w << 32); tag = rec[j][W - 1].x; }
             const uint32_t lb = (tag >> lb_shift) & (uint32_t)(BK_BUCKETS - 1);
-            const uint32_t res = tile_put<W, false>(sk, sv, key, lb, a.dflt);
+            const uint32_t res = tile_put<W, TP_ADD>(sk, sv, key, lb, a.dflt);
             if (res == 2u) a.defer_idx[atomicAdd(a.n_new + 1, 1ULL)] = (uint32_t)i;
             else fresh += res;
           }
@@ -683,6 +701,149 @@ __global__ void __launch_bounds__(TI_THREADS, 2) tile_insert_kernel(const TileAr
   }
   fresh = warp_sum(fresh);
   if ((threadIdx.x & 31) == 0 && fresh) atomicAdd(a.n_new, (unsigned long long)fresh);
+}
+
+// The order-dependent reducers (FIRST = the reference's DiscardReducer / RH / LP insert, LAST = ReplaceReducer,
+// KH/robinhood_offset_hashmap_ptr.hpp:85-97) on the same tiles.  The level-1 records carry their key's batch position
+// (l1_scatter_kernel<W, true>).  Pass A claims the keys as above and races the positions in the VALUE word of the staged slot:
+// FIRST: empty slots start at 0xffffffff, atomicMin(position); keys that were in the table before the batch (bitmap `old`)
+// keep their value.  LAST: every slot starts at 0, atomicMax(position + 1); a key of the table that no record touched gets its
+// value back from the table tile.  Pass B (per slot, after a block barrier) replaces the winning position by its value
+// vals[position] (or dflt).  The write-back seals the occupied slots under FIRST (aux = AUX_SEALED_FIRST, as seal_kernel does)
+// so that the general kernel, which takes the deferred keys afterwards, never overrides them.
+template <int W> constexpr size_t tile_ord_smem_bytes() { return tile_smem_bytes<W>() + (size_t)BkGeom<W>::SLOTS / 8; }
+
+template <int W, bool LAST>
+__global__ void __launch_bounds__(TI_THREADS, 2) tile_insert_ord_kernel(const TileArgs a) {
+  constexpr int SLOTS = BkGeom<W>::SLOTS;
+  constexpr int TI_MLP = TiMlp<W>::value;
+  static_assert(SLOTS % TI_THREADS == 0, "a warp stages 32 consecutive slots: one word of the bitmap");
+  extern __shared__ __align__(16) unsigned char ti_smem[];
+  uint64_t *sk = reinterpret_cast<uint64_t *>(ti_smem);
+  uint32_t *sv = reinterpret_cast<uint32_t *>(sk + (size_t)SLOTS * W);
+  uint32_t *old = sv + SLOTS;                                      // [SLOTS / 32] FIRST: the slot held a key before the batch
+  const uint64_t n_tiles = a.t.capacity / SLOTS;
+  const int lb_shift = 32 - a.lbk;
+  const uint32_t rpt = 1u << a.rpt_log2;
+  const bool load = a.fresh == 0;
+  const uint32_t none = LAST ? 0u : 0xffffffffu;
+  uint32_t fresh = 0;
+
+  for (uint64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+    uint4 *g = reinterpret_cast<uint4 *>(a.t.slots) + tile * (uint64_t)SLOTS * W;
+    if (a.fresh == 1) {
+      bool any = false;
+      if (a.slab) {
+        for (uint32_t q = 0; q < rpt; ++q) {
+          const uint64_t r = tile * rpt + q;
+          any = any || a.ends[(size_t)r * BK_CSTRIDE] > r * a.slab;
+        }
+      } else any = a.ends[tile] > (tile ? a.ends[tile - 1] : 0ULL);
+      if (!any) continue;
+    }
+    for (int i = threadIdx.x; i < SLOTS; i += TI_THREADS) {        // stage
+      uint64_t w[2 * W];
+      bool occ = false;
+      if (load) {
+        LdCg<2 * W>::ld(g + (size_t)i * W, w);
+        occ = !key_is_empty<W>(w);
+      } else {
+#pragma unroll
+        for (int q = 0; q < W; ++q) w[q] = EMPTY_WORD;
+      }
+#pragma unroll
+      for (int q = 0; q < W; ++q) sk[i * W + q] = w[q];
+      sv[i] = (!LAST && occ) ? (uint32_t)w[W] : none;
+      if (!LAST) {
+        const uint32_t m = __ballot_sync(FULL_MASK, occ);
+        if ((threadIdx.x & 31) == 0) old[i >> 5] = m;
+      }
+    }
+    __syncthreads();
+
+    for (uint32_t q = 0; q < rpt; ++q) {                           // pass A
+      uint32_t begin, end;
+      if (a.slab) {
+        const uint64_t r = tile * rpt + q;
+        begin = (uint32_t)(r * a.slab);
+        end = (uint32_t)min(a.ends[(size_t)r * BK_CSTRIDE], (unsigned long long)(r + 1) * a.slab);
+      } else {
+        begin = tile ? (uint32_t)a.ends[tile - 1] : 0u;
+        end = (uint32_t)a.ends[tile];
+      }
+      for (uint64_t i0 = (uint64_t)begin + threadIdx.x; i0 < end; i0 += (uint64_t)TI_THREADS * TI_MLP) {
+        uint4 rec[TI_MLP][W];
+#pragma unroll
+        for (int j = 0; j < TI_MLP; ++j) {
+          const uint64_t i = i0 + (uint64_t)j * TI_THREADS;
+          if (i < end) {
+#pragma unroll
+            for (int w = 0; w < W; ++w) rec[j][w] = __ldg(a.recs + i * W + w);
+          }
+        }
+#pragma unroll
+        for (int j = 0; j < TI_MLP; ++j) {
+          const uint64_t i = i0 + (uint64_t)j * TI_THREADS;
+          if (i < end) {
+            uint64_t key[W];
+            uint32_t tag, pos;
+            key[0] = (uint64_t)rec[j][0].x | ((uint64_t)rec[j][0].y << 32);
+            if (W == 1) { tag = rec[j][0].z; pos = rec[j][0].w; }
+            else { key[W - 1] = (uint64_t)rec[j][0].z | ((uint64_t)rec[j][0].w << 32); tag = rec[j][W - 1].x; pos = rec[j][W - 1].y; }
+            const uint32_t lb = (tag >> lb_shift) & (uint32_t)(BK_BUCKETS - 1);
+            const uint32_t res = LAST ? tile_put<W, TP_MAX>(sk, sv, key, lb, pos + 1u)
+                                      : tile_put<W, TP_MIN>(sk, sv, key, lb, pos, load ? old : nullptr);
+            if (res == 2u) a.defer_idx[atomicAdd(a.n_new + 1, 1ULL)] = (uint32_t)i;
+            else fresh += res;
+          }
+        }
+      }
+    }
+    __syncthreads();
+
+    for (int i = threadIdx.x; i < SLOTS; i += TI_THREADS) {        // pass B + write back
+      uint64_t k[W];
+#pragma unroll
+      for (int q = 0; q < W; ++q) k[q] = sk[i * W + q];
+      const bool occ = !key_is_empty<W>(k);
+      uint32_t v = sv[i];
+      if (!occ) v = 0u;
+      else if (LAST) {
+        if (v) v = a.vals ? __ldg(a.vals + (v - 1u)) : a.dflt;
+        else v = W == 1 ? __ldcg(reinterpret_cast<const uint32_t *>(g + i) + 2) : __ldcg(reinterpret_cast<const uint32_t *>(g + (size_t)i * W + W - 1));
+      } else if (!(load && ((old[i >> 5] >> (i & 31)) & 1u))) {
+        v = a.vals ? __ldg(a.vals + v) : a.dflt;
+      }
+      const uint32_t aux = (!LAST && occ) ? AUX_SEALED_FIRST : 0u;
+      if (W == 1) g[i] = make_uint4((uint32_t)k[0], (uint32_t)(k[0] >> 32), v, aux);
+      else {
+        g[(size_t)i * W] = make_uint4((uint32_t)k[0], (uint32_t)(k[0] >> 32), (uint32_t)k[W - 1], (uint32_t)(k[W - 1] >> 32));
+        g[(size_t)i * W + W - 1] = make_uint4(v, aux, 0u, 0u);
+      }
+    }
+    __syncthreads();
+  }
+  fresh = warp_sum(fresh);
+  if ((threadIdx.x & 31) == 0 && fresh) atomicAdd(a.n_new, (unsigned long long)fresh);
+}
+
+// (key, position) of the deferred records of an ordered batch
+template <int W>
+__global__ void gather_rec_pos_kernel(const uint4 *recs, const uint32_t *idx, uint64_t n, uint32_t *pos) {
+  const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const uint4 r = recs[(size_t)idx[i] * W + W - 1];
+  pos[i] = W == 1 ? r.w : r.y;
+}
+template <int W>
+__global__ void gather_rec_pairs_kernel(const uint4 *recs, const uint32_t *idx, const uint32_t *pos, const uint32_t *vals, uint64_t n,
+                                        uint64_t *out_keys, uint32_t *out_vals) {
+  const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const uint4 r = recs[(size_t)idx[i] * W];
+  out_keys[i * W] = (uint64_t)r.x | ((uint64_t)r.y << 32);
+  if (W == 2) out_keys[i * W + 1] = (uint64_t)r.z | ((uint64_t)r.w << 32);
+  if (vals) out_vals[i] = vals[pos[i]];
 }
 
 // ---------------------------------------------------------------------------------------------------------------------
@@ -880,7 +1041,7 @@ __global__ void __launch_bounds__(TI_THREADS, 2) tile_rebuild_kernel(const Rebui
         const uint32_t val = (uint32_t)w[j][W];
         const uint64_t b = top_bits(spread_hash(hash_runtime<W>(a.hash_kind, key, a.hp)), bshift);
         uint32_t res = 2u;
-        if ((b >> BK_BUCKET_BITS) == tile) res = tile_put<W, true>(sk, sv, key, (uint32_t)b & (uint32_t)(BK_BUCKETS - 1), val);
+        if ((b >> BK_BUCKET_BITS) == tile) res = tile_put<W, TP_SET>(sk, sv, key, (uint32_t)b & (uint32_t)(BK_BUCKETS - 1), val);
         if (res == 2u) {
           const unsigned long long at = atomicAdd(a.n_placed + 1, 1ULL);
           if (at < a.defer_cap) {

@@ -67,6 +67,9 @@ struct BulkBatch {
   DevBuf<uint4> recs;
   DevBuf<uint64_t> ovf;
   DevBuf<uint32_t> regs;
+  // FIRST / LAST tables: the records carry batch positions (ord = INS_FIRST / INS_LAST), vals = the batch's values (may be null)
+  int ord = 0;
+  const uint32_t *vals = nullptr;
   // the whole batch again as ONE array, for the rare case that the general route has to take over (table that does not suit the
   // tiles, skewed batch); unset: the caller's key pointer / pieces are used
   std::function<const uint64_t *(DevBuf<uint64_t> &, cudaStream_t)> refetch;

@@ -14,6 +14,7 @@
 #include <mutex>
 #include <vector>
 #include <cub/device/device_scan.cuh>
+#include <cub/device/device_radix_sort.cuh>
 #include <cub/block/block_scan.cuh>
 
 #include "kh_common.h"
@@ -511,10 +512,12 @@ uint64_t insert_resident(kh_table *t, const uint64_t *d_keys, const uint32_t *d_
 bool bulk_on() { static const bool on = !(getenv("KH_BULK") && atoi(getenv("KH_BULK")) == 0); return on; }
 constexpr uint64_t BULK_MAX_KEYS = 3ULL << 29;      // record positions are 32-bit: (1.125 + 1) * n + pads stays below 2^32
 
-// COUNT batch with one addend for all keys, 64-byte buckets, large enough to pay for streaming the table once
-bool bulk_candidate(const kh_table *t, const uint32_t *d_vals, uint64_t n) {
-  return bulk_on() && t->window_on && t->reducer == KH_REDUCE_COUNT && !d_vals && t->LB * t->G == 64 &&
-         n >= t->window_min_keys && n >= 1024 && n <= BULK_MAX_KEYS;
+// COUNT batch with one addend for all keys, or a FIRST / LAST batch (values or not) that lies in one piece; 64-byte buckets,
+// large enough to pay for streaming the table once
+bool bulk_candidate(const kh_table *t, const uint32_t *d_vals, uint64_t n, const BkSegs *segs = nullptr) {
+  static const bool ord_on = !(getenv("KH_BULK_ORD") && atoi(getenv("KH_BULK_ORD")) == 0);
+  const bool kind_ok = t->reducer == KH_REDUCE_COUNT ? !d_vals : (ord_on && !segs);
+  return bulk_on() && t->window_on && kind_ok && t->LB * t->G == 64 && n >= t->window_min_keys && n >= 1024 && n <= BULK_MAX_KEYS;
 }
 
 // level-1 regions: as many as the LARGEST table this batch can lead to has tiles (then region == tile or finer and no
@@ -548,6 +551,7 @@ void bulk_feed(BulkBatch &b, kh_table *t, const uint64_t *d_keys, uint64_t m, cu
                const BkSegs *dsegs = nullptr) {
   if (!m) return;
   L1Args a;
+  a.pos_base = 0;
   a.keys = d_keys; a.n = m; a.lp = b.lp; a.hash_kind = t->hash_kind; a.h32 = hash_bits(t->hash_kind) == 32 ? 1 : 0; a.hp = t->hp;
   a.cursors = b.cursors.p; a.recs = b.recs.p; a.slab = b.slab;
   a.ovf_keys = b.ovf.p; a.ovf_count = b.ovf_count.p; a.ovf_cap = b.ovf_cap; a.g_regs = b.regs.p;
@@ -566,7 +570,16 @@ void bulk_feed(BulkBatch &b, kh_table *t, const uint64_t *d_keys, uint64_t m, cu
   if (!n_tiles) return;
   const int grid = dsegs ? t->sms : (int)std::min<uint64_t>(n_tiles, (uint64_t)t->sms);
   kev_begin(t, 2, s);
-  if (t->W == 1) {
+  if (b.ord) {                                                      // records with batch positions (one piece)
+    a.pos_base = b.fed;
+    if (t->W == 1) {
+      KH_CUDA(cudaFuncSetAttribute(l1_scatter_kernel<1, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)L1Cfg<1>::SMEM_ORD));
+      KH_LAUNCH((l1_scatter_kernel<1, true>), grid, L1_THREADS, L1Cfg<1>::SMEM_ORD, s, a, sg, dsegs);
+    } else {
+      KH_CUDA(cudaFuncSetAttribute(l1_scatter_kernel<2, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)L1Cfg<2>::SMEM_ORD));
+      KH_LAUNCH((l1_scatter_kernel<2, true>), grid, L1_THREADS, L1Cfg<2>::SMEM_ORD, s, a, sg, dsegs);
+    }
+  } else if (t->W == 1) {
     KH_CUDA(cudaFuncSetAttribute(l1_scatter_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)L1Cfg<1>::SMEM));   // per device
     KH_LAUNCH(l1_scatter_kernel<1>, grid, L1_THREADS, L1Cfg<1>::SMEM, s, a, sg, dsegs);
   } else {
@@ -627,18 +640,33 @@ int64_t bulk_finish(BulkBatch &b, kh_table *t, const uint64_t *d_keys, const BkS
     if (t->has_sticky) rebuild(t, t->capacity);                                       // the tiles carry no sticky bits
   } else {
     fits = (double)t->size + std::min((double)n, batch_est * (1.0 + hll_error_rate())) <= t->max_load * (double)t->capacity;
+    if (!fits) {
+      // The doubling schedule ends at the smallest capacity 128 * 2^j whose max_load bound holds the final size (the size only
+      // grows).  The final size is at least `lo` (4 sigma of the batch estimate), so the schedule reaches capacity_for(lo) in
+      // any case: grow there at once -- one rebuild instead of one per doubling and the general kernel in between -- provided
+      // the batch cannot overfill that table (`hi`); a final doubling, if the size demands it, follows the insert as always.
+      const double sig = 4.0 * hll_error_rate();
+      const double lo = std::max((double)t->size, batch_est * (1.0 - sig));
+      const double hi = (double)t->size + std::min((double)n, batch_est * (1.0 + sig));
+      const uint64_t cap_lo = std::max(t->capacity, capacity_for(t, (uint64_t)lo));
+      if (hi <= 0.5 * (t->max_load + 1.0) * (double)cap_lo) {
+        if (cap_lo != t->capacity) rebuild(t, cap_lo, t->size == 0);
+        fits = true;
+      }
+    }
     if (fits && t->has_sticky) rebuild(t, t->capacity);
   }
   const uint64_t tile_slots = (uint64_t)BK_TILE_BYTES / t->slot_bytes();
   const int lbk = log2_u64(std::max<uint64_t>(t->capacity / t->bucket_slots(), 1));
   const int tile_bits = lbk - BK_BUCKET_BITS;                        // log2(number of tiles)
+  // ordered batches: a key on the overflow list has lost its batch position, the general route takes the whole batch
   const bool suits = fits && t->capacity >= tile_slots && n * 4 >= t->capacity && lbk <= 32 && tile_bits - b.lp <= BK_MAX_LP &&
-                     n_ovf <= b.ovf_cap;
+                     n_ovf <= (b.ord ? 0ULL : b.ovf_cap);
   if (!suits) {
     b.recs.release(); b.ovf.release();
     DevBuf<uint64_t> flat;
     const uint64_t *keys = b.refetch ? b.refetch(flat, s) : flatten_segments(t, d_keys, n, segs, flat, s);
-    insert_general(t, keys, nullptr, n, dflt, estimate != 0, s);
+    insert_general(t, keys, b.vals, n, dflt, estimate != 0, s);
     KH_CUDA(cudaStreamSynchronize(s));
     return (int64_t)(t->size - size0);
   }
@@ -652,7 +680,7 @@ int64_t bulk_finish(BulkBatch &b, kh_table *t, const uint64_t *d_keys, const BkS
   // memory, which saves the level-2 pass (kh_bulk.cuh: region_insert_kernel).  OFF by default: measured at 1 B keys / 16 tiles
   // per region the remote atomics cost 78 ms against 19.6 ms for level 2 + tile insert.  KH_CLUSTER=1 switches it on.
   const bool cluster_on = getenv("KH_CLUSTER") && atoi(getenv("KH_CLUSTER")) != 0;         // read per call: tests switch it
-  const int cluster_tb = (cluster_on && tile_bits > b.lp && tile_bits - b.lp <= 4) ? tile_bits - b.lp : 0;
+  const int cluster_tb = (cluster_on && !b.ord && tile_bits > b.lp && tile_bits - b.lp <= 4) ? tile_bits - b.lp : 0;
   if (tile_bits > b.lp && !cluster_tb) {
     // more tiles than regions: split every region by the next tag bits.  Default: into one SLAB per tile, sized for a
     // uniform hash like the level-1 slabs (no histogram pass; a record that does not fit hands its key to the overflow
@@ -700,11 +728,11 @@ int64_t bulk_finish(BulkBatch &b, kh_table *t, const uint64_t *d_keys, const BkS
     if (use_slab) KH_CUDA(cudaMemcpyAsync(&n_ovf, b.ovf_count.p, sizeof(n_ovf), cudaMemcpyDeviceToHost, s));
     KH_CUDA(cudaStreamSynchronize(s));                               // tmp goes out of scope; the overflow count is final
     recs = recs2.p; ends = a.tile_cur; slab = use_slab ? slab2 : 0; rpt_log2 = 0;
-    if (n_ovf > b.ovf_cap) {                                         // a heavily skewed batch: the general route takes over
+    if (n_ovf > (b.ord ? 0ULL : b.ovf_cap)) {                        // a heavily skewed batch: the general route takes over
       b.recs.release(); recs2.release();
       DevBuf<uint64_t> flat;
       const uint64_t *keys = b.refetch ? b.refetch(flat, s) : flatten_segments(t, d_keys, n, segs, flat, s);
-      insert_general(t, keys, nullptr, n, dflt, estimate != 0, s);
+      insert_general(t, keys, b.vals, n, dflt, estimate != 0, s);
       KH_CUDA(cudaStreamSynchronize(s));
       return (int64_t)(t->size - size0);
     }
@@ -716,9 +744,18 @@ int64_t bulk_finish(BulkBatch &b, kh_table *t, const uint64_t *d_keys, const BkS
     TileArgs a;
     a.t = t->view(); a.recs = recs; a.ends = ends; a.slab = slab; a.rpt_log2 = rpt_log2; a.lbk = lbk;
     a.fresh = t->uninit ? 2 : (t->size == 0 ? 1 : 0); a.dflt = dflt; a.n_new = t->counters.p; a.defer_idx = defer.p;
+    a.vals = b.vals;
     const int grid = (int)std::min<uint64_t>(t->capacity / tile_slots, (uint64_t)t->sms * 2);
     kev_begin(t, 0, s);
-    if (cluster_tb) {
+    if (b.ord) {
+      const size_t smem = W == 1 ? tile_ord_smem_bytes<1>() : tile_ord_smem_bytes<2>();
+      const void *fn = W == 1 ? (b.ord == INS_LAST ? (const void *)tile_insert_ord_kernel<1, true> : (const void *)tile_insert_ord_kernel<1, false>)
+                              : (b.ord == INS_LAST ? (const void *)tile_insert_ord_kernel<2, true> : (const void *)tile_insert_ord_kernel<2, false>);
+      KH_CUDA(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+      void *params[] = {(void *)&a};
+      KH_CUDA(cudaLaunchKernel(fn, dim3((unsigned)grid), dim3(TI_THREADS), params, smem, s));
+      g_launches.fetch_add(1, std::memory_order_relaxed);
+    } else if (cluster_tb) {
       const int T = 1 << cluster_tb;
       const size_t smem = W == 1 ? tile_smem_bytes<1>() : tile_smem_bytes<2>();
       const void *fn = W == 1 ? (const void *)region_insert_kernel<1> : (const void *)region_insert_kernel<2>;
@@ -752,22 +789,40 @@ int64_t bulk_finish(BulkBatch &b, kh_table *t, const uint64_t *d_keys, const BkS
   if (n_def) {       // chains that leave their tile, the all-ones key: a handful of keys through the global kernel
     Trace tr("bulk.deferred", s);
     DevBuf<uint64_t> nk(n_def * W);
-    if (W == 1) KH_LAUNCH((gather_rec_keys_kernel<1>), t->grid_for(n_def, 256), 256, 0, s, recs, defer.p, n_def, nk.p);
-    else KH_LAUNCH((gather_rec_keys_kernel<2>), t->grid_for(n_def, 256), 256, 0, s, recs, defer.p, n_def, nk.p);
-    insert_resident(t, nk.p, nullptr, n_def, dflt, s);
+    if (b.ord) {     // in batch order, with their values: sort the (position, record) pairs of the deferred keys by position
+      DevBuf<uint32_t> pos(n_def), pos_sorted(n_def), idx_sorted(n_def), nv(b.vals ? n_def : 0);
+      const int g = (int)((n_def + 255) / 256);
+      if (W == 1) KH_LAUNCH((gather_rec_pos_kernel<1>), g, 256, 0, s, recs, defer.p, n_def, pos.p);
+      else KH_LAUNCH((gather_rec_pos_kernel<2>), g, 256, 0, s, recs, defer.p, n_def, pos.p);
+      size_t tmp_bytes = 0;
+      KH_CUDA(cub::DeviceRadixSort::SortPairs(nullptr, tmp_bytes, pos.p, pos_sorted.p, defer.p, idx_sorted.p, (int)n_def, 0, 32, s));
+      DevBuf<unsigned char> tmp(tmp_bytes);
+      KH_CUDA(cub::DeviceRadixSort::SortPairs(tmp.p, tmp_bytes, pos.p, pos_sorted.p, defer.p, idx_sorted.p, (int)n_def, 0, 32, s));
+      g_launches.fetch_add(1, std::memory_order_relaxed);
+      if (W == 1) KH_LAUNCH((gather_rec_pairs_kernel<1>), g, 256, 0, s, recs, idx_sorted.p, pos_sorted.p, b.vals, n_def, nk.p, nv.p);
+      else KH_LAUNCH((gather_rec_pairs_kernel<2>), g, 256, 0, s, recs, idx_sorted.p, pos_sorted.p, b.vals, n_def, nk.p, nv.p);
+      insert_resident(t, nk.p, b.vals ? nv.p : nullptr, n_def, dflt, s);
+      KH_CUDA(cudaStreamSynchronize(s));                             // the temporaries go out of scope
+    } else {
+      if (W == 1) KH_LAUNCH((gather_rec_keys_kernel<1>), t->grid_for(n_def, 256), 256, 0, s, recs, defer.p, n_def, nk.p);
+      else KH_LAUNCH((gather_rec_keys_kernel<2>), t->grid_for(n_def, 256), 256, 0, s, recs, defer.p, n_def, nk.p);
+      insert_resident(t, nk.p, nullptr, n_def, dflt, s);
+    }
   }
   if (n_ovf) insert_resident(t, b.ovf.p, nullptr, n_ovf, dflt, s);
   KH_CUDA(cudaStreamSynchronize(s));
   return (int64_t)(t->size - size0);
 }
 
-int64_t insert_bulk(kh_table *t, const uint64_t *d_keys, uint64_t n, uint32_t dflt, int estimate, const BkSegs *segs, cudaStream_t s) {
+int64_t insert_bulk(kh_table *t, const uint64_t *d_keys, const uint32_t *d_vals, uint64_t n, uint32_t dflt, int estimate,
+                    const BkSegs *segs, cudaStream_t s) {
   Trace tr_ins("insert.total(bulk)", s);
   struct Materialize {                  // whatever happens: never leave uninitialised slots behind
     kh_table *t; cudaStream_t s;
     ~Materialize() { if (t->uninit) { try { materialize(t, s); cudaStreamSynchronize(s); } catch (...) {} } }
   } guard{t, s};
   BulkBatch b;
+  if (t->reducer != KH_REDUCE_COUNT) { b.ord = t->reducer == KH_REDUCE_FIRST ? INS_FIRST : INS_LAST; b.vals = d_vals; }
   bulk_begin(b, t, n, s);
   { Trace tr("bulk.level1", s); bulk_feed(b, t, d_keys, n, s, segs); }
   const int64_t got = bulk_finish(b, t, d_keys, segs, dflt, estimate, s);
@@ -971,7 +1026,7 @@ int64_t kh::insert_dev_impl(kh_table *t, const uint64_t *d_keys, const uint32_t 
   if (n == 0) return 0;
   const uint64_t size0 = t->size;
   const BkSegs *segs = pre ? pre->segs : nullptr;
-  if (bulk_candidate(t, d_vals, n)) return insert_bulk(t, d_keys, n, dflt, estimate, segs, s);
+  if (bulk_candidate(t, d_vals, n, segs)) return insert_bulk(t, d_keys, d_vals, n, dflt, estimate, segs, s);
   DevBuf<uint64_t> flat;
   d_keys = flatten_segments(t, d_keys, n, segs, flat, s);
   struct Materialize {                  // whatever path follows (or throws): never leave uninitialised slots behind

@@ -967,3 +967,93 @@ def test_kmer_generation_fused_with_sender(kh, oracle_mod, p, k, canonical):
         for h in peers:
             if h:
                 lib.khx_peer_destroy(h)
+
+
+@pytest.mark.parametrize("W", [1, 2])
+@pytest.mark.parametrize("red", ["FIRST", "LAST"])
+@pytest.mark.parametrize("with_vals,lp", [(True, None), (False, None), (True, 6)])
+def test_ordered_bulk_insert(kh, oracle_mod, monkeypatch, W, red, with_vals, lp):
+    """FIRST / LAST tables through the bulk route (l1_scatter_kernel<W, true> records with batch positions ->
+    tile_insert_ord_kernel): the value a key keeps is the one of its first / last occurrence in batch order, over three
+    batches (fresh table, live table, live table after growth), with and without per-key values, with the level-2 split forced
+    (lp = 6), against the oracle.  The all-ones key (side slot) and repeated keys at both ends of the batch are included."""
+    import torch
+    if lp is not None:
+        monkeypatch.setenv("KH_BULK_LP", str(lp))
+    o = oracle_mod.port
+    rng = np.random.default_rng(500 + W + (red == "LAST") * 10)
+    distinct, n = 900_000, 2_000_000
+    base = rng.integers(0, 2**62, size=(distinct, W), dtype=np.uint64)
+    base[5] = 2**64 - 1
+    m = kh.HashMap(W, "MURMUR64avx", red)
+    m.set_insert_window(True, 32 << 20, 1 << 20)
+    m.kernel_timing(True)
+    gm = o.Map(W, red)
+    for batch in range(3):
+        hi = distinct if batch else distinct // 2
+        keys = base[rng.integers(0, hi, size=n)]
+        keys[:3] = base[5]; keys[-3:] = base[5]; keys[7] = base[11]; keys[-7] = base[11]
+        keys = np.ascontiguousarray(keys if W == 2 else keys[:, 0])
+        vals = rng.integers(1, 2**31, size=n).astype(np.uint32) if with_vals else None
+        dk = torch.from_numpy(keys.view(np.int64)).cuda()
+        dv = torch.from_numpy(vals.view(np.int32)).cuda() if with_vals else None
+        before = gm.size()
+        new = m.insert(dk, dv, default=batch + 2)
+        gm.insert(keys, vals, default=batch + 2)
+        assert new == gm.size() - before and m.size() == gm.size()
+        ek, ev = sort_pairs(*gm.to_vector())
+        tk, tv = sort_pairs(*m.to_vector())
+        assert np.array_equal(tk, ek) and np.array_equal(tv, ev)
+    assert m.kernel_time("scatter")[1] >= 3                        # the bulk route ran for every batch (level-1 launches)
+
+
+@pytest.mark.parametrize("red", ["FIRST", "LAST"])
+def test_ordered_bulk_deferred_keys_keep_batch_order(kh, oracle_mod, red):
+    """tiles filled close to max_load 0.97: chains leave their tile, the deferred records go to the general kernel in batch
+    order with their values (sorted by the position the records carry); a second batch goes into the live table"""
+    import torch
+    rng = np.random.default_rng(31)
+    n_uniq = int(4 * 8192 * 0.97 * 0.95)
+    uniq = rng.integers(0, 2**62, size=n_uniq, dtype=np.uint64)
+    keys = np.ascontiguousarray(np.concatenate([uniq[rng.integers(0, n_uniq, size=6 * n_uniq)], uniq]))
+    m = kh.HashMap(1, "MURMUR64avx", red, min_load=0.1, max_load=0.97)
+    m.set_insert_window(True, 1 << 12, 1)
+    om = oracle_mod.port.Map(1, red)
+    m.reserve(n_uniq)
+    for batch in range(2):
+        vals = rng.integers(1, 2**31, size=keys.shape[0]).astype(np.uint32)
+        assert m.insert_no_estimate(keys, vals) == om.insert(keys, vals)
+        check_against(m, om)
+        keys = np.ascontiguousarray(np.concatenate([keys[:50000], rng.integers(0, 2**62, size=200, dtype=np.uint64)]))
+
+
+@pytest.mark.parametrize("red,max_load", [("COUNT", 0.5), ("COUNT", 0.9), ("FIRST", 0.7), ("LAST", 0.8)])
+def test_bulk_insert_no_estimate_grows_to_the_doubling_schedules_capacity(kh, oracle_mod, red, max_load):
+    """insert_no_estimate from capacity 128 (config 2's doubling mode) on the bulk route: the table grows at once to the capacity
+    the doubling schedule is bound to reach (lower bound of the batch's HyperLogLog estimate) instead of doubling 18 times; the
+    final capacity is the schedule's -- the smallest 128 * 2^j whose max_load bound holds the size -- and the contents are
+    the oracle's.  A second batch (mostly known keys) stays in place."""
+    import torch
+    rng = np.random.default_rng(901)
+    distinct, n = 1_500_000, 4_000_000
+    base = rng.integers(0, 2**62, size=distinct, dtype=np.uint64)
+    m = kh.HashMap(1, "MURMUR64avx", red, min_load=0.2, max_load=max_load)
+    m.set_insert_window(True, 32 << 20, 1 << 20)
+    m.kernel_timing(True)
+    om = oracle_mod.port.Map(1, red)
+    assert m.capacity() == 128
+    for batch in range(2):
+        keys = np.ascontiguousarray(base[rng.integers(0, distinct if batch == 0 else distinct // 3, size=n)])
+        vals = None if red == "COUNT" else rng.integers(1, 2**31, size=n).astype(np.uint32)
+        dk = torch.from_numpy(keys.view(np.int64)).cuda()
+        dv = None if vals is None else torch.from_numpy(vals.view(np.int32)).cuda()
+        assert m.insert_no_estimate(dk, dv) == om.insert(keys, vals)
+        assert m.size() == om.size()
+        cap = 128
+        while m.size() > max_load * cap:
+            cap *= 2
+        assert m.capacity() == cap
+        ek, ev = sort_pairs(*om.to_vector())
+        tk, tv = sort_pairs(*m.to_vector())
+        assert np.array_equal(tk, ek) and np.array_equal(tv, ev)
+    assert m.kernel_time("scatter")[1] >= 2 and m.kernel_time("rebuild")[1] <= 2
