@@ -234,6 +234,17 @@ int kh_partition_dev(int device, int hash_kind, uint32_t seed, int key_words, ui
 int kh_partition_fast_dev(int device, int hash_kind, uint32_t seed, int key_words, uint32_t p,
                           const uint64_t *d_keys, uint64_t n, uint64_t *d_out_keys, uint32_t *d_out_perm,
                           uint64_t *counts);
+/* kh_partition_fast_dev without any allocation.  No counterpart in the reference: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * Same arguments, same results as kh_partition_fast_dev.  The kernels' scratch (histogram, cursors, totals: 3 counters per
+ * destination) lies in a static device array of KH_PARTITION_NOALLOC_MAX_P * 24 bytes that every GPU loading the library
+ * holds until exit; p above KH_PARTITION_NOALLOC_MAX_P is rejected with KH_ERR_INVALID.  The call runs on the calling
+ * thread's per-thread stream and returns when the results are complete; it calls no cudaMalloc / cudaFree / pool routine.
+ * All calls on one device share the array: calls that overlap on the GPU (several host threads) race on it. */
+#define KH_PARTITION_NOALLOC_MAX_P 1024
+int kh_partition_fast_noalloc_dev(int device, int hash_kind, uint32_t seed, int key_words, uint32_t p,
+                                  const uint64_t *d_keys, uint64_t n, uint64_t *d_out_keys, uint32_t *d_out_perm,
+                                  uint64_t *counts);
 int kh_rank_host(int device, int hash_kind, uint32_t seed, int key_words, uint32_t p,
                  const uint64_t *keys, uint64_t n, uint32_t *out_rank);
 /* out[perm[i]] = in[i] for 1- or 4-byte elements (results of a permuted query back to input order) */

@@ -129,6 +129,7 @@ SIGNATURES = {
     "khx_plan_scatter_dev": (_int, [_vp, _int, _u32, _u32, _vp, _u64, _vp, _vp, _vp]),
     "khx_insert_recv_dev": (_i64, [_vp, _vp, _u64, _vp, _u32, _u32]),
     "kh_partition_fast_dev": (_int, [_int, _int, _u32, _int, _u32, _vp, _u64, _vp, _vp, _vp]),
+    "kh_partition_fast_noalloc_dev": (_int, [_int, _int, _u32, _int, _u32, _vp, _u64, _vp, _vp, _vp]),
     "kh_rank_host": (_int, [_int, _int, _u32, _int, _u32, _vp, _u64, _vp]),
     "kh_unpermute_dev": (_int, [_int, _int, _vp, _vp, _u64, _vp]),
     "khd_create": (_vp, [_int, _int, _int, _int, _int, _int]),

@@ -12,6 +12,7 @@
 // The scatter can write each destination segment through its own base pointer, which is how
 // dist.cu stores straight into the peer GPUs' receive buffers over NVLink.
 #include <algorithm>
+#include <mutex>
 #include <vector>
 #include <cub/device/device_scan.cuh>
 #include "kh_common.h"
@@ -186,6 +187,29 @@ void partition_dev(int device, int kind, const HashParams &hp, int W, uint32_t p
   KH_CUDA(cudaStreamSynchronize(s));
 }
 
+// ---- static scratch of kh_partition_fast_noalloc_dev ---------------------------------------------------------------------------------
+// hist | cursors | totals, KH_PARTITION_NOALLOC_MAX_P counters each.  In host code the array's NAME is a host-side stand-in, not a
+// device address: the address on a given device comes from cudaGetSymbolAddress with that device current (once per device).
+static __device__ __align__(256) unsigned long long g_part_scratch[3 * KH_PARTITION_NOALLOC_MAX_P];
+
+static unsigned long long *noalloc_scratch(int device) {            // the caller has made `device` current
+  static std::mutex mu;
+  static unsigned long long *addr[64] = {nullptr};
+  if (device < 0 || device >= 64) { set_error("device %d out of range", device); throw CudaError{KH_ERR_INVALID}; }
+  std::lock_guard<std::mutex> lk(mu);
+  if (!addr[device]) {
+    unsigned long long *ptr = nullptr;
+    const cudaError_t e = cudaGetSymbolAddress((void **)&ptr, g_part_scratch);
+    if (e != cudaSuccess || !ptr) {
+      cudaGetLastError();
+      set_error("cudaGetSymbolAddress(g_part_scratch) on device %d: %s", device, cudaGetErrorString(e));
+      throw CudaError{KH_ERR_CUDA};
+    }
+    addr[device] = ptr;
+  }
+  return addr[device];
+}
+
 }  // namespace kh
 
 using namespace kh;
@@ -239,6 +263,53 @@ int kh_partition_fast_dev(int device, int hash_kind, uint32_t seed, int key_word
     } else {
       if (d_out_perm) KH_LAUNCH((window_scatter_kernel<2, true>), sms * 4, WIN_BLOCK, 0, s, d_keys, n, spec, cursors.p, d_out_keys, d_out_perm);
       else KH_LAUNCH((window_scatter_kernel<2, false>), sms * 4, WIN_BLOCK, 0, s, d_keys, n, spec, cursors.p, d_out_keys, d_out_perm);
+    }
+    KH_CUDA(cudaStreamSynchronize(s));
+    for (uint32_t r = 0; r < p; ++r) counts[r] = h[r];
+    return KH_OK;
+  });
+}
+
+// kh_partition_fast_dev for callers that cannot allocate (code under CUDA graph capture, tight serving loops, harnesses that forbid
+// cudaMalloc): the same two kernels, their scratch -- histogram, cursors and totals, 3 x p counters -- in a file-scope device array
+// instead of pool allocations.  Every GPU that loads the library holds the KH_PARTITION_NOALLOC_MAX_P * 24 bytes until exit.  All
+// calls on a device share the array: the histogram is cleared at the start of every call, and calls that overlap on the GPU (two
+// host threads, i.e. two per-thread streams) race on it.  No counterpart in the reference.
+int kh_partition_fast_noalloc_dev(int device, int hash_kind, uint32_t seed, int key_words, uint32_t p,
+                                  const uint64_t *d_keys, uint64_t n, uint64_t *d_out_keys, uint32_t *d_out_perm,
+                                  uint64_t *counts) {
+  return (int)guarded([&]() -> int64_t {
+    if (kh_device_count() <= 0) { set_error("no CUDA device: kmerhash_b200 has no CPU fallback"); return KH_ERR_CUDA; }
+    if (key_words < 1 || key_words > 2 || !hash_kind_supported(hash_kind) || p == 0 || !counts || (n && (!d_keys || !d_out_keys))) {
+      set_error("bad partition arguments"); return KH_ERR_INVALID;
+    }
+    if (p > (uint32_t)KH_PARTITION_NOALLOC_MAX_P) {
+      set_error("kh_partition_fast_noalloc_dev: p = %u exceeds the static scratch (at most %d destinations)", p, KH_PARTITION_NOALLOC_MAX_P);
+      return KH_ERR_INVALID;
+    }
+    if (n >= (1ULL << 32)) { set_error("partition batch must be < 2^32 keys"); return KH_ERR_INVALID; }
+    for (uint32_t r = 0; r < p; ++r) counts[r] = 0;
+    if (n == 0) return KH_OK;
+    DeviceGuard g(device);
+    unsigned long long *scratch = noalloc_scratch(device);          // device address of g_part_scratch on THIS device
+    unsigned long long *hist = scratch, *cursors = scratch + KH_PARTITION_NOALLOC_MAX_P, *totals = scratch + 2 * KH_PARTITION_NOALLOC_MAX_P;
+    const int kind = fold_kind(hash_kind);
+    const BinSpec spec{1, 0, p, kind, make_hash_params(kind, seed, key_words)};
+    const int sms = sm_count(device);
+    cudaStream_t s = cudaStreamPerThread;
+    KH_CUDA(cudaMemsetAsync(hist, 0, p * sizeof(unsigned long long), s));             // the array keeps the last call's contents
+    const int hgrid = (int)std::max<uint64_t>(1, std::min<uint64_t>((n + 2047) / 2048, (uint64_t)sms * 4));
+    if (key_words == 1) KH_LAUNCH((bin_hist_kernel<1>), hgrid, 512, 0, s, d_keys, n, spec, (int)p, hist);
+    else KH_LAUNCH((bin_hist_kernel<2>), hgrid, 512, 0, s, d_keys, n, spec, (int)p, hist);
+    KH_LAUNCH(bin_cursor_kernel, 1, REGION_FINE, 0, s, hist, (int)p, cursors, totals);
+    unsigned long long h[KH_PARTITION_NOALLOC_MAX_P];
+    KH_CUDA(cudaMemcpyAsync(h, totals, p * sizeof(unsigned long long), cudaMemcpyDeviceToHost, s));
+    if (key_words == 1) {
+      if (d_out_perm) KH_LAUNCH((window_scatter_kernel<1, true>), sms * 4, WIN_BLOCK, 0, s, d_keys, n, spec, cursors, d_out_keys, d_out_perm);
+      else KH_LAUNCH((window_scatter_kernel<1, false>), sms * 4, WIN_BLOCK, 0, s, d_keys, n, spec, cursors, d_out_keys, d_out_perm);
+    } else {
+      if (d_out_perm) KH_LAUNCH((window_scatter_kernel<2, true>), sms * 4, WIN_BLOCK, 0, s, d_keys, n, spec, cursors, d_out_keys, d_out_perm);
+      else KH_LAUNCH((window_scatter_kernel<2, false>), sms * 4, WIN_BLOCK, 0, s, d_keys, n, spec, cursors, d_out_keys, d_out_perm);
     }
     KH_CUDA(cudaStreamSynchronize(s));
     for (uint32_t r = 0; r < p; ++r) counts[r] = h[r];
