@@ -119,7 +119,7 @@ __global__ void __launch_bounds__(GEN_THREADS, 2) kmer_tiles_kernel(const __grid
   __shared__ typename Scan::TempStorage scan_tmp;
   __shared__ unsigned long long s_base;
   __shared__ uint32_t s_firstbreak;
-  __shared__ uint32_t s_cnt[WIN_MAX_DST], s_lo[WIN_MAX_DST + 1];
+  __shared__ uint32_t s_cnt[WIN_MAX_DST], s_lo[WIN_MAX_DST + 1], s_vlo[WIN_MAX_DST + 1];
   __shared__ unsigned long long s_gbase[WIN_MAX_DST];
   extern __shared__ __align__(16) unsigned char gen_smem[];
   uint64_t *otile = reinterpret_cast<uint64_t *>(gen_smem);
@@ -401,13 +401,20 @@ __global__ void __launch_bounds__(GEN_THREADS, 2) kmer_tiles_kernel(const __grid
         own_loc[j] = (own << 16) | (start + __popc(peers & lt_mask));
       }
       __syncthreads();
-      if (tid < (int)p) {
-        uint32_t st = 0;
-        for (uint32_t r = 0; r < (uint32_t)tid; ++r) st += s_cnt[r];
-        const uint32_t c = s_cnt[tid];
-        s_lo[tid] = st;
-        if (tid == (int)p - 1) s_lo[p] = st + c;
-        s_gbase[tid] = c ? atomicAdd(&a.cursors[tid], (unsigned long long)c) : 0ULL;
+      if (tid < 32) {                                     // lane r < p: owner r's run -- its place in the slab and its VIRTUAL start:
+        constexpr uint32_t LK = 128 / (8 * W);           // congruent to the destination address modulo a 128-byte line, so that a warp
+        const uint32_t c = tid < (int)p ? s_cnt[tid] : 0u;   // of the copy-out stores whole aligned lines of the peer buffer
+        const unsigned long long gb = c ? atomicAdd(&a.cursors[tid], (unsigned long long)c) : 0ULL;
+        uint32_t st = 0, vs = 0;
+        for (uint32_t r = 0; r < p; ++r) {
+          const uint32_t cr = __shfl_sync(FULL_MASK, c, r);
+          const unsigned long long gr = __shfl_sync(FULL_MASK, gb, r);
+          const uint32_t ar = (uint32_t)(reinterpret_cast<uintptr_t>(a.dst.base[r]) / (8 * W) + gr) & (LK - 1);
+          vs += (ar - vs) & (LK - 1);
+          if (tid == (int)r) { s_lo[r] = st; s_vlo[r] = vs; s_gbase[r] = gb; }
+          st += cr; vs += cr;
+        }
+        if (tid == 0) { s_lo[p] = st; s_vlo[WIN_MAX_DST] = vs; }
       }
       __syncthreads();
 #pragma unroll
@@ -417,13 +424,16 @@ __global__ void __launch_bounds__(GEN_THREADS, 2) kmer_tiles_kernel(const __grid
       }
       __syncthreads();
       // sorted tile out: consecutive threads = consecutive positions inside an owner's run
-      for (uint32_t e = tid; e < ototal; e += GEN_THREADS) {
+      const uint32_t v_end = s_vlo[WIN_MAX_DST];
+      for (uint32_t v = tid; v < v_end; v += GEN_THREADS) {
         uint32_t r = 0;
 #pragma unroll
-        for (int q = 1; q < WIN_MAX_DST; ++q) r += (q < (int)p && e >= s_lo[q]) ? 1u : 0u;
-        const unsigned long long gpos = s_gbase[r] + (e - s_lo[r]);
+        for (int q = 1; q < WIN_MAX_DST; ++q) r += (q < (int)p && v >= s_vlo[q]) ? 1u : 0u;
+        const uint32_t off = v - s_vlo[r];
+        if (off >= s_cnt[r]) continue;                   // the gap in front of the next run
+        const unsigned long long gpos = s_gbase[r] + off;
         if (gpos < a.slab_cap) {
-          const uint32_t src = sidx[e];
+          const uint32_t src = sidx[s_lo[r] + off];
           uint64_t *o = a.dst.base[r] + gpos * W;
 #pragma unroll
           for (int q = 0; q < W; ++q) o[q] = otile[(size_t)gen_slot(src) * W + q];
