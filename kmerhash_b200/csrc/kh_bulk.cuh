@@ -973,16 +973,6 @@ __global__ void __launch_bounds__(TI_THREADS, 2) region_insert_kernel(const Tile
   if ((threadIdx.x & 31) == 0 && fresh) atomicAdd(a.n_new, (unsigned long long)fresh);
 }
 
-// keys of deferred / overflowed records -> a plain key array for the global insert kernel
-template <int W>
-__global__ void gather_rec_keys_kernel(const uint4 *recs, const uint32_t *idx, uint64_t n, uint64_t *out_keys) {
-  const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
-  for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
-    const uint4 r = __ldg(recs + (size_t)idx[i] * W);
-    out_keys[i * W] = (uint64_t)r.x | ((uint64_t)r.y << 32);
-    if (W == 2) out_keys[i * W + W - 1] = (uint64_t)r.z | ((uint64_t)r.w << 32);
-  }
-}
 
 // =====================================================================================================================
 // rebuild: old table -> new table as one streaming pass (reserve / rehash / shrink-after-erase / sticky cleaning)

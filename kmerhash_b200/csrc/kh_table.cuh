@@ -382,10 +382,17 @@ struct InsertArgs {
   // after growing the table.  defer_idx == nullptr: probe the whole table, then report "full".
   uint32_t *defer_idx;
   uint64_t probe_limit;
+  // The keys the bulk route's tile insert handed on (kh_bulk.cuh), taken straight from its records and its device-side counter
+  // so that no host round trip lies between the two kernels: n_dev != null: the batch has min(n, *n_dev) keys;
+  // rec_idx != null: key i = the key of record recs[rec_idx[i] * W] (then `keys` is unused).
+  const unsigned long long *n_dev;
+  const uint4 *recs;
+  const uint32_t *rec_idx;
 };
 
 template <int W, int LB, int G, int MODE>
 __global__ void __launch_bounds__(256) insert_kernel(InsertArgs a) {
+  const uint64_t n_keys = a.n_dev ? min((unsigned long long)a.n, *a.n_dev) : a.n;
   using Ge = Geom<W, LB, G>;
   const int lane = threadIdx.x & 31;
   const int gl = lane & (G - 1);
@@ -397,13 +404,19 @@ __global__ void __launch_bounds__(256) insert_kernel(InsertArgs a) {
   constexpr uint64_t NONE = ~0ULL;
   uint32_t fresh = 0;
 
-  for (uint64_t base = warp_id * 32; base < a.n; base += warps_total * 32) {
+  for (uint64_t base = warp_id * 32; base < n_keys; base += warps_total * 32) {
     const uint64_t i = base + lane;
-    const bool valid = i < a.n;
+    const bool valid = i < n_keys;
     uint64_t key[W];
 #pragma unroll
     for (int q = 0; q < W; ++q) key[q] = 0;
-    if (valid) load_key<W>(a.keys, i, key);
+    if (valid) {
+      if (a.rec_idx) {
+        const uint4 r = __ldg(a.recs + (size_t)a.rec_idx[i] * W);
+        key[0] = (uint64_t)r.x | ((uint64_t)r.y << 32);
+        if (W == 2) key[W - 1] = (uint64_t)r.z | ((uint64_t)r.w << 32);
+      } else load_key<W>(a.keys, i, key);
+    }
     uint32_t myv = a.dflt;
     if (MODE == INS_COUNT) { if (valid && a.vals) myv = __ldg(a.vals + i); }
     else {

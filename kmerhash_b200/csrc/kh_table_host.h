@@ -25,10 +25,11 @@ struct kh_table {
   HashParams hp;
   DevBuf<unsigned char> slots;
   DevBuf<uint32_t> side;              // 3 words
-  DevBuf<unsigned long long> counters;  // [0] n_new / n_hit, [1] export counter
-  DevBuf<int> status;
-  unsigned long long *h_counters = nullptr;  // pinned mirror
-  int *h_status = nullptr;
+  DevBuf<unsigned long long> counters;  // [0] n_new / n_hit, [1] export counter, [2] = the status word below
+  struct { int *p = nullptr; } status;  // lives in counters[2]: one memset clears, one copy reads counters and status
+  unsigned long long *h_counters = nullptr;  // pinned mirror (3 words)
+  int *h_status = nullptr;              // = h_counters + 2
+  uint32_t *h_regs = nullptr;           // pinned: HLL_M registers + the overflow count of a bulk batch (one copy, no staging)
   cudaStream_t stream[2] = {nullptr, nullptr};
   cudaEvent_t ev[2] = {nullptr, nullptr};
   // staging for *_host calls (grown on demand)
@@ -63,10 +64,14 @@ namespace kh {
 struct BulkBatch {
   uint64_t n = 0, fed = 0, slab = 0, ovf_cap = 0;
   int lp = 0;
-  DevBuf<unsigned long long> cursors, ovf_count;
-  DevBuf<uint4> recs;
-  DevBuf<uint64_t> ovf;
-  DevBuf<uint32_t> regs;
+  // ONE allocation (every allocation costs a round trip of ~10 us during which the GPU idles), carved into the arrays below
+  template <typename T> struct Part { T *p = nullptr; };
+  DevBuf<unsigned char> arena;
+  Part<unsigned long long> cursors, ovf_count;
+  Part<uint4> recs;
+  Part<uint64_t> ovf;
+  Part<uint32_t> regs, defer;                  // defer: record positions of the keys the tile insert hands on (n entries)
+  void release() { arena.release(); cursors.p = ovf_count.p = nullptr; recs.p = nullptr; ovf.p = nullptr; regs.p = defer.p = nullptr; }
   // FIRST / LAST tables: the records carry batch positions (ord = INS_FIRST / INS_LAST), vals = the batch's values (may be null)
   int ord = 0;
   const uint32_t *vals = nullptr;

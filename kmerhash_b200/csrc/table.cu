@@ -261,17 +261,19 @@ void kev_resolve(kh_table *t) {
   t->kev_used = 0;
 }
 
+struct RecSource { const unsigned long long *n_dev; const uint4 *recs; const uint32_t *rec_idx; };   // InsertArgs::n_dev ...
 void launch_insert(kh_table *t, const uint64_t *d_keys, const uint32_t *d_vals, uint64_t n, uint32_t dflt,
-                   int mode, cudaStream_t s, uint32_t *defer_idx = nullptr, bool l2_local = false) {
+                   int mode, cudaStream_t s, uint32_t *defer_idx = nullptr, bool l2_local = false, const RecSource *src = nullptr) {
   if (n == 0) return;
   InsertArgs a;
+  a.n_dev = src ? src->n_dev : nullptr; a.recs = src ? src->recs : nullptr; a.rec_idx = src ? src->rec_idx : nullptr;
   a.t = t->view(); a.keys = d_keys; a.vals = d_vals; a.n = n; a.dflt = dflt;
   a.hash_kind = t->hash_kind; a.hp = t->hp; a.idx_base = 0;
   a.n_new = t->counters.p; a.status = t->status.p;
   const uint64_t n_buckets = t->capacity / t->bucket_slots();
   a.defer_idx = defer_idx;
   a.probe_limit = defer_idx ? std::min<uint64_t>(n_buckets - 1, 127) : n_buckets - 1;
-  const int grid = t->grid_for(n, 256);
+  const int grid = src ? t->sms : t->grid_for(n, 256);              // src: n is an upper bound, the true count is small
   // The table layout is fixed by the BUCKET size (G x LB bytes), not by how a kernel reads a bucket, so a
   // 64-byte-bucket table can be probed 2 lanes x 32 B (best when probes miss the L2: fewer bytes in flight
   // per key, profiles/r01_sweep_*) or 1 thread x 64 B (half the instructions per key: best when the batch
@@ -309,13 +311,11 @@ void launch_lookup(kh_table *t, int op, const uint64_t *d_keys, uint64_t n, uint
 }
 
 void zero_counter(kh_table *t, cudaStream_t s) {
-  KH_CUDA(cudaMemsetAsync(t->counters.p, 0, 2 * sizeof(unsigned long long), s));
-  KH_CUDA(cudaMemsetAsync(t->status.p, 0, sizeof(int), s));
+  KH_CUDA(cudaMemsetAsync(t->counters.p, 0, 3 * sizeof(unsigned long long), s));   // counters and status
 }
 // reads counter[0] and the status flag; synchronises the stream
 uint64_t read_counter(kh_table *t, cudaStream_t s) {
-  KH_CUDA(cudaMemcpyAsync(t->h_counters, t->counters.p, 2 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, s));
-  KH_CUDA(cudaMemcpyAsync(t->h_status, t->status.p, sizeof(int), cudaMemcpyDeviceToHost, s));
+  KH_CUDA(cudaMemcpyAsync(t->h_counters, t->counters.p, 3 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, s));
   KH_CUDA(cudaStreamSynchronize(s));
   if (*t->h_status != 0) { set_error("table full: a key found no slot"); throw CudaError{KH_ERR_FULL}; }
   return t->h_counters[0];
@@ -537,10 +537,15 @@ void bulk_begin(BulkBatch &b, kh_table *t, uint64_t n, cudaStream_t s) {
   // a region's share of a uniformly hashed batch plus 12.5 % and a pad of 8 standard deviations of small shares
   b.slab = ((uint64_t)((double)n / (double)R * 1.125) + 1024 + 127) & ~127ULL;
   b.ovf_cap = n / 16 + 4096;
-  b.cursors.alloc((size_t)BK_CSTRIDE * R); b.ovf_count.alloc(1);
-  b.recs.alloc(b.slab * R * t->W); b.ovf.alloc(b.ovf_cap * t->W); b.regs.alloc(HLL_M);
-  KH_CUDA(cudaMemsetAsync(b.regs.p, 0, HLL_M * sizeof(uint32_t), s));
-  KH_CUDA(cudaMemsetAsync(b.ovf_count.p, 0, sizeof(unsigned long long), s));
+  { size_t off = 0;
+    auto take = [&](size_t bytes) { const size_t at = off; off += (bytes + 255) & ~(size_t)255; return at; };
+    const size_t o_recs = take(b.slab * R * t->W * sizeof(uint4)), o_ovf = take(b.ovf_cap * t->W * 8), o_cur = take((size_t)BK_CSTRIDE * R * 8),
+                 o_regs = take(HLL_M * 4 + 8), o_cnt = o_regs + HLL_M * 4, o_def = take(n * 4);   // registers | overflow count: one memset, one read-back
+    b.arena.alloc(off);
+    b.recs.p = reinterpret_cast<uint4 *>(b.arena.p + o_recs); b.ovf.p = reinterpret_cast<uint64_t *>(b.arena.p + o_ovf);
+    b.cursors.p = reinterpret_cast<unsigned long long *>(b.arena.p + o_cur); b.ovf_count.p = reinterpret_cast<unsigned long long *>(b.arena.p + o_cnt);
+    b.regs.p = reinterpret_cast<uint32_t *>(b.arena.p + o_regs); b.defer.p = reinterpret_cast<uint32_t *>(b.arena.p + o_def); }
+  KH_CUDA(cudaMemsetAsync(b.regs.p, 0, HLL_M * sizeof(uint32_t) + sizeof(unsigned long long), s));
   KH_LAUNCH(l1_cursor_kernel, (int)((R + 255) / 256), 256, 0, s, b.cursors.p, (int)R, (unsigned long long)b.slab);
 }
 
@@ -629,10 +634,14 @@ void insert_general(kh_table *t, const uint64_t *d_keys, const uint32_t *d_vals,
 int64_t bulk_finish(BulkBatch &b, kh_table *t, const uint64_t *d_keys, const BkSegs *segs, uint32_t dflt, int estimate, cudaStream_t s) {
   const uint64_t size0 = t->size, n = b.n;
   const int W = t->W;
+  // registers and overflow count: one copy into pinned memory (a pageable target would be staged by the driver)
+  KH_CUDA(cudaMemcpyAsync(t->h_regs, b.regs.p, HLL_M * sizeof(uint32_t) + sizeof(unsigned long long), cudaMemcpyDeviceToHost, s));
+  KH_CUDA(cudaStreamSynchronize(s));
   unsigned long long n_ovf = 0;
-  KH_CUDA(cudaMemcpyAsync(&n_ovf, b.ovf_count.p, sizeof(n_ovf), cudaMemcpyDeviceToHost, s));
+  std::memcpy(&n_ovf, t->h_regs + HLL_M, sizeof(n_ovf));
   uint8_t batch_regs[HLL_M];
-  const double batch_est = hll_finish(t->hash_kind, b.regs.p, batch_regs, s);        // synchronises s
+  for (int i = 0; i < HLL_M; ++i) batch_regs[i] = (uint8_t)t->h_regs[i];
+  const double batch_est = hll_estimate_from_regs(batch_regs, hash_bits(t->hash_kind));
   bool fits = true;
   if (estimate) {
     const double est = merge_batch_registers(t, batch_regs);
@@ -663,7 +672,7 @@ int64_t bulk_finish(BulkBatch &b, kh_table *t, const uint64_t *d_keys, const BkS
   const bool suits = fits && t->capacity >= tile_slots && n * 4 >= t->capacity && lbk <= 32 && tile_bits - b.lp <= BK_MAX_LP &&
                      n_ovf <= (b.ord ? 0ULL : b.ovf_cap);
   if (!suits) {
-    b.recs.release(); b.ovf.release();
+    b.release();
     DevBuf<uint64_t> flat;
     const uint64_t *keys = b.refetch ? b.refetch(flat, s) : flatten_segments(t, d_keys, n, segs, flat, s);
     insert_general(t, keys, b.vals, n, dflt, estimate != 0, s);
@@ -729,7 +738,7 @@ int64_t bulk_finish(BulkBatch &b, kh_table *t, const uint64_t *d_keys, const BkS
     KH_CUDA(cudaStreamSynchronize(s));                               // tmp goes out of scope; the overflow count is final
     recs = recs2.p; ends = a.tile_cur; slab = use_slab ? slab2 : 0; rpt_log2 = 0;
     if (n_ovf > (b.ord ? 0ULL : b.ovf_cap)) {                        // a heavily skewed batch: the general route takes over
-      b.recs.release(); recs2.release();
+      b.release(); recs2.release();
       DevBuf<uint64_t> flat;
       const uint64_t *keys = b.refetch ? b.refetch(flat, s) : flatten_segments(t, d_keys, n, segs, flat, s);
       insert_general(t, keys, b.vals, n, dflt, estimate != 0, s);
@@ -737,13 +746,13 @@ int64_t bulk_finish(BulkBatch &b, kh_table *t, const uint64_t *d_keys, const BkS
       return (int64_t)(t->size - size0);
     }
   }
-  DevBuf<uint32_t> defer(n);
+  uint32_t *const defer = b.defer.p;
   uint64_t n_def = 0;
   { Trace tr("bulk.tiles", s);
     zero_counter(t, s);
     TileArgs a;
     a.t = t->view(); a.recs = recs; a.ends = ends; a.slab = slab; a.rpt_log2 = rpt_log2; a.lbk = lbk;
-    a.fresh = t->uninit ? 2 : (t->size == 0 ? 1 : 0); a.dflt = dflt; a.n_new = t->counters.p; a.defer_idx = defer.p;
+    a.fresh = t->uninit ? 2 : (t->size == 0 ? 1 : 0); a.dflt = dflt; a.n_new = t->counters.p; a.defer_idx = defer;
     a.vals = b.vals;
     const int grid = (int)std::min<uint64_t>(t->capacity / tile_slots, (uint64_t)t->sms * 2);
     kev_begin(t, 0, s);
@@ -784,29 +793,31 @@ int64_t bulk_finish(BulkBatch &b, kh_table *t, const uint64_t *d_keys, const BkS
     }
     kev_end(t, s);
     t->uninit = false;                                               // enqueued: every tile gets written
+    if (!b.ord) {
+      // chains that leave their tile, the all-ones key: a handful of keys through the global kernel, which takes them from the
+      // records and their number from the tile kernel's counter (no host round trip in between); it probes the whole table
+      const RecSource src{t->counters.p + 1, recs, defer};
+      launch_insert(t, nullptr, nullptr, n, dflt, INS_COUNT, s, nullptr, false, &src);
+    }
     t->size += read_counter(t, s);
-    n_def = t->h_counters[1]; }
-  if (n_def) {       // chains that leave their tile, the all-ones key: a handful of keys through the global kernel
+    n_def = b.ord ? t->h_counters[1] : 0; }
+  if (n_def) {       // ordered tables: the deferred keys in batch order, with their values
     Trace tr("bulk.deferred", s);
     DevBuf<uint64_t> nk(n_def * W);
-    if (b.ord) {     // in batch order, with their values: sort the (position, record) pairs of the deferred keys by position
+    {                // sort the (position, record) pairs of the deferred keys by position
       DevBuf<uint32_t> pos(n_def), pos_sorted(n_def), idx_sorted(n_def), nv(b.vals ? n_def : 0);
       const int g = (int)((n_def + 255) / 256);
-      if (W == 1) KH_LAUNCH((gather_rec_pos_kernel<1>), g, 256, 0, s, recs, defer.p, n_def, pos.p);
-      else KH_LAUNCH((gather_rec_pos_kernel<2>), g, 256, 0, s, recs, defer.p, n_def, pos.p);
+      if (W == 1) KH_LAUNCH((gather_rec_pos_kernel<1>), g, 256, 0, s, recs, defer, n_def, pos.p);
+      else KH_LAUNCH((gather_rec_pos_kernel<2>), g, 256, 0, s, recs, defer, n_def, pos.p);
       size_t tmp_bytes = 0;
-      KH_CUDA(cub::DeviceRadixSort::SortPairs(nullptr, tmp_bytes, pos.p, pos_sorted.p, defer.p, idx_sorted.p, (int)n_def, 0, 32, s));
+      KH_CUDA(cub::DeviceRadixSort::SortPairs(nullptr, tmp_bytes, pos.p, pos_sorted.p, defer, idx_sorted.p, (int)n_def, 0, 32, s));
       DevBuf<unsigned char> tmp(tmp_bytes);
-      KH_CUDA(cub::DeviceRadixSort::SortPairs(tmp.p, tmp_bytes, pos.p, pos_sorted.p, defer.p, idx_sorted.p, (int)n_def, 0, 32, s));
+      KH_CUDA(cub::DeviceRadixSort::SortPairs(tmp.p, tmp_bytes, pos.p, pos_sorted.p, defer, idx_sorted.p, (int)n_def, 0, 32, s));
       g_launches.fetch_add(1, std::memory_order_relaxed);
       if (W == 1) KH_LAUNCH((gather_rec_pairs_kernel<1>), g, 256, 0, s, recs, idx_sorted.p, pos_sorted.p, b.vals, n_def, nk.p, nv.p);
       else KH_LAUNCH((gather_rec_pairs_kernel<2>), g, 256, 0, s, recs, idx_sorted.p, pos_sorted.p, b.vals, n_def, nk.p, nv.p);
       insert_resident(t, nk.p, b.vals ? nv.p : nullptr, n_def, dflt, s);
       KH_CUDA(cudaStreamSynchronize(s));                             // the temporaries go out of scope
-    } else {
-      if (W == 1) KH_LAUNCH((gather_rec_keys_kernel<1>), t->grid_for(n_def, 256), 256, 0, s, recs, defer.p, n_def, nk.p);
-      else KH_LAUNCH((gather_rec_keys_kernel<2>), t->grid_for(n_def, 256), 256, 0, s, recs, defer.p, n_def, nk.p);
-      insert_resident(t, nk.p, nullptr, n_def, dflt, s);
     }
   }
   if (n_ovf) insert_resident(t, b.ovf.p, nullptr, n_ovf, dflt, s);
@@ -880,10 +891,11 @@ kh_table *kh_create(int device, int map_kind, int key_words, int hash_kind, uint
       KH_CUDA(cudaStreamCreateWithFlags(&t->stream[i], cudaStreamNonBlocking));
       KH_CUDA(cudaEventCreateWithFlags(&t->ev[i], cudaEventDisableTiming));
     }
-    t->side.alloc(4); t->counters.alloc(2); t->status.alloc(1);
+    t->side.alloc(4); t->counters.alloc(3); t->status.p = reinterpret_cast<int *>(t->counters.p + 2);
     KH_CUDA(cudaMemset(t->side.p, 0, 4 * sizeof(uint32_t)));
-    KH_CUDA(cudaHostAlloc((void **)&t->h_counters, 2 * sizeof(unsigned long long), cudaHostAllocDefault));
-    KH_CUDA(cudaHostAlloc((void **)&t->h_status, sizeof(int), cudaHostAllocDefault));
+    KH_CUDA(cudaHostAlloc((void **)&t->h_counters, 3 * sizeof(unsigned long long), cudaHostAllocDefault));
+    t->h_status = reinterpret_cast<int *>(t->h_counters + 2);
+    KH_CUDA(cudaHostAlloc((void **)&t->h_regs, (HLL_M + 2) * sizeof(uint32_t), cudaHostAllocDefault));
     rebuild(t, 128);
     return KH_OK;
   });
@@ -897,8 +909,8 @@ void kh_destroy(kh_table *t) {
   for (int i = 0; i < 2; ++i) { if (t->stream[i]) cudaStreamDestroy(t->stream[i]); if (t->ev[i]) cudaEventDestroy(t->ev[i]); }
   for (auto &e : t->kev) { cudaEventDestroy(e.first); cudaEventDestroy(e.second); }
   if (t->h_counters) cudaFreeHost(t->h_counters);
-  if (t->h_status) cudaFreeHost(t->h_status);
-  t->slots.release(); t->side.release(); t->counters.release(); t->status.release();
+  if (t->h_regs) cudaFreeHost(t->h_regs);
+  t->slots.release(); t->side.release(); t->counters.release();
   for (int i = 0; i < 2; ++i) { t->d_keys[i].release(); t->d_vals[i].release(); t->d_u8[i].release(); }
   delete t;
   if (prev >= 0) cudaSetDevice(prev);
