@@ -989,17 +989,32 @@ struct RebuildArgs {
   unsigned long long defer_cap;
 };
 
+// The old slots are 30-60 % occupied, so a warp that hashed and placed "its" slots would run the expensive part (hash, probe,
+// claim: ~150 instructions) with most lanes idle -- and this kernel is issue-bound (ncu r02e: sm throughput 65 %, dram 10 %).
+// Instead every warp packs the occupied entries of the 32 * TI_MLP slots it loaded into a small stage in shared memory
+// (ballot + prefix) and works through them with all lanes busy.
+constexpr int RB_STAGE = 64;                                      // entries per warp and pass (two loads per lane)
+template <int W> constexpr size_t rebuild_smem_bytes() { return tile_smem_bytes<W>() + (size_t)(TI_THREADS / 32) * RB_STAGE * (8 * W + 4); }
+
 template <int W>
 __global__ void __launch_bounds__(TI_THREADS, 2) tile_rebuild_kernel(const RebuildArgs a) {
   constexpr int SLOTS = BkGeom<W>::SLOTS;
   constexpr int TI_MLP = TiMlp<W>::value;
+  constexpr int JP = RB_STAGE / 32;                                // loads per lane and pass
+  static_assert(TI_MLP % JP == 0, "a pass stages whole loads");
   extern __shared__ __align__(16) unsigned char ti_smem[];
   uint64_t *sk = reinterpret_cast<uint64_t *>(ti_smem);
   uint32_t *sv = reinterpret_cast<uint32_t *>(sk + (size_t)SLOTS * W);
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  uint64_t *stk = reinterpret_cast<uint64_t *>(sv + SLOTS) + (size_t)warp * RB_STAGE * W;          // this warp's stage: keys
+  uint32_t *stv = reinterpret_cast<uint32_t *>(reinterpret_cast<uint64_t *>(sv + SLOTS) + (size_t)(TI_THREADS / 32) * RB_STAGE * W) +
+                  warp * RB_STAGE;                                                                  // ... and values
+  const uint32_t lt_mask = (1u << lane) - 1u;
   const uint64_t n_tiles = a.dst.capacity / SLOTS;
   // old slots feeding new tile t: [t * per, (t + 1) * per), per = SLOTS * src.capacity / dst.capacity
   const uint64_t per_num = (uint64_t)SLOTS * a.src.capacity;       // < 2^64: capacities <= 2^40
   const uint64_t per = per_num / a.dst.capacity;                   // 0 when the table grows by more than SLOTS x
+  const uint64_t tiles_per_slot = per ? 1 : a.dst.capacity / per_num;
   const int bshift = 64 - a.lbk;
   uint32_t placed = 0;
   for (uint64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
@@ -1009,11 +1024,11 @@ __global__ void __launch_bounds__(TI_THREADS, 2) tile_rebuild_kernel(const Rebui
     uint64_t s0, s1;
     if (per) { s0 = tile * per; s1 = s0 + per; }
     else {                                                         // several new tiles per old slot: the first of them takes it
-      const uint64_t tiles_per_slot = a.dst.capacity / per_num;
       s0 = tile / tiles_per_slot; s1 = (tile % tiles_per_slot == 0) ? s0 + 1 : s0;
     }
     const uint4 *old = reinterpret_cast<const uint4 *>(a.src.slots);
-    for (uint64_t i0 = s0 + threadIdx.x; i0 < s1; i0 += (uint64_t)TI_THREADS * TI_MLP) {
+    // warp-uniform trip count: all lanes of a warp share i0 - lane
+    for (uint64_t i0 = s0 + threadIdx.x; i0 - lane < s1; i0 += (uint64_t)TI_THREADS * TI_MLP) {
       uint64_t w[TI_MLP][2 * W];
 #pragma unroll
       for (int j = 0; j < TI_MLP; ++j) {
@@ -1023,23 +1038,39 @@ __global__ void __launch_bounds__(TI_THREADS, 2) tile_rebuild_kernel(const Rebui
         if (i < s1) LdCg<2 * W>::ld(old + i * W, w[j]);
       }
 #pragma unroll
-      for (int j = 0; j < TI_MLP; ++j) {
-        if (key_is_empty<W>(w[j])) continue;
-        uint64_t key[W];
+      for (int j0 = 0; j0 < TI_MLP; j0 += JP) {
+        uint32_t total = 0;
 #pragma unroll
-        for (int q = 0; q < W; ++q) key[q] = w[j][q];
-        const uint32_t val = (uint32_t)w[j][W];
-        const uint64_t b = top_bits(spread_hash(hash_runtime<W>(a.hash_kind, key, a.hp)), bshift);
-        uint32_t res = 2u;
-        if ((b >> BK_BUCKET_BITS) == tile) res = tile_put<W, TP_SET>(sk, sv, key, (uint32_t)b & (uint32_t)(BK_BUCKETS - 1), val);
-        if (res == 2u) {
-          const unsigned long long at = atomicAdd(a.n_placed + 1, 1ULL);
-          if (at < a.defer_cap) {
+        for (int jj = 0; jj < JP; ++jj) {
+          const bool occ = !key_is_empty<W>(w[j0 + jj]);
+          const uint32_t m = __ballot_sync(FULL_MASK, occ);
+          if (occ) {
+            const uint32_t pos = total + __popc(m & lt_mask);
 #pragma unroll
-            for (int q = 0; q < W; ++q) a.defer_keys[at * W + q] = key[q];
-            a.defer_vals[at] = val;
+            for (int q = 0; q < W; ++q) stk[pos * W + q] = w[j0 + jj][q];
+            stv[pos] = (uint32_t)w[j0 + jj][W];
           }
-        } else placed += res;
+          total += __popc(m);
+        }
+        __syncwarp();
+        for (uint32_t e = lane; e < total; e += 32) {
+          uint64_t key[W];
+#pragma unroll
+          for (int q = 0; q < W; ++q) key[q] = stk[e * W + q];
+          const uint32_t val = stv[e];
+          const uint64_t b = top_bits(spread_hash(hash_runtime<W>(a.hash_kind, key, a.hp)), bshift);
+          uint32_t res = 2u;
+          if ((b >> BK_BUCKET_BITS) == tile) res = tile_put<W, TP_SET>(sk, sv, key, (uint32_t)b & (uint32_t)(BK_BUCKETS - 1), val);
+          if (res == 2u) {
+            const unsigned long long at = atomicAdd(a.n_placed + 1, 1ULL);
+            if (at < a.defer_cap) {
+#pragma unroll
+              for (int q = 0; q < W; ++q) a.defer_keys[at * W + q] = key[q];
+              a.defer_vals[at] = val;
+            }
+          } else placed += res;
+        }
+        __syncwarp();
       }
     }
     __syncthreads();

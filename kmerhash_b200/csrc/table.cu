@@ -364,11 +364,11 @@ bool rebuild_streamed(kh_table *t, uint64_t new_cap, cudaStream_t s) {
     const int grid = (int)std::min<uint64_t>(new_cap / tile_slots, (uint64_t)t->sms * 2);
     kev_begin(t, 0, s);
     if (W == 1) {
-      KH_CUDA(cudaFuncSetAttribute(tile_rebuild_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tile_smem_bytes<1>()));
-      KH_LAUNCH(tile_rebuild_kernel<1>, grid, TI_THREADS, tile_smem_bytes<1>(), s, a);
+      KH_CUDA(cudaFuncSetAttribute(tile_rebuild_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)rebuild_smem_bytes<1>()));
+      KH_LAUNCH(tile_rebuild_kernel<1>, grid, TI_THREADS, rebuild_smem_bytes<1>(), s, a);
     } else {
-      KH_CUDA(cudaFuncSetAttribute(tile_rebuild_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tile_smem_bytes<2>()));
-      KH_LAUNCH(tile_rebuild_kernel<2>, grid, TI_THREADS, tile_smem_bytes<2>(), s, a);
+      KH_CUDA(cudaFuncSetAttribute(tile_rebuild_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)rebuild_smem_bytes<2>()));
+      KH_LAUNCH(tile_rebuild_kernel<2>, grid, TI_THREADS, rebuild_smem_bytes<2>(), s, a);
     }
     kev_end(t, s);
     KH_CUDA(cudaMemcpyAsync(&side_present, t->side.p, sizeof(uint32_t), cudaMemcpyDeviceToHost, s));
