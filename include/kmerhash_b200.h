@@ -337,6 +337,14 @@ int khx_scatter_slabs_dev(kh_table *t, int dist_hash, uint32_t dist_seed, const 
 int64_t khx_insert_pipelined_dev(kh_table *t, khx_peer *x, int dist_hash, uint32_t dist_seed, const uint64_t *d_keys, uint64_t n,
                                  uint64_t slab_cap, int parity, int chunks, uint64_t epoch0, uint32_t default_val,
                                  uint64_t *counts_matrix, int *overflowed);
+/* The same schedule with the COPY ENGINES on the links (what mxx's non-blocking alltoallv leaves to the MPI progress engine,
+ * KH/incremental_mxx.hpp:3437-3645): every piece is partitioned by owner into a staging buffer in this GPU's memory (its own
+ * keys straight into its own slab), cudaMemcpyAsync moves each (piece, owner) run into the owner's slab on a copy stream, the
+ * flag barrier of the piece follows on that stream, and the SMs meanwhile partition the next piece and run the level-1 pass
+ * of the pieces that have arrived.  Arguments, results and limits as khx_insert_pipelined_dev. */
+int64_t khx_insert_ce_dev(kh_table *t, khx_peer *x, int dist_hash, uint32_t dist_seed, const uint64_t *d_keys, uint64_t n,
+                          uint64_t slab_cap, int parity, int chunks, uint64_t epoch0, uint32_t default_val,
+                          uint64_t *counts_matrix, int *overflowed);
 /* k-mer generation fused with the sender (SURVEY.md 2.4 "fused with k-mer gen on the way in"; KmerParser -> transform_input ->
  * assign_count_permute of the reference, KI/io/kmer_parser.hpp:232-293, KH/distributed_batched_robinhood_map.hpp:632-741): reads ->
  * canonical k-mers -> owner -> peer stores, one kernel, the k-mers never written to this GPU's memory.  d_counts as for

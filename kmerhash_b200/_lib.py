@@ -118,6 +118,7 @@ SIGNATURES = {
     "khx_peer_meta_ptr": (_vp, [_vp, _int]),
     "khx_scatter_slabs_dev": (_int, [_vp, _int, _u32, _vp, _u64, _vp, _u64, _int, _vp, _int]),
     "khx_insert_pipelined_dev": (_i64, [_vp, _vp, _int, _u32, _vp, _u64, _u64, _int, _int, _u64, _u32, _vp, _vp]),
+    "khx_insert_ce_dev": (_i64, [_vp, _vp, _int, _u32, _vp, _u64, _u64, _int, _int, _u64, _u32, _vp, _vp]),
     "khx_kmers_scatter_slabs_dev": (_int, [_vp, _vp, _vp, _u64, _int, _int, _int, _u32, _vp, _u64, _int, _vp]),
     "khx_peer_close_imports": (None, [_vp]),
     "khx_peer_poisoned": (_int, [_vp]),

@@ -125,7 +125,9 @@ template <int W> constexpr size_t ps_smem_bytes(uint32_t p, bool meta, bool perm
 // META: the insert sender (metadata per owner into `meta`).  PERM: the query sender -- out_perm[r * slab_cap + i] = index
 // (in `keys`) of the i-th key stored into owner r's slab, so the answers, which come back in slab order, can be put
 // into input order.  cursors[r] ends as the number of keys this rank has for owner r (also beyond slab_cap).
-template <int W, bool META, bool PERM>
+// ALIGN: pad the runs of the sorted tile to the line offsets of their destinations (see ps_vtile; pays over NVLink, not for a
+// destination in this GPU's own memory)
+template <int W, bool META, bool PERM, bool ALIGN = true>
 __global__ void __launch_bounds__(PS_BLOCK, 3) scatter_slabs_kernel(const uint64_t *keys, uint64_t n, BinSpec dist, int store_kind,
                                                                      HashParams store_hp, const __grid_constant__ BinDst dst,
                                                                      unsigned long long slab_cap, unsigned long long *cursors,
@@ -160,7 +162,8 @@ __global__ void __launch_bounds__(PS_BLOCK, 3) scatter_slabs_kernel(const uint64
       if (e < n) asm volatile("prefetch.global.L2 [%0];" ::"l"(keys + e * W));
     }
     if (threadIdx.x < WIN_MAX_DST) cnt[threadIdx.x] = 0;
-    for (int i = threadIdx.x; i < VT / 4; i += PS_BLOCK) reinterpret_cast<uint32_t *>(sown)[i] = 0xffffffffu;   // gaps: no owner
+    if (ALIGN)
+      for (int i = threadIdx.x; i < VT / 4; i += PS_BLOCK) reinterpret_cast<uint32_t *>(sown)[i] = 0xffffffffu;   // gaps: no owner
     __syncthreads();
 
     uint64_t k[KPT][W];
@@ -217,7 +220,7 @@ __global__ void __launch_bounds__(PS_BLOCK, 3) scatter_slabs_kernel(const uint64
         const uint32_t cr = __shfl_sync(FULL_MASK, c, r);
         const unsigned long long gr = __shfl_sync(FULL_MASK, gb, r);
         const uint32_t ar = (uint32_t)(reinterpret_cast<uintptr_t>(dst.base[r]) / (8 * W) + gr) & (uint32_t)(LK - 1);
-        st += (ar - st) & (uint32_t)(LK - 1);
+        if (ALIGN) st += (ar - st) & (uint32_t)(LK - 1);
         if (threadIdx.x == r) { lo[r] = st; gbase[r] = gb; }
         st += cr;
       }
@@ -421,6 +424,9 @@ struct khx_peer {
   bool imports_closed = false;           // khx_peer_close_imports ran (teardown step 1)
   uint64_t *remote[WIN_MAX_DST] = {nullptr};
   bool opened[WIN_MAX_DST] = {false};    // mapped with cudaIpcOpenMemHandle (must be closed)
+  // copy-engine schedule (khx_insert_ce_dev): its stream and the pinned per-piece count rows, made on first use
+  cudaStream_t copy_stream = nullptr;
+  unsigned long long *h_piece_counts = nullptr;   // [16][WIN_MAX_DST]
 };
 
 static khx_peer *peer_create(int device, uint32_t rank, uint32_t p, uint64_t capacity_keys, int key_words, uint32_t reply_bytes);
@@ -469,6 +475,8 @@ void khx_peer_destroy(khx_peer *x) {
   khx_peer_close_imports(x);
   int prev = -1; cudaGetDevice(&prev); cudaSetDevice(x->device);
   if (x->local) cudaFree(x->local);
+  if (x->copy_stream) cudaStreamDestroy(x->copy_stream);
+  if (x->h_piece_counts) cudaFreeHost(x->h_piece_counts);
   if (prev >= 0) cudaSetDevice(prev);
   delete x;
 }
@@ -947,16 +955,20 @@ int64_t khx_insert_recv_dev(kh_table *t, const uint64_t *d_keys, uint64_t n, con
 // counts_matrix (HOST, p x p): keys sender g had for owner r, summed over the pieces.  *overflowed = 1: a sub-slab was too
 // small -- the same verdict on every rank, the table is untouched and the caller repeats the batch on the exact path.
 // Epochs epoch0 .. epoch0 + chunks - 1 are consumed.  Returns the number of new keys.
-int64_t khx_insert_pipelined_dev(kh_table *t, khx_peer *x, int dist_hash, uint32_t dist_seed, const uint64_t *d_keys, uint64_t n,
-                                 uint64_t slab_cap, int parity, int chunks, uint64_t epoch0, uint32_t default_val,
-                                 uint64_t *counts_matrix, int *overflowed) {
+// ce = false: the sender kernels store into the peers' slabs themselves (SM stores over NVLink).
+// ce = true:  the sender kernels partition into a LOCAL staging buffer (and, for the keys this rank owns, straight into its own
+//             slab); the COPY ENGINES move every (piece, owner) run to the owner's slab while the SMs go on with the next piece's
+//             partition and the previous pieces' level-1 passes.  NVLink time leaves the SMs' critical path.
+static int64_t insert_pipelined_impl(kh_table *t, khx_peer *x, int dist_hash, uint32_t dist_seed, const uint64_t *d_keys, uint64_t n,
+                                     uint64_t slab_cap, int parity, int chunks, uint64_t epoch0, uint32_t default_val,
+                                     uint64_t *counts_matrix, int *overflowed, bool ce) {
   return guarded([&]() -> int64_t {
     if (!t || !x || !counts_matrix || !overflowed || (n && !d_keys) || epoch0 == 0) { set_error("null argument"); return KH_ERR_INVALID; }
     const uint32_t p = x->p;
     const int W = t->W;
     if (!hash_kind_supported(dist_hash) || n >= (1ULL << 32) || x->W != W || parity < 0 || parity > 1 || chunks < 1 || chunks > 16 ||
         slab_cap % (2ULL * chunks) != 0 || 2ULL * p * slab_cap > x->capacity || p > (uint32_t)BK_MAX_SEG) {
-      set_error("khx_insert_pipelined_dev: bad arguments (slab_cap must be a multiple of 2 * chunks, 2 * p * slab_cap keys must fit)");
+      set_error("khx_insert_pipelined_dev / khx_insert_ce_dev: bad arguments (slab_cap must be a multiple of 2 * chunks, 2 * p * slab_cap keys must fit)");
       return KH_ERR_INVALID;
     }
     if (x->poisoned) { set_error("khx_insert_pipelined_dev: an earlier barrier on these buffers timed out; recreate them"); return KH_ERR_CUDA; }
@@ -987,14 +999,59 @@ int64_t khx_insert_pipelined_dev(kh_table *t, khx_peer *x, int dist_hash, uint32
     const uint64_t tile_send = PS_TILE_BYTES / (8 * W);
     const uint64_t tile_l1 = l1_tile_keys(W);
     const size_t smem = W == 1 ? ps_smem_bytes<1>(p, false, false) : ps_smem_bytes<2>(p, false, false);
+    // ce: staging for the runs that leave this GPU, [owner][slab_cap] keys; the copy stream; pinned count rows; one event per piece
+    DevBuf<uint64_t> stage;
+    cudaStream_t C = S;                                       // the stream that carries the barrier of a piece
+    std::vector<cudaEvent_t> evp(ce ? chunks : 0, nullptr);
+    struct EvGuard2 { std::vector<cudaEvent_t> &e; ~EvGuard2() { for (auto v : e) if (v) cudaEventDestroy(v); } } evg2{evp};
+    if (ce) {
+      if (!x->copy_stream) KH_CUDA(cudaStreamCreateWithFlags(&x->copy_stream, cudaStreamNonBlocking));
+      if (!x->h_piece_counts) KH_CUDA(cudaHostAlloc((void **)&x->h_piece_counts, 16 * WIN_MAX_DST * sizeof(unsigned long long), cudaHostAllocDefault));
+      C = x->copy_stream;
+      stage.alloc((size_t)p * slab_cap * W);
+      for (auto &e : evp) KH_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+      cudaEvent_t e0;                                         // the copy stream starts behind what S has queued (the memsets above)
+      KH_CUDA(cudaEventCreateWithFlags(&e0, cudaEventDisableTiming));
+      KH_CUDA(cudaEventRecord(e0, S)); KH_CUDA(cudaStreamWaitEvent(C, e0, 0)); KH_CUDA(cudaEventDestroy(e0));
+    }
+    const uint64_t my_slab = ((uint64_t)parity * p + x->rank) * slab_cap;       // this rank's slab in every owner's buffer
+    // the partition kernels leave one SM's worth of CTAs unlaunched, as the level-1 kernels of the pieces do (kh::bulk_feed): the
+    // one-warp barrier kernels must find a free SM while those persistent kernels run
+    const uint64_t ps_ctas = (uint64_t)std::max(t->sms - 1, 1) * 3;
+    if (ce) {
+      for (int c = 0; c < chunks; ++c) {                      // all partitions first: they depend on nothing
+        const uint64_t k0 = n * (uint64_t)c / chunks, k1 = n * (uint64_t)(c + 1) / chunks, m = k1 - k0;
+        unsigned long long *cursors = d_counts.p + (size_t)c * p;
+        if (m) {
+          BinDst dst{};
+          for (uint32_t r = 0; r < p; ++r)
+            dst.base[r] = r == x->rank ? x->local + (my_slab + (uint64_t)c * sub_cap) * W : stage.p + ((uint64_t)r * slab_cap + (uint64_t)c * sub_cap) * W;
+          const int grid = (int)std::max<uint64_t>(1, std::min<uint64_t>((m + tile_send - 1) / tile_send, ps_ctas));
+          if (W == 1) KH_LAUNCH((scatter_slabs_kernel<1, false, false, false>), grid, PS_BLOCK, smem, S, d_keys + k0 * W, m, dist, t->hash_kind, t->hp, dst,
+                                (unsigned long long)sub_cap, cursors, (unsigned long long *)nullptr, (uint32_t *)nullptr);
+          else KH_LAUNCH((scatter_slabs_kernel<2, false, false, false>), grid, PS_BLOCK, smem, S, d_keys + k0 * W, m, dist, t->hash_kind, t->hp, dst,
+                         (unsigned long long)sub_cap, cursors, (unsigned long long *)nullptr, (uint32_t *)nullptr);
+        }
+        KH_CUDA(cudaMemcpyAsync(x->h_piece_counts + (size_t)c * WIN_MAX_DST, cursors, p * sizeof(unsigned long long), cudaMemcpyDeviceToHost, S));
+        KH_CUDA(cudaEventRecord(evp[c], S));
+      }
+    }
     for (int c = 0; c < chunks; ++c) {
       const uint64_t k0 = n * (uint64_t)c / chunks, k1 = n * (uint64_t)(c + 1) / chunks, m = k1 - k0;
       unsigned long long *cursors = d_counts.p + (size_t)c * p;
-      if (m) {
+      if (ce) {
+        KH_CUDA(cudaEventSynchronize(evp[c]));                // piece c is partitioned and its counts are here
+        for (uint32_t q = 1; q < p; ++q) {                    // start with the right-hand neighbour: the ranks' copies do not pile up on one owner
+          const uint32_t r = (x->rank + q) % p;
+          const uint64_t cnt = std::min<uint64_t>(x->h_piece_counts[(size_t)c * WIN_MAX_DST + r], sub_cap);
+          if (cnt) KH_CUDA(cudaMemcpyAsync(x->remote[r] + (my_slab + (uint64_t)c * sub_cap) * W, stage.p + ((uint64_t)r * slab_cap + (uint64_t)c * sub_cap) * W,
+                                           cnt * 8 * W, cudaMemcpyDeviceToDevice, C));
+        }
+      } else if (m) {
         BinDst dst{};
-        for (uint32_t r = 0; r < p; ++r) dst.base[r] = x->remote[r] + (((uint64_t)parity * p + x->rank) * slab_cap + (uint64_t)c * sub_cap) * W;
+        for (uint32_t r = 0; r < p; ++r) dst.base[r] = x->remote[r] + (my_slab + (uint64_t)c * sub_cap) * W;
         // one CTA per SM: the level-1 kernel of the previous piece holds the rest of the SM
-        const int grid = (int)std::max<uint64_t>(1, std::min<uint64_t>((m + tile_send - 1) / tile_send, (uint64_t)t->sms * (c == 0 ? 3 : 1)));
+        const int grid = (int)std::max<uint64_t>(1, std::min<uint64_t>((m + tile_send - 1) / tile_send, c == 0 ? ps_ctas : ps_ctas / 3));
         if (W == 1) KH_LAUNCH((scatter_slabs_kernel<1, false, false>), grid, PS_BLOCK, smem, S, d_keys + k0 * W, m, dist, t->hash_kind, t->hp, dst,
                               (unsigned long long)sub_cap, cursors, (unsigned long long *)nullptr, (uint32_t *)nullptr);
         else KH_LAUNCH((scatter_slabs_kernel<2, false, false>), grid, PS_BLOCK, smem, S, d_keys + k0 * W, m, dist, t->hash_kind, t->hp, dst,
@@ -1002,18 +1059,19 @@ int64_t khx_insert_pipelined_dev(kh_table *t, khx_peer *x, int dist_hash, uint32
       }
       const int slot = (int)(x->count_syncs & 1);
       ++x->count_syncs;
-      KH_LAUNCH(peer_sync_kernel, 1, 32, 0, S, hd, x->rank, p, (unsigned long long)(epoch0 + c), cursors, 1, slot, d_flags.p, timeout_ns);
-      KH_LAUNCH(make_segs_kernel, 1, 32, 0, S, hd.h[x->rank], slot, p, x->rank, (unsigned long long)sub_cap,
+      KH_LAUNCH(peer_sync_kernel, 1, 32, 0, C, hd, x->rank, p, (unsigned long long)(epoch0 + c), cursors, 1, slot, d_flags.p, timeout_ns);
+      KH_LAUNCH(make_segs_kernel, 1, 32, 0, C, hd.h[x->rank], slot, p, x->rank, (unsigned long long)sub_cap,
                 (unsigned long long)((uint64_t)parity * p * slab_cap + (uint64_t)c * sub_cap), (unsigned long long)slab_cap,
                 (unsigned long long)tile_l1, d_segs.p + c, d_matrix.p + (size_t)c * p * p, d_flags.p + 1);
-      KH_CUDA(cudaEventRecord(ev[c], S));
+      KH_CUDA(cudaEventRecord(ev[c], C));
       KH_CUDA(cudaStreamWaitEvent(R, ev[c], 0));
       bulk_pipe_feed(b, t, x->local, (uint64_t)p * sub_cap, d_segs.p + c, R);
     }
     std::vector<unsigned long long> h_matrix((size_t)chunks * p * p);
     int h_flags[2] = {0, 0};
-    KH_CUDA(cudaMemcpyAsync(h_matrix.data(), d_matrix.p, h_matrix.size() * sizeof(unsigned long long), cudaMemcpyDeviceToHost, S));
-    KH_CUDA(cudaMemcpyAsync(h_flags, d_flags.p, sizeof(h_flags), cudaMemcpyDeviceToHost, S));
+    KH_CUDA(cudaMemcpyAsync(h_matrix.data(), d_matrix.p, h_matrix.size() * sizeof(unsigned long long), cudaMemcpyDeviceToHost, C));
+    KH_CUDA(cudaMemcpyAsync(h_flags, d_flags.p, sizeof(h_flags), cudaMemcpyDeviceToHost, C));
+    KH_CUDA(cudaStreamSynchronize(C));
     KH_CUDA(cudaStreamSynchronize(S));
     KH_CUDA(cudaStreamSynchronize(R));
     if (h_flags[0]) {
@@ -1047,6 +1105,17 @@ int64_t khx_insert_pipelined_dev(kh_table *t, khx_peer *x, int dist_hash, uint32
     };
     return bulk_pipe_finish(b, t, n_recv, default_val, S);
   });
+}
+
+int64_t khx_insert_pipelined_dev(kh_table *t, khx_peer *x, int dist_hash, uint32_t dist_seed, const uint64_t *d_keys, uint64_t n,
+                                 uint64_t slab_cap, int parity, int chunks, uint64_t epoch0, uint32_t default_val,
+                                 uint64_t *counts_matrix, int *overflowed) {
+  return insert_pipelined_impl(t, x, dist_hash, dist_seed, d_keys, n, slab_cap, parity, chunks, epoch0, default_val, counts_matrix, overflowed, false);
+}
+int64_t khx_insert_ce_dev(kh_table *t, khx_peer *x, int dist_hash, uint32_t dist_seed, const uint64_t *d_keys, uint64_t n,
+                          uint64_t slab_cap, int parity, int chunks, uint64_t epoch0, uint32_t default_val,
+                          uint64_t *counts_matrix, int *overflowed) {
+  return insert_pipelined_impl(t, x, dist_hash, dist_seed, d_keys, n, slab_cap, parity, chunks, epoch0, default_val, counts_matrix, overflowed, true);
 }
 
 }  // extern "C"

@@ -573,7 +573,9 @@ void bulk_feed(BulkBatch &b, kh_table *t, const uint64_t *d_keys, uint64_t m, cu
     a.keys = d_keys + segs->base[0] * t->W;
   }
   if (!n_tiles) return;
-  const int grid = dsegs ? t->sms : (int)std::min<uint64_t>(n_tiles, (uint64_t)t->sms);
+  // dsegs (the pieces of a pipelined exchange): one SM stays free for the one-warp barrier kernel of the next piece, which could
+  // not start while these persistent CTAs -- each holds a whole SM's registers -- are running
+  const int grid = dsegs ? std::max(t->sms - 1, 1) : (int)std::min<uint64_t>(n_tiles, (uint64_t)t->sms);
   kev_begin(t, 2, s);
   if (b.ord) {                                                      // records with batch positions (one piece)
     a.pos_base = b.fed;

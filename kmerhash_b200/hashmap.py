@@ -204,13 +204,15 @@ class HashMap:
         check(lib.khx_scatter_slabs_dev(self._h, HASH_KINDS[dist_hash], dist_seed, k.data_ptr(), n, peer_handle, int(slab_cap),
                                         int(parity), counts.data_ptr(), int(reset)), "scatter_slabs")
 
-    def insert_pipelined(self, keys, peer_handle, p, slab_cap, parity, chunks, epoch0, default=1, dist_hash="MURMUR64avx", dist_seed=9876543):
+    def insert_pipelined(self, keys, peer_handle, p, slab_cap, parity, chunks, epoch0, default=1, dist_hash="MURMUR64avx", dist_seed=9876543,
+                         copy_engine=False):
         """one rank of the pipelined distributed insert (khx_insert_pipelined_dev): returns (new keys, p x p count matrix,
         overflowed)"""
         k, n = _dev_keys(keys, self.W, self.device)
         mat = np.zeros((p, p), dtype=np.uint64)
         over = C.c_int(0)
-        got = check(lib.khx_insert_pipelined_dev(self._h, peer_handle, HASH_KINDS[dist_hash], dist_seed, k.data_ptr(), n, int(slab_cap),
+        fn = lib.khx_insert_ce_dev if copy_engine else lib.khx_insert_pipelined_dev
+        got = check(fn(self._h, peer_handle, HASH_KINDS[dist_hash], dist_seed, k.data_ptr(), n, int(slab_cap),
                                                  int(parity), int(chunks), int(epoch0), default, mat.ctypes.data, C.byref(over)),
                     "insert_pipelined")
         return got, mat, bool(over.value)

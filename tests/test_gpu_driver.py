@@ -123,8 +123,8 @@ def test_kmercounter_driver_is_built():
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("world,pipe", [(2, "1"), (2, "4")])
-def test_distributed_map_on_real_gpus_under_torchrun(world, pipe):
+@pytest.mark.parametrize("world,pipe,mode", [(2, "1", "sm"), (2, "4", "sm"), (2, "4", "ce")])
+def test_distributed_map_on_real_gpus_under_torchrun(world, pipe, mode):
     """one process per GPU (torchrun, NCCL + CUDA-IPC mapped peer buffers): tools/dist_parity.py checks every rank's table
     contents against the oracle's per-rank rule through the slab exchange, its overflow fallback, slab growth, empty
     batches, queries in input order and erase.  Needs >= 2 visible GPUs (the emulated-p tests cover the kernels on one)."""
@@ -135,8 +135,9 @@ def test_distributed_map_on_real_gpus_under_torchrun(world, pipe):
     if torch.cuda.device_count() < world:
         pytest.skip("needs %d GPUs" % world)
     s = socket.socket(); s.bind(("127.0.0.1", 0)); port = s.getsockname()[1]; s.close()
-    # 5 M keys per rank: large enough for the bulk insert and for the pipelined exchange (run with it on and off)
-    env = dict(os.environ, KH_PARITY_SHORT="1", KH_PARITY_N0="5000000,150000", KH_PIPE_CHUNKS=pipe)
+    # 5 M keys per rank: large enough for the bulk insert and for the pipelined exchange (run with it off, with the sender
+    # kernels storing over NVLink, and with the copy engines moving the partitioned runs)
+    env = dict(os.environ, KH_PARITY_SHORT="1", KH_PARITY_N0="5000000,150000", KH_PIPE_CHUNKS=pipe, KH_PIPE_MODE=mode)
     r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", str(world),
                         "--master-addr", "127.0.0.1", "--master-port", str(port), os.path.join(ROOT, "tools", "dist_parity.py")],
                        capture_output=True, text=True, timeout=600, env=env)
