@@ -425,7 +425,9 @@ struct khx_peer {
   uint64_t *remote[WIN_MAX_DST] = {nullptr};
   bool opened[WIN_MAX_DST] = {false};    // mapped with cudaIpcOpenMemHandle (must be closed)
   // copy-engine schedule (khx_insert_ce_dev): its stream and the pinned per-piece count rows, made on first use
-  cudaStream_t copy_stream = nullptr;
+  cudaStream_t copy_stream = nullptr;    // carries the barrier of every piece
+  cudaStream_t link_stream[WIN_MAX_DST] = {nullptr};   // one per destination: the copies of a piece run on several copy engines at once
+  cudaEvent_t link_done[WIN_MAX_DST] = {nullptr};
   unsigned long long *h_piece_counts = nullptr;   // [16][WIN_MAX_DST]
 };
 
@@ -476,6 +478,8 @@ void khx_peer_destroy(khx_peer *x) {
   int prev = -1; cudaGetDevice(&prev); cudaSetDevice(x->device);
   if (x->local) cudaFree(x->local);
   if (x->copy_stream) cudaStreamDestroy(x->copy_stream);
+  for (auto &st : x->link_stream) if (st) cudaStreamDestroy(st);
+  for (auto &e : x->link_done) if (e) cudaEventDestroy(e);
   if (x->h_piece_counts) cudaFreeHost(x->h_piece_counts);
   if (prev >= 0) cudaSetDevice(prev);
   delete x;
@@ -992,7 +996,14 @@ static int64_t insert_pipelined_impl(kh_table *t, khx_peer *x, int dist_hash, ui
     KH_CUDA(cudaMemsetAsync(d_flags.p, 0, 2 * sizeof(int), S));
     std::vector<cudaEvent_t> ev(chunks, nullptr);
     struct EvGuard { std::vector<cudaEvent_t> &e; ~EvGuard() { for (auto v : e) if (v) cudaEventDestroy(v); } } evg{ev};
-    for (auto &e : ev) KH_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+    // KH_TRACE=1: the events carry times; the schedule of this call is printed at its end (rank 0's view of the overlap)
+    const bool tr_on = getenv("KH_TRACE") && atoi(getenv("KH_TRACE")) != 0;
+    const unsigned ev_flags = tr_on ? cudaEventDefault : cudaEventDisableTiming;
+    for (auto &e : ev) KH_CUDA(cudaEventCreateWithFlags(&e, ev_flags));
+    std::vector<cudaEvent_t> evt(tr_on ? 2 + chunks : 0, nullptr);      // [0] start (S), [1 + c] level 1 of piece c done (R), [1 + chunks] finish
+    EvGuard evgt{evt};
+    for (auto &e : evt) KH_CUDA(cudaEventCreate(&e));
+    if (tr_on) KH_CUDA(cudaEventRecord(evt[0], S));
 
     BulkBatch b;
     bulk_pipe_begin(b, t, (uint64_t)p * slab_cap, R);
@@ -1006,10 +1017,14 @@ static int64_t insert_pipelined_impl(kh_table *t, khx_peer *x, int dist_hash, ui
     struct EvGuard2 { std::vector<cudaEvent_t> &e; ~EvGuard2() { for (auto v : e) if (v) cudaEventDestroy(v); } } evg2{evp};
     if (ce) {
       if (!x->copy_stream) KH_CUDA(cudaStreamCreateWithFlags(&x->copy_stream, cudaStreamNonBlocking));
+      for (uint32_t q = 1; q < p; ++q) {
+        if (!x->link_stream[q]) KH_CUDA(cudaStreamCreateWithFlags(&x->link_stream[q], cudaStreamNonBlocking));
+        if (!x->link_done[q]) KH_CUDA(cudaEventCreateWithFlags(&x->link_done[q], cudaEventDisableTiming));
+      }
       if (!x->h_piece_counts) KH_CUDA(cudaHostAlloc((void **)&x->h_piece_counts, 16 * WIN_MAX_DST * sizeof(unsigned long long), cudaHostAllocDefault));
       C = x->copy_stream;
       stage.alloc((size_t)p * slab_cap * W);
-      for (auto &e : evp) KH_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+      for (auto &e : evp) KH_CUDA(cudaEventCreateWithFlags(&e, ev_flags));
       cudaEvent_t e0;                                         // the copy stream starts behind what S has queued (the memsets above)
       KH_CUDA(cudaEventCreateWithFlags(&e0, cudaEventDisableTiming));
       KH_CUDA(cudaEventRecord(e0, S)); KH_CUDA(cudaStreamWaitEvent(C, e0, 0)); KH_CUDA(cudaEventDestroy(e0));
@@ -1044,8 +1059,13 @@ static int64_t insert_pipelined_impl(kh_table *t, khx_peer *x, int dist_hash, ui
         for (uint32_t q = 1; q < p; ++q) {                    // start with the right-hand neighbour: the ranks' copies do not pile up on one owner
           const uint32_t r = (x->rank + q) % p;
           const uint64_t cnt = std::min<uint64_t>(x->h_piece_counts[(size_t)c * WIN_MAX_DST + r], sub_cap);
-          if (cnt) KH_CUDA(cudaMemcpyAsync(x->remote[r] + (my_slab + (uint64_t)c * sub_cap) * W, stage.p + ((uint64_t)r * slab_cap + (uint64_t)c * sub_cap) * W,
-                                           cnt * 8 * W, cudaMemcpyDeviceToDevice, C));
+          if (!cnt) continue;
+          // link stream q is ordered behind its copy of the previous piece and behind nothing else: the host has seen piece c's
+          // partition complete; the barrier stream waits for all of them
+          KH_CUDA(cudaMemcpyAsync(x->remote[r] + (my_slab + (uint64_t)c * sub_cap) * W, stage.p + ((uint64_t)r * slab_cap + (uint64_t)c * sub_cap) * W,
+                                  cnt * 8 * W, cudaMemcpyDeviceToDevice, x->link_stream[q]));
+          KH_CUDA(cudaEventRecord(x->link_done[q], x->link_stream[q]));
+          KH_CUDA(cudaStreamWaitEvent(C, x->link_done[q], 0));
         }
       } else if (m) {
         BinDst dst{};
@@ -1066,6 +1086,7 @@ static int64_t insert_pipelined_impl(kh_table *t, khx_peer *x, int dist_hash, ui
       KH_CUDA(cudaEventRecord(ev[c], C));
       KH_CUDA(cudaStreamWaitEvent(R, ev[c], 0));
       bulk_pipe_feed(b, t, x->local, (uint64_t)p * sub_cap, d_segs.p + c, R);
+      if (tr_on) KH_CUDA(cudaEventRecord(evt[1 + c], R));
     }
     std::vector<unsigned long long> h_matrix((size_t)chunks * p * p);
     int h_flags[2] = {0, 0};
@@ -1103,7 +1124,20 @@ static int64_t insert_pipelined_impl(kh_table *t, khx_peer *x, int dist_hash, ui
         }
       return flat.p;
     };
-    return bulk_pipe_finish(b, t, n_recv, default_val, S);
+    const int64_t got = bulk_pipe_finish(b, t, n_recv, default_val, S);
+    if (tr_on) {
+      KH_CUDA(cudaEventRecord(evt[1 + chunks], S));
+      KH_CUDA(cudaEventSynchronize(evt[1 + chunks]));
+      auto at = [&](cudaEvent_t e) { float ms = 0; cudaEventElapsedTime(&ms, evt[0], e); return ms; };
+      char line[512]; int o = snprintf(line, sizeof line, "[kh-trace] pipelined(%s, rank %u) ms since start:", ce ? "ce" : "sm", x->rank);
+      for (int c = 0; c < chunks; ++c) {
+        if (ce) o += snprintf(line + o, sizeof line - o, " P%d %.3f", c, at(evp[c]));
+        o += snprintf(line + o, sizeof line - o, " B%d %.3f L%d %.3f |", c, at(ev[c]), c, at(evt[1 + c]));
+      }
+      snprintf(line + o, sizeof line - o, " done %.3f", at(evt[1 + chunks]));
+      fprintf(stderr, "%s\n", line);
+    }
+    return got;
   });
 }
 
