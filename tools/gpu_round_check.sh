@@ -3,9 +3,11 @@ mkdir -p gpurun_out
 timeout 1500 python -m pytest tests -m gpu -x -q --timeout 600 > gpurun_out/pytest_gpu.log 2>&1; echo "pytest rc=$?" >> gpurun_out/pytest_gpu.log
 tail -n 4 gpurun_out/pytest_gpu.log
 timeout 900 python bench.py --steps 20 --warmup 5 > gpurun_out/bench1.json 2> gpurun_out/bench1.err; echo "bench rc=$?"; tail -n 3 gpurun_out/bench1.err
+if [ "$1" = "ref" ]; then
 ( time timeout 1200 python bench.py --impl reference --steps 20 --warmup 5 > gpurun_out/bench_ref.json 2> gpurun_out/bench_ref.err ) 2>&1 | tail -n 4; echo "ref rc=$?"
 cut -c1-600 gpurun_out/bench_ref.json
+fi
 timeout 300 python bench.py --steps 2 --warmup 1 --no-cpu-baseline --no-e2e > gpurun_out/plain.log 2>&1 && \
 timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 600 --csv --log-file gpurun_out/launches.csv python bench.py --steps 2 --warmup 1 --no-cpu-baseline --no-e2e > gpurun_out/ncu_launch.log 2>&1; echo "ncu1 rc=$?"
-timeout 900 ncu --set full --clock-control none --import-source on -k regex:'l1_scatter_kernel|tile_insert_kernel|tile_rebuild_kernel|lookup_kernel' -s 4 -c 6 -o gpurun_out/r02e_bench python bench.py --steps 2 --warmup 1 --no-cpu-baseline --no-e2e > gpurun_out/ncu_full.log 2>&1; echo "ncu2 rc=$?"
+timeout 900 ncu --set full --clock-control none --import-source on -k regex:'l1_scatter_kernel|tile_insert_kernel|tile_rebuild_kernel|lookup_kernel|insert_kernel' -s 5 -c 7 -o gpurun_out/r02f_bench python bench.py --steps 2 --warmup 1 --no-cpu-baseline --no-e2e > gpurun_out/ncu_full.log 2>&1; echo "ncu2 rc=$?"
 exit 0
