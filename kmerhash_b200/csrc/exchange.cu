@@ -820,17 +820,16 @@ int64_t khx_query_slabs_dev(kh_table *t, khx_peer *x, int op, uint64_t slab_cap,
       KH_CUDA(cudaStreamSynchronize(t->stream[0]));
       return kh_erase_dev(t, flat.p, n);
     }
+    // one launch per sender slab, back to back (no synchronisation in between), the answers stored straight into the askers' buffers
     const size_t elem = op == 0 ? 4 : 1;
+    const uint64_t *keys[WIN_MAX_DST]; void *reply[WIN_MAX_DST]; uint64_t cnt[WIN_MAX_DST];
     for (uint32_t q = 0; q < p; ++q) {
-      if (!counts[q]) continue;
-      if (!x->remote[q]) { set_error("peer %u not mapped", q); return KH_ERR_INVALID; }
-      const uint64_t *keys = x->local + (uint64_t)q * slab_cap * W;
-      unsigned char *reply = reinterpret_cast<unsigned char *>(x->remote[q]) + x->capacity * 8 * W + (uint64_t)x->rank * slab_cap * elem;
-      const int64_t rc = op == 0 ? kh_find_dev(t, keys, counts[q], reinterpret_cast<uint32_t *>(reply), nonexistent)
-                                 : kh_count_dev(t, keys, counts[q], reply);
-      if (rc < 0) return rc;
-      total += rc;
+      cnt[q] = counts[q];
+      if (counts[q] && !x->remote[q]) { set_error("peer %u not mapped", q); return KH_ERR_INVALID; }
+      keys[q] = x->local + (uint64_t)q * slab_cap * W;
+      reply[q] = counts[q] ? reinterpret_cast<unsigned char *>(x->remote[q]) + x->capacity * 8 * W + (uint64_t)x->rank * slab_cap * elem : nullptr;
     }
+    total = query_pieces_dev(t, op, (int)p, keys, cnt, reply, nonexistent);
     return total;
   });
 }

@@ -85,6 +85,11 @@ void bulk_pipe_begin(BulkBatch &b, kh_table *t, uint64_t n_upper, cudaStream_t s
 void bulk_pipe_feed(BulkBatch &b, kh_table *t, const uint64_t *d_base, uint64_t m_upper, const BkSegs *dsegs, cudaStream_t s);
 int64_t bulk_pipe_finish(BulkBatch &b, kh_table *t, uint64_t n_recv, uint32_t dflt, cudaStream_t s);
 bool bulk_pipe_candidate(const kh_table *t, uint64_t n);
+// find (op 0: 4-byte answers) / count (op 1: 1-byte answers) over several key arrays with one answer array each (the per-sender
+// slabs of a peer receive buffer, exchange.cu): the launches go out back to back on the table's two streams, ONE counter
+// read-back and synchronisation at the end.  Returns the number of hits.
+int64_t query_pieces_dev(kh_table *t, int op, int n_pieces, const uint64_t *const *d_keys, const uint64_t *n, void *const *d_out,
+                         uint32_t nonexistent);
 // what a caller's pipeline already knows about a batch: its HyperLogLog registers (HLL_M bytes on the HOST, may be null:
 // accumulated behind the PCIe copy) and/or the pieces it lies in (kh_bulk.cuh: BkSegs; the slabs of a peer receive buffer)
 struct PreEstimate { const uint8_t *regs; const BkSegs *segs; };

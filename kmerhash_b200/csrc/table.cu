@@ -845,6 +845,24 @@ int64_t insert_bulk(kh_table *t, const uint64_t *d_keys, const uint32_t *d_vals,
 
 }  // namespace
 
+int64_t kh::query_pieces_dev(kh_table *t, int op, int n_pieces, const uint64_t *const *d_keys, const uint64_t *n, void *const *d_out,
+                             uint32_t nonexistent) {
+  cudaStream_t s0 = t->stream[0], s1 = t->stream[1];
+  zero_counter(t, s0);
+  KH_CUDA(cudaEventRecord(t->ev[0], s0));
+  KH_CUDA(cudaStreamWaitEvent(s1, t->ev[0], 0));
+  int used = 0;
+  for (int q = 0; q < n_pieces; ++q) {
+    if (!n[q]) continue;
+    cudaStream_t s = (used++ & 1) ? s1 : s0;
+    if (op == 0) launch_lookup(t, OP_FIND, d_keys[q], n[q], reinterpret_cast<uint32_t *>(d_out[q]), nullptr, nullptr, nonexistent, t->counters.p, s);
+    else launch_lookup(t, OP_COUNT, d_keys[q], n[q], nullptr, reinterpret_cast<uint8_t *>(d_out[q]), nullptr, 0, t->counters.p, s);
+  }
+  KH_CUDA(cudaEventRecord(t->ev[1], s1));
+  KH_CUDA(cudaStreamWaitEvent(s0, t->ev[1], 0));
+  return (int64_t)read_counter(t, s0);
+}
+
 // ---- the bulk insert in pieces, for the pipelined multi-GPU receiver (exchange.cu) -------------------------------------------
 void kh::bulk_pipe_begin(BulkBatch &b, kh_table *t, uint64_t n_upper, cudaStream_t s) { bulk_begin(b, t, n_upper, s); }
 void kh::bulk_pipe_feed(BulkBatch &b, kh_table *t, const uint64_t *d_base, uint64_t m_upper, const BkSegs *dsegs, cudaStream_t s) {
