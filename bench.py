@@ -699,10 +699,13 @@ def ours_multi(args):
             "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ti + tf,
             "higher_is_better": True, "scaling": "weak" if args.config != "5s" else "strong", "vs_baseline": None, "dtype": "u64", "data": "synthetic",
             "config": {"workload": "BenchmarkDistHashTables-shaped: %d random 31-mer uint64 keys per GPU, "
-                                   "hash-partitioned (murmur3 x86_128, seed 9876543) over %d GPUs, exchange by peer stores over NVLink (NCCL as fallback), "
+                                   "hash-partitioned (murmur3 x86_128, seed 9876543) over %d GPUs, exchange over NVLink into CUDA-IPC mapped peer buffers (one piece: the sender kernel stores into the owners' slabs; "
+                                   "several pieces: partition into local staging + copy engines, overlapped with the receiver's level 1; NCCL as fallback), "
                                    "count map insert, then %d finds per GPU with reply" % (n, world, nq),
                        "n_keys_per_gpu": n, "n_query_per_gpu": nq, "hash": args.hash, "config": args.config,
                        "exchange_pieces": dm.pipe_chunks,
+                       "exchange_schedule": ("one piece, SM stores" if dm.pipe_chunks <= 1 else
+                                             "%d pieces, %s" % (dm.pipe_chunks, "copy engines" if os.environ.get("KH_PIPE_MODE", "ce") == "ce" else "SM stores")),
                        "input": ("generate_input of the reference with srand(23 + rank)" if args.config == "1" else "torch generator on the device, seed 1000 + rank, every distinct key 1..8 times"),
                        "l2": "inputs larger than L2; tables rebuilt from capacity 128 every step"},
             "finds_per_s": world * nq / (tf * 1e-3), "finds_per_s_median": world * nq / (tf_med * 1e-3),
@@ -712,7 +715,7 @@ def ours_multi(args):
             "parity_check": parity,
             "exchange": {"bytes_sent_per_rank_insert": int(xbytes), "GB_per_s_per_rank_if_serial": xbytes / (ti * 1e-3) / 1e9,
                          "nvlink_peak_GB_per_s_per_direction": 900},
-            "roofline": {"bound": "hbm", "kernel": "insert phase per GPU (sender scatter over NVLink, flag barrier, receiver's level-1 scatter + tile insert)",
+            "roofline": {"bound": "hbm", "kernel": "insert phase per GPU (owner partition / sender scatter, transfer over NVLink, flag barriers, receiver's level-1 scatter + tile insert)",
                          "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
                          "algorithmic_bytes_per_key": BYTES_PER_INSERT},
             "gpu_launches": int(launches.item()), "clocks": clocks,
