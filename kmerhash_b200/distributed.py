@@ -260,6 +260,9 @@ class DistributedMap:
         # piece is faster (3.16 against 3.27 ms)
         self.pipe_chunks = int(os.environ.get("KH_PIPE_CHUNKS", "4" if self.p >= 4 else "1"))
         self.pipe_min_keys = 1 << 22
+        # above this many keys per rank and batch (slab capacity) the one-piece schedule runs: it is the one measured at 1 B keys per
+        # GPU (config 5); the pieces' staging and record buffers grow with the batch
+        self.pipe_max_keys = int(os.environ.get("KH_PIPE_MAX_KEYS", str(1 << 29)))
         self._copy_stream = self._lib_stream = None   # host -> device pipeline of the sender (_send_slabs)
         self._dev_keys = self._C = None
         self._exact_dirty = False         # the last batch went through the exact path: its buffer use overlaps both halves
@@ -469,7 +472,7 @@ class DistributedMap:
             self._exact_dirty = False
         parity = self.parity
         if (reads is None and self.pipe_chunks > 1 and torch.is_tensor(keys) and keys.is_cuda and p <= 8 and hasattr(self.e, "insert_pipelined")
-                and self.slab_cap % (2 * self.pipe_chunks) == 0 and self.pipe_min_keys <= p * self.slab_cap <= 3 << 29):
+                and self.slab_cap % (2 * self.pipe_chunks) == 0 and self.pipe_min_keys <= p * self.slab_cap <= min(self.pipe_max_keys, 3 << 29)):
             # every rank takes this branch or none: the decision rests on the slab size, which all ranks share, and on where the
             # keys live, which a collective caller keeps uniform (device tensors on every rank, or host arrays on every rank)
             keys = self.e.canonicalize(keys)
