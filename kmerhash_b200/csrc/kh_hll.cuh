@@ -66,9 +66,12 @@ inline double hll_estimate_from_regs(const uint8_t *regs, int bits) {
   const double m = (double)HLL_M;
   double amm = 0.7213 / (1.0 + 1.079 / m);
   amm *= m * m;
+  // 2^-r from a table: the same exact powers of two, added in the same order, as ldexp gives -- at a tenth of the time (this runs
+  // on the host between two kernels of every insert batch, with the GPU waiting)
+  static const struct Pow2Table { double v[256]; Pow2Table() { for (int r = 0; r < 256; ++r) v[r] = std::ldexp(1.0, -r); } } pow2;
   double sum = 0.0;
   uint32_t zeros = 0;
-  for (int i = 0; i < HLL_M; ++i) { sum += std::ldexp(1.0, -(int)regs[i]); zeros += regs[i] == 0; }
+  for (int i = 0; i < HLL_M; ++i) { sum += pow2.v[regs[i]]; zeros += regs[i] == 0; }
   double est = amm / sum;
   if (est <= 5.0 * (m / 2.0)) {
     if (zeros > 0) return m * std::log(m / (double)zeros);

@@ -643,7 +643,7 @@ int64_t bulk_finish(BulkBatch &b, kh_table *t, const uint64_t *d_keys, const BkS
   std::memcpy(&n_ovf, t->h_regs + HLL_M, sizeof(n_ovf));
   uint8_t batch_regs[HLL_M];
   for (int i = 0; i < HLL_M; ++i) batch_regs[i] = (uint8_t)t->h_regs[i];
-  const double batch_est = hll_estimate_from_regs(batch_regs, hash_bits(t->hash_kind));
+  const double batch_est = estimate ? 0.0 : hll_estimate_from_regs(batch_regs, hash_bits(t->hash_kind));   // used by insert_no_estimate only
   bool fits = true;
   if (estimate) {
     const double est = merge_batch_registers(t, batch_regs);
