@@ -211,22 +211,35 @@ __global__ void __launch_bounds__(PS_BLOCK, 3) scatter_slabs_kernel(const uint64
     }
     __syncthreads();
 
-    if (threadIdx.x < 32) {                          // lane r < p: owner r's run -- its place in the slab, then in the padded tile
+    unsigned long long gb_pending = 0;                // !ALIGN: warp 0's slab positions, not yet consumed
+    if (threadIdx.x < 32) {                          // lane r < p: owner r's run -- its place in the slab, then in the (padded) tile
       const uint32_t c = threadIdx.x < p ? cnt[threadIdx.x] : 0u;
       const unsigned long long gb = c ? atomicAdd(&cursors[threadIdx.x], (unsigned long long)c) : 0ULL;
       my_total += c;
-      uint32_t st = 0;                                // run r starts at the first position >= the end of run r-1 that is congruent
-      for (uint32_t r = 0; r < p; ++r) {              // to its destination address modulo a line
-        const uint32_t cr = __shfl_sync(FULL_MASK, c, r);
-        const unsigned long long gr = __shfl_sync(FULL_MASK, gb, r);
-        const uint32_t ar = (uint32_t)(reinterpret_cast<uintptr_t>(dst.base[r]) / (8 * W) + gr) & (uint32_t)(LK - 1);
-        if (ALIGN) st += (ar - st) & (uint32_t)(LK - 1);
-        if (threadIdx.x == r) { lo[r] = st; gbase[r] = gb; }
-        st += cr;
+      uint32_t st = 0;
+      if (ALIGN) {                                    // run r starts at the first position >= the end of run r-1 that is congruent
+        for (uint32_t r = 0; r < p; ++r) {            // to its destination address modulo a line
+          const uint32_t cr = __shfl_sync(FULL_MASK, c, r);
+          const unsigned long long gr = __shfl_sync(FULL_MASK, gb, r);
+          const uint32_t ar = (uint32_t)(reinterpret_cast<uintptr_t>(dst.base[r]) / (8 * W) + gr) & (uint32_t)(LK - 1);
+          st += (ar - st) & (uint32_t)(LK - 1);
+          if (threadIdx.x == r) { lo[r] = st; gbase[r] = gb; }
+          st += cr;
+        }
+      } else {
+        // unpadded: the runs' places in the tile do not depend on the slab positions, so the atomics' round trip is left pending
+        // across the barrier and hides behind the shared-memory scatter of all warps; warp 0 stores the positions afterwards
+        for (uint32_t r = 0; r < p; ++r) {
+          const uint32_t cr = __shfl_sync(FULL_MASK, c, r);
+          if (threadIdx.x == r) lo[r] = st;
+          st += cr;
+        }
+        gb_pending = gb;
       }
       if (threadIdx.x == 0) vend = st;
     }
     __syncthreads();
+    if (!ALIGN && threadIdx.x < p) gbase[threadIdx.x] = gb_pending;      // read by the copy-out, behind the next barrier
 
 #pragma unroll
     for (int j = 0; j < KPT; ++j) {
@@ -653,10 +666,20 @@ int khx_scatter_slabs_dev(kh_table *t, int dist_hash, uint32_t dist_seed, const 
       const uint64_t tile = PS_TILE_BYTES / (8 * t->W);
       const int grid = (int)std::max<uint64_t>(1, std::min<uint64_t>((n + tile - 1) / tile, (uint64_t)t->sms * 3));
       const size_t smem = t->W == 1 ? ps_smem_bytes<1>(p, false, false) : ps_smem_bytes<2>(p, false, false);
-      if (t->W == 1) KH_LAUNCH((scatter_slabs_kernel<1, false, false>), grid, PS_BLOCK, smem, s, d_keys, n, dist, t->hash_kind, t->hp, dst,
-                               (unsigned long long)slab_cap, cursors, (unsigned long long *)nullptr, (uint32_t *)nullptr);
-      else KH_LAUNCH((scatter_slabs_kernel<2, false, false>), grid, PS_BLOCK, smem, s, d_keys, n, dist, t->hash_kind, t->hp, dst,
-                     (unsigned long long)slab_cap, cursors, (unsigned long long *)nullptr, (uint32_t *)nullptr);
+      // KH_SENDER_UNPADDED=1: the variant the copy-engine schedule uses for its local partition (tools/sender_local_bench.py and
+      // the emulated-exchange tests can reach it on one GPU this way)
+      const bool unpadded = getenv("KH_SENDER_UNPADDED") && atoi(getenv("KH_SENDER_UNPADDED")) != 0;
+      if (unpadded) {
+        if (t->W == 1) KH_LAUNCH((scatter_slabs_kernel<1, false, false, false>), grid, PS_BLOCK, smem, s, d_keys, n, dist, t->hash_kind, t->hp, dst,
+                                 (unsigned long long)slab_cap, cursors, (unsigned long long *)nullptr, (uint32_t *)nullptr);
+        else KH_LAUNCH((scatter_slabs_kernel<2, false, false, false>), grid, PS_BLOCK, smem, s, d_keys, n, dist, t->hash_kind, t->hp, dst,
+                       (unsigned long long)slab_cap, cursors, (unsigned long long *)nullptr, (uint32_t *)nullptr);
+      } else {
+        if (t->W == 1) KH_LAUNCH((scatter_slabs_kernel<1, false, false>), grid, PS_BLOCK, smem, s, d_keys, n, dist, t->hash_kind, t->hp, dst,
+                                 (unsigned long long)slab_cap, cursors, (unsigned long long *)nullptr, (uint32_t *)nullptr);
+        else KH_LAUNCH((scatter_slabs_kernel<2, false, false>), grid, PS_BLOCK, smem, s, d_keys, n, dist, t->hash_kind, t->hp, dst,
+                       (unsigned long long)slab_cap, cursors, (unsigned long long *)nullptr, (uint32_t *)nullptr);
+      }
     }
     return KH_OK;
   });
