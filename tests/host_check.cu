@@ -56,4 +56,26 @@ int khtest_kmer(int k, int mode /*0 canonical, 1 revcomp*/, const uint64_t *in, 
 
 int khtest_dna_code(int c) { return (int)dna_code((uint8_t)c); }
 
+// DNA5 / DNA16 k-mers (alphabet ids 5 / 16; 4 = DNA): reverse complement and canonical form as the kernels compute them
+int khtest_kmer_alpha(int alpha, int k, int mode /*0 canonical, 1 revcomp*/, const uint64_t *in, size_t n, uint64_t *out) {
+  const int W = kmer_words_alpha(alpha, k);
+  if (W < 1 || W > 2) return -1;
+  for (size_t i = 0; i < n; ++i) {
+    if (W == 1) {
+      uint64_t a[1] = {in[i]}, r[1];
+      if (mode == 0) kmer_canonical_alpha<1>(a, alpha, k, r); else kmer_revcomp_alpha<1>(a, alpha, k, r);
+      out[i] = r[0];
+    } else {
+      uint64_t a[2] = {in[2 * i], in[2 * i + 1]}, r[2];
+      if (mode == 0) kmer_canonical_alpha<2>(a, alpha, k, r); else kmer_revcomp_alpha<2>(a, alpha, k, r);
+      out[2 * i] = r[0]; out[2 * i + 1] = r[1];
+    }
+  }
+  return 0;
+}
+int khtest_alpha_code(int alpha, int c) {
+  return alpha == KH_ALPHA_DNA ? (int)alpha_code<2>((uint8_t)c) : alpha == KH_ALPHA_DNA5 ? (int)alpha_code<3>((uint8_t)c) : (int)alpha_code<4>((uint8_t)c);
+}
+int khtest_kmer_words_alpha(int alpha, int k) { return kmer_words_alpha(alpha, k); }
+
 }

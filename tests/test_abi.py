@@ -109,6 +109,31 @@ def test_kernel_arithmetic_on_host_vs_oracle_random(hostlib, oracle_mod):
         assert np.array_equal(out.reshape(exp.shape), exp), k
 
 
+def test_alphabet_arithmetic_on_host_vs_golden(hostlib):
+    """DNA5 / DNA16: the kernels' own helpers (kh_kmer.cuh: alpha_code, kmer_revcomp_alpha = bit reversal,
+    kmer_canonical_alpha), compiled for the host, against the vectors the compiled reference produced
+    (tests/golden/alphabet_vectors.npz, KI/common/alphabets.hpp:197-292, KI/common/kmer.hpp:1476-1497)"""
+    u64p = np.ctypeslib.ndpointer(np.uint64, flags="C")
+    hostlib.khtest_kmer_alpha.argtypes = [C.c_int, C.c_int, C.c_int, u64p, C.c_size_t, u64p]
+    g = dict(np.load(os.path.join(ROOT, "tests", "golden", "alphabet_vectors.npz")))
+    text = g["text"]
+    for alpha, k in ((5, 7), (5, 21), (5, 31), (5, 42), (16, 15), (16, 17), (16, 31), (16, 32)):
+        w = np.ascontiguousarray(g["windows_a%d_k%d" % (alpha, k)])
+        W = 1 if w.ndim == 1 else w.shape[1]
+        assert hostlib.khtest_kmer_words_alpha(alpha, k) == W
+        for mode, name in ((1, "revcomp"), (0, "canonical")):
+            out = np.empty_like(w)
+            assert hostlib.khtest_kmer_alpha(alpha, k, mode, w, w.shape[0], out) == 0
+            assert np.array_equal(out, g["%s_a%d_k%d" % (name, alpha, k)]), (alpha, k, name)
+        # the first window, rebuilt from the code table: base i of the window sits B * (k - 1 - i) bits up
+        B = 3 if alpha == 5 else 4
+        v = 0
+        for i in range(k):
+            v = (v << B) | hostlib.khtest_alpha_code(alpha, int(text[i]))
+        first = int(w[0]) if W == 1 else int(w[0, 0]) | (int(w[0, 1]) << 64)
+        assert v == first, (alpha, k)
+
+
 def test_murmur32fin_rejected(kh):
     # murmur3finalizer_avx32 is defined for keys <= 4 bytes only (murmurhash3finalizer_32_avx.hpp:527)
     with pytest.raises((ValueError, kh.KmerHashError)):
